@@ -1,0 +1,212 @@
+/*
+ * tlfea_b200.h -- C ABI of libtlfea_b200.so
+ *
+ * B200-native (sm_100a) replacement for ONE hot path of
+ * uwsbel/Total-Lagrangian-FEA: per-element Gauss-point quadrature of internal
+ * force and consistent tangent for FEAT10 / ANCF3243 / ANCF3443 under SVK,
+ * Mooney-Rivlin and Kelvin-Voigt damping, plus deterministic (atomic-free)
+ * assembly into the fixed CSR pattern of  H = M/h + h K_t (+C_visc) + h^2 rho J^T J.
+ *
+ * The reference has no FFI: its boundary is two abstract C++ classes that
+ * drivers include directly.  Every entry point below names the reference
+ * method (file:line, relative to the reference root) whose behaviour it
+ * replaces.  Plain pointers and sizes only -- no Eigen, no torch types.
+ *
+ * Conventions
+ *   - every call returns TLFEA_OK (0) or a negative tlfea_status;
+ *     tlfea_last_error() gives a message for the calling thread.  (The
+ *     reference prints and exit()s: lib_utils/cuda_utils.h:12-18.)
+ *   - host input arrays are copied; `_devptr_` getters return borrowed device
+ *     pointers that stay valid until destroy.
+ *   - connectivity layout is the reference's: FEAT10 and ANCF3443 column-major
+ *     conn[n*n_elem + e] (Eigen::MatrixXi, FEAT10Data.cuh:36-39,
+ *     ANCF3443Data.cuh:212-213); ANCF3243 row-major conn[e*2 + n]
+ *     (ANCF3243Data.cuh:310-312).
+ *   - per-Gauss-point 3x3 outputs are column-major like the reference's
+ *     Eigen::Map (F(i,j) -> p[j*3+i]); grad_N is [(e*Q+q)*3S + j*S + a].
+ *   - all work is enqueued on the handle's stream; getters synchronise it.
+ */
+#ifndef TLFEA_B200_H
+#define TLFEA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  TLFEA_OK = 0,
+  TLFEA_ERR_INVALID = -1,   /* bad argument / call order (reference: std::cerr + return) */
+  TLFEA_ERR_CUDA = -2,      /* CUDA runtime failure (reference: exit(EXIT_FAILURE)) */
+  TLFEA_ERR_UNSUPPORTED = -3,
+  TLFEA_ERR_NO_DEVICE = -4  /* no CUDA device: there is NO CPU fallback */
+} tlfea_status;
+
+/* Values match the reference enum ElementType (lib_src/elements/ElementBase.h:19). */
+typedef enum { TLFEA_TYPE_3243 = 0, TLFEA_TYPE_3443 = 1, TLFEA_TYPE_T10 = 2 } tlfea_elem_type;
+
+/* Bit-compatible with SyncedNewtonParams (lib_src/solvers/SyncedNewton.cuh:29-33). */
+typedef struct {
+  double inner_atol, inner_rtol, outer_tol, rho;
+  int max_outer, max_inner;
+  double time_step;
+} tlfea_newton_params;
+
+typedef struct tlfea_elem tlfea_elem;
+typedef struct tlfea_newton tlfea_newton;
+
+const char *tlfea_last_error(void);
+int tlfea_version(void);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+int64_t tlfea_launch_count(void);
+int tlfea_device_count(void);
+
+/* ---------------------------------------------------------------- elements */
+
+/* GPU_FEAT10_Data(n_elem,n_nodes)+Initialize()  FEAT10Data.cuh:377-433
+ * GPU_ANCF3243_Data(n_nodes,n_elem)             ANCF3243Data.cuh:434-440
+ * GPU_ANCF3443_Data(n_nodes,n_elem)             ANCF3443Data.cuh:445-455
+ * `device` is the CUDA ordinal the handle lives on. */
+int tlfea_elem_create(int type, int n_elem, int n_nodes, int device, tlfea_elem **out);
+/* Destroy()  FEAT10Data.cuh:714-779 */
+int tlfea_elem_destroy(tlfea_elem *h);
+int tlfea_elem_sync(tlfea_elem *h);
+
+/* Setup(tet5pt_x,y,z,w, x,y,z, connectivity)  FEAT10Data.cuh:435-533.
+ * Quadrature tables are taken from the caller exactly as the reference does. */
+int tlfea_elem_setup_t10(tlfea_elem *h, const double *qx, const double *qy, const double *qz, const double *qw,
+                         const double *x, const double *y, const double *z, const int *conn_colmajor);
+
+/* Setup(L,W,H, gauss_xi_m,..., weights..., x12,y12,z12, connectivity)  ANCF3243Data.cuh:511-522,653-664.
+ * x,y,z hold 4 coefficients per node (position, r_u, r_v, r_w): length 4*n_nodes.
+ * B_inv is built inside (cpu_utils.cc:125-209 restated with our own LU). */
+int tlfea_elem_setup_3243(tlfea_elem *h, const double *L, const double *W, const double *H, const double *x,
+                          const double *y, const double *z, const int *conn_rowmajor);
+/* ANCF3443Data.cuh Setup; conn column-major [4][n_elem]. */
+int tlfea_elem_setup_3443(tlfea_elem *h, const double *L, const double *W, const double *H, const double *x,
+                          const double *y, const double *z, const int *conn_colmajor);
+
+/* SetDensity / SetDamping / SetSVK(E,nu) / SetMooneyRivlin  FEAT10Data.cuh:538-634 */
+int tlfea_elem_set_density(tlfea_elem *h, double rho0);
+int tlfea_elem_set_damping(tlfea_elem *h, double eta_damp, double lambda_damp);
+int tlfea_elem_set_svk(tlfea_elem *h, double E, double nu);
+int tlfea_elem_set_mooney_rivlin(tlfea_elem *h, double mu10, double mu01, double kappa);
+/* SetExternalForce(VectorXd 3*n_coef)  FEAT10Data.cuh:636-646 */
+int tlfea_elem_set_external_force(tlfea_elem *h, const double *f_ext, int n);
+/* SetNodalFixed(VectorXi)  FEAT10Data.cu:728-749 (a second call is an error, as in the reference) */
+int tlfea_elem_set_nodal_fixed(tlfea_elem *h, const int *fixed_nodes, int n_fixed);
+/* SetLinearConstraintsCSR(offsets,columns,values,rhs)  ANCF3243Data.cuh:810-940: rows = constraints, cols = DOFs */
+int tlfea_elem_set_linear_constraints_csr(tlfea_elem *h, int n_constraints, const int *offsets, const int *columns,
+                                          const double *values, const double *rhs);
+/* UpdatePositions / UpdateConstraintTargets  FEAT10Data.cuh:672-712 (n = n_coef) */
+int tlfea_elem_update_positions(tlfea_elem *h, const double *x, const double *y, const double *z, int n);
+int tlfea_elem_update_constraint_targets(tlfea_elem *h, const double *x, const double *y, const double *z, int n);
+
+/* CalcDnDuPre / CalcDsDuPre  FEAT10Data.cu:284-292, ANCF3243Data.cu:102-198, ANCF3443Data.cu:96-182 */
+int tlfea_elem_precompute(tlfea_elem *h);
+/* BuildMassCSRPattern  FEAT10Data.cu:372-440 (sorted unique coefficient pairs) */
+int tlfea_elem_build_mass_pattern(tlfea_elem *h);
+/* CalcMassMatrix  FEAT10Data.cu:351-370 */
+int tlfea_elem_calc_mass(tlfea_elem *h);
+/* CalcP  FEAT10Data.cu:294-312 (no viscous part: v_guess = nullptr) */
+int tlfea_elem_calc_p(tlfea_elem *h);
+/* CalcInternalForce  FEAT10Data.cu:314-333 -- ACCUMULATES into f_int from the stored P, like the reference */
+int tlfea_elem_calc_internal_force(tlfea_elem *h);
+int tlfea_elem_clear_internal_force(tlfea_elem *h);
+/* CalcConstraintData  FEAT10Data.cu:335-349 */
+int tlfea_elem_calc_constraint(tlfea_elem *h);
+
+int tlfea_elem_n_elem(const tlfea_elem *h);
+int tlfea_elem_n_coef(const tlfea_elem *h);        /* get_n_coef() */
+int tlfea_elem_n_shape(const tlfea_elem *h);
+int tlfea_elem_n_qp(const tlfea_elem *h);
+int tlfea_elem_n_constraint(const tlfea_elem *h);
+int64_t tlfea_elem_mass_nnz(const tlfea_elem *h);
+
+/* Retrieve*ToCPU  FEAT10Data.cu:603-726; out buffers are caller-allocated */
+int tlfea_elem_get_internal_force(tlfea_elem *h, double *out, int n);                    /* 3*n_coef */
+int tlfea_elem_get_positions(tlfea_elem *h, double *x, double *y, double *z, int n);     /* n_coef each */
+int tlfea_elem_get_F(tlfea_elem *h, double *out, int64_t n);                              /* n_elem*Q*9 */
+int tlfea_elem_get_P(tlfea_elem *h, double *out, int64_t n);                              /* n_elem*Q*9 */
+int tlfea_elem_get_grad_N(tlfea_elem *h, double *out, int64_t n);                         /* n_elem*Q*3S */
+int tlfea_elem_get_detJ(tlfea_elem *h, double *out, int64_t n);                           /* n_elem*Q */
+int tlfea_elem_get_mass_csr(tlfea_elem *h, int *offsets, int *columns, double *values);  /* n_coef+1, nnz, nnz */
+int tlfea_elem_get_constraint(tlfea_elem *h, double *out, int n);
+int tlfea_elem_get_connectivity(tlfea_elem *h, int *out, int64_t n);
+
+/* GetX12DevicePtr.. / GetExternalForceDevicePtr  FEAT10Data.cuh:648-670 */
+const double *tlfea_elem_devptr_x(tlfea_elem *h);
+const double *tlfea_elem_devptr_y(tlfea_elem *h);
+const double *tlfea_elem_devptr_z(tlfea_elem *h);
+double *tlfea_elem_devptr_f_ext(tlfea_elem *h);
+double *tlfea_elem_devptr_f_int(tlfea_elem *h);
+
+/* ------------------------------------------------------------------ solver */
+
+/* SyncedNewtonSolver(ElementBase*, n_constraints)  SyncedNewton.cuh:37-149 */
+int tlfea_newton_create(tlfea_elem *e, int n_constraints, tlfea_newton **out);
+int tlfea_newton_destroy(tlfea_newton *s);
+/* SetParameters(void*)  SyncedNewton.cuh:206-229 */
+int tlfea_newton_set_params(tlfea_newton *s, const tlfea_newton_params *p);
+/* Setup()  SyncedNewton.cuh:231-245 (zero v, v_prev, lambda) */
+int tlfea_newton_setup(tlfea_newton *s);
+/* AnalyzeHessianSparsity()  SyncedNewton.cu:546-907: DOF-level pattern + our slot maps */
+int tlfea_newton_analyze_sparsity(tlfea_newton *s);
+/* SetFixedSparsityPattern(bool)  SyncedNewton.cuh:351-356 */
+int tlfea_newton_set_fixed_pattern(tlfea_newton *s, int fixed);
+
+/* THE BENCHMARKED UNIT.  From current x (and v_guess): f_int, and
+ * H.values = M/h + h*K_t (+C_visc) + h^2*rho*J^T J, from zero, pattern fixed.
+ * Replaces, per Newton iteration, SyncedNewton.cu:1046-1052 (compute_p, clear,
+ * compute_internal_force) and :1080-1097 (memset, hessian mass / tangent /
+ * constraints). */
+int tlfea_newton_assemble(tlfea_newton *s);
+/* force half only (what AdamW/Nesterov consume): SyncedNewton.cu:1046-1052 */
+int tlfea_newton_assemble_force(tlfea_newton *s);
+/* constraints_eval + compute_grad_l + ||g||  SyncedNewton.cu:1056-1064; writes ||g||_2 to *norm_g */
+int tlfea_newton_residual(tlfea_newton *s, double *norm_g);
+/* One implicit step: OneStepNewtonCuDSS (SyncedNewton.cu:909-1394) with the
+ * cuDSS SPD solve replaced by block-Jacobi PCG (cuDSS is not in this image). */
+int tlfea_newton_solve_step(tlfea_newton *s);
+/* last step's statistics: Newton iterations, total PCG iterations, final ||g||, final ||c|| */
+int tlfea_newton_last_stats(tlfea_newton *s, int *newton_iters, int *pcg_iters, double *norm_g, double *norm_c);
+int tlfea_newton_set_pcg(tlfea_newton *s, int max_iters, double rel_tol);
+
+int64_t tlfea_newton_nnz(const tlfea_newton *s);
+int tlfea_newton_n_dofs(const tlfea_newton *s);
+/* DOF-level CSR as the reference exposes it to cuDSS (SyncedNewton.cu:1010-1013).
+ * row_offsets is 64-bit: nnz(H) of the 10M-tet block exceeds 2^31 (the
+ * reference's int would overflow).  col_indices/values may be NULL. */
+int tlfea_newton_get_hessian_csr(tlfea_newton *s, int64_t *row_offsets, int *col_indices, double *values);
+int tlfea_newton_get_g(tlfea_newton *s, double *out, int n);
+int tlfea_newton_get_v(tlfea_newton *s, double *out, int n);
+int tlfea_newton_set_v(tlfea_newton *s, const double *v, int n);
+int tlfea_newton_set_v_prev(tlfea_newton *s, const double *v, int n);
+/* GetVelocityGuessDevicePtr()  SyncedNewton.cuh:341-343 */
+double *tlfea_newton_devptr_v(tlfea_newton *s);
+double *tlfea_newton_devptr_hessian_values(tlfea_newton *s);
+double *tlfea_newton_devptr_g(tlfea_newton *s);
+/* y = H x on the device with the assembled values (tests, PCG) */
+int tlfea_newton_spmv(tlfea_newton *s, const double *d_x, double *d_y);
+/* sum of the CUDA-event time (ms) of assemble calls since the last reset, and their count */
+int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset);
+/* per-kernel CUDA-event timing of the next assemble calls (0/1) */
+int tlfea_newton_set_profile(tlfea_newton *s, int on);
+int tlfea_newton_kernel_ms(tlfea_newton *s, double *gp_ms, double *row_ms, double *other_ms);
+
+/* --------------------------------------------------------------- multi-GPU */
+/* Element-partitioned assembly (new design; the reference is single-GPU).
+ * `interface_dofs` lists this rank's local DOF ids shared with other ranks in
+ * the global canonical order; tlfea_dist_pack/unpack move them through a
+ * contiguous buffer that the host side reduces with NCCL (torch.distributed).*/
+int tlfea_dist_pack(tlfea_newton *s, const double *d_vec, const int *d_idx, int n, double *d_buf);
+int tlfea_dist_unpack(tlfea_newton *s, double *d_vec, const int *d_idx, int n, const double *d_buf);
+
+/* FP64 FMA peak micro-benchmark (roofline denominator for the tangent kernel): TFLOP/s */
+int tlfea_fp64_peak(int device, double *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TLFEA_B200_H */

@@ -1,0 +1,174 @@
+// common.cuh -- shared state, error handling and launch accounting for libtlfea_b200.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <string>
+
+#include "../../include/tlfea_b200.h"
+
+namespace tlfea {
+
+extern thread_local std::string g_last_error;
+extern std::atomic<int64_t> g_launches;
+
+inline int fail(int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  return code;
+}
+
+#define TL_CUDA(call)                                                                              \
+  do {                                                                                             \
+    cudaError_t _e = (call);                                                                       \
+    if (_e != cudaSuccess)                                                                         \
+      return tlfea::fail(TLFEA_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call,              \
+                         cudaGetErrorString(_e));                                                  \
+  } while (0)
+
+#define TL_CHECK(cond, ...)                                          \
+  do {                                                               \
+    if (!(cond)) return tlfea::fail(TLFEA_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+#define TL_TRY(expr)          \
+  do {                        \
+    int _s = (expr);          \
+    if (_s != TLFEA_OK) return _s; \
+  } while (0)
+
+// every kernel launch goes through this so bench.py can report gpu_launches
+#define TL_LAUNCH(kernel, grid, block, smem, stream, ...)      \
+  do {                                                         \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__); \
+    tlfea::g_launches.fetch_add(1, std::memory_order_relaxed);  \
+  } while (0)
+
+template <typename T>
+inline int dmalloc(T **p, size_t n) {
+  *p = nullptr;
+  if (n == 0) n = 1;
+  TL_CUDA(cudaMalloc((void **)p, n * sizeof(T)));
+  return TLFEA_OK;
+}
+
+template <typename T>
+inline void dfree(T *&p) {
+  if (p) cudaFree(p);
+  p = nullptr;
+}
+
+inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
+
+constexpr int MAX_Q = 48;
+struct QuadW {
+  double w[MAX_Q];  // combined quadrature weight per stiffness Gauss point
+};
+
+// Coefficient-level sparsity + the maps that replace the reference's per-entry
+// binary search (FEAT10DataFunc.cuh:487-502) and its FP64 atomics.
+struct Pattern {
+  int n_coef = 0;
+  int S = 0;
+  int64_t n_visits = 0;           // n_elem * S
+  int64_t nnz = 0;                // coefficient-level nnz (mass pattern)
+  int max_deg = 0;                // longest coefficient row
+  int max_inc = 0;                // most elements incident to one coefficient
+  int *d_off = nullptr;           // [n_coef+1]  sorted-unique adjacency, == reference d_csr_offsets
+  int *d_cols = nullptr;          // [nnz]       == reference d_csr_columns
+  int *d_inc_ptr = nullptr;       // [n_coef+1]  coefficient -> its (element, local) visits
+  int *d_inc_ea = nullptr;        // [n_visits]  e*S + a, ascending within a coefficient
+  uint16_t *d_slot = nullptr;     // [n_visits*S] position of column ecoef[e][b] in the visit's row
+  void release() {
+    dfree(d_off);
+    dfree(d_cols);
+    dfree(d_inc_ptr);
+    dfree(d_inc_ea);
+    dfree(d_slot);
+  }
+};
+
+int build_pattern(const int *d_ecoef, int n_elem, int S, int n_coef, cudaStream_t stream, Pattern *out);
+
+}  // namespace tlfea
+
+enum { TL_MODEL_SVK = 0, TL_MODEL_MR = 1 };
+enum { TL_CONS_NONE = 0, TL_CONS_FIXED_NODES = 1, TL_CONS_LINEAR_CSR = 2 };
+
+struct tlfea_elem {
+  int type = 0, n_elem = 0, n_nodes = 0, n_coef = 0, S = 0, Q = 0, device = 0;
+  cudaStream_t stream = nullptr;
+  bool is_setup = false, is_precomputed = false, is_pattern = false, is_mass = false;
+
+  int *d_conn = nullptr;    // caller layout (reference layout), n_elem * nodes_per_elem
+  int nodes_per_elem = 0;
+  int *d_ecoef = nullptr;   // [n_elem][S] coefficient ids, row-major
+  double *d_x = nullptr, *d_y = nullptr, *d_z = nullptr;           // current coefficients   (x12,y12,z12)
+  double *d_xr = nullptr, *d_yr = nullptr, *d_zr = nullptr;        // reference coefficients (x12_jac,..)
+  double *d_gradN = nullptr;  // [n_elem][Q][3S]
+  double *d_detJ = nullptr;   // [n_elem][Q]
+  double *d_F = nullptr, *d_P = nullptr;  // [n_elem][Q][9], allocated on first CalcP
+  double *d_f_int = nullptr, *d_f_ext = nullptr;
+  double *d_fe = nullptr;     // [n_elem][S][3] element force staging
+  double *d_mass = nullptr;   // [pattern.nnz]
+  double *d_LWH = nullptr;    // ANCF: [n_elem][3]
+  double *d_Binv = nullptr;   // ANCF: [n_elem][S*S]
+  tlfea::QuadW qw;
+  double t10_q[4][5];         // FEAT10 quadrature points/weights as given by the caller
+  tlfea::Pattern pat;
+
+  // material (FEAT10Data.cuh:538-634)
+  int model = TL_MODEL_SVK;
+  double rho0 = 0, E = 0, nu = 0, lambda = 0, mu = 0, mu10 = 0, mu01 = 0, kappa = 0, eta = 0, lambda_d = 0;
+
+  // constraints
+  int cons_mode = TL_CONS_NONE;
+  int n_constraint = 0;
+  int n_fixed = 0;
+  int *d_fixed = nullptr;
+  double *d_constraint = nullptr;
+  // general linear constraints (rows = constraints) and transpose (rows = DOFs)
+  int *d_j_off = nullptr, *d_j_cols = nullptr;
+  double *d_j_vals = nullptr, *d_j_rhs = nullptr;
+  int *d_jt_off = nullptr, *d_jt_cols = nullptr;
+  double *d_jt_vals = nullptr;
+  int64_t j_nnz = 0;
+};
+
+struct tlfea_newton {
+  tlfea_elem *e = nullptr;
+  int n_constraints = 0;
+  tlfea_newton_params prm{};
+  bool analyzed = false, fixed_pattern = false;
+  int64_t nnz = 0;  // DOF-level nnz = 9 * pattern.nnz
+  double *d_H = nullptr;
+  double *d_gp = nullptr;  // per-Gauss-point records
+  int rec_doubles = 0;
+  double *d_v = nullptr, *d_v_prev = nullptr, *d_lambda = nullptr, *d_g = nullptr, *d_dv = nullptr, *d_r = nullptr;
+  double *d_xp = nullptr, *d_yp = nullptr, *d_zp = nullptr;
+  // constraint term h^2 rho J^T J as a (slot, coefficient) list with unique slots
+  int64_t n_cons_slots = 0;
+  int64_t *d_cons_slot = nullptr;
+  double *d_cons_val = nullptr;
+  // PCG workspace
+  double *d_pcg[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  double *d_scal = nullptr;  // device scalars
+  double *h_scal = nullptr;  // pinned
+  int pcg_max_iters = 200;
+  double pcg_rel_tol = 1e-8;
+  int last_newton = 0, last_pcg = 0;
+  double last_norm_g = 0, last_norm_c = 0;
+  // timing
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  double ms_total = 0;
+  int calls = 0;
+  bool profile = false;
+  double k_ms[3] = {0, 0, 0};
+};

@@ -1,0 +1,819 @@
+// newton.cu -- host-side mirror of SyncedNewtonSolver (lib_src/solvers/SyncedNewton.{cu,cuh})
+// for the hot path: sparsity analysis, the fused force + tangent + H assembly, the residual,
+// and one implicit ALM/Newton step whose SPD solve is a block-Jacobi PCG (cuDSS is absent here).
+#include <algorithm>
+#include <cmath>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace tlfea {
+int launch_gp(tlfea_elem *h, const double *v, double *rec, double *fe, double *F_out, double *P_out);
+int ensure_pattern(tlfea_elem *h);
+
+// ---------------------------------------------------------------------------
+// small vector kernels (SyncedNewton.cu:412-534)
+// ---------------------------------------------------------------------------
+__global__ void k_grad_L(int n_coef, const int *__restrict__ off, const int *__restrict__ cols,
+                         const double *__restrict__ mass, const double *__restrict__ v,
+                         const double *__restrict__ v_prev, const double *__restrict__ f_int,
+                         const double *__restrict__ f_ext, double inv_h, double h, const int *jt_off,
+                         const int *jt_cols, const double *jt_vals, const double *lam, const double *con, double rho,
+                         double *g) {
+  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= (int64_t)n_coef * 3) return;
+  const int ni = (int)(tid / 3), di = (int)(tid % 3);
+  double res = 0.0;
+  for (int idx = off[ni]; idx < off[ni + 1]; idx++) {
+    const int64_t tj = (int64_t)cols[idx] * 3 + di;
+    res += mass[idx] * (v[tj] - v_prev[tj]) * inv_h;  // (M (v - v_prev)) / h, reference order
+  }
+  res -= (-f_int[tid]);
+  res -= f_ext[tid];
+  if (jt_off) {
+    for (int idx = jt_off[tid]; idx < jt_off[tid + 1]; idx++) {
+      const int c = jt_cols[idx];
+      res += h * jt_vals[idx] * (lam[c] + rho * con[c]);
+    }
+  }
+  g[tid] = res;
+}
+
+// fixed-node constraints: J^T has exactly one unit entry per constrained DOF
+__global__ void k_grad_L_fixed(int n_fixed, const int *__restrict__ fixed, const double *__restrict__ lam,
+                               const double *__restrict__ con, double h, double rho, double *g) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= 3 * n_fixed) return;
+  const int64_t dof = (int64_t)fixed[c / 3] * 3 + c % 3;
+  g[dof] += h * 1.0 * (lam[c] + rho * con[c]);
+}
+
+__global__ void k_fixed_cons_slots(int n_fixed, const int *__restrict__ fixed, const int *__restrict__ off,
+                                   const int *__restrict__ cols, int64_t *slot, double *val) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= 3 * n_fixed) return;
+  const int n = fixed[c / 3], d = c % 3;
+  const int rs = off[n], deg = off[n + 1] - rs;
+  int lo = 0, hi = deg - 1, pos = 0;
+  while (lo <= hi) {
+    int mid = (lo + hi) >> 1, cc = cols[rs + mid];
+    if (cc == n) {
+      pos = mid;
+      break;
+    }
+    if (cc < n)
+      lo = mid + 1;
+    else
+      hi = mid - 1;
+  }
+  slot[c] = 9 * (int64_t)rs + (int64_t)d * 3 * deg + 3 * pos + d;
+  val[c] = 1.0;
+}
+
+// H += h^2 rho * (J^T J) on its precomputed unique slots   (SyncedNewton.cu:291-341)
+__global__ void k_add_constraint_term(int64_t n, const int64_t *__restrict__ slot, const double *__restrict__ val,
+                                      double factor, double *H) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) H[slot[i]] += factor * val[i];
+}
+
+__global__ void k_axpy(int64_t n, double a, const double *x, double *y) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] += a * x[i];
+}
+__global__ void k_update_pos(int n, const double *xp, const double *yp, const double *zp, const double *v, double h,
+                             double *x, double *y, double *z) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  x[i] = xp[i] + v[3 * (int64_t)i + 0] * h;
+  y[i] = yp[i] + v[3 * (int64_t)i + 1] * h;
+  z[i] = zp[i] + v[3 * (int64_t)i + 2] * h;
+}
+__global__ void k_dual_update(int n, const double *con, double rho, double *lam) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) lam[i] += rho * con[i];
+}
+
+// deterministic dot product: fixed grid, fixed tree
+constexpr int DOT_BLOCKS = 592;  // 4 x 148 SMs
+__global__ void __launch_bounds__(256) k_dot_partial(int64_t n, const double *__restrict__ a,
+                                                     const double *__restrict__ b, double *partial) {
+  __shared__ double sh[256];
+  double s = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) s += a[i] * b[i];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
+}
+__global__ void __launch_bounds__(1024) k_dot_final(int nb, const double *__restrict__ partial, double *out) {
+  __shared__ double sh[1024];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < nb; i += 1024) s += partial[i];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = sh[0];
+}
+
+// y = H x; one warp per coefficient (3 scalar rows), fixed shuffle tree
+__global__ void __launch_bounds__(256) k_spmv(int n_coef, const int *__restrict__ off, const int *__restrict__ cols,
+                                              const double *__restrict__ H, const double *__restrict__ x, double *y) {
+  const int row = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= n_coef) return;
+  const int rs = off[row], deg = off[row + 1] - rs;
+  const int64_t base = 9 * (int64_t)rs;
+  double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+  for (int s = lane; s < deg; s += 32) {
+    const int64_t j = 3 * (int64_t)cols[rs + s];
+    const double x0 = x[j], x1 = x[j + 1], x2 = x[j + 2];
+    const double *h0 = H + base + 3 * s, *h1 = h0 + 3 * deg, *h2 = h1 + 3 * deg;
+    s0 += h0[0] * x0 + h0[1] * x1 + h0[2] * x2;
+    s1 += h1[0] * x0 + h1[1] * x1 + h1[2] * x2;
+    s2 += h2[0] * x0 + h2[1] * x1 + h2[2] * x2;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  }
+  if (lane == 0) {
+    y[3 * (int64_t)row] = s0;
+    y[3 * (int64_t)row + 1] = s1;
+    y[3 * (int64_t)row + 2] = s2;
+  }
+}
+
+// z = D^-1 r with D the 3x3 diagonal blocks of H (block-Jacobi)
+__global__ void k_block_jacobi(int n_coef, const int *__restrict__ off, const int *__restrict__ cols,
+                               const double *__restrict__ H, const double *__restrict__ r, double *z) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_coef) return;
+  const int rs = off[i], deg = off[i + 1] - rs;
+  int lo = 0, hi = deg - 1, pos = 0;
+  while (lo <= hi) {
+    int mid = (lo + hi) >> 1, c = cols[rs + mid];
+    if (c == i) {
+      pos = mid;
+      break;
+    }
+    if (c < i)
+      lo = mid + 1;
+    else
+      hi = mid - 1;
+  }
+  const double *h0 = H + 9 * (int64_t)rs + 3 * pos, *h1 = h0 + 3 * deg, *h2 = h1 + 3 * deg;
+  const double a = h0[0], b = h0[1], c = h0[2], d = h1[0], e = h1[1], f = h1[2], g = h2[0], hh = h2[1], k = h2[2];
+  const double A = e * k - f * hh, B = -(d * k - f * g), C = d * hh - e * g;
+  const double det = a * A + b * B + c * C;
+  const double r0 = r[3 * (int64_t)i], r1 = r[3 * (int64_t)i + 1], r2 = r[3 * (int64_t)i + 2];
+  if (fabs(det) < 1e-300) {
+    z[3 * (int64_t)i] = r0;
+    z[3 * (int64_t)i + 1] = r1;
+    z[3 * (int64_t)i + 2] = r2;
+    return;
+  }
+  const double id = 1.0 / det;
+  z[3 * (int64_t)i] = (A * r0 + (-(b * k - c * hh)) * r1 + (b * f - c * e) * r2) * id;
+  z[3 * (int64_t)i + 1] = (B * r0 + (a * k - c * g) * r1 + (-(a * f - c * d)) * r2) * id;
+  z[3 * (int64_t)i + 2] = (C * r0 + (-(a * hh - b * g)) * r1 + (a * e - b * d) * r2) * id;
+}
+
+__global__ void k_pcg_update_xr(int64_t n, const double *scal, const double *p, const double *Ap, double *x,
+                                double *r) {
+  // alpha = rz / pAp
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double alpha = scal[0] / scal[1];
+  x[i] += alpha * p[i];
+  r[i] -= alpha * Ap[i];
+}
+__global__ void k_pcg_update_p(int64_t n, const double *scal, const double *z, double *p) {
+  // beta = rz_new / rz_old
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double beta = scal[2] / scal[0];
+  p[i] = z[i] + beta * p[i];
+}
+__global__ void k_neg_copy(int64_t n, const double *g, double *r) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) r[i] = -g[i];
+}
+__global__ void k_copy_scalar(double *dst, const double *src) { *dst = *src; }
+
+template <int S, int Q>
+static int launch_row_t(tlfea_newton *s, const RowArgs &a, int grid, size_t smem, bool damp) {
+  tlfea_elem *e = s->e;
+#define TL_ROW(MODEL, DAMP)                                                                                     \
+  do {                                                                                                          \
+    if (smem > 48 * 1024)                                                                                       \
+      TL_CUDA(cudaFuncSetAttribute(row_kernel<S, Q, MODEL, DAMP>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                   (int)smem));                                                                 \
+    TL_LAUNCH((row_kernel<S, Q, MODEL, DAMP>), grid, ROW_WARPS * 32, smem, e->stream, a);                        \
+  } while (0)
+  if (e->model == TL_MODEL_SVK) {
+    if (damp)
+      TL_ROW(TL_MODEL_SVK, true);
+    else
+      TL_ROW(TL_MODEL_SVK, false);
+  } else {
+    if (damp)
+      TL_ROW(TL_MODEL_MR, true);
+    else
+      TL_ROW(TL_MODEL_MR, false);
+  }
+#undef TL_ROW
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
+static int dot(tlfea_newton *s, const double *a, const double *b, double *d_out) {
+  const int64_t n = 3 * (int64_t)s->e->n_coef;
+  double *partial = s->d_scal + 8;
+  TL_LAUNCH(k_dot_partial, DOT_BLOCKS, 256, 0, s->e->stream, n, a, b, partial);
+  TL_LAUNCH(k_dot_final, 1, 1024, 0, s->e->stream, DOT_BLOCKS, partial, d_out);
+  return TLFEA_OK;
+}
+
+static int norm2(tlfea_newton *s, const double *a, int64_t n, double *out) {
+  double *partial = s->d_scal + 8;
+  TL_LAUNCH(k_dot_partial, DOT_BLOCKS, 256, 0, s->e->stream, n, a, a, partial);
+  TL_LAUNCH(k_dot_final, 1, 1024, 0, s->e->stream, DOT_BLOCKS, partial, s->d_scal + 4);
+  TL_CUDA(cudaMemcpyAsync(s->h_scal, s->d_scal + 4, sizeof(double), cudaMemcpyDeviceToHost, s->e->stream));
+  TL_CUDA(cudaStreamSynchronize(s->e->stream));
+  *out = std::sqrt(s->h_scal[0]);
+  return TLFEA_OK;
+}
+
+static int do_assemble(tlfea_newton *s, bool tangent) {
+  tlfea_elem *e = s->e;
+  TL_CHECK(e->is_precomputed, "CalcDnDuPre/CalcDsDuPre must run before assembling");
+  if (tangent) {
+    TL_CHECK(s->analyzed, "AnalyzeHessianSparsity must run before assembling");
+    TL_CHECK(e->is_mass, "CalcMassMatrix must run before assembling H = M/h + ...");
+    TL_CHECK(s->prm.time_step > 0.0, "time_step must be positive (SetParameters)");
+  }
+  TL_CUDA(cudaSetDevice(e->device));
+  TL_TRY(ensure_pattern(e));
+  const bool damp = (e->eta != 0.0 || e->lambda_d != 0.0);
+  TL_CUDA(cudaEventRecord(s->ev[0], e->stream));
+  TL_TRY(launch_gp(e, damp ? s->d_v : nullptr, tangent ? s->d_gp : nullptr, e->d_fe, nullptr, nullptr));
+  if (s->profile) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
+  if (!tangent) {
+    TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)e->n_coef * 3, 128), 128, 0, e->stream, e->n_coef,
+              e->pat.d_inc_ptr, e->pat.d_inc_ea, e->d_fe, e->d_f_int, 0);
+  } else {
+    const double h = s->prm.time_step;
+    RowArgs a;
+    a.n_coef = e->n_coef;
+    a.off = e->pat.d_off;
+    a.inc_ptr = e->pat.d_inc_ptr;
+    a.inc_ea = e->pat.d_inc_ea;
+    a.slot = e->pat.d_slot;
+    a.mass = e->d_mass;
+    a.rec = s->d_gp;
+    a.gradN = e->d_gradN;
+    a.detJ = e->d_detJ;
+    a.fe = e->d_fe;
+    a.qw = e->qw;
+    a.h = h;
+    a.inv_h = 1.0 / h;
+    a.c1 = h * e->lambda + e->lambda_d;
+    a.c2 = h * e->mu + e->eta;
+    a.c3 = h * e->mu + e->eta;
+    a.c4 = h;
+    a.mu = e->mu;
+    a.lambda_d = e->lambda_d;
+    a.eta = e->eta;
+    a.H = s->d_H;
+    a.f_int = e->d_f_int;
+    a.row_stride = ((e->pat.max_deg * 9 + 1) | 1);  // odd stride: warps start on different banks
+    const size_t smem = (size_t)ROW_WARPS * a.row_stride * sizeof(double);
+    TL_CHECK(smem <= 200 * 1024, "coefficient row too long for the shared-memory row buffer (max_deg=%d)",
+             e->pat.max_deg);
+    const int rows_blocks = (e->n_coef + ROW_WARPS - 1) / ROW_WARPS;
+    const int grid = std::min(rows_blocks, 148 * 16);
+    switch (e->type) {
+      case TLFEA_TYPE_T10: TL_TRY((launch_row_t<10, 5>(s, a, grid, smem, damp))); break;
+      case TLFEA_TYPE_3243: TL_TRY((launch_row_t<8, 12>(s, a, grid, smem, damp))); break;
+      default: TL_TRY((launch_row_t<16, 48>(s, a, grid, smem, damp)));
+    }
+    if (s->profile) TL_CUDA(cudaEventRecord(s->ev[3], e->stream));
+    if (s->n_cons_slots > 0) {
+      TL_LAUNCH(k_add_constraint_term, blocks_for(s->n_cons_slots, 256), 256, 0, e->stream, s->n_cons_slots,
+                s->d_cons_slot, s->d_cons_val, h * h * s->prm.rho, s->d_H);
+    }
+  }
+  TL_CUDA(cudaGetLastError());
+  TL_CUDA(cudaEventRecord(s->ev[1], e->stream));
+  return TLFEA_OK;
+}
+
+static int collect_timing(tlfea_newton *s, bool tangent) {
+  TL_CUDA(cudaEventSynchronize(s->ev[1]));
+  float ms = 0;
+  TL_CUDA(cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]));
+  s->ms_total += ms;
+  s->calls++;
+  if (s->profile && tangent) {
+    float a = 0, b = 0, c = 0;
+    cudaEventElapsedTime(&a, s->ev[0], s->ev[2]);
+    cudaEventElapsedTime(&b, s->ev[2], s->ev[3]);
+    cudaEventElapsedTime(&c, s->ev[3], s->ev[1]);
+    s->k_ms[0] += a;
+    s->k_ms[1] += b;
+    s->k_ms[2] += c;
+  }
+  return TLFEA_OK;
+}
+
+static int eval_constraints(tlfea_newton *s) {
+  if (s->n_constraints > 0 && s->e->cons_mode != TL_CONS_NONE) return tlfea_elem_calc_constraint(s->e);
+  return TLFEA_OK;
+}
+
+static int compute_residual(tlfea_newton *s) {
+  tlfea_elem *e = s->e;
+  const double h = s->prm.time_step;
+  TL_CHECK(h > 0.0, "time_step must be positive (SetParameters)");
+  TL_CHECK(e->is_mass, "CalcMassMatrix must run before the residual");
+  TL_TRY(eval_constraints(s));
+  const bool lin = (s->n_constraints > 0 && e->cons_mode == TL_CONS_LINEAR_CSR);
+  TL_LAUNCH(k_grad_L, blocks_for((int64_t)e->n_coef * 3, 256), 256, 0, e->stream, e->n_coef, e->pat.d_off,
+            e->pat.d_cols, e->d_mass, s->d_v, s->d_v_prev, e->d_f_int, e->d_f_ext, 1.0 / h, h,
+            lin ? e->d_jt_off : nullptr, e->d_jt_cols, e->d_jt_vals, s->d_lambda, e->d_constraint, s->prm.rho, s->d_g);
+  if (s->n_constraints > 0 && e->cons_mode == TL_CONS_FIXED_NODES && e->n_fixed > 0) {
+    TL_LAUNCH(k_grad_L_fixed, blocks_for(3 * e->n_fixed, 256), 256, 0, e->stream, e->n_fixed, e->d_fixed,
+              s->d_lambda, e->d_constraint, h, s->prm.rho, s->d_g);
+  }
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
+// block-Jacobi PCG on H dv = r, dv starts at 0 (SyncedNewton.cu:1112-1114 zeroes delta_v before the solve)
+static int pcg_solve(tlfea_newton *s, int *iters_out) {
+  tlfea_elem *e = s->e;
+  const int64_t n = 3 * (int64_t)e->n_coef;
+  double *x = s->d_dv, *r = s->d_r, *z = s->d_pcg[0], *p = s->d_pcg[1], *Ap = s->d_pcg[2];
+  const unsigned gb = blocks_for(n, 256), nb = blocks_for(e->n_coef, 256), sb = blocks_for((int64_t)e->n_coef * 32, 256);
+  TL_CUDA(cudaMemsetAsync(x, 0, n * sizeof(double), e->stream));
+  TL_LAUNCH(k_block_jacobi, nb, 256, 0, e->stream, e->n_coef, e->pat.d_off, e->pat.d_cols, s->d_H, r, z);
+  TL_CUDA(cudaMemcpyAsync(p, z, n * sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
+  TL_TRY(dot(s, r, z, s->d_scal + 0));  // rz
+  double r0 = 0;
+  TL_TRY(norm2(s, r, n, &r0));
+  int it = 0;
+  if (r0 > 0.0) {
+    for (it = 1; it <= s->pcg_max_iters; it++) {
+      TL_LAUNCH(k_spmv, sb, 256, 0, e->stream, e->n_coef, e->pat.d_off, e->pat.d_cols, s->d_H, p, Ap);
+      TL_TRY(dot(s, p, Ap, s->d_scal + 1));
+      TL_LAUNCH(k_pcg_update_xr, gb, 256, 0, e->stream, n, s->d_scal, p, Ap, x, r);
+      double rn = 0;
+      TL_TRY(norm2(s, r, n, &rn));
+      if (rn <= s->pcg_rel_tol * r0) break;
+      TL_LAUNCH(k_block_jacobi, nb, 256, 0, e->stream, e->n_coef, e->pat.d_off, e->pat.d_cols, s->d_H, r, z);
+      TL_TRY(dot(s, r, z, s->d_scal + 2));
+      TL_LAUNCH(k_pcg_update_p, gb, 256, 0, e->stream, n, s->d_scal, z, p);
+      TL_LAUNCH(k_copy_scalar, 1, 1, 0, e->stream, s->d_scal + 0, s->d_scal + 2);
+    }
+  }
+  TL_CUDA(cudaGetLastError());
+  *iters_out = std::min(it, s->pcg_max_iters);
+  return TLFEA_OK;
+}
+
+}  // namespace tlfea
+
+using namespace tlfea;
+
+extern "C" {
+
+int tlfea_newton_create(tlfea_elem *e, int n_constraints, tlfea_newton **out) {
+  TL_CHECK(e && out, "null input");
+  TL_CHECK(n_constraints >= 0, "negative n_constraints");
+  TL_CUDA(cudaSetDevice(e->device));
+  tlfea_newton *s = new tlfea_newton();
+  s->e = e;
+  s->n_constraints = n_constraints;
+  const size_t nd = 3 * (size_t)e->n_coef;
+  TL_TRY(dmalloc(&s->d_v, nd));
+  TL_TRY(dmalloc(&s->d_v_prev, nd));
+  TL_TRY(dmalloc(&s->d_lambda, (size_t)std::max(n_constraints, 1)));
+  TL_TRY(dmalloc(&s->d_g, nd));
+  TL_TRY(dmalloc(&s->d_dv, nd));
+  TL_TRY(dmalloc(&s->d_r, nd));
+  TL_TRY(dmalloc(&s->d_xp, (size_t)e->n_coef));
+  TL_TRY(dmalloc(&s->d_yp, (size_t)e->n_coef));
+  TL_TRY(dmalloc(&s->d_zp, (size_t)e->n_coef));
+  TL_TRY(dmalloc(&s->d_scal, 8 + DOT_BLOCKS));
+  TL_CUDA(cudaMallocHost((void **)&s->h_scal, 8 * sizeof(double)));
+  for (auto &ev : s->ev) TL_CUDA(cudaEventCreate(&ev));
+  TL_CUDA(cudaMemsetAsync(s->d_v, 0, nd * sizeof(double), e->stream));
+  TL_CUDA(cudaMemsetAsync(s->d_v_prev, 0, nd * sizeof(double), e->stream));
+  TL_CUDA(cudaMemsetAsync(s->d_lambda, 0, std::max(n_constraints, 1) * sizeof(double), e->stream));
+  TL_CUDA(cudaMemsetAsync(s->d_g, 0, nd * sizeof(double), e->stream));
+  TL_CUDA(cudaStreamSynchronize(e->stream));
+  *out = s;
+  return TLFEA_OK;
+}
+
+int tlfea_newton_destroy(tlfea_newton *s) {
+  if (!s) return TLFEA_OK;
+  cudaSetDevice(s->e->device);
+  cudaStreamSynchronize(s->e->stream);
+  dfree(s->d_H);
+  dfree(s->d_gp);
+  dfree(s->d_v);
+  dfree(s->d_v_prev);
+  dfree(s->d_lambda);
+  dfree(s->d_g);
+  dfree(s->d_dv);
+  dfree(s->d_r);
+  dfree(s->d_xp);
+  dfree(s->d_yp);
+  dfree(s->d_zp);
+  dfree(s->d_cons_slot);
+  dfree(s->d_cons_val);
+  for (auto &p : s->d_pcg) dfree(p);
+  dfree(s->d_scal);
+  if (s->h_scal) cudaFreeHost(s->h_scal);
+  for (auto &ev : s->ev)
+    if (ev) cudaEventDestroy(ev);
+  delete s;
+  return TLFEA_OK;
+}
+
+int tlfea_newton_set_params(tlfea_newton *s, const tlfea_newton_params *p) {
+  TL_CHECK(s && p, "null input");
+  s->prm = *p;
+  return TLFEA_OK;
+}
+
+int tlfea_newton_setup(tlfea_newton *s) {
+  TL_CHECK(s, "null handle");
+  tlfea_elem *e = s->e;
+  TL_CUDA(cudaSetDevice(e->device));
+  const size_t nd = 3 * (size_t)e->n_coef;
+  TL_CUDA(cudaMemsetAsync(s->d_v, 0, nd * sizeof(double), e->stream));
+  TL_CUDA(cudaMemsetAsync(s->d_v_prev, 0, nd * sizeof(double), e->stream));
+  TL_CUDA(cudaMemsetAsync(s->d_lambda, 0, std::max(s->n_constraints, 1) * sizeof(double), e->stream));
+  TL_CUDA(cudaMemsetAsync(s->d_g, 0, nd * sizeof(double), e->stream));
+  return TLFEA_OK;
+}
+
+int tlfea_newton_analyze_sparsity(tlfea_newton *s) {
+  TL_CHECK(s, "null handle");
+  if (s->analyzed) return TLFEA_OK;
+  tlfea_elem *e = s->e;
+  TL_CUDA(cudaSetDevice(e->device));
+  TL_TRY(ensure_pattern(e));
+  s->nnz = 9 * e->pat.nnz;
+  TL_TRY(dmalloc(&s->d_H, (size_t)s->nnz));
+  s->rec_doubles = (e->model == TL_MODEL_MR) ? REC_MR : REC_SVK;
+  // records are sized for the larger layout lazily: reallocated if the material model changes
+  TL_TRY(dmalloc(&s->d_gp, (size_t)e->n_elem * e->Q * s->rec_doubles));
+  if (s->n_constraints > 0) {
+    TL_CHECK(e->cons_mode != TL_CONS_NONE, "solver has constraints but the element has none set up");
+    TL_CHECK(s->n_constraints == e->n_constraint, "n_constraints (%d) != element constraints (%d)", s->n_constraints,
+             e->n_constraint);
+    if (e->cons_mode == TL_CONS_FIXED_NODES) {
+      s->n_cons_slots = 3 * (int64_t)e->n_fixed;
+      TL_TRY(dmalloc(&s->d_cons_slot, (size_t)s->n_cons_slots));
+      TL_TRY(dmalloc(&s->d_cons_val, (size_t)s->n_cons_slots));
+      if (e->n_fixed > 0)
+        TL_LAUNCH(k_fixed_cons_slots, blocks_for(3 * e->n_fixed, 256), 256, 0, e->stream, e->n_fixed, e->d_fixed,
+                  e->pat.d_off, e->pat.d_cols, s->d_cons_slot, s->d_cons_val);
+    } else {
+      // general linear constraints: J^T J on the host (small systems), merged per slot in row order
+      std::vector<int> off(e->n_coef + 1), cols(e->pat.nnz);
+      TL_CUDA(cudaMemcpy(off.data(), e->pat.d_off, off.size() * sizeof(int), cudaMemcpyDeviceToHost));
+      TL_CUDA(cudaMemcpy(cols.data(), e->pat.d_cols, cols.size() * sizeof(int), cudaMemcpyDeviceToHost));
+      std::vector<int> joff(e->n_constraint + 1), jcols(e->j_nnz);
+      std::vector<double> jvals(e->j_nnz);
+      TL_CUDA(cudaMemcpy(joff.data(), e->d_j_off, joff.size() * sizeof(int), cudaMemcpyDeviceToHost));
+      TL_CUDA(cudaMemcpy(jcols.data(), e->d_j_cols, jcols.size() * sizeof(int), cudaMemcpyDeviceToHost));
+      TL_CUDA(cudaMemcpy(jvals.data(), e->d_j_vals, jvals.size() * sizeof(double), cudaMemcpyDeviceToHost));
+      std::vector<std::pair<int64_t, double>> entries;
+      for (int c = 0; c < e->n_constraint; c++)
+        for (int a = joff[c]; a < joff[c + 1]; a++)
+          for (int b = joff[c]; b < joff[c + 1]; b++) {
+            const int di = jcols[a], dj = jcols[b], ci = di / 3, cj = dj / 3;
+            const int rs = off[ci], deg = off[ci + 1] - rs;
+            auto it = std::lower_bound(cols.begin() + rs, cols.begin() + rs + deg, cj);
+            // the reference silently drops entries outside the pattern (SyncedNewton.cu:336)
+            if (it == cols.begin() + rs + deg || *it != cj) continue;
+            const int pos = (int)(it - (cols.begin() + rs));
+            entries.emplace_back(9 * (int64_t)rs + (int64_t)(di % 3) * 3 * deg + 3 * pos + dj % 3,
+                                 jvals[a] * jvals[b]);
+          }
+      std::stable_sort(entries.begin(), entries.end(),
+                       [](const std::pair<int64_t, double> &x, const std::pair<int64_t, double> &y) {
+                         return x.first < y.first;
+                       });
+      std::vector<int64_t> us;
+      std::vector<double> uv;
+      for (auto &en : entries) {
+        if (!us.empty() && us.back() == en.first)
+          uv.back() += en.second;
+        else {
+          us.push_back(en.first);
+          uv.push_back(en.second);
+        }
+      }
+      s->n_cons_slots = (int64_t)us.size();
+      TL_TRY(dmalloc(&s->d_cons_slot, us.size()));
+      TL_TRY(dmalloc(&s->d_cons_val, us.size()));
+      TL_CUDA(cudaMemcpy(s->d_cons_slot, us.data(), us.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+      TL_CUDA(cudaMemcpy(s->d_cons_val, uv.data(), us.size() * sizeof(double), cudaMemcpyHostToDevice));
+    }
+  }
+  TL_CUDA(cudaGetLastError());
+  TL_CUDA(cudaStreamSynchronize(e->stream));
+  s->analyzed = true;
+  return TLFEA_OK;
+}
+
+int tlfea_newton_set_fixed_pattern(tlfea_newton *s, int fixed) {
+  TL_CHECK(s, "null handle");
+  s->fixed_pattern = fixed != 0;
+  return TLFEA_OK;
+}
+
+static int ensure_records(tlfea_newton *s) {
+  const int need = (s->e->model == TL_MODEL_MR) ? REC_MR : REC_SVK;
+  if (need != s->rec_doubles) {
+    dfree(s->d_gp);
+    s->rec_doubles = need;
+    TL_TRY(dmalloc(&s->d_gp, (size_t)s->e->n_elem * s->e->Q * need));
+  }
+  return TLFEA_OK;
+}
+
+int tlfea_newton_assemble(tlfea_newton *s) {
+  TL_CHECK(s, "null handle");
+  TL_CHECK(s->analyzed, "AnalyzeHessianSparsity must run before assembling");
+  TL_TRY(ensure_records(s));
+  TL_TRY(do_assemble(s, true));
+  return collect_timing(s, true);
+}
+
+int tlfea_newton_assemble_force(tlfea_newton *s) {
+  TL_CHECK(s, "null handle");
+  TL_TRY(do_assemble(s, false));
+  return collect_timing(s, false);
+}
+
+int tlfea_newton_residual(tlfea_newton *s, double *norm_g) {
+  TL_CHECK(s, "null handle");
+  TL_CUDA(cudaSetDevice(s->e->device));
+  TL_TRY(compute_residual(s));
+  if (norm_g) TL_TRY(norm2(s, s->d_g, 3 * (int64_t)s->e->n_coef, norm_g));
+  return TLFEA_OK;
+}
+
+int tlfea_newton_set_pcg(tlfea_newton *s, int max_iters, double rel_tol) {
+  TL_CHECK(s && max_iters > 0 && rel_tol >= 0.0, "bad PCG settings");
+  s->pcg_max_iters = max_iters;
+  s->pcg_rel_tol = rel_tol;
+  return TLFEA_OK;
+}
+
+int tlfea_newton_solve_step(tlfea_newton *s) {
+  TL_CHECK(s, "null handle");
+  tlfea_elem *e = s->e;
+  TL_CUDA(cudaSetDevice(e->device));
+  if (!s->analyzed) TL_TRY(tlfea_newton_analyze_sparsity(s));
+  TL_TRY(ensure_records(s));
+  const int64_t n = 3 * (int64_t)e->n_coef;
+  const size_t cb = (size_t)e->n_coef * sizeof(double);
+  for (int i = 0; i < 3; i++)
+    if (!s->d_pcg[i]) TL_TRY(dmalloc(&s->d_pcg[i], (size_t)n));
+  const double h = s->prm.time_step;
+  // update_pos_prev  (SyncedNewton.cu:1035)
+  TL_CUDA(cudaMemcpyAsync(s->d_xp, e->d_x, cb, cudaMemcpyDeviceToDevice, e->stream));
+  TL_CUDA(cudaMemcpyAsync(s->d_yp, e->d_y, cb, cudaMemcpyDeviceToDevice, e->stream));
+  TL_CUDA(cudaMemcpyAsync(s->d_zp, e->d_z, cb, cudaMemcpyDeviceToDevice, e->stream));
+  s->last_newton = 0;
+  s->last_pcg = 0;
+  s->last_norm_c = 0;
+  for (int outer = 0; outer < s->prm.max_outer; outer++) {
+    double norm_g0 = -1.0;
+    for (int it = 0; it < s->prm.max_inner; it++) {
+      // force + H in one fused pass; the reference evaluates the force first and skips H on
+      // convergence, we assemble both and discard H in that case (one extra pass at most).
+      TL_TRY(do_assemble(s, true));
+      TL_TRY(collect_timing(s, true));
+      TL_TRY(compute_residual(s));
+      double norm_g = 0;
+      TL_TRY(norm2(s, s->d_g, n, &norm_g));
+      s->last_norm_g = norm_g;
+      if (norm_g0 < 0.0) norm_g0 = norm_g;
+      if (norm_g < s->prm.inner_atol ||
+          (s->prm.inner_rtol > 0.0 && norm_g0 > 0.0 && norm_g <= s->prm.inner_rtol * norm_g0))
+        break;
+      TL_LAUNCH(k_neg_copy, blocks_for(n, 256), 256, 0, e->stream, n, s->d_g, s->d_r);
+      int pit = 0;
+      TL_TRY(pcg_solve(s, &pit));
+      s->last_pcg += pit;
+      s->last_newton++;
+      TL_LAUNCH(k_axpy, blocks_for(n, 256), 256, 0, e->stream, n, 1.0, s->d_dv, s->d_v);
+      TL_LAUNCH(k_update_pos, blocks_for(e->n_coef, 256), 256, 0, e->stream, e->n_coef, s->d_xp, s->d_yp, s->d_zp,
+                s->d_v, h, e->d_x, e->d_y, e->d_z);
+    }
+    TL_CUDA(cudaMemcpyAsync(s->d_v_prev, s->d_v, n * sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
+    if (s->n_constraints > 0) {
+      TL_TRY(eval_constraints(s));
+      TL_LAUNCH(k_dual_update, blocks_for(s->n_constraints, 256), 256, 0, e->stream, s->n_constraints,
+                e->d_constraint, s->prm.rho, s->d_lambda);
+      double nc = 0;
+      TL_TRY(norm2(s, e->d_constraint, s->n_constraints, &nc));
+      s->last_norm_c = nc;
+      if (nc < s->prm.outer_tol) break;
+    }
+  }
+  TL_CUDA(cudaGetLastError());
+  TL_CUDA(cudaStreamSynchronize(e->stream));
+  return TLFEA_OK;
+}
+
+int tlfea_newton_last_stats(tlfea_newton *s, int *newton_iters, int *pcg_iters, double *norm_g, double *norm_c) {
+  TL_CHECK(s, "null handle");
+  if (newton_iters) *newton_iters = s->last_newton;
+  if (pcg_iters) *pcg_iters = s->last_pcg;
+  if (norm_g) *norm_g = s->last_norm_g;
+  if (norm_c) *norm_c = s->last_norm_c;
+  return TLFEA_OK;
+}
+
+int64_t tlfea_newton_nnz(const tlfea_newton *s) { return s ? s->nnz : -1; }
+int tlfea_newton_n_dofs(const tlfea_newton *s) { return s ? 3 * s->e->n_coef : -1; }
+
+int tlfea_newton_get_hessian_csr(tlfea_newton *s, int64_t *row_offsets, int *col_indices, double *values) {
+  TL_CHECK(s && s->analyzed, "AnalyzeHessianSparsity must run first");
+  tlfea_elem *e = s->e;
+  TL_CUDA(cudaSetDevice(e->device));
+  TL_CUDA(cudaStreamSynchronize(e->stream));
+  if (row_offsets || col_indices) {
+    // expansion of the coefficient pattern: row 3i+d gets 3*deg(i) columns {3j,3j+1,3j+2}
+    // (build_dof_row_nnz_from_coef_csr / fill_dof_cols_from_coef_csr, SyncedNewton.cu:162-205)
+    std::vector<int> off(e->n_coef + 1), cols(e->pat.nnz);
+    TL_CUDA(cudaMemcpy(off.data(), e->pat.d_off, off.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    TL_CUDA(cudaMemcpy(cols.data(), e->pat.d_cols, cols.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    if (row_offsets) {
+      row_offsets[0] = 0;
+      for (int i = 0; i < e->n_coef; i++) {
+        const int64_t deg = off[i + 1] - off[i];
+        for (int d = 0; d < 3; d++) row_offsets[3 * (size_t)i + d + 1] = row_offsets[3 * (size_t)i + d] + 3 * deg;
+      }
+    }
+    if (col_indices) {
+      for (int i = 0; i < e->n_coef; i++) {
+        const int rs = off[i], deg = off[i + 1] - rs;
+        for (int d = 0; d < 3; d++) {
+          int64_t o = 9 * (int64_t)rs + (int64_t)d * 3 * deg;
+          for (int k = 0; k < deg; k++) {
+            const int b = 3 * cols[rs + k];
+            col_indices[o++] = b;
+            col_indices[o++] = b + 1;
+            col_indices[o++] = b + 2;
+          }
+        }
+      }
+    }
+  }
+  if (values) TL_CUDA(cudaMemcpy(values, s->d_H, (size_t)s->nnz * sizeof(double), cudaMemcpyDeviceToHost));
+  return TLFEA_OK;
+}
+
+static int vec_d2h(tlfea_newton *s, double *out, const double *src, int n) {
+  TL_CHECK(s && out && n == 3 * s->e->n_coef, "size mismatch");
+  TL_CUDA(cudaSetDevice(s->e->device));
+  TL_CUDA(cudaMemcpyAsync(out, src, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s->e->stream));
+  TL_CUDA(cudaStreamSynchronize(s->e->stream));
+  return TLFEA_OK;
+}
+static int vec_h2d(tlfea_newton *s, double *dst, const double *in, int n) {
+  TL_CHECK(s && in && n == 3 * s->e->n_coef, "size mismatch");
+  TL_CUDA(cudaSetDevice(s->e->device));
+  TL_CUDA(cudaMemcpyAsync(dst, in, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s->e->stream));
+  TL_CUDA(cudaStreamSynchronize(s->e->stream));
+  return TLFEA_OK;
+}
+int tlfea_newton_get_g(tlfea_newton *s, double *out, int n) { return vec_d2h(s, out, s ? s->d_g : nullptr, n); }
+int tlfea_newton_get_v(tlfea_newton *s, double *out, int n) { return vec_d2h(s, out, s ? s->d_v : nullptr, n); }
+int tlfea_newton_set_v(tlfea_newton *s, const double *v, int n) { return vec_h2d(s, s ? s->d_v : nullptr, v, n); }
+int tlfea_newton_set_v_prev(tlfea_newton *s, const double *v, int n) {
+  return vec_h2d(s, s ? s->d_v_prev : nullptr, v, n);
+}
+double *tlfea_newton_devptr_v(tlfea_newton *s) { return s ? s->d_v : nullptr; }
+double *tlfea_newton_devptr_hessian_values(tlfea_newton *s) { return s ? s->d_H : nullptr; }
+double *tlfea_newton_devptr_g(tlfea_newton *s) { return s ? s->d_g : nullptr; }
+
+int tlfea_newton_spmv(tlfea_newton *s, const double *d_x, double *d_y) {
+  TL_CHECK(s && s->analyzed && d_x && d_y, "bad input");
+  tlfea_elem *e = s->e;
+  TL_CUDA(cudaSetDevice(e->device));
+  TL_LAUNCH(k_spmv, blocks_for((int64_t)e->n_coef * 32, 256), 256, 0, e->stream, e->n_coef, e->pat.d_off,
+            e->pat.d_cols, s->d_H, d_x, d_y);
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
+int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset) {
+  TL_CHECK(s, "null handle");
+  if (ms_total) *ms_total = s->ms_total;
+  if (calls) *calls = s->calls;
+  if (reset) {
+    s->ms_total = 0;
+    s->calls = 0;
+    s->k_ms[0] = s->k_ms[1] = s->k_ms[2] = 0;
+  }
+  return TLFEA_OK;
+}
+int tlfea_newton_set_profile(tlfea_newton *s, int on) {
+  TL_CHECK(s, "null handle");
+  s->profile = on != 0;
+  return TLFEA_OK;
+}
+int tlfea_newton_kernel_ms(tlfea_newton *s, double *gp_ms, double *row_ms, double *other_ms) {
+  TL_CHECK(s, "null handle");
+  if (gp_ms) *gp_ms = s->k_ms[0];
+  if (row_ms) *row_ms = s->k_ms[1];
+  if (other_ms) *other_ms = s->k_ms[2];
+  return TLFEA_OK;
+}
+
+// ---------------------------------------------------------------------------
+__global__ void k_pack(int n, const double *__restrict__ vec, const int *__restrict__ idx, double *buf) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) buf[i] = vec[idx[i]];
+}
+__global__ void k_unpack(int n, double *vec, const int *__restrict__ idx, const double *__restrict__ buf) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) vec[idx[i]] = buf[i];
+}
+int tlfea_dist_pack(tlfea_newton *s, const double *d_vec, const int *d_idx, int n, double *d_buf) {
+  TL_CHECK(s && d_vec && d_idx && d_buf && n >= 0, "bad input");
+  if (n == 0) return TLFEA_OK;
+  TL_CUDA(cudaSetDevice(s->e->device));
+  TL_LAUNCH(k_pack, blocks_for(n, 256), 256, 0, s->e->stream, n, d_vec, d_idx, d_buf);
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+int tlfea_dist_unpack(tlfea_newton *s, double *d_vec, const int *d_idx, int n, const double *d_buf) {
+  TL_CHECK(s && d_vec && d_idx && d_buf && n >= 0, "bad input");
+  if (n == 0) return TLFEA_OK;
+  TL_CUDA(cudaSetDevice(s->e->device));
+  TL_LAUNCH(k_unpack, blocks_for(n, 256), 256, 0, s->e->stream, n, d_vec, d_idx, d_buf);
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
+// FP64 FMA peak: 8 independent chains per thread, 4096 dependent steps each
+__global__ void __launch_bounds__(256) k_fp64_peak(double *out, int iters) {
+  double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6,
+         a7 = a0 + 7;
+  const double m = 1.0000001, c = 1e-9;
+  for (int i = 0; i < iters; i++) {
+    a0 = a0 * m + c; a1 = a1 * m + c; a2 = a2 * m + c; a3 = a3 * m + c;
+    a4 = a4 * m + c; a5 = a5 * m + c; a6 = a6 * m + c; a7 = a7 * m + c;
+  }
+  out[(int64_t)blockIdx.x * 256 + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+int tlfea_fp64_peak(int device, double *tflops) {
+  TL_CHECK(tflops, "null out");
+  TL_CUDA(cudaSetDevice(device));
+  const int blocks = 148 * 16, iters = 8192;
+  double *d = nullptr;
+  TL_TRY(dmalloc(&d, (size_t)blocks * 256));
+  cudaEvent_t a, b;
+  TL_CUDA(cudaEventCreate(&a));
+  TL_CUDA(cudaEventCreate(&b));
+  double best = 0;
+  for (int rep = 0; rep < 5; rep++) {
+    TL_CUDA(cudaEventRecord(a));
+    k_fp64_peak<<<blocks, 256>>>(d, iters);
+    g_launches.fetch_add(1);
+    TL_CUDA(cudaEventRecord(b));
+    TL_CUDA(cudaEventSynchronize(b));
+    float ms = 0;
+    TL_CUDA(cudaEventElapsedTime(&ms, a, b));
+    const double fl = 2.0 * 8 * (double)iters * blocks * 256;
+    best = std::max(best, fl / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  cudaFree(d);
+  *tflops = best;
+  return TLFEA_OK;
+}
+
+}  // extern "C"

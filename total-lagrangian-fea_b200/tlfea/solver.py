@@ -1,0 +1,137 @@
+"""Host-side mirror of SyncedNewtonSolver (lib_src/solvers/SyncedNewton.{cu,cuh}) over the C ABI."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import NewtonParams, c_dp, c_ip, check, lib
+from .elements import ElementBase
+
+
+def SyncedNewtonParams(inner_atol, inner_rtol, outer_tol, rho, max_outer, max_inner, time_step) -> NewtonParams:
+    """SyncedNewtonParams {inner_atol, inner_rtol, outer_tol, rho, max_outer, max_inner, time_step}
+    (SyncedNewton.cuh:29-33)."""
+    return NewtonParams(inner_atol, inner_rtol, outer_tol, rho, int(max_outer), int(max_inner), time_step)
+
+
+def _d(a):
+    return a.ctypes.data_as(c_dp)
+
+
+class SolverBase:
+    """SolverBase (lib_src/solvers/SolverBase.h:16-22)."""
+
+    def Solve(self):
+        raise NotImplementedError
+
+    def SetParameters(self, params):
+        raise NotImplementedError
+
+
+class SyncedNewtonSolver(SolverBase):
+    def __init__(self, data: ElementBase, n_constraints: int):
+        self.data = data
+        self._h = _lib.c_vp()
+        check(lib.tlfea_newton_create(data._h, int(n_constraints), C.byref(self._h)))
+        self.n_dofs = lib.tlfea_newton_n_dofs(self._h)
+
+    def __del__(self):
+        try:
+            if self._h:
+                lib.tlfea_newton_destroy(self._h)
+                self._h = _lib.c_vp()
+        except Exception:
+            pass
+
+    # ---- reference API ---------------------------------------------------
+    def Setup(self):
+        check(lib.tlfea_newton_setup(self._h))
+
+    def SetParameters(self, params: NewtonParams):
+        self._params = params
+        check(lib.tlfea_newton_set_params(self._h, C.byref(params)))
+
+    def AnalyzeHessianSparsity(self):
+        check(lib.tlfea_newton_analyze_sparsity(self._h))
+
+    def SetFixedSparsityPattern(self, fixed: bool):
+        check(lib.tlfea_newton_set_fixed_pattern(self._h, int(bool(fixed))))
+
+    def Solve(self):
+        """One implicit step (OneStepNewtonCuDSS, SyncedNewton.cu:909-1394)."""
+        check(lib.tlfea_newton_solve_step(self._h))
+
+    def GetVelocityGuessDevicePtr(self):
+        return lib.tlfea_newton_devptr_v(self._h)
+
+    # ---- the benchmarked unit and its inspection hooks ---------------------
+    def Assemble(self):
+        check(lib.tlfea_newton_assemble(self._h))
+
+    def AssembleForce(self):
+        check(lib.tlfea_newton_assemble_force(self._h))
+
+    def Residual(self) -> float:
+        out = C.c_double(0.0)
+        check(lib.tlfea_newton_residual(self._h, C.byref(out)))
+        return out.value
+
+    def SetPCG(self, max_iters: int, rel_tol: float):
+        check(lib.tlfea_newton_set_pcg(self._h, int(max_iters), float(rel_tol)))
+
+    def LastStats(self):
+        a, b = C.c_int(0), C.c_int(0)
+        g, c = C.c_double(0), C.c_double(0)
+        check(lib.tlfea_newton_last_stats(self._h, C.byref(a), C.byref(b), C.byref(g), C.byref(c)))
+        return {"newton_iters": a.value, "pcg_iters": b.value, "norm_g": g.value, "norm_c": c.value}
+
+    def nnz(self) -> int:
+        return lib.tlfea_newton_nnz(self._h)
+
+    def RetrieveHessianCSR(self, want_cols=True, want_values=True):
+        nnz = self.nnz()
+        ro = np.empty(self.n_dofs + 1, dtype=np.int64)
+        ci = np.empty(nnz, dtype=np.int32) if want_cols else None
+        va = np.empty(nnz) if want_values else None
+        check(lib.tlfea_newton_get_hessian_csr(
+            self._h, ro.ctypes.data_as(_lib.c_i64p),
+            None if ci is None else ci.ctypes.data_as(c_ip), None if va is None else _d(va)))
+        return ro, ci, va
+
+    def RetrieveHessianValues(self):
+        va = np.empty(self.nnz())
+        check(lib.tlfea_newton_get_hessian_csr(self._h, None, None, _d(va)))
+        return va
+
+    def RetrieveGradient(self):
+        out = np.empty(self.n_dofs)
+        check(lib.tlfea_newton_get_g(self._h, _d(out), self.n_dofs))
+        return out
+
+    def RetrieveVelocity(self):
+        out = np.empty(self.n_dofs)
+        check(lib.tlfea_newton_get_v(self._h, _d(out), self.n_dofs))
+        return out
+
+    def SetVelocityGuess(self, v):
+        v = np.ascontiguousarray(v, dtype=np.float64)
+        check(lib.tlfea_newton_set_v(self._h, _d(v), v.shape[0]))
+
+    def SetVelocityPrev(self, v):
+        v = np.ascontiguousarray(v, dtype=np.float64)
+        check(lib.tlfea_newton_set_v_prev(self._h, _d(v), v.shape[0]))
+
+    def Timing(self, reset=False):
+        ms, calls = C.c_double(0), C.c_int(0)
+        check(lib.tlfea_newton_timing(self._h, C.byref(ms), C.byref(calls), int(reset)))
+        return ms.value, calls.value
+
+    def SetProfile(self, on: bool):
+        check(lib.tlfea_newton_set_profile(self._h, int(on)))
+
+    def KernelMs(self):
+        a, b, c = C.c_double(0), C.c_double(0), C.c_double(0)
+        check(lib.tlfea_newton_kernel_ms(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"gp_ms": a.value, "row_ms": b.value, "other_ms": c.value}
