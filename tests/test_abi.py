@@ -1,0 +1,57 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every symbol
+include/tlfea_b200.h declares, the ctypes table is in sync with the header, and the product
+refuses to run without a CUDA device (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from conftest import ROOT, _has_gpu
+
+HEADER = os.path.join(ROOT, "include", "tlfea_b200.h")
+
+
+def _declared():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(tlfea_[A-Za-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_exported_and_bound():
+    import tlfea
+    from tlfea import _lib
+
+    names = _declared()
+    assert len(names) > 60
+    raw = C.CDLL(_lib.LIB_PATH)
+    for n in names:
+        assert hasattr(raw, n), f"{n} declared in the header but not exported"
+    assert sorted(_lib.exported_symbols()) == names
+    assert tlfea.lib.tlfea_version() >= 100
+
+
+def test_params_struct_layout():
+    from tlfea import NewtonParams
+
+    # SyncedNewtonParams {double x4; int x2; double} -> 48 bytes (SyncedNewton.cuh:29-33)
+    assert C.sizeof(NewtonParams) == 48
+    assert NewtonParams.time_step.offset == 40
+
+
+@pytest.mark.skipif(_has_gpu(), reason="checks the no-device error path")
+def test_no_cpu_fallback():
+    import tlfea
+
+    with pytest.raises(tlfea.TlfeaError) as ei:
+        tlfea.GPU_FEAT10_Data(4, 20)
+    assert ei.value.code == -4  # TLFEA_ERR_NO_DEVICE
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "total-lagrangian-fea_b200")
+    for dp, _, fns in os.walk(pkg):
+        for fn in fns:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                txt = open(os.path.join(dp, fn)).read()
+                assert "oracle" not in txt.lower() or fn == "README.md", f"{fn} mentions the oracle"

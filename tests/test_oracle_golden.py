@@ -1,0 +1,138 @@
+"""CPU tests: pin the oracle (oracle/tlfea_oracle.c, a C restatement of the reference's CUDA device
+functions) against golden vectors produced by the reference's own numpy prototypes
+(tests/golden/make_golden.py) and against analytical invariants.
+
+FP64 tolerance: 1e-12 relative to the largest entry (north_star), written at each assert.
+"""
+import numpy as np
+import pytest
+
+from conftest import rel_err
+from oracle import oracle as orc
+
+TOL = 1e-12
+
+
+@pytest.fixture(scope="module")
+def o(golden_t10):
+    return orc.T10Oracle(golden_t10["E"], golden_t10["X"])
+
+
+def _dense_from_csr(o, H):
+    ro, ci = orc.dof_pattern(o.off, o.cols)
+    n = ro.shape[0] - 1
+    D = np.zeros((n, n))
+    for r in range(n):
+        D[r, ci[ro[r]:ro[r + 1]]] = H[ro[r]:ro[r + 1]]
+    return D
+
+
+def test_precompute_matches_prototype(o, golden_t10):
+    g = golden_t10["grad_N"]  # (ne,5,10,3)
+    ours = o.grad_N.reshape(-1, 5, 3, 10).transpose(0, 1, 3, 2)  # stored [j*10+a]
+    assert rel_err(ours, g) < TOL
+    assert rel_err(o.detJ, golden_t10["detJ"]) < TOL
+    assert rel_err(o.qw, golden_t10["w"]) < 1e-15
+    # sum detJ*w = volume of the 3x2x1 beam
+    assert abs((o.detJ * o.qw[None, :]).sum() - 6.0) < 1e-11
+
+
+def test_pattern_is_sorted_unique_adjacency(o, golden_t10):
+    E = golden_t10["E"]
+    nn = golden_t10["X"].shape[0]
+    adj = [set() for _ in range(nn)]
+    for e in E:
+        for i in e:
+            adj[i].update(int(j) for j in e)
+    off = np.zeros(nn + 1, dtype=np.int64)
+    cols = []
+    for i in range(nn):
+        c = sorted(adj[i])
+        cols.extend(c)
+        off[i + 1] = len(cols)
+    assert np.array_equal(o.off, off)
+    assert np.array_equal(o.cols, np.array(cols))
+
+
+def test_force_svk_matches_prototype(o, golden_t10):
+    mat = orc.Material.svk(float(golden_t10["Emod"]), float(golden_t10["nu"]))
+    f, F, P = o.force(golden_t10["x"], mat)
+    assert rel_err(f, golden_t10["f_int"]) < TOL
+
+
+def test_force_damped_matches_prototype(o, golden_t10):
+    g = golden_t10
+    mat = orc.Material.svk(float(g["Emod"]), float(g["nu"]), float(g["eta_d"]), float(g["lam_d"]))
+    f, _, _ = o.force(g["x"], mat, v=g["v"].reshape(-1))
+    assert rel_err(f, g["f_damped"]) < TOL
+
+
+def test_tangent_svk_matches_prototype(o, golden_t10):
+    g = golden_t10
+    mat = orc.Material.svk(float(g["Emod"]), float(g["nu"]))
+    H = o.tangent(g["x"], mat, 1.0)
+    assert rel_err(_dense_from_csr(o, H), g["K"]) < TOL
+
+
+def test_viscous_tangent_matches_prototype(o, golden_t10):
+    g = golden_t10
+    h = 1e-3
+    mat0 = orc.Material.svk(float(g["Emod"]), float(g["nu"]))
+    matd = orc.Material.svk(float(g["Emod"]), float(g["nu"]), float(g["eta_d"]), float(g["lam_d"]))
+    # H = h*K + C (viscous block is NOT scaled by h: FEAT10DataFunc.cuh:764-790)
+    Hd = o.tangent(g["x"], matd, h)
+    want = h * g["K"] + g["C"]
+    assert rel_err(_dense_from_csr(o, Hd), want) < TOL
+    H0 = o.tangent(g["x"], mat0, h)
+    assert rel_err(_dense_from_csr(o, H0), h * g["K"]) < TOL
+
+
+def test_mass_matches_prototype(o, golden_t10):
+    g = golden_t10
+    m = o.mass(float(g["rho"]))
+    nn = o.nn
+    Md = np.zeros((nn, nn))
+    for i in range(nn):
+        Md[i, o.cols[o.off[i]:o.off[i + 1]]] = m[o.off[i]:o.off[i + 1]]
+    # prototype mass is 3N x 3N with the scalar replicated on xyz
+    assert rel_err(Md, g["M"][0::3, 0::3]) < TOL
+    assert abs(m.sum() - float(g["rho"]) * 6.0) / (float(g["rho"]) * 6.0) < 1e-12
+
+
+@pytest.mark.parametrize("model", ["svk", "mr"])
+def test_tangent_is_derivative_of_force(o, golden_t10, model):
+    """K_t ~ d f_int / d x by central differences (no golden vector exists for Mooney-Rivlin)."""
+    g = golden_t10
+    if model == "svk":
+        mat = orc.Material.svk(float(g["Emod"]), float(g["nu"]))
+    else:
+        mu = float(g["mu"])
+        K = float(g["Emod"]) / (3 * (1 - 2 * float(g["nu"])))
+        mat = orc.Material.mooney_rivlin(0.3 * mu, 0.2 * mu, 1.5 * K)
+    x = g["x"].copy()
+    Kd = _dense_from_csr(o, o.tangent(x, mat, 1.0))
+    rng = np.random.default_rng(0)
+    eps = 1e-6
+    for _ in range(6):
+        dof = int(rng.integers(0, 3 * o.nn))
+        xp, xm = x.copy(), x.copy()
+        xp.reshape(-1)[dof] += eps
+        xm.reshape(-1)[dof] -= eps
+        col = (o.force(xp, mat)[0] - o.force(xm, mat)[0]) / (2 * eps)
+        assert rel_err(Kd[:, dof], col) < 1e-6  # FD truncation + rounding bound, not the parity bound
+
+
+def test_rest_state_and_rigid_motion(o, golden_t10):
+    g = golden_t10
+    mat = orc.Material.svk(float(g["Emod"]), float(g["nu"]))
+    f0, F, P = o.force(g["X"], mat)
+    assert np.abs(f0).max() < 1e-6 * np.abs(g["f_int"]).max()
+    # rigid rotation + translation: zero internal force
+    th = 0.7
+    R = np.array([[np.cos(th), -np.sin(th), 0], [np.sin(th), np.cos(th), 0], [0, 0, 1.0]])
+    fr, _, _ = o.force(g["X"] @ R.T + np.array([0.3, -1.0, 2.0]), mat)
+    assert np.abs(fr).max() < 1e-6 * np.abs(g["f_int"]).max()
+    # K_t * (rigid translation) = 0
+    Kd = _dense_from_csr(o, o.tangent(g["x"], mat, 1.0))
+    t = np.tile([1.0, 0.0, 0.0], o.nn)
+    assert np.abs(Kd @ t).max() < 1e-9 * np.abs(Kd).max()

@@ -1,0 +1,202 @@
+"""GPU parity tests, FEAT10: the CUDA path (through the C ABI) against the oracle and the golden
+vectors on the same inputs.  Integer work (CSR pattern) bit-exact; FP64 values within 1e-12
+relative to the largest entry of the compared array (north_star tolerance)."""
+import numpy as np
+import pytest
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+E_MOD, NU, RHO, H_STEP = 7e8, 0.33, 2700.0, 1e-3
+
+
+def _mat(orc, model, damp):
+    eta, lam_d = (1e5, 2e5) if damp else (0.0, 0.0)
+    if model == "svk":
+        return orc.Material.svk(E_MOD, NU, eta, lam_d)
+    mu = E_MOD / (2 * (1 + NU))
+    K = E_MOD / (3 * (1 - 2 * NU))
+    return orc.Material.mooney_rivlin(0.3 * mu, 0.2 * mu, 1.5 * K, eta, lam_d)
+
+
+def _make(X, E, model="svk", damp=False, fixed=None, alm_rho=1e14):
+    import tlfea
+
+    d = tlfea.GPU_FEAT10_Data(E.shape[0], X.shape[0])
+    d.Initialize()
+    d.Setup(*tlfea.tet5pt_quadrature(), X[:, 0], X[:, 1], X[:, 2], E)
+    d.SetDensity(RHO)
+    if model == "svk":
+        d.SetSVK(E_MOD, NU)
+    else:
+        mu = E_MOD / (2 * (1 + NU))
+        K = E_MOD / (3 * (1 - 2 * NU))
+        d.SetMooneyRivlin(0.3 * mu, 0.2 * mu, 1.5 * K)
+    if damp:
+        d.SetDamping(1e5, 2e5)
+    nfix = 0
+    if fixed is not None:
+        d.SetNodalFixed(fixed)
+        nfix = 3 * len(fixed)
+    d.CalcDnDuPre()
+    d.CalcMassMatrix()
+    s = tlfea.SyncedNewtonSolver(d, nfix)
+    s.SetParameters(tlfea.SyncedNewtonParams(1e-4, 0.0, 1e-6, alm_rho, 1, 1, H_STEP))
+    s.Setup()
+    s.AnalyzeHessianSparsity()
+    return d, s
+
+
+@pytest.fixture(scope="module")
+def mesh():
+    from tlfea import meshgen
+
+    X, E = meshgen.kuhn_block(4)
+    x = meshgen.perturb(X, 0.05 / 4, 1234)
+    v = 0.1 * np.random.Generator(np.random.PCG64(1235)).uniform(-1, 1, size=X.shape)
+    return X, E, x, v
+
+
+def test_precompute_mass_pattern_vs_oracle(mesh):
+    from oracle import oracle as orc
+
+    X, E, x, v = mesh
+    d, s = _make(X, E)
+    o = orc.T10Oracle(E, X)
+    assert rel_err(d.RetrieveDnDuPreToCPU().reshape(o.grad_N.shape), o.grad_N) < TOL
+    assert rel_err(d.RetrieveDetJToCPU().reshape(o.detJ.shape), o.detJ) < TOL
+    off, cols, vals = d.RetrieveMassCSRToCPU()
+    assert np.array_equal(off, o.off) and np.array_equal(cols, o.cols)  # bit-exact
+    assert rel_err(vals, o.mass(RHO)) < TOL
+    ro, ci, _ = s.RetrieveHessianCSR(want_values=False)
+    ro_ref, ci_ref = orc.dof_pattern(o.off, o.cols)
+    assert np.array_equal(ro, ro_ref) and np.array_equal(ci, ci_ref)  # bit-exact
+
+
+@pytest.mark.parametrize("model,damp", [("svk", False), ("svk", True), ("mr", False), ("mr", True)])
+def test_force_tangent_hessian_vs_oracle(mesh, model, damp):
+    from oracle import oracle as orc
+
+    X, E, x, v = mesh
+    fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
+    d, s = _make(X, E, model, damp, fixed)
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    s.SetVelocityGuess(v.reshape(-1))
+    s.Assemble()
+    o = orc.T10Oracle(E, X)
+    mat = _mat(orc, model, damp)
+    f_ref, F_ref, P_ref = o.force(x, mat, v.reshape(-1) if damp else None)
+    H_ref = o.hessian(x, mat, H_STEP, RHO, fixed, 1e14)
+    assert rel_err(d.RetrieveInternalForceToCPU(), f_ref) < TOL
+    # the ALM penalty h^2*rho = 1e8 sits on a few diagonal entries; compare those and the rest separately
+    H = s.RetrieveHessianValues()
+    big = np.abs(H_ref) > 0.5 * H_STEP**2 * 1e14
+    assert big.sum() == 3 * len(fixed)
+    assert rel_err(H[big], H_ref[big]) < TOL
+    assert rel_err(H[~big], H_ref[~big]) < TOL
+
+
+def test_calc_p_and_accumulating_force(mesh):
+    """CalcP stores elastic F,P; CalcInternalForce ACCUMULATES (FEAT10Data.cu:294-333)."""
+    from oracle import oracle as orc
+
+    X, E, x, v = mesh
+    d, s = _make(X, E)
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    d.CalcP()
+    o = orc.T10Oracle(E, X)
+    f_ref, F_ref, P_ref = o.force(x, _mat(orc, "svk", False))
+    assert rel_err(d.RetrieveDeformationGradientToCPU().reshape(F_ref.shape), F_ref) < TOL
+    assert rel_err(d.RetrievePFromFToCPU().reshape(P_ref.shape), P_ref) < TOL
+    d.ClearInternalForce()
+    d.CalcInternalForce()
+    assert rel_err(d.RetrieveInternalForceToCPU(), f_ref) < TOL
+    d.CalcInternalForce()
+    assert rel_err(d.RetrieveInternalForceToCPU(), 2 * f_ref) < TOL
+
+
+def test_golden_prototype_vectors(golden_t10):
+    """Straight against the reference numpy prototype's outputs (tests/golden)."""
+    g = golden_t10
+    d, s = _make(g["X"], g["E"])
+    x = g["x"]
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    s.Assemble()
+    assert rel_err(d.RetrieveInternalForceToCPU(), g["f_int"]) < TOL
+    ro, ci, H = s.RetrieveHessianCSR()
+    n = ro.shape[0] - 1
+    D = np.zeros((n, n))
+    for r in range(n):
+        D[r, ci[ro[r]:ro[r + 1]]] = H[ro[r]:ro[r + 1]]
+    want = g["M"] * (RHO / float(g["rho"])) / H_STEP + H_STEP * g["K"]
+    assert rel_err(D, want) < TOL
+
+
+def test_bit_reproducible(mesh):
+    X, E, x, v = mesh
+    d, s = _make(X, E)
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    s.Assemble()
+    H1, f1 = s.RetrieveHessianValues(), d.RetrieveInternalForceToCPU()
+    for _ in range(3):
+        s.Assemble()
+        assert np.array_equal(H1, s.RetrieveHessianValues())
+        assert np.array_equal(f1, d.RetrieveInternalForceToCPU())
+
+
+def test_properties_at_scale():
+    """Size-independent properties on a mesh the oracle would not finish quickly (48^3 cells,
+    663 552 tets): symmetry of H, H*(translation) = (M/h)*(translation), sum f_int = 0."""
+    import torch
+    import tlfea
+    from tlfea import meshgen
+
+    n = 48
+    X, E = meshgen.kuhn_block(n)
+    x = meshgen.perturb(X, 0.05 / n, 1234)
+    d, s = _make(X, E)
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    s.Assemble()
+    f = d.RetrieveInternalForceToCPU().reshape(-1, 3)
+    assert np.abs(f.sum(0)).max() < 1e-9 * np.abs(f).max()
+    nd = s.n_dofs
+    t = torch.zeros(nd, dtype=torch.float64, device="cuda")
+    t[0::3] = 1.0
+    y = torch.empty_like(t)
+    tlfea._lib.check(tlfea.lib.tlfea_newton_spmv(s._h, t.data_ptr(), y.data_ptr()))
+    d.Sync()
+    off, cols, mvals = d.RetrieveMassCSRToCPU()
+    rowsum = np.add.reduceat(mvals, off[:-1]) / H_STEP
+    yy = y.cpu().numpy().reshape(-1, 3)
+    assert rel_err(yy[:, 0], rowsum) < 1e-9
+    assert np.abs(yy[:, 1:]).max() < 1e-9 * np.abs(rowsum).max()
+    # symmetry: x^T H y == y^T H x for random vectors
+    g = torch.Generator(device="cuda").manual_seed(1)
+    a = torch.rand(nd, dtype=torch.float64, device="cuda", generator=g)
+    b = torch.rand(nd, dtype=torch.float64, device="cuda", generator=g)
+    Ha, Hb = torch.empty_like(a), torch.empty_like(a)
+    tlfea._lib.check(tlfea.lib.tlfea_newton_spmv(s._h, a.data_ptr(), Ha.data_ptr()))
+    tlfea._lib.check(tlfea.lib.tlfea_newton_spmv(s._h, b.data_ptr(), Hb.data_ptr()))
+    d.Sync()
+    lhs, rhs = torch.dot(b, Ha).item(), torch.dot(a, Hb).item()
+    assert abs(lhs - rhs) < 1e-10 * abs(lhs)
+
+
+def test_newton_step_converges(golden_t10):
+    """One implicit step on the 36-tet beam: PCG-based Newton drives ||g|| below tolerance."""
+    import tlfea
+
+    g = golden_t10
+    X = g["X"]
+    fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
+    d, s = _make(X, g["E"], fixed=fixed, alm_rho=1e12)
+    fext = np.zeros(3 * X.shape[0])
+    fext[2::3] = -100.0
+    d.SetExternalForce(fext)
+    s.SetParameters(tlfea.SyncedNewtonParams(1e-4, 0.0, 1e-6, 1e12, 3, 10, H_STEP))
+    s.SetPCG(2000, 1e-12)
+    s.Solve()
+    st = s.LastStats()
+    assert st["norm_g"] < 1e-4, st
+    assert st["norm_c"] < 1e-6, st
