@@ -1,0 +1,398 @@
+#!/usr/bin/env python
+"""bench.py -- Gauss-point force+tangent evaluations / s, FEAT10, on N B200s of one node.
+
+A "step" is ONE pass of the hot path over the whole synthetic mesh: from the current nodal
+positions, f_int and the fully assembled H.values = M/h + h*K_t + h^2*rho*J^T J.
+Workload: structured Kuhn-split FEAT10 block, n^3 cells x 6 tets (n=119 -> 10 110 954 tets,
+50.6 M Gauss points), SVK E=7e8 nu=0.33 rho0=2700, h=1e-3, face x=0 pinned (ALM rho=1e14).
+N>1: the SAME mesh, element-partitioned in x-slabs (strong scaling); every rank assembles its
+own elements (sub-assembled H, no matrix exchange) and the interface-plane f_int is summed
+over NCCL.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--n CELLS] [--impl reference]
+
+`--impl reference` times the CPU restatement of the reference algorithm (oracle/, OpenMP on all
+host cores) on a bounded sample of the same workload; the reference's own CUDA sources cannot be
+built here (Eigen + cuDSS + Bazel), see DESIGN.md.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "total-lagrangian-fea_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+E_MOD, NU, RHO0, H_STEP, ALM_RHO = 7e8, 0.33, 2700.0, 1e-3, 1e14
+METRIC = "feat10_gauss_point_force_tangent_evals_per_s"
+UNIT = "GP/s"
+# ALGORITHMIC bytes per element (SURVEY.md 8d / DESIGN.md): reads conn 40 + gradN 1200 + detJ 40
+# + x 24*Nn/Ne; writes f_int 24*Nn/Ne + 8*nnz_H/Ne.  Nn/Ne and nnz_H/Ne are taken from the mesh.
+ALGO_FLOP_PER_GP = 7900.0
+
+
+def algorithmic_bytes(n_elem: int, n_nodes: int, nnz_h: int) -> float:
+    return n_elem * (40 + 1200 + 40) + 24.0 * n_nodes * 2 + 8.0 * nnz_h
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.idx)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, reasons, mx, pw = [], set(), None, []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in open(self.path):
+            p = [t.strip() for t in ln.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx = float(p[2])
+                pw.append(float(p[3]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, p[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.path)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm),
+                       power_w_max=max(pw) if pw else None)
+        return out
+
+
+def build_problem(n: int, rank: int, world: int, device: int):
+    """Set up the rank's slab exactly as a reference driver would set up its mesh
+    (test_feat10_bunny_newton.cc:37-208): Setup, material, CalcDnDuPre, CalcMassMatrix,
+    SetNodalFixed, solver, AnalyzeHessianSparsity."""
+    import tlfea
+    from tlfea import partition
+
+    slab = partition.kuhn_slab(n, rank, world)
+    x = partition.perturb_global(slab, 0.05 / n, 1234)
+    X, E = slab.X, slab.E
+    d = tlfea.GPU_FEAT10_Data(E.shape[0], X.shape[0], device)
+    d.Initialize()
+    d.Setup(*tlfea.tet5pt_quadrature(), X[:, 0], X[:, 1], X[:, 2], E)
+    d.SetDensity(RHO0)
+    d.SetSVK(E_MOD, NU)
+    fixed = np.nonzero(slab.node_gid < slab.plane_nodes)[0].astype(np.int32)  # global face x = 0
+    if len(fixed):
+        d.SetNodalFixed(fixed)
+    d.CalcDnDuPre()
+    d.CalcMassMatrix()
+    s = tlfea.SyncedNewtonSolver(d, 3 * len(fixed))
+    s.SetParameters(tlfea.SyncedNewtonParams(1e-4, 0.0, 1e-6, ALM_RHO, 1, 1, H_STEP))
+    s.Setup()
+    s.AnalyzeHessianSparsity()
+    s.SetFixedSparsityPattern(True)
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    return slab, x, d, s
+
+
+def cpu_sample(n_cpu: int, reps: int):
+    """The CPU restatement of the reference algorithm on an n_cpu^3-cell block of the same mesh
+    family: force + H, all host threads.  Returns (GP/s, threads, description, seconds)."""
+    from oracle import oracle as orc
+    from tlfea import meshgen
+
+    X, E = meshgen.kuhn_block(n_cpu)
+    x = meshgen.perturb(X, 0.05 / n_cpu, 1234)
+    o = orc.T10Oracle(E, X)
+    mat = orc.Material.svk(E_MOD, NU)
+    mass = o.mass(RHO0)
+    fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
+    J, _ = orc.fixed_node_jacobians(fixed, o.nn)
+    H = np.zeros(9 * o.cols.shape[0])
+
+    def one():
+        H[:] = 0.0
+        f, _, _ = o.force(x, mat)
+        orc.hessian_mass(o.off, o.cols, mass, H_STEP, H)
+        o.tangent(x, mat, H_STEP, H)
+        orc.hessian_constraints(*J, H_STEP, ALM_RHO, o.off, o.cols, H)
+        return f
+
+    one()  # warm-up
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        one()
+        ts.append(time.perf_counter() - t0)
+    dt = float(np.mean(ts))
+    return E.shape[0] * 5 / dt, orc.num_threads(), f"kuhn block n={n_cpu} ({E.shape[0]} tets) x {reps} passes", dt
+
+
+class _DevArray:
+    """Borrowed device pointer -> torch tensor (no copy) through __cuda_array_interface__."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (int(ptr), False), "version": 2}
+
+
+def run_reference(args):
+    """`--impl reference`: the reference algorithm's CPU restatement on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import __graft_entry__ as g
+
+    g.build()
+    n_cpu = args.cpu_n
+    # one "step" = one pass over the bounded sample
+    from oracle import oracle as orc  # noqa: F401
+
+    gps, threads, desc, dt = cpu_sample(n_cpu, max(args.steps, 1))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": gps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"feat10_kuhn_block_n{args.n}_svk_force_tangent_H", "sample": desc,
+                   "note": "CPU restatement (oracle/tlfea_oracle.c, OpenMP) of the reference algorithm; the reference's "
+                           "CUDA sources are unbuildable here (Eigen, cuDSS, Bazel)"},
+        "cpu_baseline": {"value": gps, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
+        "e2e": {"value": gps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--n", type=int, default=119, help="cells per edge of the global block (119 -> 10.1M tets)")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-n", type=int, default=32, help="cells per edge of the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the tlfea hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    if rank == 0:
+        import __graft_entry__ as g
+
+        g.build()
+    if world > 1:
+        dist.barrier()
+    import tlfea
+
+    launches0 = tlfea.lib.tlfea_launch_count()
+    t_setup = time.perf_counter()
+    slab, x, d, s = build_problem(args.n, rank, world, local)
+    stream = torch.cuda.current_stream().cuda_stream
+    d.SetStream(stream)
+    torch.cuda.synchronize()
+    t_setup = time.perf_counter() - t_setup
+
+    n_nodes_l, n_elem_l = slab.X.shape[0], slab.E.shape[0]
+    f_int = torch.as_tensor(_DevArray(d.GetInternalForceDevicePtr(), 3 * n_nodes_l), device=dev)
+    pn3 = 3 * slab.plane_nodes
+    halo = torch.zeros(max(world - 1, 1) * pn3, dtype=torch.float64, device=dev)
+
+    def halo_sum():
+        """interface-plane f_int summed over the two ranks that share each plane (NCCL allreduce of
+        the compact interface vector: slot p holds the plane between rank p and p+1)."""
+        if world == 1:
+            return
+        halo.zero_()
+        if slab.has_left:
+            halo[(rank - 1) * pn3: rank * pn3] = f_int[:pn3]
+        if slab.has_right:
+            halo[rank * pn3:(rank + 1) * pn3] = f_int[-pn3:]
+        dist.all_reduce(halo)
+        if slab.has_left:
+            f_int[:pn3] = halo[(rank - 1) * pn3: rank * pn3]
+        if slab.has_right:
+            f_int[-pn3:] = halo[rank * pn3:(rank + 1) * pn3]
+
+    def step():
+        s.Assemble()
+        halo_sum()
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    sync_all()
+    s.Timing(reset=True)
+    s.SetProfile(True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = tlfea.lib.tlfea_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    wall0 = time.perf_counter()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    sync_all()
+    wall = time.perf_counter() - wall0
+    clocks = sampler.stop() if rank == 0 else None
+    launches_timed = tlfea.lib.tlfea_launch_count() - l0
+    ms_total = ev0.elapsed_time(ev1)
+    kms = s.KernelMs()
+    s.SetProfile(False)
+
+    # max over ranks of the device time; totals over ranks of the work
+    red = torch.tensor([ms_total, wall * 1e3], dtype=torch.float64, device=dev)
+    tot = torch.tensor([n_elem_l, float(s.nnz()), n_nodes_l, launches_timed], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot)
+    ms_step = red[0].item() / args.steps
+    n_elem_g, nnz_g, n_nodes_sum, launches_all = (int(v) for v in tot.tolist())
+    gp_total = n_elem_g * 5
+    value = gp_total / (ms_step * 1e-3)
+
+    # ---- roofline of the dominant kernel (row-gather tangent assembly), rank 0's launch
+    row_ms = kms["row_ms"] / args.steps
+    gp_ms = kms["gp_ms"] / args.steps
+    algo_b = algorithmic_bytes(n_elem_l, n_nodes_l, s.nnz())
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    fp64 = None
+    if rank == 0:
+        import ctypes as C
+
+        tf = C.c_double(0)
+        tlfea.lib.tlfea_fp64_peak(local, C.byref(tf))
+        fp64 = tf.value
+    dom_ms = max(row_ms, 1e-9)
+    achieved = algo_b / (dom_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "row_kernel<10,5,SVK>", "achieved": achieved, "peak": hbm_peak,
+                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                "algorithmic_bytes_per_launch": algo_b, "kernel_ms": row_ms, "gp_kernel_ms": gp_ms,
+                "step_share": row_ms / max(ms_step, 1e-9)}
+    if fp64:
+        fl = ALGO_FLOP_PER_GP * n_elem_l * 5
+        roofline["fp64"] = {"achieved_tflops": fl / ((row_ms + gp_ms) * 1e-3) / 1e12, "peak_tflops": fp64,
+                            "frac": fl / ((row_ms + gp_ms) * 1e-3) / 1e12 / fp64,
+                            "peak_source": "tlfea_fp64_peak DFMA micro-benchmark, same run",
+                            "algorithmic_flop_per_gp": ALGO_FLOP_PER_GP}
+
+    # ---- e2e: host buffers in, host f_int + ||g|| out, through the reference-facing API
+    e2e = None
+    if not args.no_e2e:
+        hx = [torch.from_numpy(np.ascontiguousarray(x[:, k])).pin_memory().numpy() for k in range(3)]
+        h2d = 3 * n_nodes_l * 8
+        d2h = 3 * n_nodes_l * 8 + 8
+
+        def e2e_step():
+            d.UpdatePositions(hx[0], hx[1], hx[2])   # H2D of the step's input
+            s.Assemble()
+            halo_sum()
+            ng = s.Residual()                         # D2H scalar ||g|| (SyncedNewton.cu:1063-1064)
+            f = d.RetrieveInternalForceToCPU()        # D2H of the step's result
+            return ng, f
+
+        for _ in range(2):
+            e2e_step()
+        sync_all()
+        t0 = time.perf_counter()
+        ke = max(3, args.steps // 2)
+        for _ in range(ke):
+            e2e_step()
+        sync_all()
+        te = torch.tensor([(time.perf_counter() - t0) / ke], dtype=torch.float64, device=dev)
+        bts = torch.tensor([h2d, d2h], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+            dist.all_reduce(bts)
+        e2e = {"value": gp_total / te.item(), "unit": UNIT, "h2d_bytes_per_step": int(bts[0].item()),
+               "d2h_bytes_per_step": int(bts[1].item()), "ms_per_step": te.item() * 1e3,
+               "what": "UpdatePositions(host x,y,z) -> Assemble -> halo sum -> Residual ||g|| -> RetrieveInternalForceToCPU; "
+                       "H stays device-resident for the solver, as in the reference"}
+
+    cpu_base = None
+    if rank == 0 and not args.no_cpu_baseline:
+        gps, threads, desc, dt = cpu_sample(args.cpu_n, 5)
+        cpu_base = {"value": gps, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc,
+                    "seconds_per_pass": dt}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": f"feat10_kuhn_block_n{args.n}_svk_force_tangent_H", "n_elem": n_elem_g,
+                       "gauss_points": gp_total, "nnz_H_sum_over_ranks": nnz_g, "material": "SVK E=7e8 nu=0.33",
+                       "h": H_STEP, "partition": f"x-slabs x{world}, sub-assembled H, NCCL halo sum of f_int",
+                       "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
+                       "setup_s": t_setup},
+            "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all,
+            "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -72,6 +72,9 @@ int tlfea_elem_create(int type, int n_elem, int n_nodes, int device, tlfea_elem 
 /* Destroy()  FEAT10Data.cuh:714-779 */
 int tlfea_elem_destroy(tlfea_elem *h);
 int tlfea_elem_sync(tlfea_elem *h);
+/* Run all of the handle's work on a caller-owned cudaStream_t (the reference uses the default
+ * stream throughout; a host framework passes its current stream).  NULL = legacy default stream. */
+int tlfea_elem_set_stream(tlfea_elem *h, void *cuda_stream);
 
 /* Setup(tet5pt_x,y,z,w, x,y,z, connectivity)  FEAT10Data.cuh:435-533.
  * Quadrature tables are taken from the caller exactly as the reference does. */

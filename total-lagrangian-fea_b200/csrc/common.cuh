@@ -105,6 +105,7 @@ enum { TL_CONS_NONE = 0, TL_CONS_FIXED_NODES = 1, TL_CONS_LINEAR_CSR = 2 };
 struct tlfea_elem {
   int type = 0, n_elem = 0, n_nodes = 0, n_coef = 0, S = 0, Q = 0, device = 0;
   cudaStream_t stream = nullptr;
+  bool own_stream = true;
   bool is_setup = false, is_precomputed = false, is_pattern = false, is_mass = false;
 
   int *d_conn = nullptr;    // caller layout (reference layout), n_elem * nodes_per_elem

@@ -351,8 +351,18 @@ int tlfea_elem_destroy(tlfea_elem *h) {
   dfree(h->d_jt_cols);
   dfree(h->d_jt_vals);
   h->pat.release();
-  cudaStreamDestroy(h->stream);
+  if (h->own_stream) cudaStreamDestroy(h->stream);
   delete h;
+  return TLFEA_OK;
+}
+
+int tlfea_elem_set_stream(tlfea_elem *h, void *stream) {
+  TL_CHECK(h, "null handle");
+  TL_CUDA(cudaSetDevice(h->device));
+  TL_CUDA(cudaStreamSynchronize(h->stream));
+  if (h->own_stream) cudaStreamDestroy(h->stream);
+  h->stream = (cudaStream_t)stream;
+  h->own_stream = false;
   return TLFEA_OK;
 }
 

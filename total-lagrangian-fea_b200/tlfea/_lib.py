@@ -48,6 +48,7 @@ _SIGS = {
     "tlfea_elem_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(c_vp)]),
     "tlfea_elem_destroy": (C.c_int, [c_vp]),
     "tlfea_elem_sync": (C.c_int, [c_vp]),
+    "tlfea_elem_set_stream": (C.c_int, [c_vp, c_vp]),
     "tlfea_elem_setup_t10": (C.c_int, [c_vp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_ip]),
     "tlfea_elem_setup_3243": (C.c_int, [c_vp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_ip]),
     "tlfea_elem_setup_3443": (C.c_int, [c_vp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_ip]),

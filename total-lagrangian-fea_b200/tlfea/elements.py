@@ -130,6 +130,10 @@ class ElementBase:
     def CalcConstraintData(self):
         check(lib.tlfea_elem_calc_constraint(self._h))
 
+    def SetStream(self, cuda_stream: int):
+        """Run the handle's work on a caller-owned cudaStream_t (raw pointer value)."""
+        check(lib.tlfea_elem_set_stream(self._h, cuda_stream))
+
     def Sync(self):
         check(lib.tlfea_elem_sync(self._h))
 

@@ -1,0 +1,97 @@
+"""Element partition of the structured FEAT10 block across ranks (new design: the reference is
+single-GPU).  Slabs of whole cell layers along x; each rank builds ONLY its own slab with a local
+node numbering in which the two interface planes are contiguous, so halo packs are plain slices.
+
+Sub-assembled storage: each rank assembles f_int and H over its own elements only; the global
+operator is the sum over ranks.  f_int (and every SpMV result) is completed by a halo SUM on
+the interface planes; H itself is never exchanged.
+"""
+from __future__ import annotations
+
+import itertools
+from dataclasses import dataclass
+
+import numpy as np
+
+_EDGES = [(0, 1), (1, 2), (0, 2), (0, 3), (1, 3), (2, 3)]
+
+
+@dataclass
+class Slab:
+    n: int                 # cells per edge of the global block
+    rank: int
+    n_parts: int
+    layer0: int            # first cell layer (along x) owned
+    layer1: int            # one past the last
+    X: np.ndarray          # (n_local_nodes, 3) reference coordinates
+    E: np.ndarray          # (n_local_elems, 10) local node ids
+    node_gid: np.ndarray   # (n_local_nodes,) global node id (i*N+j)*N+k on the (2n+1)^3 lattice
+    plane_nodes: int       # nodes per lattice plane = (2n+1)^2
+    has_left: bool
+    has_right: bool
+
+    @property
+    def left_plane(self) -> slice:
+        """local node ids shared with rank-1"""
+        return slice(0, self.plane_nodes)
+
+    @property
+    def right_plane(self) -> slice:
+        """local node ids shared with rank+1"""
+        return slice(self.X.shape[0] - self.plane_nodes, self.X.shape[0])
+
+
+def slab_bounds(n: int, n_parts: int):
+    return [(n * p) // n_parts for p in range(n_parts + 1)]
+
+
+def kuhn_slab(n: int, rank: int, n_parts: int) -> Slab:
+    """The rank's part of meshgen.kuhn_block(n): same tets, same orientation, same element order
+    (restricted to the slab), local node id ((i-2*layer0)*N + j)*N + k."""
+    b = slab_bounds(n, n_parts)
+    l0, l1 = b[rank], b[rank + 1]
+    N = 2 * n + 1
+    ni = 2 * (l1 - l0) + 1
+    lin = np.arange(N, dtype=np.float64) / (2.0 * n)
+    li = (np.arange(ni, dtype=np.float64) + 2 * l0) / (2.0 * n)
+    X = np.empty((ni * N * N, 3))
+    X[:, 0] = np.repeat(li, N * N)
+    X[:, 1] = np.tile(np.repeat(lin, N), ni)
+    X[:, 2] = np.tile(lin, ni * N)
+    gi = np.repeat(np.arange(ni, dtype=np.int64) + 2 * l0, N * N)
+    node_gid = gi * N * N + np.tile(np.arange(N * N, dtype=np.int64), ni)
+
+    ci, cj, ck = np.meshgrid(np.arange(l1 - l0), np.arange(n), np.arange(n), indexing="ij")
+    base = np.stack([2 * ci.ravel(), 2 * cj.ravel(), 2 * ck.ravel()], axis=1).astype(np.int64)
+    n_cells = base.shape[0]
+    E = np.empty((n_cells, 6, 10), dtype=np.int32)
+    for t, perm in enumerate(itertools.permutations(range(3))):
+        v = np.zeros((4, 3), dtype=np.int64)
+        for s in range(3):
+            v[s + 1] = v[s]
+            v[s + 1, perm[s]] += 2
+        if np.linalg.det((v[1:] - v[0]).astype(np.float64)) < 0:
+            v[[2, 3]] = v[[3, 2]]
+        loc = [v[0], v[1], v[2], v[3]] + [(v[a] + v[c]) // 2 for a, c in _EDGES]
+        for a, off in enumerate(loc):
+            p = base + off[None, :]
+            E[:, t, a] = ((p[:, 0] * N + p[:, 1]) * N + p[:, 2]).astype(np.int32)
+    return Slab(n, rank, n_parts, l0, l1, X, E.reshape(n_cells * 6, 10), node_gid, N * N, rank > 0,
+                rank < n_parts - 1)
+
+
+def perturb_global(slab: Slab, amplitude: float, seed: int) -> np.ndarray:
+    """Same perturbation every rank would see on the GLOBAL mesh (so interface nodes agree):
+    a counter-based hash of (seed, global node id, component) -> U(-1,1)."""
+    gid = slab.node_gid.astype(np.uint64)
+    out = np.empty_like(slab.X)
+    for c in range(3):
+        z = gid * np.uint64(3) + np.uint64(c) + np.uint64(seed) * np.uint64(0x9E3779B97F4A7C15)
+        # splitmix64
+        z = (z + np.uint64(0x9E3779B97F4A7C15))
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+        u = (z >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+        out[:, c] = slab.X[:, c] + amplitude * (2.0 * u - 1.0)
+    return out
