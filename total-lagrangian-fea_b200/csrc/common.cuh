@@ -97,6 +97,22 @@ struct Pattern {
 
 int build_pattern(const int *d_ecoef, int n_elem, int S, int n_coef, cudaStream_t stream, Pattern *out);
 
+// Spatial row tiles for the tile assembly kernel (tiles.cu, tile_kernel.cuh).
+struct Tiles {
+  int n_tiles = 0;
+  int64_t n_entries = 0;          // (tile, element) incidences
+  int max_rows = 0, max_buf = 0;  // largest tile: rows, row-buffer doubles
+  int *d_trow = nullptr;          // [n_coef]       rows in tile (Morton) order
+  int *d_tile_ptr = nullptr;      // [n_tiles+1]    into d_trow
+  int *d_te_ptr = nullptr;        // [n_tiles+1]    into the entry arrays
+  int *d_te_elem = nullptr;       // [n_entries]    element id, ascending inside a tile
+  uint8_t *d_te_lrow = nullptr;   // [n_entries*S]  local row of shape function a, 255 = row not in this tile
+  uint8_t *d_te_rank = nullptr;   // [n_entries*S]  commit rank of the contribution inside its row
+  uint16_t *d_slot_e = nullptr;   // [n_elem*S*S]   column slot of (a,b) in row ecoef[e][a]
+  int *d_err = nullptr;           // [4] device error flags
+  void release();
+};
+
 }  // namespace tlfea
 
 enum { TL_MODEL_SVK = 0, TL_MODEL_MR = 1 };
@@ -143,8 +159,15 @@ struct tlfea_elem {
   int64_t j_nnz = 0;
 };
 
+namespace tlfea {
+int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, Tiles *out);
+}
+
 struct tlfea_newton {
   tlfea_elem *e = nullptr;
+  tlfea::Tiles tiles;
+  bool have_tiles = false;
+  int use_tiles = 1;  // 0: row-gather kernel, 1: tile kernel where supported
   int n_constraints = 0;
   tlfea_newton_params prm{};
   bool analyzed = false, fixed_pattern = false;

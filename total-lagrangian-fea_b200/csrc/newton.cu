@@ -7,6 +7,7 @@
 
 #include "common.cuh"
 #include "kernels.cuh"
+#include "tile_kernel.cuh"
 
 namespace tlfea {
 int launch_gp(tlfea_elem *h, const double *v, double *rec, double *fe, double *F_out, double *P_out);
@@ -252,6 +253,57 @@ static int norm2(tlfea_newton *s, const double *a, int64_t n, double *out) {
   return TLFEA_OK;
 }
 
+constexpr int TILE_WARPS = 8;
+constexpr int TILE_BUDGET = 22000;  // doubles of shared-memory row buffer per tile
+
+static bool tiles_supported(const tlfea_newton *s) {
+  return s->use_tiles && s->e->type == TLFEA_TYPE_T10 && s->e->model == TL_MODEL_SVK &&
+         s->e->pat.max_inc <= 255 && s->e->pat.max_deg * 9 <= TILE_BUDGET;
+}
+
+static int ensure_tiles(tlfea_newton *s) {
+  if (s->have_tiles) return TLFEA_OK;
+  TL_TRY(build_tiles(s->e, TILE_BUDGET, TK_MAX_ROWS, &s->tiles));
+  s->have_tiles = true;
+  return TLFEA_OK;
+}
+
+static int launch_tile(tlfea_newton *s, const RowArgs &r) {
+  tlfea_elem *e = s->e;
+  const Tiles &t = s->tiles;
+  TileArgs a;
+  a.n_tiles = t.n_tiles;
+  a.trow = t.d_trow;
+  a.tile_ptr = t.d_tile_ptr;
+  a.te_ptr = t.d_te_ptr;
+  a.te_elem = t.d_te_elem;
+  a.te_lrow = t.d_te_lrow;
+  a.te_rank = t.d_te_rank;
+  a.slot_e = t.d_slot_e;
+  a.off = r.off;
+  a.mass = r.mass;
+  a.rec = r.rec;
+  a.gradN = r.gradN;
+  a.detJ = r.detJ;
+  a.fe = r.fe;
+  a.qw = r.qw;
+  a.inv_h = r.inv_h;
+  a.c1 = r.c1;
+  a.c2 = r.c2;
+  a.c3 = r.c3;
+  a.c4 = r.c4;
+  a.mu = r.mu;
+  a.H = r.H;
+  a.f_int = r.f_int;
+  a.err = t.d_err;
+  a.buf_doubles = TILE_BUDGET;
+  const size_t smem = TileShape<10, 5, TILE_WARPS>::smem_bytes(TILE_BUDGET);
+  TL_CUDA(cudaFuncSetAttribute(tile_kernel<10, 5, TILE_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  TL_LAUNCH((tile_kernel<10, 5, TILE_WARPS>), t.n_tiles, TILE_WARPS * 32, smem, e->stream, a);
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
 static int do_assemble(tlfea_newton *s, bool tangent) {
   tlfea_elem *e = s->e;
   TL_CHECK(e->is_precomputed, "CalcDnDuPre/CalcDsDuPre must run before assembling");
@@ -300,10 +352,15 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
              e->pat.max_deg);
     const int rows_blocks = (e->n_coef + ROW_WARPS - 1) / ROW_WARPS;
     const int grid = std::min(rows_blocks, 148 * 16);
-    switch (e->type) {
-      case TLFEA_TYPE_T10: TL_TRY((launch_row_t<10, 5>(s, a, grid, smem, damp))); break;
-      case TLFEA_TYPE_3243: TL_TRY((launch_row_t<8, 12>(s, a, grid, smem, damp))); break;
-      default: TL_TRY((launch_row_t<16, 48>(s, a, grid, smem, damp)));
+    if (tiles_supported(s)) {
+      TL_TRY(ensure_tiles(s));
+      TL_TRY(launch_tile(s, a));
+    } else {
+      switch (e->type) {
+        case TLFEA_TYPE_T10: TL_TRY((launch_row_t<10, 5>(s, a, grid, smem, damp))); break;
+        case TLFEA_TYPE_3243: TL_TRY((launch_row_t<8, 12>(s, a, grid, smem, damp))); break;
+        default: TL_TRY((launch_row_t<16, 48>(s, a, grid, smem, damp)));
+      }
     }
     if (s->profile) TL_CUDA(cudaEventRecord(s->ev[3], e->stream));
     if (s->n_cons_slots > 0) {
@@ -322,6 +379,11 @@ static int collect_timing(tlfea_newton *s, bool tangent) {
   TL_CUDA(cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]));
   s->ms_total += ms;
   s->calls++;
+  if (s->have_tiles && tangent) {
+    int flag = 0;
+    TL_CUDA(cudaMemcpy(&flag, s->tiles.d_err, sizeof(int), cudaMemcpyDeviceToHost));
+    if (flag) return fail(TLFEA_ERR_CUDA, "tile kernel: ordered-commit wait timed out (device flag %d)", flag);
+  }
   if (s->profile && tangent) {
     float a = 0, b = 0, c = 0;
     cudaEventElapsedTime(&a, s->ev[0], s->ev[2]);
@@ -430,6 +492,7 @@ int tlfea_newton_destroy(tlfea_newton *s) {
   cudaStreamSynchronize(s->e->stream);
   dfree(s->d_H);
   dfree(s->d_gp);
+  s->tiles.release();
   dfree(s->d_v);
   dfree(s->d_v_prev);
   dfree(s->d_lambda);
@@ -735,6 +798,19 @@ int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset
     s->calls = 0;
     s->k_ms[0] = s->k_ms[1] = s->k_ms[2] = 0;
   }
+  return TLFEA_OK;
+}
+int tlfea_newton_set_assembly(tlfea_newton *s, int mode) {
+  TL_CHECK(s && (mode == 0 || mode == 1), "mode must be 0 (row gather) or 1 (tiles)");
+  s->use_tiles = mode;
+  return TLFEA_OK;
+}
+int tlfea_newton_tile_stats(tlfea_newton *s, int *n_tiles, int64_t *n_entries, int *max_rows, int *max_buf) {
+  TL_CHECK(s, "null handle");
+  if (n_tiles) *n_tiles = s->have_tiles ? s->tiles.n_tiles : 0;
+  if (n_entries) *n_entries = s->have_tiles ? s->tiles.n_entries : 0;
+  if (max_rows) *max_rows = s->have_tiles ? s->tiles.max_rows : 0;
+  if (max_buf) *max_buf = s->have_tiles ? s->tiles.max_buf : 0;
   return TLFEA_OK;
 }
 int tlfea_newton_set_profile(tlfea_newton *s, int on) {
