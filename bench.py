@@ -324,7 +324,7 @@ def main():
         fp64 = tf.value
     dom_ms = max(row_ms, 1e-9)
     achieved = algo_b / (dom_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "row_kernel<10,5,SVK>", "achieved": achieved, "peak": hbm_peak,
+    roofline = {"bound": "hbm", "kernel": "tile_kernel<10,5,8>" if s.TileStats()["n_tiles"] else "row_kernel<10,5,SVK>", "achieved": achieved, "peak": hbm_peak,
                 "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                 "algorithmic_bytes_per_launch": algo_b, "kernel_ms": row_ms, "gp_kernel_ms": gp_ms,
@@ -384,7 +384,7 @@ def main():
                        "gauss_points": gp_total, "nnz_H_sum_over_ranks": nnz_g, "material": "SVK E=7e8 nu=0.33",
                        "h": H_STEP, "partition": f"x-slabs x{world}, sub-assembled H, NCCL halo sum of f_int",
                        "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
-                       "setup_s": t_setup},
+                       "setup_s": t_setup, "tiles": s.TileStats()},
             "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all,
             "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
         }

@@ -160,7 +160,7 @@ struct tlfea_elem {
 };
 
 namespace tlfea {
-int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, Tiles *out);
+int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int round_size, Tiles *out);
 }
 
 struct tlfea_newton {

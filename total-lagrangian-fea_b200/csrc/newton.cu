@@ -263,7 +263,7 @@ static bool tiles_supported(const tlfea_newton *s) {
 
 static int ensure_tiles(tlfea_newton *s) {
   if (s->have_tiles) return TLFEA_OK;
-  TL_TRY(build_tiles(s->e, TILE_BUDGET, TK_MAX_ROWS, &s->tiles));
+  TL_TRY(build_tiles(s->e, TILE_BUDGET, TK_MAX_ROWS, TILE_WARPS, &s->tiles));
   s->have_tiles = true;
   return TLFEA_OK;
 }

@@ -89,15 +89,11 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
     }
   }
   __syncthreads();
-  // ---- rows start from the mass term M_ij/h on the block diagonals (SyncedNewton.cu:213-259)
-  for (int r = warp; r < nrows; r += W) {
-    const int rs = p.off[grow[r]];
-    const int n9 = roff[r + 1] - roff[r];
-    double *dst = rowbuf + roff[r];
-    for (int idx = lane; idx < n9; idx += 32) {
-      const int s = idx / 9, c = idx - 9 * s;
-      dst[idx] = (c == 0 || c == 4 || c == 8) ? p.mass[rs + s] * p.inv_h : 0.0;
-    }
+  // ---- zero the row buffer (the mass term M_ij/h is added while streaming the rows out)
+  {
+    const int total = roff[nrows];
+    double2 *z2 = reinterpret_cast<double2 *>(rowbuf);
+    for (int i = tid; i < (total + 1) / 2; i += W * 32) z2[i] = make_double2(0.0, 0.0);
   }
   __syncthreads();
 
@@ -218,17 +214,22 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
     }
   }
   __syncthreads();
-  // ---- stream the finished block rows out as three scalar CSR rows of length 3*deg each
+  // ---- stream the finished block rows out as three scalar CSR rows of length 3*deg each,
+  //      adding the mass term H(3i+d,3j+d) += M_ij/h (SyncedNewton.cu:213-259)
   for (int r = warp; r < nrows; r += W) {
     const int row = grow[r];
-    const int64_t base = 9 * (int64_t)p.off[row];
-    const int n9 = roff[r + 1] - roff[r];
-    const int rowlen = n9 / 3;
+    const int rs = p.off[row];
+    const int64_t base = 9 * (int64_t)rs;
+    const int rowlen = (roff[r + 1] - roff[r]) / 3;
     const double *src = rowbuf + roff[r];
-    for (int idx = lane; idx < n9; idx += 32) {
-      const int d = idx / rowlen, c = idx - d * rowlen;
-      const int s = c / 3, e2 = c - 3 * s;
-      p.H[base + idx] = src[s * 9 + d * 3 + e2];
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+      for (int c = lane; c < rowlen; c += 32) {
+        const int s = c / 3, e2 = c - 3 * s;
+        double v = src[s * 9 + d * 3 + e2];
+        if (e2 == d) v += p.mass[rs + s] * p.inv_h;
+        p.H[base + d * rowlen + c] = v;
+      }
     }
     if (lane < 3) p.f_int[(int64_t)row * 3 + lane] = frow[3 * r + lane];
   }

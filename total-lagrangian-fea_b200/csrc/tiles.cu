@@ -161,6 +161,68 @@ __global__ void k_slot_by_elem(int64_t n_visits, int S, const int *__restrict__ 
   slot_e[(int64_t)inc_ea[v] * S + b] = slot[tid];
 }
 
+// Commit schedule of one tile (one warp per tile): reorder the tile's entries into ROUNDS of at most
+// `round_size` entries that share no tile row, so that the entries of a round commit concurrently
+// and a row's turn counter only orders entries of different rounds.  rank = number of earlier
+// entries (in the new order) that touch the row.  Any fixed order is deterministic.
+constexpr int SCHED_MAX_ENTRIES = 2048;
+__global__ void __launch_bounds__(128) k_schedule(int n_tiles, int S, int round_size, const int *__restrict__ te_ptr,
+                                                  const int *__restrict__ elem_in, const uint8_t *__restrict__ lrow_in,
+                                                  const uint8_t *__restrict__ rank_in, int *elem_out,
+                                                  uint8_t *lrow_out, uint8_t *rank_out) {
+  __shared__ uint8_t s_done[4][SCHED_MAX_ENTRIES];
+  __shared__ uint8_t s_cnt[4][256];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t = blockIdx.x * 4 + w;
+  if (t >= n_tiles) return;
+  const int base = te_ptr[t], ne = te_ptr[t + 1] - base;
+  if (ne > SCHED_MAX_ENTRIES) {  // keep the ascending-element order
+    for (int i = lane; i < ne; i += 32) elem_out[base + i] = elem_in[base + i];
+    for (int64_t i = lane; i < (int64_t)ne * S; i += 32) {
+      lrow_out[(int64_t)base * S + i] = lrow_in[(int64_t)base * S + i];
+      rank_out[(int64_t)base * S + i] = rank_in[(int64_t)base * S + i];
+    }
+    return;
+  }
+  for (int i = lane; i < ne; i += 32) s_done[w][i] = 0;
+  for (int i = lane; i < 256; i += 32) s_cnt[w][i] = 0;
+  __syncwarp();
+  int pos = 0, first = 0;
+  while (pos < ne) {
+    unsigned used[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int picked = 0;
+    for (int j = first; j < ne && picked < round_size; j++) {
+      if (s_done[w][j]) continue;
+      const int lr = (lane < S) ? lrow_in[(int64_t)(base + j) * S + lane] : 255;
+      const int wd = lr >> 5;
+      const unsigned bit = (lr != 255) ? (1u << (lr & 31)) : 0u;
+      unsigned uw = 0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) uw = (wd == k) ? used[k] : uw;
+      if (__ballot_sync(0xffffffffu, (uw & bit) != 0) != 0) continue;
+#pragma unroll
+      for (int k = 0; k < 8; k++) used[k] |= __reduce_or_sync(0xffffffffu, (wd == k) ? bit : 0u);
+      if (lane == 0) {
+        elem_out[base + pos] = elem_in[base + j];
+        s_done[w][j] = 1;
+      }
+      if (lane < S) {
+        lrow_out[(int64_t)(base + pos) * S + lane] = (uint8_t)lr;
+        uint8_t rk = 0;
+        if (lr != 255) {
+          rk = s_cnt[w][lr];
+          s_cnt[w][lr] = rk + 1;
+        }
+        rank_out[(int64_t)(base + pos) * S + lane] = rk;
+      }
+      __syncwarp();
+      pos++;
+      picked++;
+    }
+    while (first < ne && s_done[w][first]) first++;
+  }
+}
+
 template <typename K>
 static int sort_keys_t(K *d_in, K *d_out, int64_t n, int end_bit, cudaStream_t st) {
   size_t tmp_bytes = 0;
@@ -188,7 +250,7 @@ void Tiles::release() {
 }
 
 // budget_doubles: capacity of the shared-memory row buffer; max_rows <= 254
-int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, Tiles *out) {
+int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int round_size, Tiles *out) {
   const Pattern &pat = h->pat;
   const int n = pat.n_coef, S = pat.S;
   cudaStream_t st = h->stream;
@@ -298,6 +360,23 @@ int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, Tiles *ou
   TL_TRY(dmalloc(&t.d_te_rank, (size_t)t.n_entries * S));
   TL_LAUNCH(k_entry_rows, blocks_for(t.n_entries * S, 256), 256, 0, st, t.n_entries, S, te_tile, t.d_te_elem,
             h->d_ecoef, tile_of_row, lrow_of_row, vidx, pat.d_inc_ptr, t.d_te_lrow, t.d_te_rank);
+  // ---- 4b. conflict-free commit rounds
+  if (round_size > 0) {
+    int *elem2 = nullptr;
+    uint8_t *lrow2 = nullptr, *rank2 = nullptr;
+    TL_TRY(dmalloc(&elem2, (size_t)t.n_entries));
+    TL_TRY(dmalloc(&lrow2, (size_t)t.n_entries * S));
+    TL_TRY(dmalloc(&rank2, (size_t)t.n_entries * S));
+    TL_LAUNCH(k_schedule, blocks_for(t.n_tiles, 4), 128, 0, st, t.n_tiles, S, round_size, t.d_te_ptr, t.d_te_elem,
+              t.d_te_lrow, t.d_te_rank, elem2, lrow2, rank2);
+    TL_CUDA(cudaStreamSynchronize(st));
+    cudaFree(t.d_te_elem);
+    cudaFree(t.d_te_lrow);
+    cudaFree(t.d_te_rank);
+    t.d_te_elem = elem2;
+    t.d_te_lrow = lrow2;
+    t.d_te_rank = rank2;
+  }
   // ---- 5. slot map indexed by (element, a, b)
   TL_TRY(dmalloc(&t.d_slot_e, (size_t)nv * S));
   TL_LAUNCH(k_slot_by_elem, blocks_for(nv * S, 256), 256, 0, st, nv, S, pat.d_inc_ea, pat.d_slot, t.d_slot_e);
