@@ -254,7 +254,7 @@ static int norm2(tlfea_newton *s, const double *a, int64_t n, double *out) {
 }
 
 constexpr int TILE_WARPS = 8;
-constexpr int TILE_BUDGET = 22000;  // doubles of shared-memory row buffer per tile
+constexpr int TILE_BUDGET = 21500;  // doubles of shared-memory row buffer per tile
 
 static bool tiles_supported(const tlfea_newton *s) {
   return s->use_tiles && s->e->type == TLFEA_TYPE_T10 && s->e->model == TL_MODEL_SVK &&
