@@ -106,8 +106,11 @@ struct Tiles {
   int *d_tile_ptr = nullptr;      // [n_tiles+1]    into d_trow
   int *d_te_ptr = nullptr;        // [n_tiles+1]    into the entry arrays
   int *d_te_elem = nullptr;       // [n_entries]    element id, ascending inside a tile
-  uint8_t *d_te_lrow = nullptr;   // [n_entries*S]  local row of shape function a, 255 = row not in this tile
-  uint8_t *d_te_rank = nullptr;   // [n_entries*S]  commit rank of the contribution inside its row
+  int batch = 0, warps = 0;       // elements staged per batch, warps per CTA (rows are owned by lrow % warps)
+  int n_batches = 0;
+  int *d_tb_ptr = nullptr;        // [n_tiles+1]    first global batch of a tile
+  int *d_vptr = nullptr;          // [n_batches*warps+1] visit list of (batch, warp)
+  unsigned *d_visit = nullptr;    // [n_visits]     elem-in-batch | a<<8 | local row<<16
   uint16_t *d_slot_e = nullptr;   // [n_elem*S*S]   column slot of (a,b) in row ecoef[e][a]
   int *d_err = nullptr;           // [4] device error flags
   void release();
@@ -160,7 +163,7 @@ struct tlfea_elem {
 };
 
 namespace tlfea {
-int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int round_size, Tiles *out);
+int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int batch, int warps, Tiles *out);
 }
 
 struct tlfea_newton {

@@ -254,7 +254,8 @@ static int norm2(tlfea_newton *s, const double *a, int64_t n, double *out) {
 }
 
 constexpr int TILE_WARPS = 8;
-constexpr int TILE_BUDGET = 21500;  // doubles of shared-memory row buffer per tile
+constexpr int TILE_BATCH = 12;
+constexpr int TILE_BUDGET = 20400;  // doubles of shared-memory row buffer per tile
 
 static bool tiles_supported(const tlfea_newton *s) {
   return s->use_tiles && s->e->type == TLFEA_TYPE_T10 && s->e->model == TL_MODEL_SVK &&
@@ -263,7 +264,7 @@ static bool tiles_supported(const tlfea_newton *s) {
 
 static int ensure_tiles(tlfea_newton *s) {
   if (s->have_tiles) return TLFEA_OK;
-  TL_TRY(build_tiles(s->e, TILE_BUDGET, TK_MAX_ROWS, TILE_WARPS, &s->tiles));
+  TL_TRY(build_tiles(s->e, TILE_BUDGET, TK_MAX_ROWS, TILE_BATCH, TILE_WARPS, &s->tiles));
   s->have_tiles = true;
   return TLFEA_OK;
 }
@@ -277,8 +278,9 @@ static int launch_tile(tlfea_newton *s, const RowArgs &r) {
   a.tile_ptr = t.d_tile_ptr;
   a.te_ptr = t.d_te_ptr;
   a.te_elem = t.d_te_elem;
-  a.te_lrow = t.d_te_lrow;
-  a.te_rank = t.d_te_rank;
+  a.tb_ptr = t.d_tb_ptr;
+  a.vptr = t.d_vptr;
+  a.visit = t.d_visit;
   a.slot_e = t.d_slot_e;
   a.off = r.off;
   a.mass = r.mass;
@@ -295,11 +297,10 @@ static int launch_tile(tlfea_newton *s, const RowArgs &r) {
   a.mu = r.mu;
   a.H = r.H;
   a.f_int = r.f_int;
-  a.err = t.d_err;
   a.buf_doubles = TILE_BUDGET;
-  const size_t smem = TileShape<10, 5, TILE_WARPS>::smem_bytes(TILE_BUDGET);
-  TL_CUDA(cudaFuncSetAttribute(tile_kernel<10, 5, TILE_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  TL_LAUNCH((tile_kernel<10, 5, TILE_WARPS>), t.n_tiles, TILE_WARPS * 32, smem, e->stream, a);
+  const size_t smem = TileShape<10, 5, TILE_WARPS, TILE_BATCH>::smem_bytes(TILE_BUDGET);
+  TL_CUDA(cudaFuncSetAttribute(tile_kernel<10, 5, TILE_WARPS, TILE_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  TL_LAUNCH((tile_kernel<10, 5, TILE_WARPS, TILE_BATCH>), t.n_tiles, TILE_WARPS * 32, smem, e->stream, a);
   TL_CUDA(cudaGetLastError());
   return TLFEA_OK;
 }

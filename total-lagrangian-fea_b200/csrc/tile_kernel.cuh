@@ -4,18 +4,18 @@
 // (SyncedNewton.cu:213-259) + the force scatter (FEAT10DataFunc.cuh:397-458).
 //
 // One CTA owns a TILE of H block rows (a Morton-compact set of coefficients, tiles.cu) and keeps
-// them in shared memory.  Its warps walk the tile's incident elements; for one element a warp
-//   0. prefetches the NEXT element's gradN / Gauss-point records with cp.async while it works,
-//   1. stages, per Gauss point and local node c:  u_c = F h_c  and  h_c,  and the symmetric
-//      3x3  M_q = c3 dV F F^T + c4 dV (lambda trE - mu) I   (F, dV FF^T from the Gauss-point record),
-//   2. computes the 3x3 blocks K_ab for the rows a that live in this tile: lane = (row slot, b),
-//      15 accumulators  A = sum_q (dV u_a) u_b^T,  Sg = sum_q (h_a.h_b) M_q,
-//      K_ab = c1 A + c2 A^T + Sg + c4 mu tr(A) I     (SVK.cuh:35-55 and the viscous block
-//      FEAT10DataFunc.cuh:695-762 folded into c1..c3),
-//   3. commits the blocks to the row buffer IN RANK ORDER: every contribution to a row carries
-//      its position in the row's commit schedule (tiles.cu: conflict-free rounds); a warp waits
-//      until the row's turn counter reaches its rank.  Fixed order => bit-reproducible, no FP64
-//      atomics.
+// them in shared memory; every row of the tile belongs to exactly ONE warp (local row % W), so no
+// two warps ever add to the same row and no ordering protocol is needed.  The tile's incident
+// elements are processed in BATCHES:
+//   0. cp.async brings the next batch's gradN / Gauss-point records into shared memory,
+//   1. all threads stage the batch: per Gauss point and local node c  u_c = F h_c and h_c, and the
+//      symmetric 3x3  M_q = c3 dV F F^T + c4 dV (lambda trE - mu) I,
+//   2. each warp walks ITS visits of the batch -- (element, a) pairs whose row it owns, a fixed
+//      precomputed list -- three at a time, lane = (visit slot, b): 15 accumulators
+//      A = sum_q (dV u_a) u_b^T,  Sg = sum_q (h_a.h_b) M_q,
+//      K_ab = c1 A + c2 A^T + Sg + c4 mu tr(A) I   (SVK.cuh:35-55; the Kelvin-Voigt block
+//      FEAT10DataFunc.cuh:695-762 is folded into c1..c3), added to the row buffer in list order.
+// Fixed order => bit-reproducible; no FP64 atomics (the reference: FEAT10DataFunc.cuh:662-687).
 // Finished rows (+ mass/h on the block diagonals) stream to H once.  DRAM traffic ~ gradN + records + H.
 #pragma once
 #include <cub/block/block_scan.cuh>
@@ -26,8 +26,8 @@ namespace tlfea {
 
 struct TileArgs {
   int n_tiles;
-  const int *trow, *tile_ptr, *te_ptr, *te_elem;
-  const uint8_t *te_lrow, *te_rank;
+  const int *trow, *tile_ptr, *te_ptr, *te_elem, *tb_ptr, *vptr;
+  const unsigned *visit;
   const uint16_t *slot_e;
   const int *off;
   const double *mass;
@@ -36,21 +36,19 @@ struct TileArgs {
   QuadW qw;
   double inv_h, c1, c2, c3, c4, mu;
   double *H, *f_int;
-  int *err;
   int buf_doubles;
 };
 
 constexpr int TK_MAX_ROWS = 254;
-constexpr int TK_SPIN_LIMIT = 1 << 20;
 
-template <int S, int Q, int W>
+template <int S, int Q, int W, int B>
 struct TileShape {
   static constexpr int NODE = Q * S * 6;                           // {u0,u1,u2,h0,h1,h2} per (q, node)
   static constexpr int STG = NODE + Q * 6 + ((Q + 1) & ~1);        // + M_q + dV_q
   static constexpr int RAW = ((Q * 3 * S + Q * 16 + Q) + 1) & ~1;  // gradN | records | detJ
   static size_t smem_bytes(int buf_doubles) {
-    return ((size_t)buf_doubles + 256 * 3 + (size_t)W * (STG + RAW)) * sizeof(double) +
-           (257 + 256 + 256 + 256) * sizeof(int);
+    return ((size_t)buf_doubles + 256 * 3 + (size_t)B * (STG + RAW)) * sizeof(double) +
+           (257 + 256 + 256 + B) * sizeof(int);
   }
 };
 
@@ -65,53 +63,51 @@ __device__ __forceinline__ void cp_async8(void *smem, const void *gmem) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
-template <int S, int Q, int W>
+
+template <int S, int Q, int W, int B>
 __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
   static_assert(W * 32 >= 256, "block scan covers up to 256 rows");
   static_assert((Q * 3 * S) % 2 == 0, "gradN block of one element must be 16-byte granular");
-  using Sh = TileShape<S, Q, W>;
-  constexpr int AS = 32 / S;  // rows of one element handled per pass
+  using Sh = TileShape<S, Q, W, B>;
+  constexpr int AS = 32 / S;  // visits handled per pass
+  constexpr int T = W * 32;
   constexpr int NODE = Sh::NODE, STG = Sh::STG, RAW = Sh::RAW;
   constexpr int NG = Q * 3 * S;  // gradN doubles per element
   extern __shared__ __align__(16) double sm[];
   double *rowbuf = sm;
   double *frow = rowbuf + p.buf_doubles;
-  double *stage_all = frow + 256 * 3;
-  double *raw_all = stage_all + W * STG;
-  int *roff = reinterpret_cast<int *>(raw_all + W * RAW);
+  double *stage = frow + 256 * 3;   // [B][STG]
+  double *raw = stage + B * STG;    // [B][RAW]
+  int *roff = reinterpret_cast<int *>(raw + B * RAW);
   int *grow = roff + 257;
   int *rstart = grow + 256;
-  volatile int *turn = rstart + 256;
+  int *belem = rstart + 256;        // [B] element ids of the current batch
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int tile = blockIdx.x;
   const int r0 = p.tile_ptr[tile], nrows = p.tile_ptr[tile + 1] - r0;
   const int e0 = p.te_ptr[tile], ne = p.te_ptr[tile + 1] - e0;
+  const int gb0 = p.tb_ptr[tile], nb = p.tb_ptr[tile + 1] - gb0;
 
-  double *stg = stage_all + warp * STG;
-  double *node = stg, *Mq = stg + NODE, *dVq = Mq + Q * 6;
-  double *raw = raw_all + warp * RAW;
-
-  // raw element data -> shared memory, asynchronously (gradN and records in 16-B chunks, detJ 8-B)
-  auto prefetch = [&](int e) {
-    const double *g = p.gradN + (int64_t)e * NG;
-    const double *r = p.rec + (int64_t)e * Q * 16;
-    const double *dj = p.detJ + (int64_t)e * Q;
-    for (int i = lane; i < NG / 2; i += 32) cp_async16(raw + 2 * i, g + 2 * i);
-    for (int i = lane; i < Q * 8; i += 32) cp_async16(raw + NG + 2 * i, r + 2 * i);
-    if (lane < Q) cp_async8(raw + NG + Q * 16 + lane, dj + lane);
+  // raw data of batch bi -> shared memory, asynchronously (gradN, records: 16-B chunks; detJ: 8-B)
+  auto prefetch = [&](int bi) {
+    const int n_el = min(B, ne - bi * B);
+    constexpr int C16 = NG / 2 + Q * 8;  // 16-byte chunks per element
+    for (int i = tid; i < n_el * C16; i += T) {
+      const int el = i / C16, c = i - el * C16;
+      const int e = p.te_elem[e0 + bi * B + el];
+      const double *src = (c < NG / 2) ? p.gradN + (int64_t)e * NG + 2 * c
+                                       : p.rec + (int64_t)e * Q * 16 + 2 * (c - NG / 2);
+      cp_async16(raw + el * RAW + 2 * c, src);
+    }
+    for (int i = tid; i < n_el * Q; i += T) {
+      const int el = i / Q, q = i - el * Q;
+      const int e = p.te_elem[e0 + bi * B + el];
+      cp_async8(raw + el * RAW + NG + Q * 16 + q, p.detJ + (int64_t)e * Q + q);
+    }
     cp_async_commit();
   };
-  // first entry of this warp: start its loads before the prologue
-  int e_next = -1, lrow_next = 255, rank_next = 0;
-  if (warp < ne) {
-    e_next = p.te_elem[e0 + warp];
-    if (lane < S) {
-      lrow_next = p.te_lrow[(int64_t)(e0 + warp) * S + lane];
-      rank_next = p.te_rank[(int64_t)(e0 + warp) * S + lane];
-    }
-    prefetch(e_next);
-  }
+  if (nb > 0) prefetch(0);
 
   // ---- row table: global row, CSR start, buffer offset (exclusive scan of 9*deg)
   {
@@ -121,7 +117,7 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
       rs = p.off[row];
       sz = 9 * (p.off[row + 1] - rs);
     }
-    using Scan = cub::BlockScan<int, W * 32>;
+    using Scan = cub::BlockScan<int, T>;
     __shared__ typename Scan::TempStorage tmp;
     int excl;
     Scan(tmp).ExclusiveSum(sz, excl);
@@ -130,7 +126,6 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
         grow[tid] = row;
         rstart[tid] = rs;
         roff[tid] = excl;
-        turn[tid] = 0;
         frow[3 * tid] = frow[3 * tid + 1] = frow[3 * tid + 2] = 0.0;
       }
       if (tid == nrows) roff[tid] = excl;
@@ -141,72 +136,61 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
   {
     const int total = roff[nrows];
     double2 *z2 = reinterpret_cast<double2 *>(rowbuf);
-    for (int i = tid; i < (total + 1) / 2; i += W * 32) z2[i] = make_double2(0.0, 0.0);
+    for (int i = tid; i < (total + 1) / 2; i += T) z2[i] = make_double2(0.0, 0.0);
   }
-  __syncthreads();
 
   const int k = lane / S, b = lane - k * S;
   const bool lane_on = lane < AS * S;
 
-  for (int j = warp; j < ne; j += W) {
-    const int e = e_next;
-    const int my_lrow = lrow_next, my_rank = rank_next;
-    const unsigned mask = __ballot_sync(0xffffffffu, my_lrow != 255);
-    const int n_a = __popc(mask);
-    // ---- stage the element from the prefetched raw data
+  for (int bi = 0; bi < nb; bi++) {
+    const int n_el = min(B, ne - bi * B);
     cp_async_wait_all();
-    __syncwarp();
-    for (int it = lane; it < Q * S; it += 32) {
-      const int q = it / S, c = it - q * S;
-      const double *g = raw + q * 3 * S;
+    __syncthreads();  // raw(bi) complete for all threads; every warp is done with the previous stage
+    // ---- stage the batch
+    for (int it = tid; it < n_el * Q * S; it += T) {
+      const int el = it / (Q * S), qc = it - el * (Q * S);
+      const int q = qc / S, c = qc - q * S;
+      const double *rw = raw + el * RAW;
+      const double *g = rw + q * 3 * S;
       const double h0 = g[c], h1 = g[S + c], h2 = g[2 * S + c];
-      const double2 *r2 = reinterpret_cast<const double2 *>(raw + NG + q * 16);
+      const double2 *r2 = reinterpret_cast<const double2 *>(rw + NG + q * 16);
       const double2 f01 = r2[0], f23 = r2[1], f45 = r2[2], f67 = r2[3];
-      const double f8 = raw[NG + q * 16 + 8];
-      double2 *N2 = reinterpret_cast<double2 *>(node + (q * S + c) * 6);
+      const double f8 = rw[NG + q * 16 + 8];
+      double2 *N2 = reinterpret_cast<double2 *>(stage + el * STG + qc * 6);
       N2[0] = make_double2(f01.x * h0 + f01.y * h1 + f23.x * h2, f23.y * h0 + f45.x * h1 + f45.y * h2);
       N2[1] = make_double2(f67.x * h0 + f67.y * h1 + f8 * h2, h0);
       N2[2] = make_double2(h1, h2);
     }
-    if (lane < Q) {
-      const double *r = raw + NG + lane * 16;
+    for (int it = tid; it < n_el * Q; it += T) {
+      const int el = it / Q, q = it - el * Q;
+      const double *r = raw + el * RAW + NG + q * 16;
       const double dg = p.c4 * r[15];
-      double2 *M2 = reinterpret_cast<double2 *>(Mq + lane * 6);
+      double *st = stage + el * STG + NODE;
+      double2 *M2 = reinterpret_cast<double2 *>(st + q * 6);
       M2[0] = make_double2(p.c3 * r[9] + dg, p.c3 * r[10]);
       M2[1] = make_double2(p.c3 * r[11], p.c3 * r[12] + dg);
       M2[2] = make_double2(p.c3 * r[13], p.c3 * r[14] + dg);
-      dVq[lane] = raw[NG + Q * 16 + lane] * p.qw.w[lane];
+      st[Q * 6 + q] = raw[el * RAW + NG + Q * 16 + q] * p.qw.w[q];
     }
-    __syncwarp();
-    // ---- next entry: metadata to registers, raw data to shared memory (in flight during the passes)
-    if (j + W < ne) {
-      e_next = p.te_elem[e0 + j + W];
-      if (lane < S) {
-        lrow_next = p.te_lrow[(int64_t)(e0 + j + W) * S + lane];
-        rank_next = p.te_rank[(int64_t)(e0 + j + W) * S + lane];
-      }
-      prefetch(e_next);
-    }
+    if (tid < n_el) belem[tid] = p.te_elem[e0 + bi * B + tid];
+    __syncthreads();  // stage visible; raw free
+    if (bi + 1 < nb) prefetch(bi + 1);
 
-    // ---- phase 1: all blocks of this element that belong to the tile, kept in registers
-    constexpr int MAXP = (S + AS - 1) / AS;
-    double val[MAXP][9];
-    double fadd[MAXP];
-    int slot[MAXP], lrp[MAXP], rkp[MAXP];
-#pragma unroll
-    for (int pass = 0; pass < MAXP; pass++) {
-      if (pass * AS >= n_a) break;  // warp-uniform
-      const int idx = pass * AS + k;
-      const bool valid = lane_on && idx < n_a;
-      const int a = valid ? (int)__fns(mask, 0, idx + 1) : 0;
-      const int lr_s = __shfl_sync(0xffffffffu, my_lrow, a);
-      rkp[pass] = __shfl_sync(0xffffffffu, my_rank, a);
-      lrp[pass] = valid ? lr_s : -1;
-      slot[pass] = 0;
-      fadd[pass] = 0.0;
+    // ---- this warp's visits of the batch, AS at a time
+    const int v0 = p.vptr[(int64_t)(gb0 + bi) * W + warp], v1 = p.vptr[(int64_t)(gb0 + bi) * W + warp + 1];
+    for (int vb = v0; vb < v1; vb += AS) {
+      const bool valid = lane_on && (vb + k < v1);
+      unsigned d = valid ? p.visit[vb + k] : 0u;
+      const int el = d & 0xff, a = (d >> 8) & 0xff, lr = valid ? (int)(d >> 16) : -1;
+      double val[9];
+      int slot = 0;
+      double fadd = 0.0;
       if (valid) {
-        slot[pass] = p.slot_e[((int64_t)e * S + a) * S + b];
-        if (b < 3) fadd[pass] = p.fe[((int64_t)e * S + a) * 3 + b];
+        const int e = belem[el];
+        slot = p.slot_e[((int64_t)e * S + a) * S + b];
+        if (b < 3) fadd = p.fe[((int64_t)e * S + a) * 3 + b];
+        const double *node = stage + el * STG;
+        const double *Mq = node + NODE, *dVq = Mq + Q * 6;
         double A[9], Sg[6];
 #pragma unroll
         for (int i = 0; i < 9; i++) A[i] = 0.0;
@@ -230,46 +214,48 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
           Sg[3] += hab * m23.y; Sg[4] += hab * m45.x; Sg[5] += hab * m45.y;
         }
         const double dg = p.c4 * p.mu * (A[0] + A[4] + A[8]);
-        val[pass][0] = p.c1 * A[0] + p.c2 * A[0] + Sg[0] + dg;
-        val[pass][1] = p.c1 * A[1] + p.c2 * A[3] + Sg[1];
-        val[pass][2] = p.c1 * A[2] + p.c2 * A[6] + Sg[2];
-        val[pass][3] = p.c1 * A[3] + p.c2 * A[1] + Sg[1];
-        val[pass][4] = p.c1 * A[4] + p.c2 * A[4] + Sg[3] + dg;
-        val[pass][5] = p.c1 * A[5] + p.c2 * A[7] + Sg[4];
-        val[pass][6] = p.c1 * A[6] + p.c2 * A[2] + Sg[2];
-        val[pass][7] = p.c1 * A[7] + p.c2 * A[5] + Sg[4];
-        val[pass][8] = p.c1 * A[8] + p.c2 * A[8] + Sg[5] + dg;
+        val[0] = p.c1 * A[0] + p.c2 * A[0] + Sg[0] + dg;
+        val[1] = p.c1 * A[1] + p.c2 * A[3] + Sg[1];
+        val[2] = p.c1 * A[2] + p.c2 * A[6] + Sg[2];
+        val[3] = p.c1 * A[3] + p.c2 * A[1] + Sg[1];
+        val[4] = p.c1 * A[4] + p.c2 * A[4] + Sg[3] + dg;
+        val[5] = p.c1 * A[5] + p.c2 * A[7] + Sg[4];
+        val[6] = p.c1 * A[6] + p.c2 * A[2] + Sg[2];
+        val[7] = p.c1 * A[7] + p.c2 * A[5] + Sg[4];
+        val[8] = p.c1 * A[8] + p.c2 * A[8] + Sg[5] + dg;
       }
-    }
-    // ---- phase 2: ordered commits (wait for each row's turn; rows of one element are distinct)
+      // ---- add to the warp's own rows in list order.  Visit slots of one pass may hit the same
+      //      row (two elements of the batch): then slot k waits for the slots before it.
+      bool clash = false;
 #pragma unroll
-    for (int pass = 0; pass < MAXP; pass++) {
-      if (pass * AS >= n_a) break;
-      const int lr = lrp[pass], rk = rkp[pass];
-      const bool valid = lr >= 0;
-      if (valid && b == 0) {
-        int spins = 0;
-        while (turn[lr] != rk) {
-          __nanosleep(20);
-          if (((++spins) & 255) == 0 && (spins > TK_SPIN_LIMIT || *((volatile int *)p.err) != 0)) {
-            atomicExch(p.err, 1);
-            break;
-          }
+      for (int kk = 1; kk < AS; kk++) {
+        const int lr_cur = __shfl_sync(0xffffffffu, lr, kk * S);
+#pragma unroll
+        for (int jj = 0; jj < kk; jj++) {
+          const int lr_prev = __shfl_sync(0xffffffffu, lr, jj * S);
+          clash |= (lr_cur >= 0) && (lr_cur == lr_prev);
         }
-        __threadfence_block();
       }
-      __syncwarp();
-      if (valid) {
-        double *dst = rowbuf + roff[lr] + slot[pass] * 9;
+      if (!clash) {
+        if (valid) {
+          double *dst = rowbuf + roff[lr] + slot * 9;
 #pragma unroll
-        for (int i = 0; i < 9; i++) dst[i] += val[pass][i];
-        if (b < 3) frow[3 * lr + b] += fadd[pass];
+          for (int i = 0; i < 9; i++) dst[i] += val[i];
+          if (b < 3) frow[3 * lr + b] += fadd;
+        }
+      } else {
+#pragma unroll
+        for (int kk = 0; kk < AS; kk++) {
+          if (valid && k == kk) {
+            double *dst = rowbuf + roff[lr] + slot * 9;
+#pragma unroll
+            for (int i = 0; i < 9; i++) dst[i] += val[i];
+            if (b < 3) frow[3 * lr + b] += fadd;
+          }
+          __syncwarp();
+        }
       }
       __syncwarp();
-      if (valid && b == 0) {
-        __threadfence_block();
-        turn[lr] = rk + 1;
-      }
     }
   }
   __syncthreads();

@@ -161,66 +161,47 @@ __global__ void k_slot_by_elem(int64_t n_visits, int S, const int *__restrict__ 
   slot_e[(int64_t)inc_ea[v] * S + b] = slot[tid];
 }
 
-// Commit schedule of one tile (one warp per tile): reorder the tile's entries into ROUNDS of at most
-// `round_size` entries that share no tile row, so that the entries of a round commit concurrently
-// and a row's turn counter only orders entries of different rounds.  rank = number of earlier
-// entries (in the new order) that touch the row.  Any fixed order is deterministic.
-constexpr int SCHED_MAX_ENTRIES = 2048;
-__global__ void __launch_bounds__(128) k_schedule(int n_tiles, int S, int round_size, const int *__restrict__ te_ptr,
-                                                  const int *__restrict__ elem_in, const uint8_t *__restrict__ lrow_in,
-                                                  const uint8_t *__restrict__ rank_in, int *elem_out,
-                                                  uint8_t *lrow_out, uint8_t *rank_out) {
-  __shared__ uint8_t s_done[4][SCHED_MAX_ENTRIES];
-  __shared__ uint8_t s_cnt[4][256];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int t = blockIdx.x * 4 + w;
-  if (t >= n_tiles) return;
-  const int base = te_ptr[t], ne = te_ptr[t + 1] - base;
-  if (ne > SCHED_MAX_ENTRIES) {  // keep the ascending-element order
-    for (int i = lane; i < ne; i += 32) elem_out[base + i] = elem_in[base + i];
-    for (int64_t i = lane; i < (int64_t)ne * S; i += 32) {
-      lrow_out[(int64_t)base * S + i] = lrow_in[(int64_t)base * S + i];
-      rank_out[(int64_t)base * S + i] = rank_in[(int64_t)base * S + i];
-    }
-    return;
+// One descriptor per visit (row r of the tile, element e, local shape function a), grouped by
+// (batch of the tile's element list, owner warp of the row):  elem-in-batch | a<<8 | local row<<16.
+__global__ void k_visit_desc(int64_t n_visits, int S, int B, int W, const int *__restrict__ inc_ea,
+                             const int *__restrict__ ecoef, const int *__restrict__ tile_of_row,
+                             const uint8_t *__restrict__ lrow_of_row, const int *__restrict__ te_ptr,
+                             const int *__restrict__ te_elem, const int *__restrict__ tb_ptr,
+                             unsigned long long *keys, unsigned *desc) {
+  int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_visits) return;
+  const int ea = inc_ea[v];
+  const int e = ea / S, a = ea - e * S;
+  const int r = ecoef[ea];
+  const int t = tile_of_row[r], lr = lrow_of_row[r];
+  int lo = te_ptr[t], hi = te_ptr[t + 1];
+  const int base = lo;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (te_elem[mid] < e)
+      lo = mid + 1;
+    else
+      hi = mid;
   }
-  for (int i = lane; i < ne; i += 32) s_done[w][i] = 0;
-  for (int i = lane; i < 256; i += 32) s_cnt[w][i] = 0;
-  __syncwarp();
-  int pos = 0, first = 0;
-  while (pos < ne) {
-    unsigned used[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    int picked = 0;
-    for (int j = first; j < ne && picked < round_size; j++) {
-      if (s_done[w][j]) continue;
-      const int lr = (lane < S) ? lrow_in[(int64_t)(base + j) * S + lane] : 255;
-      const int wd = lr >> 5;
-      const unsigned bit = (lr != 255) ? (1u << (lr & 31)) : 0u;
-      unsigned uw = 0;
-#pragma unroll
-      for (int k = 0; k < 8; k++) uw = (wd == k) ? used[k] : uw;
-      if (__ballot_sync(0xffffffffu, (uw & bit) != 0) != 0) continue;
-#pragma unroll
-      for (int k = 0; k < 8; k++) used[k] |= __reduce_or_sync(0xffffffffu, (wd == k) ? bit : 0u);
-      if (lane == 0) {
-        elem_out[base + pos] = elem_in[base + j];
-        s_done[w][j] = 1;
-      }
-      if (lane < S) {
-        lrow_out[(int64_t)(base + pos) * S + lane] = (uint8_t)lr;
-        uint8_t rk = 0;
-        if (lr != 255) {
-          rk = s_cnt[w][lr];
-          s_cnt[w][lr] = rk + 1;
-        }
-        rank_out[(int64_t)(base + pos) * S + lane] = rk;
-      }
-      __syncwarp();
-      pos++;
-      picked++;
-    }
-    while (first < ne && s_done[w][first]) first++;
+  const int j = lo - base;
+  const unsigned long long gbw = (unsigned long long)(tb_ptr[t] + j / B) * W + (lr % W);
+  const int ebi = j % B;
+  keys[v] = (gbw << 16) | (unsigned)(ebi << 8) | (unsigned)a;
+  desc[v] = (unsigned)ebi | ((unsigned)a << 8) | ((unsigned)lr << 16);
+}
+
+__global__ void k_gbw_lower_bound(const unsigned long long *__restrict__ keys, int64_t n, int64_t n_groups, int *ptr) {
+  int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g > n_groups) return;
+  int64_t lo = 0, hi = n;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if ((int64_t)(keys[mid] >> 16) < g)
+      lo = mid + 1;
+    else
+      hi = mid;
   }
+  ptr[g] = (int)lo;
 }
 
 template <typename K>
@@ -242,15 +223,16 @@ void Tiles::release() {
   dfree(d_tile_ptr);
   dfree(d_te_ptr);
   dfree(d_te_elem);
-  dfree(d_te_lrow);
-  dfree(d_te_rank);
+  dfree(d_tb_ptr);
+  dfree(d_vptr);
+  dfree(d_visit);
   dfree(d_slot_e);
   dfree(d_err);
   n_tiles = 0;
 }
 
 // budget_doubles: capacity of the shared-memory row buffer; max_rows <= 254
-int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int round_size, Tiles *out) {
+int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int batch, int warps, Tiles *out) {
   const Pattern &pat = h->pat;
   const int n = pat.n_coef, S = pat.S;
   cudaStream_t st = h->stream;
@@ -355,27 +337,46 @@ int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int round
   TL_LAUNCH(k_split_words, blocks_for(t.n_entries, 256), 256, 0, st, k0, t.n_entries, te_tile, t.d_te_elem);
   TL_LAUNCH(k_tile_lower_bound, blocks_for(t.n_tiles + 1, 256), 256, 0, st, te_tile, (int)t.n_entries, t.n_tiles,
             t.d_te_ptr);
-  // ---- 4. local rows and commit ranks per (entry, a)
-  TL_TRY(dmalloc(&t.d_te_lrow, (size_t)t.n_entries * S));
-  TL_TRY(dmalloc(&t.d_te_rank, (size_t)t.n_entries * S));
-  TL_LAUNCH(k_entry_rows, blocks_for(t.n_entries * S, 256), 256, 0, st, t.n_entries, S, te_tile, t.d_te_elem,
-            h->d_ecoef, tile_of_row, lrow_of_row, vidx, pat.d_inc_ptr, t.d_te_lrow, t.d_te_rank);
-  // ---- 4b. conflict-free commit rounds
-  if (round_size > 0) {
-    int *elem2 = nullptr;
-    uint8_t *lrow2 = nullptr, *rank2 = nullptr;
-    TL_TRY(dmalloc(&elem2, (size_t)t.n_entries));
-    TL_TRY(dmalloc(&lrow2, (size_t)t.n_entries * S));
-    TL_TRY(dmalloc(&rank2, (size_t)t.n_entries * S));
-    TL_LAUNCH(k_schedule, blocks_for(t.n_tiles, 4), 128, 0, st, t.n_tiles, S, round_size, t.d_te_ptr, t.d_te_elem,
-              t.d_te_lrow, t.d_te_rank, elem2, lrow2, rank2);
+  // ---- 4. batches of the tile element lists and the per-(batch, warp) visit lists
+  t.batch = batch;
+  t.warps = warps;
+  {
+    std::vector<int> te_ptr_h(t.n_tiles + 1), tb(t.n_tiles + 1);
+    TL_CUDA(cudaMemcpyAsync(te_ptr_h.data(), t.d_te_ptr, te_ptr_h.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
     TL_CUDA(cudaStreamSynchronize(st));
-    cudaFree(t.d_te_elem);
-    cudaFree(t.d_te_lrow);
-    cudaFree(t.d_te_rank);
-    t.d_te_elem = elem2;
-    t.d_te_lrow = lrow2;
-    t.d_te_rank = rank2;
+    tb[0] = 0;
+    for (int i = 0; i < t.n_tiles; i++) tb[i + 1] = tb[i] + (te_ptr_h[i + 1] - te_ptr_h[i] + batch - 1) / batch;
+    t.n_batches = tb[t.n_tiles];
+    TL_TRY(dmalloc(&t.d_tb_ptr, tb.size()));
+    TL_CUDA(cudaMemcpyAsync(t.d_tb_ptr, tb.data(), tb.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    TL_CUDA(cudaStreamSynchronize(st));
+  }
+  {
+    unsigned long long *vk0 = nullptr, *vk1 = nullptr;
+    unsigned *d0 = nullptr;
+    TL_TRY(dmalloc(&vk0, (size_t)nv));
+    TL_TRY(dmalloc(&vk1, (size_t)nv));
+    TL_TRY(dmalloc(&d0, (size_t)nv));
+    TL_TRY(dmalloc(&t.d_visit, (size_t)nv));
+    TL_LAUNCH(k_visit_desc, blocks_for(nv, 256), 256, 0, st, nv, S, batch, warps, pat.d_inc_ea, h->d_ecoef, tile_of_row,
+              lrow_of_row, t.d_te_ptr, t.d_te_elem, t.d_tb_ptr, vk0, d0);
+    const int64_t n_groups = (int64_t)t.n_batches * warps;
+    int gbits = 1;
+    while ((1LL << gbits) < n_groups + 1) gbits++;
+    size_t tmp_bytes = 0;
+    TL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, vk0, vk1, d0, t.d_visit, nv, 0, 16 + gbits, st));
+    void *tmp = nullptr;
+    TL_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+    cudaError_t er = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, vk0, vk1, d0, t.d_visit, nv, 0, 16 + gbits, st);
+    g_launches.fetch_add(1);
+    TL_TRY(dmalloc(&t.d_vptr, (size_t)n_groups + 1));
+    TL_LAUNCH(k_gbw_lower_bound, blocks_for(n_groups + 1, 256), 256, 0, st, vk1, nv, n_groups, t.d_vptr);
+    cudaStreamSynchronize(st);
+    cudaFree(tmp);
+    cudaFree(vk0);
+    cudaFree(vk1);
+    cudaFree(d0);
+    TL_CUDA(er);
   }
   // ---- 5. slot map indexed by (element, a, b)
   TL_TRY(dmalloc(&t.d_slot_e, (size_t)nv * S));
