@@ -206,6 +206,7 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=32, help="cells per edge of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--assembly", type=int, default=-1, help="0 row gather, 1 tiles, 2 row gather in tile order")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
@@ -235,6 +236,8 @@ def main():
     launches0 = tlfea.lib.tlfea_launch_count()
     t_setup = time.perf_counter()
     slab, x, d, s = build_problem(args.n, rank, world, local)
+    if args.assembly >= 0:
+        s.SetAssembly(args.assembly)
     stream = torch.cuda.current_stream().cuda_stream
     d.SetStream(stream)
     torch.cuda.synchronize()

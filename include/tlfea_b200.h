@@ -197,6 +197,9 @@ int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset
 /* Assembly kernel selection: 1 (default) = spatial row tiles in shared memory where supported
  * (FEAT10 + SVK), 0 = warp-per-row gather.  Both are deterministic; results agree to rounding. */
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode);
+/* phase cycle counters of the tile kernel (only filled by -DTK_TIMING builds): prologue, wait, (unused),
+ * stage, barrier, prefetch issue, visits, write-out */
+int tlfea_newton_tile_timing(tlfea_newton *s, unsigned long long *out8, int reset);
 int tlfea_newton_tile_stats(tlfea_newton *s, int *n_tiles, int64_t *n_entries, int *max_rows, int *max_buf);
 /* per-kernel CUDA-event timing of the next assemble calls (0/1) */
 int tlfea_newton_set_profile(tlfea_newton *s, int on);

@@ -111,7 +111,10 @@ struct Tiles {
   int *d_tb_ptr = nullptr;        // [n_tiles+1]    first global batch of a tile
   int *d_vptr = nullptr;          // [n_batches*warps+1] visit list of (batch, warp)
   unsigned *d_visit = nullptr;    // [n_visits]     elem-in-batch | a<<8 | local row<<16
-  uint16_t *d_slot_e = nullptr;   // [n_elem*S*S]   column slot of (a,b) in row ecoef[e][a]
+  int *d_vea = nullptr;           // [n_visits]     e*S+a of the visit
+  uint16_t *d_vslot = nullptr;    // [n_visits*S]   column slots of the visit's S blocks
+  int *d_trs = nullptr, *d_tdeg = nullptr;  // [n_coef] CSR row start / degree in tile order
+  int max_entries = 0;            // most elements incident to one tile
   int *d_err = nullptr;           // [4] device error flags
   void release();
 };

@@ -58,6 +58,8 @@ struct RowArgs {
   double *H;
   double *f_int;
   int row_stride;  // doubles of shared memory per warp
+  const int *perm;  // optional row order (Morton tiles): rows that share elements run together
+  int chunk;        // consecutive rows (in that order) handled by one block
 };
 
 // ---------------------------------------------------------------------------
@@ -319,7 +321,10 @@ __global__ void __launch_bounds__(ROW_WARPS * 32) row_kernel(RowArgs p) {
   const int k = lane / S, b = lane % S;
   const bool lane_on = lane < VPB * S;
 
-  for (int row = blockIdx.x * ROW_WARPS + warp; row < p.n_coef; row += gridDim.x * ROW_WARPS) {
+  const int n_chunks = (p.n_coef + p.chunk - 1) / p.chunk;
+  for (int ch = blockIdx.x; ch < n_chunks; ch += gridDim.x)
+  for (int ri = ch * p.chunk + warp; ri < min(p.n_coef, (ch + 1) * p.chunk); ri += ROW_WARPS) {
+    const int row = p.perm ? p.perm[ri] : ri;
     const int rs = p.off[row];
     const int deg = p.off[row + 1] - rs;
     // H row starts from the mass term: H(3i+d,3j+d) = M_ij / h   (SyncedNewton.cu:213-259)

@@ -3,6 +3,7 @@
 // and one implicit ALM/Newton step whose SPD solve is a block-Jacobi PCG (cuDSS is absent here).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "common.cuh"
@@ -254,35 +255,63 @@ static int norm2(tlfea_newton *s, const double *a, int64_t n, double *out) {
 }
 
 constexpr int TILE_WARPS = 8;
-constexpr int TILE_BATCH = 12;
-constexpr int TILE_BUDGET = 20400;  // doubles of shared-memory row buffer per tile
+// Two tilings: one big CTA per SM (large tiles, least element re-staging) or two smaller CTAs per SM
+// (more latency hiding).  TLFEA_TILE_CTAS=1|2 selects; the budget is the row-buffer size in doubles.
+struct TileCfg {
+  int ctas, batch, budget;
+};
+static TileCfg tile_cfg() {
+  static TileCfg c = [] {
+    TileCfg t{1, 12, 18000};
+    const char *e = getenv("TLFEA_TILE_CTAS");
+    if (e && atoi(e) == 2) t = TileCfg{2, 6, 7800};
+    const char *b = getenv("TLFEA_TILE_BUDGET");
+    if (b && atoi(b) > 0) t.budget = atoi(b);
+    return t;
+  }();
+  return c;
+}
 
 static bool tiles_supported(const tlfea_newton *s) {
   return s->use_tiles && s->e->type == TLFEA_TYPE_T10 && s->e->model == TL_MODEL_SVK &&
-         s->e->pat.max_inc <= 255 && s->e->pat.max_deg * 9 <= TILE_BUDGET;
+         s->e->pat.max_inc <= 255 && s->e->pat.max_deg * 9 <= tile_cfg().budget;
 }
 
 static int ensure_tiles(tlfea_newton *s) {
   if (s->have_tiles) return TLFEA_OK;
-  TL_TRY(build_tiles(s->e, TILE_BUDGET, TK_MAX_ROWS, TILE_BATCH, TILE_WARPS, &s->tiles));
+  const TileCfg c = tile_cfg();
+  TL_TRY(build_tiles(s->e, c.budget, TK_MAX_ROWS, c.batch, TILE_WARPS, &s->tiles));
+  TL_CHECK(s->tiles.max_entries <= TK_MAX_ENT, "tile with %d incident elements exceeds the kernel's list (%d)",
+           s->tiles.max_entries, TK_MAX_ENT);
   s->have_tiles = true;
   return TLFEA_OK;
 }
 
+template <int B, int CTAS>
+static int launch_tile_t(tlfea_newton *s, const TileArgs &a) {
+  const size_t smem = TileShape<10, 5, TILE_WARPS, B>::smem_bytes(a.buf_doubles);
+  TL_CUDA(cudaFuncSetAttribute(tile_kernel<10, 5, TILE_WARPS, B, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)smem));
+  TL_LAUNCH((tile_kernel<10, 5, TILE_WARPS, B, CTAS>), a.n_tiles, TILE_WARPS * 32, smem, s->e->stream, a);
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
 static int launch_tile(tlfea_newton *s, const RowArgs &r) {
-  tlfea_elem *e = s->e;
   const Tiles &t = s->tiles;
   TileArgs a;
   a.n_tiles = t.n_tiles;
   a.trow = t.d_trow;
+  a.trs = t.d_trs;
+  a.tdeg = t.d_tdeg;
   a.tile_ptr = t.d_tile_ptr;
   a.te_ptr = t.d_te_ptr;
   a.te_elem = t.d_te_elem;
   a.tb_ptr = t.d_tb_ptr;
   a.vptr = t.d_vptr;
   a.visit = t.d_visit;
-  a.slot_e = t.d_slot_e;
-  a.off = r.off;
+  a.vea = t.d_vea;
+  a.vslot = t.d_vslot;
   a.mass = r.mass;
   a.rec = r.rec;
   a.gradN = r.gradN;
@@ -297,12 +326,10 @@ static int launch_tile(tlfea_newton *s, const RowArgs &r) {
   a.mu = r.mu;
   a.H = r.H;
   a.f_int = r.f_int;
-  a.buf_doubles = TILE_BUDGET;
-  const size_t smem = TileShape<10, 5, TILE_WARPS, TILE_BATCH>::smem_bytes(TILE_BUDGET);
-  TL_CUDA(cudaFuncSetAttribute(tile_kernel<10, 5, TILE_WARPS, TILE_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  TL_LAUNCH((tile_kernel<10, 5, TILE_WARPS, TILE_BATCH>), t.n_tiles, TILE_WARPS * 32, smem, e->stream, a);
-  TL_CUDA(cudaGetLastError());
-  return TLFEA_OK;
+  a.buf_doubles = tile_cfg().budget;
+  a.timing = reinterpret_cast<unsigned long long *>(t.d_err + 4);
+  if (tile_cfg().ctas == 2) return launch_tile_t<6, 2>(s, a);
+  return launch_tile_t<12, 1>(s, a);
 }
 
 static int do_assemble(tlfea_newton *s, bool tangent) {
@@ -352,8 +379,15 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
     TL_CHECK(smem <= 200 * 1024, "coefficient row too long for the shared-memory row buffer (max_deg=%d)",
              e->pat.max_deg);
     const int rows_blocks = (e->n_coef + ROW_WARPS - 1) / ROW_WARPS;
-    const int grid = std::min(rows_blocks, 148 * 16);
-    if (tiles_supported(s)) {
+    const int grid = std::min(rows_blocks, 148 * 32);
+    a.perm = nullptr;
+    a.chunk = ROW_WARPS;
+    if (s->use_tiles == 2 && tiles_supported(s)) {  // row gather in Morton-tile order
+      TL_TRY(ensure_tiles(s));
+      a.perm = s->tiles.d_trow;
+      a.chunk = 64;
+    }
+    if (s->use_tiles == 1 && tiles_supported(s)) {
       TL_TRY(ensure_tiles(s));
       TL_TRY(launch_tile(s, a));
     } else {
@@ -802,8 +836,14 @@ int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset
   return TLFEA_OK;
 }
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode) {
-  TL_CHECK(s && (mode == 0 || mode == 1), "mode must be 0 (row gather) or 1 (tiles)");
+  TL_CHECK(s && mode >= 0 && mode <= 2, "mode must be 0 (row gather), 1 (tiles) or 2 (row gather in tile order)");
   s->use_tiles = mode;
+  return TLFEA_OK;
+}
+int tlfea_newton_tile_timing(tlfea_newton *s, unsigned long long *out8, int reset) {
+  TL_CHECK(s && s->have_tiles && out8, "no tiles");
+  TL_CUDA(cudaMemcpy(out8, s->tiles.d_err + 4, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  if (reset) TL_CUDA(cudaMemset(s->tiles.d_err + 4, 0, 8 * sizeof(unsigned long long)));
   return TLFEA_OK;
 }
 int tlfea_newton_tile_stats(tlfea_newton *s, int *n_tiles, int64_t *n_entries, int *max_rows, int *max_buf) {

@@ -26,10 +26,10 @@ namespace tlfea {
 
 struct TileArgs {
   int n_tiles;
-  const int *trow, *tile_ptr, *te_ptr, *te_elem, *tb_ptr, *vptr;
+  const int *trow, *trs, *tdeg, *tile_ptr, *te_ptr, *te_elem, *tb_ptr, *vptr;
   const unsigned *visit;
-  const uint16_t *slot_e;
-  const int *off;
+  const int *vea;
+  const uint16_t *vslot;
   const double *mass;
   const double *rec;  // [n_elem*Q][16]
   const double *gradN, *detJ, *fe;
@@ -37,18 +37,27 @@ struct TileArgs {
   double inv_h, c1, c2, c3, c4, mu;
   double *H, *f_int;
   int buf_doubles;
+  unsigned long long *timing;  // optional [8] phase cycle counters (TK_TIMING builds)
 };
 
+#ifdef TK_TIMING
+#define TK_T(i) do { if (lane == 0) { long long _t = clock64(); atomicAdd(p.timing + (i), (unsigned long long)(_t - t_last)); t_last = _t; } } while (0)
+#else
+#define TK_T(i) do { } while (0)
+#endif
 constexpr int TK_MAX_ROWS = 254;
+constexpr int TK_MAX_ENT = 768;  // elements incident to one tile (list kept in shared memory)
 
 template <int S, int Q, int W, int B>
 struct TileShape {
   static constexpr int NODE = Q * S * 6;                           // {u0,u1,u2,h0,h1,h2} per (q, node)
-  static constexpr int STG = NODE + Q * 6 + ((Q + 1) & ~1);        // + M_q + dV_q
+  static constexpr int STG0 = NODE + Q * 6 + ((Q + 1) & ~1);       // + M_q + dV_q
+  static constexpr int STG = STG0 + ((STG0 % 16 == 2) ? 0 : ((18 - STG0 % 16) % 16));  // = 2 mod 16 doubles: broadcast reads of different elements fall in different banks
   static constexpr int RAW = ((Q * 3 * S + Q * 16 + Q) + 1) & ~1;  // gradN | records | detJ
   static size_t smem_bytes(int buf_doubles) {
-    return ((size_t)buf_doubles + 256 * 3 + (size_t)B * (STG + RAW)) * sizeof(double) +
-           (257 + 256 + 256 + B) * sizeof(int);
+    // row buffer | mass rows (buf/9) | frow | stage | raw | roff, grow, rstart, element list
+    return ((size_t)buf_doubles + (buf_doubles / 9 + 2) + 256 * 3 + (size_t)B * (STG + RAW)) * sizeof(double) +
+           (257 + 256 + 256 + TK_MAX_ENT) * sizeof(int);
   }
 };
 
@@ -64,8 +73,8 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
 
-template <int S, int Q, int W, int B>
-__global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
+template <int S, int Q, int W, int B, int CTAS>
+__global__ void __launch_bounds__(W * 32, CTAS) tile_kernel(TileArgs p) {
   static_assert(W * 32 >= 256, "block scan covers up to 256 rows");
   static_assert((Q * 3 * S) % 2 == 0, "gradN block of one element must be 16-byte granular");
   using Sh = TileShape<S, Q, W, B>;
@@ -75,48 +84,33 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
   constexpr int NG = Q * 3 * S;  // gradN doubles per element
   extern __shared__ __align__(16) double sm[];
   double *rowbuf = sm;
-  double *frow = rowbuf + p.buf_doubles;
-  double *stage = frow + 256 * 3;   // [B][STG]
-  double *raw = stage + B * STG;    // [B][RAW]
+  double *mrow = rowbuf + p.buf_doubles;            // mass values of the tile rows, row after row
+  double *frow = mrow + (p.buf_doubles / 9 + 2);
+  double *stage = frow + 256 * 3;                   // [B][STG]
+  double *raw = stage + B * STG;                    // [B][RAW]
   int *roff = reinterpret_cast<int *>(raw + B * RAW);
   int *grow = roff + 257;
   int *rstart = grow + 256;
-  int *belem = rstart + 256;        // [B] element ids of the current batch
+  int *tel = rstart + 256;                          // element ids of the tile
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef TK_TIMING
+  long long t_last = clock64();
+#endif
   const int tile = blockIdx.x;
   const int r0 = p.tile_ptr[tile], nrows = p.tile_ptr[tile + 1] - r0;
   const int e0 = p.te_ptr[tile], ne = p.te_ptr[tile + 1] - e0;
   const int gb0 = p.tb_ptr[tile], nb = p.tb_ptr[tile + 1] - gb0;
 
-  // raw data of batch bi -> shared memory, asynchronously (gradN, records: 16-B chunks; detJ: 8-B)
-  auto prefetch = [&](int bi) {
-    const int n_el = min(B, ne - bi * B);
-    constexpr int C16 = NG / 2 + Q * 8;  // 16-byte chunks per element
-    for (int i = tid; i < n_el * C16; i += T) {
-      const int el = i / C16, c = i - el * C16;
-      const int e = p.te_elem[e0 + bi * B + el];
-      const double *src = (c < NG / 2) ? p.gradN + (int64_t)e * NG + 2 * c
-                                       : p.rec + (int64_t)e * Q * 16 + 2 * (c - NG / 2);
-      cp_async16(raw + el * RAW + 2 * c, src);
-    }
-    for (int i = tid; i < n_el * Q; i += T) {
-      const int el = i / Q, q = i - el * Q;
-      const int e = p.te_elem[e0 + bi * B + el];
-      cp_async8(raw + el * RAW + NG + Q * 16 + q, p.detJ + (int64_t)e * Q + q);
-    }
-    cp_async_commit();
-  };
-  if (nb > 0) prefetch(0);
-
-  // ---- row table: global row, CSR start, buffer offset (exclusive scan of 9*deg)
+  // ---- row table: global row, CSR start, buffer offset (exclusive scan of 9*deg); element list
   {
     int row = 0, rs = 0, sz = 0;
     if (tid < nrows) {
       row = p.trow[r0 + tid];
-      rs = p.off[row];
-      sz = 9 * (p.off[row + 1] - rs);
+      rs = p.trs[r0 + tid];
+      sz = 9 * p.tdeg[r0 + tid];
     }
+    for (int i = tid; i < ne; i += T) tel[i] = p.te_elem[e0 + i];
     using Scan = cub::BlockScan<int, T>;
     __shared__ typename Scan::TempStorage tmp;
     int excl;
@@ -132,6 +126,33 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
     }
   }
   __syncthreads();
+
+  // raw data of batch bi -> shared memory, asynchronously (gradN, records: 16-B chunks; detJ: 8-B)
+  auto prefetch = [&](int bi) {
+    const int n_el = min(B, ne - bi * B);
+    constexpr int C16 = NG / 2 + Q * 8;  // 16-byte chunks per element
+    for (int i = tid; i < n_el * C16; i += T) {
+      const int el = i / C16, c = i - el * C16;
+      const int e = tel[bi * B + el];
+      const double *src = (c < NG / 2) ? p.gradN + (int64_t)e * NG + 2 * c
+                                       : p.rec + (int64_t)e * Q * 16 + 2 * (c - NG / 2);
+      cp_async16(raw + el * RAW + 2 * c, src);
+    }
+    for (int i = tid; i < n_el * Q; i += T) {
+      const int el = i / Q, q = i - el * Q;
+      cp_async8(raw + el * RAW + NG + Q * 16 + q, p.detJ + (int64_t)tel[bi * B + el] * Q + q);
+    }
+    cp_async_commit();
+  };
+  // mass rows -> shared memory (needed only when the rows stream out)
+  for (int r = warp; r < nrows; r += W) {
+    const int deg = (roff[r + 1] - roff[r]) / 9;
+    const double *src = p.mass + rstart[r];
+    double *dst = mrow + roff[r] / 9;
+    for (int s2 = lane; s2 < deg; s2 += 32) cp_async8(dst + s2, src + s2);
+  }
+  if (nb > 0) prefetch(0);
+  else cp_async_commit();
   // ---- zero the row buffer (the mass term M_ij/h is added while streaming the rows out)
   {
     const int total = roff[nrows];
@@ -139,13 +160,42 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
     for (int i = tid; i < (total + 1) / 2; i += T) z2[i] = make_double2(0.0, 0.0);
   }
 
+  TK_T(0);
   const int k = lane / S, b = lane - k * S;
   const bool lane_on = lane < AS * S;
+  int v0n = 0, v1n = 0;
+  if (nb > 0) {
+    v0n = p.vptr[(int64_t)gb0 * W + warp];
+    v1n = p.vptr[(int64_t)gb0 * W + warp + 1];
+  }
 
   for (int bi = 0; bi < nb; bi++) {
     const int n_el = min(B, ne - bi * B);
+    const int v0 = v0n, v1 = v1n;
+    if (bi + 1 < nb) {  // next batch's visit range: in flight during this batch
+      v0n = p.vptr[(int64_t)(gb0 + bi + 1) * W + warp];
+      v1n = p.vptr[(int64_t)(gb0 + bi + 1) * W + warp + 1];
+    }
+    // per-visit data of this warp's batch share -> registers, issued BEFORE the barrier wait:
+    // lane i holds the descriptor of visit v0+i; lanes 3j..3j+2 hold the element force of visit j (+10, +20)
+    const int nvis = v1 - v0;
+    unsigned d_reg = 0u;
+    double fe_reg[3] = {0.0, 0.0, 0.0};
+    int slot_nx = 0;
+    if (lane < nvis) d_reg = p.visit[v0 + lane];
+    {
+      const int vj = lane / 3, comp = lane - 3 * vj;
+#pragma unroll
+      for (int g = 0; g < 3; g++) {
+        const int j = g * 10 + vj;
+        if (lane < 30 && j < nvis) fe_reg[g] = p.fe[(int64_t)p.vea[v0 + j] * 3 + comp];
+      }
+    }
+    if (lane_on && k < nvis) slot_nx = p.vslot[(int64_t)(v0 + k) * S + b];
+    TK_T(1);
     cp_async_wait_all();
     __syncthreads();  // raw(bi) complete for all threads; every warp is done with the previous stage
+    TK_T(2);
     // ---- stage the batch
     for (int it = tid; it < n_el * Q * S; it += T) {
       const int el = it / (Q * S), qc = it - el * (Q * S);
@@ -172,23 +222,34 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
       M2[2] = make_double2(p.c3 * r[13], p.c3 * r[14] + dg);
       st[Q * 6 + q] = raw[el * RAW + NG + Q * 16 + q] * p.qw.w[q];
     }
-    if (tid < n_el) belem[tid] = p.te_elem[e0 + bi * B + tid];
+    TK_T(3);
     __syncthreads();  // stage visible; raw free
+    TK_T(4);
     if (bi + 1 < nb) prefetch(bi + 1);
+    TK_T(5);
 
     // ---- this warp's visits of the batch, AS at a time
-    const int v0 = p.vptr[(int64_t)(gb0 + bi) * W + warp], v1 = p.vptr[(int64_t)(gb0 + bi) * W + warp + 1];
     for (int vb = v0; vb < v1; vb += AS) {
-      const bool valid = lane_on && (vb + k < v1);
-      unsigned d = valid ? p.visit[vb + k] : 0u;
+      const int j = vb - v0 + k;  // visit index inside this warp's batch share
+      const bool valid = lane_on && (j < nvis);
+      unsigned d = __shfl_sync(0xffffffffu, d_reg, j & 31);
+      const int slot = slot_nx;
+      // element force component b of visit j sits in lane 3*(j%10)+b, register j/10
+      const int jg = j / 10;
+      const int fsrc = (3 * (j - 10 * jg) + b) & 31;
+      const double f0 = __shfl_sync(0xffffffffu, fe_reg[0], fsrc);
+      const double f1 = __shfl_sync(0xffffffffu, fe_reg[1], fsrc);
+      const double f2 = __shfl_sync(0xffffffffu, fe_reg[2], fsrc);
+      double fadd = (jg == 0) ? f0 : ((jg == 1) ? f1 : f2);
+      if (valid && j >= 30) {  // beyond the register prefetch window
+        if (b < 3) fadd = p.fe[(int64_t)p.vea[vb + k] * 3 + b];
+      }
+      if (valid && j >= 32) d = p.visit[vb + k];
+      if (lane_on && j + AS < nvis) slot_nx = p.vslot[(int64_t)(vb + AS + k) * S + b];  // next pass
+      if (!valid) d = 0u;
       const int el = d & 0xff, a = (d >> 8) & 0xff, lr = valid ? (int)(d >> 16) : -1;
       double val[9];
-      int slot = 0;
-      double fadd = 0.0;
       if (valid) {
-        const int e = belem[el];
-        slot = p.slot_e[((int64_t)e * S + a) * S + b];
-        if (b < 3) fadd = p.fe[((int64_t)e * S + a) * 3 + b];
         const double *node = stage + el * STG;
         const double *Mq = node + NODE, *dVq = Mq + Q * 6;
         double A[9], Sg[6];
@@ -258,26 +319,30 @@ __global__ void __launch_bounds__(W * 32, 1) tile_kernel(TileArgs p) {
       __syncwarp();
     }
   }
+  TK_T(1);
+  cp_async_wait_all();
   __syncthreads();
+  TK_T(6);
   // ---- stream the finished block rows out as three scalar CSR rows of length 3*deg each,
   //      adding the mass term H(3i+d,3j+d) += M_ij/h (SyncedNewton.cu:213-259)
   for (int r = warp; r < nrows; r += W) {
-    const int rs = rstart[r];
-    const int64_t base = 9 * (int64_t)rs;
+    const int64_t base = 9 * (int64_t)rstart[r];
     const int rowlen = (roff[r + 1] - roff[r]) / 3;
     const double *src = rowbuf + roff[r];
+    const double *mr = mrow + roff[r] / 9;
 #pragma unroll
     for (int d = 0; d < 3; d++) {
 #pragma unroll 2
       for (int c = lane; c < rowlen; c += 32) {
         const int s = c / 3, e2 = c - 3 * s;
         double v = src[s * 9 + d * 3 + e2];
-        if (e2 == d) v += p.mass[rs + s] * p.inv_h;
+        if (e2 == d) v += mr[s] * p.inv_h;
         p.H[base + d * rowlen + c] = v;
       }
     }
     if (lane < 3) p.f_int[(int64_t)grow[r] * 3 + lane] = frow[3 * r + lane];
   }
+  TK_T(7);
 }
 
 }  // namespace tlfea

@@ -133,41 +133,13 @@ __global__ void k_tile_lower_bound(const int *__restrict__ te_tile, int n, int n
   te_ptr[t] = lo;
 }
 
-__global__ void k_entry_rows(int64_t n, int S, const int *__restrict__ te_tile, const int *__restrict__ te_elem,
-                             const int *__restrict__ ecoef, const int *__restrict__ tile_of_row,
-                             const uint8_t *__restrict__ lrow_of_row, const int *__restrict__ vidx,
-                             const int *__restrict__ inc_ptr, uint8_t *lrow, uint8_t *rank) {
-  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (tid >= n * S) return;
-  const int64_t j = tid / S;
-  const int a = (int)(tid - j * S);
-  const int e = te_elem[j];
-  const int r = ecoef[(int64_t)e * S + a];
-  if (tile_of_row[r] == te_tile[j]) {
-    lrow[tid] = lrow_of_row[r];
-    rank[tid] = (uint8_t)(vidx[(int64_t)e * S + a] - inc_ptr[r]);  // ascending-element order inside the row
-  } else {
-    lrow[tid] = 255;
-    rank[tid] = 0;
-  }
-}
-
-__global__ void k_slot_by_elem(int64_t n_visits, int S, const int *__restrict__ inc_ea,
-                               const uint16_t *__restrict__ slot, uint16_t *slot_e) {
-  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (tid >= n_visits * S) return;
-  const int64_t v = tid / S;
-  const int b = (int)(tid - v * S);
-  slot_e[(int64_t)inc_ea[v] * S + b] = slot[tid];
-}
-
 // One descriptor per visit (row r of the tile, element e, local shape function a), grouped by
 // (batch of the tile's element list, owner warp of the row):  elem-in-batch | a<<8 | local row<<16.
 __global__ void k_visit_desc(int64_t n_visits, int S, int B, int W, const int *__restrict__ inc_ea,
                              const int *__restrict__ ecoef, const int *__restrict__ tile_of_row,
                              const uint8_t *__restrict__ lrow_of_row, const int *__restrict__ te_ptr,
                              const int *__restrict__ te_elem, const int *__restrict__ tb_ptr,
-                             unsigned long long *keys, unsigned *desc) {
+                             unsigned long long *keys, unsigned *desc, int *vals) {
   int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= n_visits) return;
   const int ea = inc_ea[v];
@@ -188,6 +160,31 @@ __global__ void k_visit_desc(int64_t n_visits, int S, int B, int W, const int *_
   const int ebi = j % B;
   keys[v] = (gbw << 16) | (unsigned)(ebi << 8) | (unsigned)a;
   desc[v] = (unsigned)ebi | ((unsigned)a << 8) | ((unsigned)lr << 16);
+  vals[v] = (int)v;
+}
+
+// per-visit records in (batch, warp) order: descriptor, e*S+a, and the S column slots of the visit
+__global__ void k_visit_fill(int64_t n_visits, int S, const int *__restrict__ order, const unsigned *__restrict__ desc0,
+                             const int *__restrict__ inc_ea, const uint16_t *__restrict__ slot, unsigned *desc,
+                             int *vea, uint16_t *vslot) {
+  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= n_visits * S) return;
+  const int64_t i = tid / S;
+  const int b = (int)(tid - i * S);
+  const int v = order[i];
+  vslot[tid] = slot[(int64_t)v * S + b];
+  if (b == 0) {
+    desc[i] = desc0[v];
+    vea[i] = inc_ea[v];
+  }
+}
+
+__global__ void k_tile_rows(int n, const int *__restrict__ trow, const int *__restrict__ off, int *trs, int *tdeg) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int r = trow[i];
+  trs[i] = off[r];
+  tdeg[i] = off[r + 1] - off[r];
 }
 
 __global__ void k_gbw_lower_bound(const unsigned long long *__restrict__ keys, int64_t n, int64_t n_groups, int *ptr) {
@@ -226,7 +223,10 @@ void Tiles::release() {
   dfree(d_tb_ptr);
   dfree(d_vptr);
   dfree(d_visit);
-  dfree(d_slot_e);
+  dfree(d_vea);
+  dfree(d_vslot);
+  dfree(d_trs);
+  dfree(d_tdeg);
   dfree(d_err);
   n_tiles = 0;
 }
@@ -345,7 +345,10 @@ int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int batch
     TL_CUDA(cudaMemcpyAsync(te_ptr_h.data(), t.d_te_ptr, te_ptr_h.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
     TL_CUDA(cudaStreamSynchronize(st));
     tb[0] = 0;
-    for (int i = 0; i < t.n_tiles; i++) tb[i + 1] = tb[i] + (te_ptr_h[i + 1] - te_ptr_h[i] + batch - 1) / batch;
+    for (int i = 0; i < t.n_tiles; i++) {
+      tb[i + 1] = tb[i] + (te_ptr_h[i + 1] - te_ptr_h[i] + batch - 1) / batch;
+      t.max_entries = std::max(t.max_entries, te_ptr_h[i + 1] - te_ptr_h[i]);
+    }
     t.n_batches = tb[t.n_tiles];
     TL_TRY(dmalloc(&t.d_tb_ptr, tb.size()));
     TL_CUDA(cudaMemcpyAsync(t.d_tb_ptr, tb.data(), tb.size() * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -354,20 +357,22 @@ int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int batch
   {
     unsigned long long *vk0 = nullptr, *vk1 = nullptr;
     unsigned *d0 = nullptr;
+    int *o0 = nullptr, *o1 = nullptr;
     TL_TRY(dmalloc(&vk0, (size_t)nv));
     TL_TRY(dmalloc(&vk1, (size_t)nv));
     TL_TRY(dmalloc(&d0, (size_t)nv));
-    TL_TRY(dmalloc(&t.d_visit, (size_t)nv));
+    TL_TRY(dmalloc(&o0, (size_t)nv));
+    TL_TRY(dmalloc(&o1, (size_t)nv));
     TL_LAUNCH(k_visit_desc, blocks_for(nv, 256), 256, 0, st, nv, S, batch, warps, pat.d_inc_ea, h->d_ecoef, tile_of_row,
-              lrow_of_row, t.d_te_ptr, t.d_te_elem, t.d_tb_ptr, vk0, d0);
+              lrow_of_row, t.d_te_ptr, t.d_te_elem, t.d_tb_ptr, vk0, d0, o0);
     const int64_t n_groups = (int64_t)t.n_batches * warps;
     int gbits = 1;
     while ((1LL << gbits) < n_groups + 1) gbits++;
     size_t tmp_bytes = 0;
-    TL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, vk0, vk1, d0, t.d_visit, nv, 0, 16 + gbits, st));
+    TL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, vk0, vk1, o0, o1, nv, 0, 16 + gbits, st));
     void *tmp = nullptr;
     TL_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
-    cudaError_t er = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, vk0, vk1, d0, t.d_visit, nv, 0, 16 + gbits, st);
+    cudaError_t er = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, vk0, vk1, o0, o1, nv, 0, 16 + gbits, st);
     g_launches.fetch_add(1);
     TL_TRY(dmalloc(&t.d_vptr, (size_t)n_groups + 1));
     TL_LAUNCH(k_gbw_lower_bound, blocks_for(n_groups + 1, 256), 256, 0, st, vk1, nv, n_groups, t.d_vptr);
@@ -375,14 +380,23 @@ int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int batch
     cudaFree(tmp);
     cudaFree(vk0);
     cudaFree(vk1);
-    cudaFree(d0);
+    cudaFree(o0);
     TL_CUDA(er);
+    TL_TRY(dmalloc(&t.d_visit, (size_t)nv));
+    TL_TRY(dmalloc(&t.d_vea, (size_t)nv));
+    TL_TRY(dmalloc(&t.d_vslot, (size_t)nv * S));
+    TL_LAUNCH(k_visit_fill, blocks_for(nv * S, 256), 256, 0, st, nv, S, o1, d0, pat.d_inc_ea, pat.d_slot, t.d_visit,
+              t.d_vea, t.d_vslot);
+    cudaStreamSynchronize(st);
+    cudaFree(o1);
+    cudaFree(d0);
   }
-  // ---- 5. slot map indexed by (element, a, b)
-  TL_TRY(dmalloc(&t.d_slot_e, (size_t)nv * S));
-  TL_LAUNCH(k_slot_by_elem, blocks_for(nv * S, 256), 256, 0, st, nv, S, pat.d_inc_ea, pat.d_slot, t.d_slot_e);
-  TL_TRY(dmalloc(&t.d_err, 4));
-  TL_CUDA(cudaMemsetAsync(t.d_err, 0, 4 * sizeof(int), st));
+  // ---- 5. CSR start and degree of the rows in tile order (no dependent loads in the kernel prologue)
+  TL_TRY(dmalloc(&t.d_trs, (size_t)n));
+  TL_TRY(dmalloc(&t.d_tdeg, (size_t)n));
+  TL_LAUNCH(k_tile_rows, blocks_for(n, 256), 256, 0, st, n, t.d_trow, pat.d_off, t.d_trs, t.d_tdeg);
+  TL_TRY(dmalloc(&t.d_err, 4 + 16));  // 4 flags + 8 x 64-bit phase counters
+  TL_CUDA(cudaMemsetAsync(t.d_err, 0, 20 * sizeof(int), st));
   TL_CUDA(cudaGetLastError());
   TL_CUDA(cudaStreamSynchronize(st));
   cudaFree(k0);
