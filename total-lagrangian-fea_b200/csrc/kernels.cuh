@@ -323,7 +323,10 @@ __global__ void __launch_bounds__(ROW_WARPS * 32) row_kernel(RowArgs p) {
 
   const int n_chunks = (p.n_coef + p.chunk - 1) / p.chunk;
   for (int ch = blockIdx.x; ch < n_chunks; ch += gridDim.x)
-  for (int ri = ch * p.chunk + warp; ri < min(p.n_coef, (ch + 1) * p.chunk); ri += ROW_WARPS) {
+  for (int t8 = 0; t8 < p.chunk; t8 += ROW_WARPS) {
+    // rotate the warp<->row assignment: in Morton order every 8th row is a hub (vertex) row
+    const int ri = ch * p.chunk + t8 + ((warp + ROW_WARPS - (t8 / ROW_WARPS) % ROW_WARPS) % ROW_WARPS);
+    if (ri >= p.n_coef || ri >= (ch + 1) * p.chunk) continue;
     const int row = p.perm ? p.perm[ri] : ri;
     const int rs = p.off[row];
     const int deg = p.off[row + 1] - rs;

@@ -156,7 +156,7 @@ __global__ void k_visit_desc(int64_t n_visits, int S, int B, int W, const int *_
       hi = mid;
   }
   const int j = lo - base;
-  const unsigned long long gbw = (unsigned long long)(tb_ptr[t] + j / B) * W + (lr % W);
+  const unsigned long long gbw = (unsigned long long)(tb_ptr[t] + j / B) * W + ((lr + lr / W) % W)  /* rotate: Morton-local indices that are multiples of 8 are the hub (vertex) rows */;
   const int ebi = j % B;
   keys[v] = (gbw << 16) | (unsigned)(ebi << 8) | (unsigned)a;
   desc[v] = (unsigned)ebi | ((unsigned)a << 8) | ((unsigned)lr << 16);
