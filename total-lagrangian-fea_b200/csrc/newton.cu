@@ -9,6 +9,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 #include "tile_kernel.cuh"
+#include "row2_kernel.cuh"
 
 namespace tlfea {
 int launch_gp(tlfea_elem *h, const double *v, double *rec, double *fe, double *F_out, double *P_out);
@@ -387,7 +388,20 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
       a.perm = s->tiles.d_trow;
       a.chunk = 64;
     }
-    if (s->use_tiles == 1 && tiles_supported(s)) {
+    const int r2_passes = R2_GROUP * ((e->pat.max_inc + 2) / 3);
+    if (s->use_tiles == 3 && tiles_supported(s) && r2_passes <= 32) {  // row gather + cp.async operand staging
+      TL_TRY(ensure_tiles(s));
+      a.perm = s->tiles.d_trow;
+      using Sh = Row2Shape<10, 5>;
+      const int wd = Sh::warp_doubles(e->pat.max_deg), md = Sh::mrow_doubles(e->pat.max_deg);
+      const size_t smem2 = (size_t)R2_WARPS * wd * sizeof(double);
+      TL_CHECK(smem2 <= 220 * 1024, "row too long for the row2 kernel");
+      TL_CUDA(cudaFuncSetAttribute(row2_kernel<10, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+      const int n_chunks = (e->n_coef + R2_CHUNK - 1) / R2_CHUNK;
+      const int per_sm = std::max(1, (int)((227 * 1024) / (smem2 + 1024)));
+      TL_LAUNCH((row2_kernel<10, 5>), std::min(n_chunks, 148 * per_sm * 4), R2_WARPS * 32, smem2, e->stream, a, wd, md);
+      TL_CUDA(cudaGetLastError());
+    } else if (s->use_tiles == 1 && tiles_supported(s)) {
       TL_TRY(ensure_tiles(s));
       TL_TRY(launch_tile(s, a));
     } else {
@@ -836,7 +850,7 @@ int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset
   return TLFEA_OK;
 }
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode) {
-  TL_CHECK(s && mode >= 0 && mode <= 2, "mode must be 0 (row gather), 1 (tiles) or 2 (row gather in tile order)");
+  TL_CHECK(s && mode >= 0 && mode <= 3, "mode must be 0 (row gather), 1 (tiles), 2 (row gather in tile order) or 3 (staged row gather)");
   s->use_tiles = mode;
   return TLFEA_OK;
 }
