@@ -327,7 +327,7 @@ def main():
         fp64 = tf.value
     dom_ms = max(row_ms, 1e-9)
     achieved = algo_b / (dom_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "tile_kernel<10,5,8>" if s.TileStats()["n_tiles"] else "row_kernel<10,5,SVK>", "achieved": achieved, "peak": hbm_peak,
+    roofline = {"bound": "hbm", "kernel": "row2_kernel<10,5>" if s.TileStats()["n_tiles"] else "row_kernel<10,5,SVK>", "achieved": achieved, "peak": hbm_peak,
                 "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                 "algorithmic_bytes_per_launch": algo_b, "kernel_ms": row_ms, "gp_kernel_ms": gp_ms,

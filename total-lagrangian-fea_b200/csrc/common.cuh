@@ -173,7 +173,7 @@ struct tlfea_newton {
   tlfea_elem *e = nullptr;
   tlfea::Tiles tiles;
   bool have_tiles = false;
-  int use_tiles = 1;  // 0: row-gather kernel, 1: tile kernel where supported
+  int use_tiles = 3;  // assembly kernel: 0 row gather, 1 tiles, 2 row gather in tile order, 3 staged row gather (default where supported)
   int n_constraints = 0;
   tlfea_newton_params prm{};
   bool analyzed = false, fixed_pattern = false;

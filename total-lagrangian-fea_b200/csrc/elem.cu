@@ -190,7 +190,7 @@ template <int S, int Q>
 static int launch_gp_t(tlfea_elem *h, const GPArgs &a, bool damp) {
   using Sh = GPShape<S, Q>;
   const unsigned grid = blocks_for(h->n_elem, Sh::EPB);
-  const size_t smem = a.fe ? Sh::SMEM : 0;
+  const size_t smem = Sh::SMEM;  // gradN staging tile (always), reused for the force partials
 #define TL_GP(MODEL, DAMP)                                                                                     \
   do {                                                                                                         \
     if (smem > 48 * 1024)                                                                                      \

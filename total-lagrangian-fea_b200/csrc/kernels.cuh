@@ -133,23 +133,39 @@ template <int S, int Q>
 struct GPShape {
   static constexpr int EPB = (S == 10) ? 32 : (S == 8 ? 16 : 4);  // elements per block
   static constexpr int THREADS = EPB * Q;
-  static constexpr size_t SMEM = (size_t)EPB * Q * 3 * S * sizeof(double);
+  static constexpr size_t SMEM = (size_t)EPB * Q * 3 * S * sizeof(double);  // gradN tile, then force partials
 };
 
 template <int S, int Q, int MODEL, bool DAMP>
 __global__ void __launch_bounds__(GPShape<S, Q>::THREADS) gp_kernel(GPArgs p) {
   constexpr int EPB = GPShape<S, Q>::EPB;
-  extern __shared__ double part[];  // [EPB][Q][3S]
+  extern __shared__ double part[];  // [EPB][Q][3S]: gradN of the block's elements, later the force partials
   const int el = threadIdx.x / Q, q = threadIdx.x % Q;
   const int e = blockIdx.x * EPB + el;
   const bool active = e < p.n_elem;
+  {
+    // coalesced copy of the block's contiguous gradN range into shared memory
+    const int64_t base = (int64_t)blockIdx.x * EPB * Q * 3 * S;
+    const int64_t n_here = min((int64_t)EPB, (int64_t)p.n_elem - (int64_t)blockIdx.x * EPB) * Q * 3 * S;
+    const double2 *src = reinterpret_cast<const double2 *>(p.gradN + base);
+    double2 *dst = reinterpret_cast<double2 *>(part);
+    for (int64_t i = threadIdx.x; i < n_here / 2; i += GPShape<S, Q>::THREADS) dst[i] = src[i];
+  }
+  __syncthreads();
+  double hreg[3 * S];
+  if (active) {
+    const double *gs = part + (size_t)(el * Q + q) * 3 * S;
+#pragma unroll
+    for (int i = 0; i < 3 * S; i++) hreg[i] = gs[i];
+  }
+  __syncthreads();  // part is reused for the force partials below
   if (active) {
     const int64_t t = (int64_t)e * Q + q;
     const int *ec = p.ecoef + (int64_t)e * S;
-    const double *g = p.gradN + t * 3 * S;
+    const double *g = hreg;
     double F[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
     double Fd[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
-#pragma unroll 2
+#pragma unroll
     for (int a = 0; a < S; a++) {
       const int c = ec[a];
       const double xa[3] = {p.x[c], p.y[c], p.z[c]};
@@ -286,7 +302,7 @@ __global__ void __launch_bounds__(GPShape<S, Q>::THREADS) gp_kernel(GPArgs p) {
     }
     if (p.fe) {
       double *pt = part + (size_t)(el * Q + q) * 3 * S;
-#pragma unroll 2
+#pragma unroll
       for (int a = 0; a < S; a++) {
         const double ha[3] = {g[a], g[S + a], g[2 * S + a]};
 #pragma unroll
