@@ -202,7 +202,7 @@ def test_newton_step_converges(golden_t10):
     assert st["norm_c"] < 1e-6, st
 
 
-@pytest.mark.parametrize("mode", [1, 2, 3])
+@pytest.mark.parametrize("mode", [1, 2, 3, 4])
 @pytest.mark.parametrize("damp", [False, True])
 def test_assembly_kernels_agree(mesh, damp, mode):
     """All deterministic assembly kernels (0 warp-per-row gather, 1 spatial tiles, 2 gather in tile
@@ -215,8 +215,9 @@ def test_assembly_kernels_agree(mesh, damp, mode):
     s.SetVelocityGuess(v.reshape(-1))
     s.SetAssembly(mode)
     s.Assemble()
-    st = s.TileStats()
-    assert st["n_tiles"] > 1 and st["n_entries"] >= E.shape[0]
+    if mode != 4:
+        st = s.TileStats()
+        assert st["n_tiles"] > 1 and st["n_entries"] >= E.shape[0]
     H1, f1 = s.RetrieveHessianValues(), d.RetrieveInternalForceToCPU()
     s.Assemble()
     assert np.array_equal(H1, s.RetrieveHessianValues())

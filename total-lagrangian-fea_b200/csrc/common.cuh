@@ -167,19 +167,22 @@ struct tlfea_elem {
 
 namespace tlfea {
 int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int batch, int warps, Tiles *out);
+int build_row_order(const tlfea_elem *h, int **d_order);
 }
 
 struct tlfea_newton {
   tlfea_elem *e = nullptr;
   tlfea::Tiles tiles;
   bool have_tiles = false;
-  int use_tiles = 3;  // assembly kernel: 0 row gather, 1 tiles, 2 row gather in tile order, 3 staged row gather (default where supported)
+  int use_tiles = 4;  // assembly: 0 row gather, 1 tiles, 2 row gather in tile order, 3 staged row gather, 4 element kernel + row reduce (default where supported)
   int n_constraints = 0;
   tlfea_newton_params prm{};
   bool analyzed = false, fixed_pattern = false;
   int64_t nnz = 0;  // DOF-level nnz = 9 * pattern.nnz
   double *d_H = nullptr;
   double *d_gp = nullptr;  // per-Gauss-point records
+  double *d_stage = nullptr;  // symmetric element block records of the two-phase assembly (ek_kernel.cuh)
+  void *d_rowdesc = nullptr;  // RowDesc[n_coef] in Morton processing order (ek_kernel.cuh)
   int rec_doubles = 0;
   double *d_v = nullptr, *d_v_prev = nullptr, *d_lambda = nullptr, *d_g = nullptr, *d_dv = nullptr, *d_r = nullptr;
   double *d_xp = nullptr, *d_yp = nullptr, *d_zp = nullptr;

@@ -4,12 +4,14 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "common.cuh"
 #include "kernels.cuh"
 #include "tile_kernel.cuh"
 #include "row2_kernel.cuh"
+#include "ek_kernel.cuh"
 
 namespace tlfea {
 int launch_gp(tlfea_elem *h, const double *v, double *rec, double *fe, double *F_out, double *P_out);
@@ -255,6 +257,137 @@ static int norm2(tlfea_newton *s, const double *a, int64_t n, double *out) {
   return TLFEA_OK;
 }
 
+static int ensure_records(tlfea_newton *s) {
+  const int need = (s->e->model == TL_MODEL_MR) ? REC_MR : REC_SVK;
+  if (need != s->rec_doubles) {
+    dfree(s->d_gp);
+    s->rec_doubles = need;
+    TL_TRY(dmalloc(&s->d_gp, (size_t)s->e->n_elem * s->e->Q * need));
+  }
+  return TLFEA_OK;
+}
+
+// ---------------------------------------------------------------------------
+// two-phase assembly (ek_kernel.cuh): element kernel -> symmetric block records -> row reduce
+// ---------------------------------------------------------------------------
+struct EKCfg {
+  int g, w;
+};
+static EKCfg ek_cfg() {
+  static EKCfg c = [] {
+    EKCfg t{5, 8};
+    const char *e = getenv("TLFEA_EK_CFG");  // "65" = groups of 6, 5 warps ... (tuning aid)
+    if (e && strlen(e) == 2) t = EKCfg{e[0] - '0', e[1] - '0'};
+    return t;
+  }();
+  return c;
+}
+
+static bool ek_supported(const tlfea_newton *s) {
+  const tlfea_elem *e = s->e;
+  return s->use_tiles == 4 && e->type == TLFEA_TYPE_T10 && e->model == TL_MODEL_SVK;
+}
+
+template <int G, int W, bool DAMP, bool TANGENT>
+static int launch_ek_t(tlfea_elem *e, const EKArgs &a) {
+  const size_t smem = EKShape<G, DAMP>::smem_bytes(W);
+  TL_CHECK(smem <= 227 * 1024, "element kernel configuration needs %zu bytes of shared memory", smem);
+  TL_CUDA(cudaFuncSetAttribute(ek_kernel<G, W, DAMP, TANGENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int n_groups = (a.n_elem + G - 1) / G;
+  const int grid = std::max(1, std::min(148, (n_groups + W - 1) / W));
+  TL_LAUNCH((ek_kernel<G, W, DAMP, TANGENT>), grid, W * 32, smem, e->stream, a);
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
+template <bool DAMP, bool TANGENT>
+static int launch_ek_cfg(tlfea_elem *e, const EKArgs &a) {
+  const EKCfg c = ek_cfg();
+  if (DAMP) return launch_ek_t<5, 7, DAMP, TANGENT>(e, a);
+  if (c.g == 6 && c.w == 7) return launch_ek_t<6, 7, DAMP, TANGENT>(e, a);
+  if (c.g == 6 && c.w == 6) return launch_ek_t<6, 6, DAMP, TANGENT>(e, a);
+  if (c.g == 4 && c.w == 9) return launch_ek_t<4, 9, DAMP, TANGENT>(e, a);
+  if (c.g == 3 && c.w == 9) return launch_ek_t<3, 9, DAMP, TANGENT>(e, a);
+  return launch_ek_t<5, 8, DAMP, TANGENT>(e, a);
+}
+
+static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
+  tlfea_elem *e = s->e;
+  const double h = s->prm.time_step;
+  if (tangent && !s->d_stage)
+    TL_TRY(dmalloc(&s->d_stage, (size_t)e->n_elem * SymLayout<10>::ELEM_DOUBLES));
+  if (tangent && !s->d_rowdesc) {
+    int *d_order = nullptr;
+    TL_TRY(build_row_order(e, &d_order));
+    RowDesc *desc = nullptr;
+    TL_TRY(dmalloc(&desc, (size_t)e->n_coef));
+    TL_LAUNCH(k_row_desc, blocks_for(e->n_coef, 256), 256, 0, e->stream, e->n_coef, d_order, e->pat.d_off,
+              e->pat.d_inc_ptr, desc);
+    TL_CUDA(cudaStreamSynchronize(e->stream));
+    cudaFree(d_order);
+    s->d_rowdesc = desc;
+  }
+  EKArgs a;
+  a.n_elem = e->n_elem;
+  a.ecoef = e->d_ecoef;
+  a.x = e->d_x;
+  a.y = e->d_y;
+  a.z = e->d_z;
+  a.v = damp ? s->d_v : nullptr;
+  a.gradN = e->d_gradN;
+  a.detJ = e->d_detJ;
+  a.qw = e->qw;
+  a.lambda = e->lambda;
+  a.mu = e->mu;
+  a.eta = e->eta;
+  a.lambda_d = e->lambda_d;
+  a.c1 = h * e->lambda + e->lambda_d;
+  a.c2 = h * e->mu + e->eta;
+  a.c3 = h * e->mu + e->eta;
+  a.c4 = h;
+  a.fe = e->d_fe;
+  a.stage = tangent ? s->d_stage : nullptr;
+  if (tangent) {
+    if (damp)
+      TL_TRY((launch_ek_cfg<true, true>(e, a)));
+    else
+      TL_TRY((launch_ek_cfg<false, true>(e, a)));
+  } else {
+    if (damp)
+      TL_TRY((launch_ek_cfg<true, false>(e, a)));
+    else
+      TL_TRY((launch_ek_cfg<false, false>(e, a)));
+  }
+  if (s->profile) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
+  if (!tangent) {
+    TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)e->n_coef * 3, 128), 128, 0, e->stream, e->n_coef,
+              e->pat.d_inc_ptr, e->pat.d_inc_ea, e->d_fe, e->d_f_int, 0);
+    return TLFEA_OK;
+  }
+  RKArgs r;
+  r.n_coef = e->n_coef;
+  r.desc = static_cast<const RowDesc *>(s->d_rowdesc);
+  r.inc_ea = e->pat.d_inc_ea;
+  r.slot = e->pat.d_slot;
+  r.mass = e->d_mass;
+  r.stage = s->d_stage;
+  r.fe = e->d_fe;
+  r.inv_h = 1.0 / h;
+  r.H = s->d_H;
+  r.f_int = e->d_f_int;
+  r.row_stride = ((e->pat.max_deg * 9 + 32 + 1) | 1);  // block row + 32 doubles for the force gather
+  const size_t smem = (size_t)RK_WARPS * r.row_stride * sizeof(double);
+  TL_CHECK(smem <= 220 * 1024, "coefficient row too long for the row-reduce kernel (max_deg=%d)", e->pat.max_deg);
+  if (smem > 48 * 1024)
+    TL_CUDA(cudaFuncSetAttribute(rk_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int n_chunks = (e->n_coef + RK_WARPS - 1) / RK_WARPS;
+  const int per_sm = std::max(1, std::min(3, (int)((227 * 1024) / (smem + 2048))));
+  TL_LAUNCH((rk_kernel<10>), std::min(n_chunks, 148 * per_sm), RK_WARPS * 32, smem, e->stream, r);
+  TL_CUDA(cudaGetLastError());
+  if (s->profile) TL_CUDA(cudaEventRecord(s->ev[3], e->stream));
+  return TLFEA_OK;
+}
+
 constexpr int TILE_WARPS = 8;
 // Two tilings: one big CTA per SM (large tiles, least element re-staging) or two smaller CTAs per SM
 // (more latency hiding).  TLFEA_TILE_CTAS=1|2 selects; the budget is the row-buffer size in doubles.
@@ -345,6 +478,17 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
   TL_TRY(ensure_pattern(e));
   const bool damp = (e->eta != 0.0 || e->lambda_d != 0.0);
   TL_CUDA(cudaEventRecord(s->ev[0], e->stream));
+  if (ek_supported(s)) {
+    TL_TRY(assemble_ek(s, tangent, damp));
+    if (tangent && s->n_cons_slots > 0) {
+      TL_LAUNCH(k_add_constraint_term, blocks_for(s->n_cons_slots, 256), 256, 0, e->stream, s->n_cons_slots,
+                s->d_cons_slot, s->d_cons_val, s->prm.time_step * s->prm.time_step * s->prm.rho, s->d_H);
+    }
+    TL_CUDA(cudaGetLastError());
+    TL_CUDA(cudaEventRecord(s->ev[1], e->stream));
+    return TLFEA_OK;
+  }
+  if (tangent) TL_TRY(ensure_records(s));
   TL_TRY(launch_gp(e, damp ? s->d_v : nullptr, tangent ? s->d_gp : nullptr, e->d_fe, nullptr, nullptr));
   if (s->profile) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
   if (!tangent) {
@@ -541,6 +685,9 @@ int tlfea_newton_destroy(tlfea_newton *s) {
   cudaStreamSynchronize(s->e->stream);
   dfree(s->d_H);
   dfree(s->d_gp);
+  dfree(s->d_stage);
+  if (s->d_rowdesc) cudaFree(s->d_rowdesc);
+  s->d_rowdesc = nullptr;
   s->tiles.release();
   dfree(s->d_v);
   dfree(s->d_v_prev);
@@ -588,9 +735,7 @@ int tlfea_newton_analyze_sparsity(tlfea_newton *s) {
   TL_TRY(ensure_pattern(e));
   s->nnz = 9 * e->pat.nnz;
   TL_TRY(dmalloc(&s->d_H, (size_t)s->nnz));
-  s->rec_doubles = (e->model == TL_MODEL_MR) ? REC_MR : REC_SVK;
-  // records are sized for the larger layout lazily: reallocated if the material model changes
-  TL_TRY(dmalloc(&s->d_gp, (size_t)e->n_elem * e->Q * s->rec_doubles));
+  s->rec_doubles = 0;  // Gauss-point records (row-gather path only) are allocated on first use
   if (s->n_constraints > 0) {
     TL_CHECK(e->cons_mode != TL_CONS_NONE, "solver has constraints but the element has none set up");
     TL_CHECK(s->n_constraints == e->n_constraint, "n_constraints (%d) != element constraints (%d)", s->n_constraints,
@@ -658,20 +803,9 @@ int tlfea_newton_set_fixed_pattern(tlfea_newton *s, int fixed) {
   return TLFEA_OK;
 }
 
-static int ensure_records(tlfea_newton *s) {
-  const int need = (s->e->model == TL_MODEL_MR) ? REC_MR : REC_SVK;
-  if (need != s->rec_doubles) {
-    dfree(s->d_gp);
-    s->rec_doubles = need;
-    TL_TRY(dmalloc(&s->d_gp, (size_t)s->e->n_elem * s->e->Q * need));
-  }
-  return TLFEA_OK;
-}
-
 int tlfea_newton_assemble(tlfea_newton *s) {
   TL_CHECK(s, "null handle");
   TL_CHECK(s->analyzed, "AnalyzeHessianSparsity must run before assembling");
-  TL_TRY(ensure_records(s));
   TL_TRY(do_assemble(s, true));
   return collect_timing(s, true);
 }
@@ -702,7 +836,6 @@ int tlfea_newton_solve_step(tlfea_newton *s) {
   tlfea_elem *e = s->e;
   TL_CUDA(cudaSetDevice(e->device));
   if (!s->analyzed) TL_TRY(tlfea_newton_analyze_sparsity(s));
-  TL_TRY(ensure_records(s));
   const int64_t n = 3 * (int64_t)e->n_coef;
   const size_t cb = (size_t)e->n_coef * sizeof(double);
   for (int i = 0; i < 3; i++)
@@ -850,7 +983,7 @@ int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset
   return TLFEA_OK;
 }
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode) {
-  TL_CHECK(s && mode >= 0 && mode <= 3, "mode must be 0 (row gather), 1 (tiles), 2 (row gather in tile order) or 3 (staged row gather)");
+  TL_CHECK(s && mode >= 0 && mode <= 4, "mode must be 0..4 (0 row gather, 1 tiles, 2 gather in tile order, 3 staged gather, 4 element kernel + row reduce)");
   s->use_tiles = mode;
   return TLFEA_OK;
 }

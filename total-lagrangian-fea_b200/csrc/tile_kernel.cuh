@@ -61,6 +61,7 @@ struct TileShape {
   }
 };
 
+#define TL_HAVE_CP_ASYNC
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem)),
                "l"(gmem));

@@ -408,4 +408,36 @@ int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int batch
   return TLFEA_OK;
 }
 
+// Morton order of the coefficient rows only (what the row-reduce kernel of ek_kernel.cuh walks).
+int build_row_order(const tlfea_elem *h, int **d_order) {
+  const int n = h->pat.n_coef;
+  cudaStream_t st = h->stream;
+  const int cpn = (h->type == TLFEA_TYPE_T10) ? 1 : 4;
+  unsigned long long *d_mm = nullptr, *k0 = nullptr, *k1 = nullptr;
+  int *v0 = nullptr;
+  TL_TRY(dmalloc(&d_mm, 6));
+  const unsigned long long init[6] = {~0ULL, ~0ULL, ~0ULL, 0, 0, 0};
+  TL_CUDA(cudaMemcpyAsync(d_mm, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  TL_LAUNCH(k_minmax3, 592, 256, 0, st, n, cpn, h->d_xr, h->d_yr, h->d_zr, d_mm);
+  TL_TRY(dmalloc(&k0, (size_t)n));
+  TL_TRY(dmalloc(&k1, (size_t)n));
+  TL_TRY(dmalloc(&v0, (size_t)n));
+  TL_TRY(dmalloc(d_order, (size_t)n));
+  TL_LAUNCH(k_morton, blocks_for(n, 256), 256, 0, st, n, cpn, h->d_xr, h->d_yr, h->d_zr, d_mm, k0, v0);
+  size_t tmp_bytes = 0;
+  TL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k0, k1, v0, *d_order, n, 0, 63, st));
+  void *tmp = nullptr;
+  TL_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+  cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k0, k1, v0, *d_order, n, 0, 63, st);
+  g_launches.fetch_add(1);
+  cudaStreamSynchronize(st);
+  cudaFree(tmp);
+  cudaFree(k0);
+  cudaFree(k1);
+  cudaFree(v0);
+  cudaFree(d_mm);
+  TL_CUDA(e);
+  return TLFEA_OK;
+}
+
 }  // namespace tlfea
