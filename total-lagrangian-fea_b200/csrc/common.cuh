@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <string>
+#include <vector>
 
 #include "../../include/tlfea_b200.h"
 
@@ -14,6 +15,9 @@ namespace tlfea {
 
 extern thread_local std::string g_last_error;
 extern std::atomic<int64_t> g_launches;
+// element handles that are still alive: a solver may be destroyed after its element (garbage collectors
+// finalise in arbitrary order) and must not touch the freed handle then
+bool elem_is_live(const void *h);
 
 inline int fail(int code, const char *fmt, ...) {
   char buf[512];
@@ -168,10 +172,12 @@ struct tlfea_elem {
 namespace tlfea {
 int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int batch, int warps, Tiles *out);
 int build_row_order(const tlfea_elem *h, int **d_order);
+int build_completion_order(const tlfea_elem *h, int chunk, int **d_order, std::vector<int> *chunk_ptr);
 }
 
 struct tlfea_newton {
   tlfea_elem *e = nullptr;
+  int device = 0;
   tlfea::Tiles tiles;
   bool have_tiles = false;
   int use_tiles = 4;  // assembly: 0 row gather, 1 tiles, 2 row gather in tile order, 3 staged row gather, 4 element kernel + row reduce (default where supported)
@@ -182,7 +188,10 @@ struct tlfea_newton {
   double *d_H = nullptr;
   double *d_gp = nullptr;  // per-Gauss-point records
   double *d_stage = nullptr;  // symmetric element block records of the two-phase assembly (ek_kernel.cuh)
-  void *d_rowdesc = nullptr;  // RowDesc[n_coef] in Morton processing order (ek_kernel.cuh)
+  void *d_rowdesc = nullptr;  // RowDesc[n_coef] in processing order (completion order, Morton ties; ek_kernel.cuh)
+  std::vector<int> chunk_ptr;  // rows completed by element chunk k: [chunk_ptr[k], chunk_ptr[k+1])
+  int ek_chunk = 0;            // elements per chunk of the interleaved E/R schedule
+  int *d_tickets = nullptr;    // one ticket counter per chunk
   int rec_doubles = 0;
   double *d_v = nullptr, *d_v_prev = nullptr, *d_lambda = nullptr, *d_g = nullptr, *d_dv = nullptr, *d_r = nullptr;
   double *d_xp = nullptr, *d_yp = nullptr, *d_zp = nullptr;

@@ -49,7 +49,7 @@ struct EKArgs {
   double lambda, mu, eta, lambda_d;
   double c1, c2, c3, c4;  // c1 = h lambda + lambda_d, c2 = c3 = h mu + eta, c4 = h
   double *fe;             // [n_elem][10][3]
-  double *stage;          // [n_elem][55][9] or nullptr (force only)
+  double *stage;          // [n_elem][10][10][9] visit-major block records, or nullptr (force only)
 };
 
 #ifndef TL_HAVE_CP_ASYNC
@@ -66,39 +66,42 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 #endif
 
-constexpr int EK_REC = 26;  // per Gauss point: M(6) | F(9) | dV | P*dV(9) | pad
+constexpr int EK_REC = 9;     // per Gauss point: M(6) | dV | pad(2); odd stride => conflict-free lane writes
+constexpr int EK_GQ = 31;     // stride of the per-(element, point) u / force-partial rows (30 used)
+constexpr int EK_VIS = 90;    // doubles of one visit record: K_ab, b = 0..9
+constexpr int EK_ELEM = 900;  // doubles of one element record: [a][b][9]
 
 template <int G, bool DAMP>
 struct EKShape {
-  static constexpr int H_D = G * 150;                  // gradN of a group
-  static constexpr int DJ_D = (G * 5 + 1) / 2 * 2;     // detJ of a group (even => 16-byte aligned sections)
-  static constexpr int X_D = G * 30;                   // nodal coordinates [el][a][3]
-  static constexpr int EC_D = G * 5;                   // G*10 ints
-  static constexpr int U_D = 150;                      // u = F h of the element in flight
-  static constexpr int FP_D = 90;                      // force partials [3][30]
+  static constexpr int H_D = G * 150;               // gradN of a group
+  static constexpr int DJ_D = (G * 5 + 1) / 2 * 2;  // detJ of a group
+  static constexpr int X_D = G * 30;                // nodal coordinates [el][a][3]
+  static constexpr int EC_D = (G * 5 + 1) / 2 * 2;  // G*10 ints
+  static constexpr int U_D = G * 5 * EK_GQ;         // u = F h per (element, point)
   static constexpr int REC_D = G * 5 * EK_REC;
-  static constexpr int K_D = 496;                      // symmetric block record
+  static constexpr int K_D = 2 * EK_ELEM;           // records of the element pair in flight; also the force partials
   static constexpr int OFF_H = 0;
   static constexpr int OFF_DJ = OFF_H + 2 * H_D;
   static constexpr int OFF_X = OFF_DJ + 2 * DJ_D;
   static constexpr int OFF_V = OFF_X + 2 * X_D;
   static constexpr int OFF_EC = OFF_V + (DAMP ? 2 * X_D : 0);
-  static constexpr int OFF_U = OFF_EC + 2 * ((EC_D + 1) / 2 * 2);
-  static constexpr int OFF_FP = OFF_U + U_D;
-  static constexpr int OFF_REC = OFF_FP + FP_D;
-  static constexpr int OFF_K = OFF_REC + REC_D;
-  static constexpr int WARP_D = (OFF_K + K_D + 1) / 2 * 2;
+  static constexpr int OFF_U = OFF_EC + 2 * EC_D;
+  static constexpr int OFF_REC = OFF_U + (U_D + 1) / 2 * 2;
+  static constexpr int OFF_K = OFF_REC + (REC_D + 1) / 2 * 2;
+  static constexpr int WARP_D = OFF_K + K_D;
+  static_assert(G * 5 * EK_GQ <= K_D, "force partials alias the record staging");
   static constexpr size_t smem_bytes(int warps) { return (size_t)warps * WARP_D * sizeof(double); }
 };
 
 template <int G, int W, bool DAMP, bool TANGENT>
 __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
   using Sh = EKShape<G, DAMP>;
-  constexpr int ELEM_D = SymLayout<10>::ELEM_DOUBLES;  // 495
+  static_assert(G * 5 <= 32 && G % 2 == 0, "a group is G*5 Gauss-point lanes and G/2 element pairs");
   extern __shared__ __align__(16) double ek_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *wb = ek_smem + (size_t)warp * Sh::WARP_D;
-  double *s_u = wb + Sh::OFF_U, *s_fp = wb + Sh::OFF_FP, *s_rec = wb + Sh::OFF_REC, *s_k = wb + Sh::OFF_K;
+  double *s_u = wb + Sh::OFF_U, *s_rec = wb + Sh::OFF_REC, *s_k = wb + Sh::OFF_K;
+  double *s_fp = s_k;  // force partials live in the record staging before the block step needs it
 
   const int n_groups = (p.n_elem + G - 1) / G;
   const int gstride = gridDim.x * W;
@@ -109,7 +112,7 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
     if (grp >= n_groups) return;
     const int e0 = grp * G;
     const int n_int = min(G, p.n_elem - e0) * 10;
-    int *dst = reinterpret_cast<int *>(wb + Sh::OFF_EC + buf * ((Sh::EC_D + 1) / 2 * 2));
+    int *dst = reinterpret_cast<int *>(wb + Sh::OFF_EC + buf * Sh::EC_D);
     const int *src = p.ecoef + (int64_t)e0 * 10;
     for (int i = lane; i < n_int / 2; i += 32) cp_async8(dst + 2 * i, src + 2 * i);
   };
@@ -123,7 +126,7 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
     double *dj = wb + Sh::OFF_DJ + buf * Sh::DJ_D;
     const double *sj = p.detJ + (int64_t)e0 * 5;
     for (int i = lane; i < ne * 5; i += 32) cp_async8(dj + i, sj + i);
-    const int *ec = reinterpret_cast<const int *>(wb + Sh::OFF_EC + buf * ((Sh::EC_D + 1) / 2 * 2));
+    const int *ec = reinterpret_cast<const int *>(wb + Sh::OFF_EC + buf * Sh::EC_D);
     double *dx = wb + Sh::OFF_X + buf * Sh::X_D;
     for (int i = lane; i < ne * 10; i += 32) {
       const int c = ec[i];
@@ -148,8 +151,24 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
   issue_data(g_first, 0);
   cp_async_commit();
 
-  const int a = (lane < 30) ? lane % 10 : lane - 30;
-  const int g = lane / 10;  // 0..2 work, 3 = the two spare lanes
+  // block step: lane = (element of the pair, 2x2 tile (I, J), I <= J, of the 5x5 tile grid)
+  const int el2 = (lane >= 15) ? 1 : 0;
+  int tile = lane - 15 * el2;
+  if (tile > 14) tile = 14;  // lanes 30, 31 shadow the last tile and never store
+  const bool lane_on = lane < 30;
+  int tI, tJ;
+  if (tile < 5) {
+    tI = 0; tJ = tile;
+  } else if (tile < 9) {
+    tI = 1; tJ = tile - 4;
+  } else if (tile < 12) {
+    tI = 2; tJ = tile - 7;
+  } else if (tile < 14) {
+    tI = 3; tJ = tile - 9;
+  } else {
+    tI = 4; tJ = 4;
+  }
+  const int a1 = 2 * tI, b1 = 2 * tJ;
 
   int it = 0;
   for (int grp = g_first; grp < n_groups; grp += gstride, it++) {
@@ -220,127 +239,153 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
         for (int i = 0; i < 3; i++)
 #pragma unroll
           for (int j = 0; j < 3; j++) {
-            double a1 = 0.0, a2 = 0.0;
+            double s1 = 0.0, s2 = 0.0;
 #pragma unroll
             for (int k = 0; k < 3; k++) {
-              a1 += Fd[k][i] * F[k][j];
-              a2 += F[k][i] * Fd[k][j];
+              s1 += Fd[k][i] * F[k][j];
+              s2 += F[k][i] * Fd[k][j];
             }
-            Ed[i][j] = 0.5 * (a1 + a2);
+            Ed[i][j] = 0.5 * (s1 + s2);
           }
         const double trEd = Ed[0][0] + Ed[1][1] + Ed[2][2];
 #pragma unroll
         for (int i = 0; i < 3; i++)
 #pragma unroll
           for (int j = 0; j < 3; j++) {
-            double s = 0.0;
+            double sv = 0.0;
 #pragma unroll
             for (int k = 0; k < 3; k++)
-              s += F[i][k] * (2.0 * p.eta * Ed[k][j] + ((k == j) ? p.lambda_d * trEd : 0.0));
-            P[i][j] += s;
+              sv += F[i][k] * (2.0 * p.eta * Ed[k][j] + ((k == j) ? p.lambda_d * trEd : 0.0));
+            P[i][j] += sv;
           }
       }
-      double *r = s_rec + lane * EK_REC;
-      const double sI = p.c4 * dV * (p.lambda * trE - p.mu);
-      const double cf = p.c3 * dV;
-      r[0] = cf * FFT[0][0] + sI;
-      r[1] = cf * FFT[0][1];
-      r[2] = cf * FFT[0][2];
-      r[3] = cf * FFT[1][1] + sI;
-      r[4] = cf * FFT[1][2];
-      r[5] = cf * FFT[2][2] + sI;
 #pragma unroll
       for (int i = 0; i < 3; i++)
 #pragma unroll
-        for (int j = 0; j < 3; j++) {
-          r[6 + i * 3 + j] = F[i][j];
-          r[16 + i * 3 + j] = P[i][j] * dV;
+        for (int j = 0; j < 3; j++) P[i][j] *= dV;
+      // element-force partials of this point and u_a = F h_a for the block step
+      double *fpq = s_fp + lane * EK_GQ;
+      double *uq = s_u + lane * EK_GQ;
+#pragma unroll
+      for (int aa = 0; aa < 10; aa++) {
+        const double ha[3] = {hq[aa], hq[10 + aa], hq[20 + aa]};
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+          fpq[aa * 3 + i] = P[i][0] * ha[0] + P[i][1] * ha[1] + P[i][2] * ha[2];
+          if (TANGENT) uq[i * 10 + aa] = F[i][0] * ha[0] + F[i][1] * ha[1] + F[i][2] * ha[2];
         }
-      r[15] = dV;
+      }
+      if (TANGENT) {
+        double *r = s_rec + lane * EK_REC;
+        const double sI = p.c4 * dV * (p.lambda * trE - p.mu);
+        const double cf = p.c3 * dV;
+        r[0] = cf * FFT[0][0] + sI;
+        r[1] = cf * FFT[0][1];
+        r[2] = cf * FFT[0][2];
+        r[3] = cf * FFT[1][1] + sI;
+        r[4] = cf * FFT[1][2];
+        r[5] = cf * FFT[2][2] + sI;
+        r[6] = dV;
+      }
+    }
+    __syncwarp();
+    // element forces: sum of the 5 point partials in fixed order, one coalesced 240-byte row per element
+    for (int el = 0; el < ne; el++) {
+      if (lane < 30) {
+        const double *fq = s_fp + el * 5 * EK_GQ + lane;
+        p.fe[(int64_t)(e0 + el) * 30 + lane] =
+            (((fq[0] + fq[EK_GQ]) + fq[2 * EK_GQ]) + fq[3 * EK_GQ]) + fq[4 * EK_GQ];
+      }
     }
     __syncwarp();
 
-    // ------------------------------------------------------------ block step, element by element
-    for (int el = 0; el < ne; el++) {
-      const int e = e0 + el;
-      const double *he = s_h + el * 150;
-      const double *re = s_rec + el * 5 * EK_REC;
-      double ha[5][3];
+    // ------------------------------------------------------------ block step, two elements at a time
+    if (TANGENT) {
+      for (int pr = 0; pr < ne; pr += 2) {
+        const int el = min(pr + el2, ne - 1);  // odd tail: the second half shadows the first and never stores
+        const bool on = lane_on && (pr + el2 < ne);
+        const double *he = s_h + el * 150;
+        const double *ue = s_u + el * 5 * EK_GQ;
+        const double *re = s_rec + el * 5 * EK_REC;
+        double A[4][9], Gs[4][6];
 #pragma unroll
-      for (int q = 0; q < 5; q++)
+        for (int t = 0; t < 4; t++) {
 #pragma unroll
-        for (int j = 0; j < 3; j++) ha[q][j] = he[q * 30 + j * 10 + a];
-      // u_a(q) = F_q h_a(q) and the force partials: point q is done by lane group q/2
-      double fp[3] = {0.0, 0.0, 0.0};
+          for (int i = 0; i < 9; i++) A[t][i] = 0.0;
 #pragma unroll
-      for (int q = 0; q < 5; q++) {
-        if (q / 2 == g) {
-          const double *rq = re + q * EK_REC;
-#pragma unroll
-          for (int i = 0; i < 3; i++) {
-            s_u[q * 30 + i * 10 + a] = rq[6 + i * 3] * ha[q][0] + rq[7 + i * 3] * ha[q][1] + rq[8 + i * 3] * ha[q][2];
-            fp[i] += rq[16 + i * 3] * ha[q][0] + rq[17 + i * 3] * ha[q][1] + rq[18 + i * 3] * ha[q][2];
-          }
+          for (int i = 0; i < 6; i++) Gs[t][i] = 0.0;
         }
-      }
-      if (g < 3) {
-#pragma unroll
-        for (int i = 0; i < 3; i++) s_fp[g * 30 + a * 3 + i] = fp[i];
-      }
-      __syncwarp();
-      if (lane < 30) p.fe[(int64_t)e * 30 + lane] = (s_fp[lane] + s_fp[30 + lane]) + s_fp[60 + lane];
-      if (TANGENT) {
-        double ua[5][3];
 #pragma unroll
         for (int q = 0; q < 5; q++) {
-          const double dV = re[q * EK_REC + 15];
+          const double *hq = he + q * 30, *uq = ue + q * EK_GQ, *rq = re + q * EK_REC;
+          const double dV = rq[6];
+          double ha[2][3], hb[2][3], ua[2][3], ub[2][3], M[6];
 #pragma unroll
-          for (int i = 0; i < 3; i++) ua[q][i] = s_u[q * 30 + i * 10 + a] * dV;
+          for (int j = 0; j < 3; j++) {
+            ha[0][j] = hq[j * 10 + a1];
+            ha[1][j] = hq[j * 10 + a1 + 1];
+            hb[0][j] = hq[j * 10 + b1];
+            hb[1][j] = hq[j * 10 + b1 + 1];
+            ua[0][j] = uq[j * 10 + a1] * dV;
+            ua[1][j] = uq[j * 10 + a1 + 1] * dV;
+            ub[0][j] = uq[j * 10 + b1];
+            ub[1][j] = uq[j * 10 + b1 + 1];
+          }
+#pragma unroll
+          for (int i = 0; i < 6; i++) M[i] = rq[i];
+#pragma unroll
+          for (int ta = 0; ta < 2; ta++)
+#pragma unroll
+            for (int tb = 0; tb < 2; tb++) {
+              const int t = ta * 2 + tb;
+              const double hab = ha[ta][0] * hb[tb][0] + ha[ta][1] * hb[tb][1] + ha[ta][2] * hb[tb][2];
+#pragma unroll
+              for (int i = 0; i < 3; i++)
+#pragma unroll
+                for (int c = 0; c < 3; c++) A[t][i * 3 + c] += ua[ta][i] * ub[tb][c];
+#pragma unroll
+              for (int i = 0; i < 6; i++) Gs[t][i] += hab * M[i];
+            }
         }
+        // h K_ab + C_ab = c1 A + c2 A^T + c4 mu tr(A) I + G      (SVK.cuh:35-55, FEAT10DataFunc.cuh:695-762)
+        if (on) {
+          double *ke = s_k + el2 * EK_ELEM;
 #pragma unroll
-        for (int s = 0; s < 2; s++) {
-          const int d = 2 * g + s;
-          int b = a + d;
-          if (b >= 10) b -= 10;
-          double A[9], Gs[6];
+          for (int ta = 0; ta < 2; ta++)
 #pragma unroll
-          for (int i = 0; i < 9; i++) A[i] = 0.0;
+            for (int tb = 0; tb < 2; tb++) {
+              const int t = ta * 2 + tb;
+              const double dg = p.c4 * p.mu * (A[t][0] + A[t][4] + A[t][8]);
+              double k[9];
+              k[0] = p.c1 * A[t][0] + p.c2 * A[t][0] + Gs[t][0] + dg;
+              k[1] = p.c1 * A[t][1] + p.c2 * A[t][3] + Gs[t][1];
+              k[2] = p.c1 * A[t][2] + p.c2 * A[t][6] + Gs[t][2];
+              k[3] = p.c1 * A[t][3] + p.c2 * A[t][1] + Gs[t][1];
+              k[4] = p.c1 * A[t][4] + p.c2 * A[t][4] + Gs[t][3] + dg;
+              k[5] = p.c1 * A[t][5] + p.c2 * A[t][7] + Gs[t][4];
+              k[6] = p.c1 * A[t][6] + p.c2 * A[t][2] + Gs[t][2];
+              k[7] = p.c1 * A[t][7] + p.c2 * A[t][5] + Gs[t][4];
+              k[8] = p.c1 * A[t][8] + p.c2 * A[t][8] + Gs[t][5] + dg;
+              const int aa = a1 + ta, bb = b1 + tb;
+              double *d1 = ke + (aa * 10 + bb) * 9;
 #pragma unroll
-          for (int i = 0; i < 6; i++) Gs[i] = 0.0;
+              for (int i = 0; i < 9; i++) d1[i] = k[i];
+              if (tI != tJ) {  // K_ba = K_ab^T
+                double *d2 = ke + (bb * 10 + aa) * 9;
 #pragma unroll
-          for (int q = 0; q < 5; q++) {
-            const double hb0 = he[q * 30 + b], hb1 = he[q * 30 + 10 + b], hb2 = he[q * 30 + 20 + b];
-            const double ub0 = s_u[q * 30 + b], ub1 = s_u[q * 30 + 10 + b], ub2 = s_u[q * 30 + 20 + b];
-            const double2 *m2 = reinterpret_cast<const double2 *>(re + q * EK_REC);
-            const double2 m01 = m2[0], m23 = m2[1], m45 = m2[2];
-            const double hab = ha[q][0] * hb0 + ha[q][1] * hb1 + ha[q][2] * hb2;
-            A[0] += ua[q][0] * ub0; A[1] += ua[q][0] * ub1; A[2] += ua[q][0] * ub2;
-            A[3] += ua[q][1] * ub0; A[4] += ua[q][1] * ub1; A[5] += ua[q][1] * ub2;
-            A[6] += ua[q][2] * ub0; A[7] += ua[q][2] * ub1; A[8] += ua[q][2] * ub2;
-            Gs[0] += hab * m01.x; Gs[1] += hab * m01.y; Gs[2] += hab * m23.x;
-            Gs[3] += hab * m23.y; Gs[4] += hab * m45.x; Gs[5] += hab * m45.y;
-          }
-          // h K_ab + C_ab = c1 A + c2 A^T + c4 mu tr(A) I + G      (SVK.cuh:35-55, FEAT10DataFunc.cuh:695-762)
-          const double dg = p.c4 * p.mu * (A[0] + A[4] + A[8]);
-          const bool on = (g < 3) && (d < 5 || a < 5);
-          if (on) {
-            double *k = s_k + ((d < 5) ? (a * 5 + d) : (50 + a)) * 9;
-            k[0] = p.c1 * A[0] + p.c2 * A[0] + Gs[0] + dg;
-            k[1] = p.c1 * A[1] + p.c2 * A[3] + Gs[1];
-            k[2] = p.c1 * A[2] + p.c2 * A[6] + Gs[2];
-            k[3] = p.c1 * A[3] + p.c2 * A[1] + Gs[1];
-            k[4] = p.c1 * A[4] + p.c2 * A[4] + Gs[3] + dg;
-            k[5] = p.c1 * A[5] + p.c2 * A[7] + Gs[4];
-            k[6] = p.c1 * A[6] + p.c2 * A[2] + Gs[2];
-            k[7] = p.c1 * A[7] + p.c2 * A[5] + Gs[4];
-            k[8] = p.c1 * A[8] + p.c2 * A[8] + Gs[5] + dg;
-          }
+                for (int i = 0; i < 3; i++)
+#pragma unroll
+                  for (int c = 0; c < 3; c++) d2[c * 3 + i] = k[i * 3 + c];
+              }
+            }
         }
         __syncwarp();
-        double *dst = p.stage + (int64_t)e * ELEM_D;
-        for (int i = lane; i < ELEM_D; i += 32) dst[i] = s_k[i];
+        // the pair's records are contiguous in global memory: one coalesced burst
+        const int npair = min(2, ne - pr);
+        double *dst = p.stage + (int64_t)(e0 + pr) * EK_ELEM;
+        for (int i = lane; i < npair * EK_ELEM; i += 32) dst[i] = s_k[i];
+        __syncwarp();
       }
-      __syncwarp();
     }
   }
   cp_async_wait_all();
@@ -364,10 +409,12 @@ struct RKArgs {
   double *H;
   double *f_int;
   int row_stride;  // doubles of shared memory per warp
+  int *counter;    // ticket counter, zeroed before the launch
 };
 
 constexpr int RK_WARPS = 8;
-constexpr int RK_U = 6;  // visits in flight per warp
+constexpr int RK_U = 5;  // visits in flight per warp
+constexpr int RK_T = 4;  // rows per ticket
 
 __global__ void k_row_desc(int n, const int *__restrict__ order, const int *__restrict__ off,
                            const int *__restrict__ inc_ptr, RowDesc *desc) {
@@ -384,156 +431,136 @@ __global__ void k_row_desc(int n, const int *__restrict__ order, const int *__re
   desc[i] = d;
 }
 
-// source of the three values lane (block bi, matrix row i) adds for a visit with local shape function a:
-// packed (offset in the element record) | stride << 12 | local column node b << 16
-template <int S>
-__device__ __forceinline__ unsigned rk_source(int a, int bi, int i) {
-  constexpr int D = SymLayout<S>::D;
-  int b, pr;
-  bool tr;
-  if (bi < D) {  // own diagonal d = bi
-    b = a + bi;
-    if (b >= S) b -= S;
-    pr = a * D + bi;
-    tr = false;
-  } else if (bi == D) {  // the half diagonal
-    b = a + D;
-    if (b >= S) b -= S;
-    tr = (a >= D);
-    pr = S * D + (tr ? a - D : a);
-  } else {  // stored by the partner: K_ab = K_ba^T
-    const int d = bi - D;
-    b = a - d;
-    if (b < 0) b += S;
-    pr = b * D + d;
-    tr = true;
-  }
-  const unsigned off = (unsigned)(pr * 9 + (tr ? i : 3 * i));
-  return off | ((tr ? 3u : 1u) << 12) | ((unsigned)b << 16);
-}
-
 template <int S>
 __global__ void __launch_bounds__(RK_WARPS * 32, 3) rk_kernel(RKArgs p) {
-  static_assert(3 * S <= 32, "one lane per (block, matrix row)");
-  constexpr int ELEM_D = SymLayout<S>::ELEM_DOUBLES;
+  static_assert(S * 9 <= 96, "a visit record is read as three coalesced 32-double rows");
+  constexpr int VIS = S * 9;
   extern __shared__ double rk_smem[];
-  __shared__ unsigned s_tab[S * 32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *rowbuf = rk_smem + (size_t)warp * p.row_stride;
-  for (int t = threadIdx.x; t < S * 32; t += RK_WARPS * 32) {
-    const int a = t >> 5, l = t & 31;
-    s_tab[t] = (l < 3 * S) ? rk_source<S>(a, l / 3, l % 3) : 0u;
+  // lane l adds doubles l, l+32, l+64 of every visit record: block b = idx / 9, entry idx % 9
+  int lb[3], lk[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const int idx = min(lane + 32 * k, VIS - 1);
+    lb[k] = idx / 9;
+    lk[k] = idx - 9 * lb[k];
   }
-  __syncthreads();
-  const bool lane_on = lane < 3 * S;
-  const int li3 = 3 * (lane % 3);
+  const bool on2 = lane + 64 < VIS;
 
-  const int n_chunks = (p.n_coef + RK_WARPS - 1) / RK_WARPS;
-  // chunk = 16 consecutive rows in processing order, one per warp; the warp<->row assignment rotates with
-  // the chunk so the periodic hub (vertex) rows of a Morton order spread over all warps.  All resident
-  // blocks work on neighbouring chunks => the element records they share are still in L2.
-  auto row_index = [&](int ch, int it) { return ch * RK_WARPS + ((warp + it) & (RK_WARPS - 1)); };
-  auto load_desc = [&](int ch, int it, int4 &d0, int &nv) {
-    const int ri = row_index(ch, it);
-    if (ch < n_chunks && ri < p.n_coef) {
-      const int4 *q = reinterpret_cast<const int4 *>(p.desc + ri);
-      d0 = q[0];
-      nv = reinterpret_cast<const int *>(q + 1)[0];
-    } else {
-      d0 = make_int4(0, 0, 0, 0);
-      nv = -1;
+  // Dynamic schedule: a warp draws tickets of RK_T consecutive rows (processing order) from a global counter,
+  // so every resident warp works at the same frontier of the Morton order and the element records the
+  // rows share are still in L2 when the next row needs them (a static grid-stride schedule drifts apart
+  // on long runs).  The next ticket and the current ticket's row descriptors / visit lists are fetched early.
+  const int n_tickets = (p.n_coef + RK_T - 1) / RK_T;
+  int t_next = 0;
+  if (lane == 0) t_next = atomicAdd(p.counter, 1);
+  while (true) {
+    const int tk = __shfl_sync(0xffffffffu, t_next, 0);
+    if (tk >= n_tickets) break;
+    if (lane == 0) t_next = atomicAdd(p.counter, 1);
+    // RK_T descriptors = RK_T*8 ints: one coalesced load
+    int dword = 0;
+    {
+      const int64_t w = (int64_t)tk * RK_T * 8 + lane;
+      if (lane < RK_T * 8 && w < (int64_t)p.n_coef * 8) dword = reinterpret_cast<const int *>(p.desc)[w];
     }
-  };
-  int ch = blockIdx.x;
-  int4 d0;
-  int nv;
-  int it = 0;
-  load_desc(ch, it, d0, nv);
-  int ea_l = (nv > lane) ? p.inc_ea[d0.w + lane] : 0;  // visits lane, (lane + 32 handled in the loop)
-  for (; ch < n_chunks; ch += gridDim.x, it++) {
-    const int row = d0.x, rs = d0.y, deg = d0.z, vb = d0.w, nvis = nv;
-    const int ea_cur = ea_l;
-    // prefetch the next row's descriptor and its visit list
-    load_desc(ch + gridDim.x, it + 1, d0, nv);
-    if (nvis < 0) continue;
-    // internal force of this coefficient: element contributions fetched 10 at a time by lanes (visit, component),
-    // parked in shared memory and summed by lanes 0..2 in ascending element order
+    int ea_r[RK_T];
+#pragma unroll
+    for (int r = 0; r < RK_T; r++) {
+      const int vb_r = __shfl_sync(0xffffffffu, dword, r * 8 + 3), nv_r = __shfl_sync(0xffffffffu, dword, r * 8 + 4);
+      ea_r[r] = (lane < nv_r) ? p.inc_ea[vb_r + lane] : 0;
+    }
+#pragma unroll
+  for (int r = 0; r < RK_T; r++) {
+    if (tk * RK_T + r >= p.n_coef) break;
+    const int row = __shfl_sync(0xffffffffu, dword, r * 8 + 0), rs = __shfl_sync(0xffffffffu, dword, r * 8 + 1);
+    const int deg = __shfl_sync(0xffffffffu, dword, r * 8 + 2), vb = __shfl_sync(0xffffffffu, dword, r * 8 + 3);
+    const int nvis = __shfl_sync(0xffffffffu, dword, r * 8 + 4);
+    const int ea_cur = ea_r[r];
+    // Every global load of the row's first phase is issued before anything waits on one:
+    // the first batch of block values + slots, the first 10 element forces, the mass row.
     double *fbuf = rowbuf + p.row_stride - 32;
-    double f = 0.0;
-    {
-      const int fv = lane / 3, fc = lane - 3 * fv;
-      for (int v0 = 0; v0 < nvis; v0 += 10) {
-        const int v = v0 + fv;
-        const int ea_s = __shfl_sync(0xffffffffu, ea_cur, v & 31);
-        const int ea = (v < 32) ? ea_s : ((v < nvis) ? p.inc_ea[vb + v] : 0);
-        if (lane < 30 && v < nvis) fbuf[lane] = p.fe[(int64_t)ea * 3 + fc];
-        __syncwarp();
-        if (lane < 3) {
-          const int m = min(10, nvis - v0);
-          for (int k = 0; k < m; k++) f += fbuf[3 * k + lane];
-        }
-        __syncwarp();
-      }
-    }
-    // H row starts from the mass term: H(3i+d,3j+d) = M_ij / h   (SyncedNewton.cu:213-259)
-    {
-      double m[3];
-#pragma unroll
-      for (int k = 0; k < 3; k++) m[k] = (lane + 32 * k < deg) ? p.mass[rs + lane + 32 * k] * p.inv_h : 0.0;
-      for (int idx = lane; idx < deg * 9; idx += 32) rowbuf[idx] = 0.0;
-      __syncwarp();
-#pragma unroll
-      for (int k = 0; k < 3; k++) {
-        const int sl = lane + 32 * k;
-        if (sl < deg) {
-          rowbuf[sl * 9] = m[k];
-          rowbuf[sl * 9 + 4] = m[k];
-          rowbuf[sl * 9 + 8] = m[k];
-        }
-      }
-      for (int sl = lane + 96; sl < deg; sl += 32) {  // very long rows
-        const double mm = p.mass[rs + sl] * p.inv_h;
-        rowbuf[sl * 9] = mm;
-        rowbuf[sl * 9 + 4] = mm;
-        rowbuf[sl * 9 + 8] = mm;
-      }
-    }
-    __syncwarp();
-    for (int v0 = 0; v0 < nvis; v0 += RK_U) {
-      double val[RK_U][3];
-      int dst[RK_U];
+    double val[RK_U][3];
+    unsigned sl[RK_U][3];
+    auto load_batch = [&](int v0) {
 #pragma unroll
       for (int u = 0; u < RK_U; u++) {
         const int v = v0 + u;
-        dst[u] = -1;
         if (v < nvis) {
-          const int ea = (v < 32) ? __shfl_sync(0xffffffffu, ea_cur, v & 31) : p.inc_ea[vb + v];
-          if (lane_on) {
-            const int e = ea / S, a = ea - e * S;
-            const unsigned t = s_tab[a * 32 + lane];
-            const double *src = p.stage + (int64_t)e * ELEM_D + (t & 0xfffu);
-            const int st = (t >> 12) & 3;
-            val[u][0] = src[0];
-            val[u][1] = src[st];
-            val[u][2] = src[2 * st];
-            dst[u] = (int)p.slot[(int64_t)(vb + v) * S + (t >> 16)] * 9 + li3;
+          const int ea_s = __shfl_sync(0xffffffffu, ea_cur, v & 31);
+          const int ea = (v < 32) ? ea_s : p.inc_ea[vb + v];
+          const double *src = p.stage + (int64_t)ea * VIS + lane;  // record of visit (e, a): [b][9], contiguous
+          const uint16_t *ss = p.slot + (int64_t)(vb + v) * S;
+          val[u][0] = src[0];
+          val[u][1] = src[32];
+          sl[u][0] = ss[lb[0]];
+          sl[u][1] = ss[lb[1]];
+          if (on2) {
+            val[u][2] = src[64];
+            sl[u][2] = ss[lb[2]];
           }
         }
       }
-      if (v0 == 0) ea_l = (nv > lane) ? p.inc_ea[d0.w + lane] : 0;  // next row's visits, in flight early
+    };
+    const int fv = lane / 3, fc = lane - 3 * fv;
+    auto load_force = [&](int v0) {
+      const int v = v0 + fv;
+      const int ea_s = __shfl_sync(0xffffffffu, ea_cur, v & 31);
+      const int ea = (v < 32) ? ea_s : ((v < nvis) ? p.inc_ea[vb + v] : 0);
+      return (lane < 30 && v < nvis) ? p.fe[(int64_t)ea * 3 + fc] : 0.0;
+    };
+    load_batch(0);
+    double fe0 = load_force(0);
+    double m[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) m[k] = (lane + 32 * k < deg) ? p.mass[rs + lane + 32 * k] : 0.0;
+    for (int idx = lane; idx < deg * 9; idx += 32) rowbuf[idx] = 0.0;
+    __syncwarp();
+    // internal force of this coefficient: lanes (visit, component) park 10 element contributions at a time in
+    // shared memory, lanes 0..2 add them in ascending element order
+    double f = 0.0;
+    for (int v0 = 0; v0 < nvis; v0 += 10) {
+      if (v0 > 0) fe0 = load_force(v0);
+      if (lane < 30) fbuf[lane] = fe0;
+      __syncwarp();
+      if (lane < 3) {
+        const int mm = min(10, nvis - v0);
+        for (int k = 0; k < mm; k++) f += fbuf[3 * k + lane];
+      }
+      __syncwarp();
+    }
+    // H row starts from the mass term: H(3i+d,3j+d) = M_ij / h   (SyncedNewton.cu:213-259)
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const int s2 = lane + 32 * k;
+      if (s2 < deg) {
+        const double mm = m[k] * p.inv_h;
+        rowbuf[s2 * 9] = mm;
+        rowbuf[s2 * 9 + 4] = mm;
+        rowbuf[s2 * 9 + 8] = mm;
+      }
+    }
+    for (int s2 = lane + 96; s2 < deg; s2 += 32) {  // very long rows
+      const double mm = p.mass[rs + s2] * p.inv_h;
+      rowbuf[s2 * 9] = mm;
+      rowbuf[s2 * 9 + 4] = mm;
+      rowbuf[s2 * 9 + 8] = mm;
+    }
+    __syncwarp();
+    for (int v0 = 0; v0 < nvis; v0 += RK_U) {
+      if (v0 > 0) load_batch(v0);
       // ordered accumulation: one visit at a time; the lanes of one visit hit distinct entries
 #pragma unroll
       for (int u = 0; u < RK_U; u++) {
-        if (dst[u] >= 0) {
-          double *q = rowbuf + dst[u];
-          q[0] += val[u][0];
-          q[1] += val[u][1];
-          q[2] += val[u][2];
+        if (v0 + u < nvis) {
+          rowbuf[sl[u][0] * 9 + lk[0]] += val[u][0];
+          rowbuf[sl[u][1] * 9 + lk[1]] += val[u][1];
+          if (on2) rowbuf[sl[u][2] * 9 + lk[2]] += val[u][2];
         }
         __syncwarp();
       }
     }
-    if (nvis == 0) ea_l = (nv > lane) ? p.inc_ea[d0.w + lane] : 0;
     if (lane < 3) p.f_int[(int64_t)row * 3 + lane] = f;
     // stream the finished block row out as three scalar CSR rows of length 3*deg
     const int64_t base = 9 * (int64_t)rs;
@@ -547,6 +574,7 @@ __global__ void __launch_bounds__(RK_WARPS * 32, 3) rk_kernel(RKArgs p) {
       }
     }
     __syncwarp();
+  }
   }
 }
 

@@ -4,6 +4,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
+#include <set>
 #include <vector>
 
 #include "ancf.cuh"
@@ -13,6 +15,19 @@
 namespace tlfea {
 thread_local std::string g_last_error;
 std::atomic<int64_t> g_launches{0};
+static std::mutex g_live_mu;
+static std::set<const void *> g_live;
+bool elem_is_live(const void *h) {
+  std::lock_guard<std::mutex> lk(g_live_mu);
+  return g_live.count(h) != 0;
+}
+static void elem_set_live(const void *h, bool live) {
+  std::lock_guard<std::mutex> lk(g_live_mu);
+  if (live)
+    g_live.insert(h);
+  else
+    g_live.erase(h);
+}
 
 // ---------------------------------------------------------------------------
 // FEAT10 reference gradients: dn_du_pre_kernel (FEAT10Data.cu:97-204)
@@ -315,12 +330,14 @@ int tlfea_elem_create(int type, int n_elem, int n_nodes, int device, tlfea_elem 
   TL_TRY(dmalloc(&h->d_fe, ne * h->S * 3));
   TL_CUDA(cudaMemsetAsync(h->d_f_int, 0, 3 * nc * sizeof(double), h->stream));
   TL_CUDA(cudaMemsetAsync(h->d_f_ext, 0, 3 * nc * sizeof(double), h->stream));
+  elem_set_live(h, true);
   *out = h;
   return TLFEA_OK;
 }
 
 int tlfea_elem_destroy(tlfea_elem *h) {
   if (!h) return TLFEA_OK;
+  elem_set_live(h, false);
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   dfree(h->d_conn);

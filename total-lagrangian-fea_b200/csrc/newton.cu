@@ -275,7 +275,7 @@ struct EKCfg {
 };
 static EKCfg ek_cfg() {
   static EKCfg c = [] {
-    EKCfg t{5, 8};
+    EKCfg t{6, 5};
     const char *e = getenv("TLFEA_EK_CFG");  // "65" = groups of 6, 5 warps ... (tuning aid)
     if (e && strlen(e) == 2) t = EKCfg{e[0] - '0', e[1] - '0'};
     return t;
@@ -292,7 +292,11 @@ template <int G, int W, bool DAMP, bool TANGENT>
 static int launch_ek_t(tlfea_elem *e, const EKArgs &a) {
   const size_t smem = EKShape<G, DAMP>::smem_bytes(W);
   TL_CHECK(smem <= 227 * 1024, "element kernel configuration needs %zu bytes of shared memory", smem);
-  TL_CUDA(cudaFuncSetAttribute(ek_kernel<G, W, DAMP, TANGENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static thread_local int attr_dev = -1;  // the opt-in is per function and device: set it once
+  if (attr_dev != e->device) {
+    TL_CUDA(cudaFuncSetAttribute(ek_kernel<G, W, DAMP, TANGENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_dev = e->device;
+  }
   const int n_groups = (a.n_elem + G - 1) / G;
   const int grid = std::max(1, std::min(148, (n_groups + W - 1) / W));
   TL_LAUNCH((ek_kernel<G, W, DAMP, TANGENT>), grid, W * 32, smem, e->stream, a);
@@ -303,22 +307,37 @@ static int launch_ek_t(tlfea_elem *e, const EKArgs &a) {
 template <bool DAMP, bool TANGENT>
 static int launch_ek_cfg(tlfea_elem *e, const EKArgs &a) {
   const EKCfg c = ek_cfg();
-  if (DAMP) return launch_ek_t<5, 7, DAMP, TANGENT>(e, a);
-  if (c.g == 6 && c.w == 7) return launch_ek_t<6, 7, DAMP, TANGENT>(e, a);
-  if (c.g == 6 && c.w == 6) return launch_ek_t<6, 6, DAMP, TANGENT>(e, a);
-  if (c.g == 4 && c.w == 9) return launch_ek_t<4, 9, DAMP, TANGENT>(e, a);
-  if (c.g == 3 && c.w == 9) return launch_ek_t<3, 9, DAMP, TANGENT>(e, a);
-  return launch_ek_t<5, 8, DAMP, TANGENT>(e, a);
+  if (DAMP) return launch_ek_t<4, 6, DAMP, TANGENT>(e, a);
+  if (c.g == 6 && c.w == 4) return launch_ek_t<6, 4, DAMP, TANGENT>(e, a);
+  if (c.g == 4 && c.w == 6) return launch_ek_t<4, 6, DAMP, TANGENT>(e, a);
+  if (c.g == 4 && c.w == 7) return launch_ek_t<4, 7, DAMP, TANGENT>(e, a);
+  if (c.g == 2 && c.w == 8) return launch_ek_t<2, 8, DAMP, TANGENT>(e, a);
+  return launch_ek_t<6, 5, DAMP, TANGENT>(e, a);
 }
 
+static int ek_chunk_elems() {
+  static int c = [] {
+    const char *e = getenv("TLFEA_EK_CHUNK");  // elements per interleaved E/R chunk (0 = two full passes)
+    return e ? atoi(e) : 0;
+  }();
+  return c;
+}
+
+// Schedule: the element range is cut into chunks; for chunk k the element kernel writes the chunk's block
+// records and the row-reduce kernel immediately consumes them for the rows that chunk completes, while the
+// records are still dirty in L2 (row order = completion order, see build_completion_order).  With a mesh whose
+// element numbering is spatially coherent nearly every record read of phase R is an L2 hit.
 static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   tlfea_elem *e = s->e;
   const double h = s->prm.time_step;
   if (tangent && !s->d_stage)
-    TL_TRY(dmalloc(&s->d_stage, (size_t)e->n_elem * SymLayout<10>::ELEM_DOUBLES));
+    TL_TRY(dmalloc(&s->d_stage, (size_t)e->n_elem * EK_ELEM));
   if (tangent && !s->d_rowdesc) {
+    int chunk = ek_chunk_elems();
+    if (chunk <= 0 || chunk >= e->n_elem) chunk = e->n_elem;
+    s->ek_chunk = chunk;
     int *d_order = nullptr;
-    TL_TRY(build_row_order(e, &d_order));
+    TL_TRY(build_completion_order(e, chunk, &d_order, &s->chunk_ptr));
     RowDesc *desc = nullptr;
     TL_TRY(dmalloc(&desc, (size_t)e->n_coef));
     TL_LAUNCH(k_row_desc, blocks_for(e->n_coef, 256), 256, 0, e->stream, e->n_coef, d_order, e->pat.d_off,
@@ -326,16 +345,13 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
     TL_CUDA(cudaStreamSynchronize(e->stream));
     cudaFree(d_order);
     s->d_rowdesc = desc;
+    TL_TRY(dmalloc(&s->d_tickets, s->chunk_ptr.size()));
   }
   EKArgs a;
-  a.n_elem = e->n_elem;
-  a.ecoef = e->d_ecoef;
   a.x = e->d_x;
   a.y = e->d_y;
   a.z = e->d_z;
   a.v = damp ? s->d_v : nullptr;
-  a.gradN = e->d_gradN;
-  a.detJ = e->d_detJ;
   a.qw = e->qw;
   a.lambda = e->lambda;
   a.mu = e->mu;
@@ -345,28 +361,24 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   a.c2 = h * e->mu + e->eta;
   a.c3 = h * e->mu + e->eta;
   a.c4 = h;
-  a.fe = e->d_fe;
-  a.stage = tangent ? s->d_stage : nullptr;
-  if (tangent) {
-    if (damp)
-      TL_TRY((launch_ek_cfg<true, true>(e, a)));
-    else
-      TL_TRY((launch_ek_cfg<false, true>(e, a)));
-  } else {
-    if (damp)
-      TL_TRY((launch_ek_cfg<true, false>(e, a)));
-    else
-      TL_TRY((launch_ek_cfg<false, false>(e, a)));
-  }
-  if (s->profile) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
+  auto launch_e = [&](int e0, int ne) -> int {
+    a.n_elem = ne;
+    a.ecoef = e->d_ecoef + (int64_t)e0 * 10;
+    a.gradN = e->d_gradN + (int64_t)e0 * 150;
+    a.detJ = e->d_detJ + (int64_t)e0 * 5;
+    a.fe = e->d_fe + (int64_t)e0 * 30;
+    a.stage = tangent ? s->d_stage + (int64_t)e0 * EK_ELEM : nullptr;
+    if (tangent) return damp ? launch_ek_cfg<true, true>(e, a) : launch_ek_cfg<false, true>(e, a);
+    return damp ? launch_ek_cfg<true, false>(e, a) : launch_ek_cfg<false, false>(e, a);
+  };
   if (!tangent) {
+    TL_TRY(launch_e(0, e->n_elem));
+    if (s->profile) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
     TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)e->n_coef * 3, 128), 128, 0, e->stream, e->n_coef,
               e->pat.d_inc_ptr, e->pat.d_inc_ea, e->d_fe, e->d_f_int, 0);
     return TLFEA_OK;
   }
   RKArgs r;
-  r.n_coef = e->n_coef;
-  r.desc = static_cast<const RowDesc *>(s->d_rowdesc);
   r.inc_ea = e->pat.d_inc_ea;
   r.slot = e->pat.d_slot;
   r.mass = e->d_mass;
@@ -380,9 +392,21 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   TL_CHECK(smem <= 220 * 1024, "coefficient row too long for the row-reduce kernel (max_deg=%d)", e->pat.max_deg);
   if (smem > 48 * 1024)
     TL_CUDA(cudaFuncSetAttribute(rk_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int n_chunks = (e->n_coef + RK_WARPS - 1) / RK_WARPS;
   const int per_sm = std::max(1, std::min(3, (int)((227 * 1024) / (smem + 2048))));
-  TL_LAUNCH((rk_kernel<10>), std::min(n_chunks, 148 * per_sm), RK_WARPS * 32, smem, e->stream, r);
+  const int n_chunks = (int)s->chunk_ptr.size() - 1;
+  TL_CUDA(cudaMemsetAsync(s->d_tickets, 0, s->chunk_ptr.size() * sizeof(int), e->stream));
+  for (int k = 0; k < n_chunks; k++) {
+    const int e0 = k * s->ek_chunk, ne = std::min(s->ek_chunk, e->n_elem - e0);
+    TL_TRY(launch_e(e0, ne));
+    if (s->profile && k == n_chunks - 1) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
+    const int r0 = s->chunk_ptr[k], nr = s->chunk_ptr[k + 1] - r0;
+    if (nr <= 0) continue;
+    r.n_coef = nr;
+    r.desc = static_cast<const RowDesc *>(s->d_rowdesc) + r0;
+    r.counter = s->d_tickets + k;
+    const int blocks = (nr + RK_WARPS * RK_T - 1) / (RK_WARPS * RK_T);
+    TL_LAUNCH((rk_kernel<10>), std::min(blocks, 148 * per_sm), RK_WARPS * 32, smem, e->stream, r);
+  }
   TL_CUDA(cudaGetLastError());
   if (s->profile) TL_CUDA(cudaEventRecord(s->ev[3], e->stream));
   return TLFEA_OK;
@@ -656,6 +680,7 @@ int tlfea_newton_create(tlfea_elem *e, int n_constraints, tlfea_newton **out) {
   TL_CUDA(cudaSetDevice(e->device));
   tlfea_newton *s = new tlfea_newton();
   s->e = e;
+  s->device = e->device;
   s->n_constraints = n_constraints;
   const size_t nd = 3 * (size_t)e->n_coef;
   TL_TRY(dmalloc(&s->d_v, nd));
@@ -681,13 +706,17 @@ int tlfea_newton_create(tlfea_elem *e, int n_constraints, tlfea_newton **out) {
 
 int tlfea_newton_destroy(tlfea_newton *s) {
   if (!s) return TLFEA_OK;
-  cudaSetDevice(s->e->device);
-  cudaStreamSynchronize(s->e->stream);
+  cudaSetDevice(s->device);
+  if (elem_is_live(s->e))
+    cudaStreamSynchronize(s->e->stream);
+  else
+    cudaDeviceSynchronize();  // the element handle went first: its stream is gone
   dfree(s->d_H);
   dfree(s->d_gp);
   dfree(s->d_stage);
   if (s->d_rowdesc) cudaFree(s->d_rowdesc);
   s->d_rowdesc = nullptr;
+  dfree(s->d_tickets);
   s->tiles.release();
   dfree(s->d_v);
   dfree(s->d_v_prev);

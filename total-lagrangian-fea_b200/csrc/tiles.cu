@@ -440,4 +440,68 @@ int build_row_order(const tlfea_elem *h, int **d_order) {
   return TLFEA_OK;
 }
 
+// Rows in COMPLETION order for the chunked two-phase assembly: primary key = id of the row's last
+// (largest) incident element, ties in Morton order.  chunk_ptr[k] = first position whose key >= k*chunk,
+// so the rows of [chunk_ptr[k], chunk_ptr[k+1]) become complete when elements [k*chunk, (k+1)*chunk)
+// have been processed.  Rows without elements land in chunk 0.
+__global__ void k_completion_keys(int n, int S, const int *__restrict__ order, const int *__restrict__ inc_ptr,
+                                  const int *__restrict__ inc_ea, unsigned long long *keys, int *vals) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int row = order[i];
+  const int vb = inc_ptr[row], ve = inc_ptr[row + 1];
+  const unsigned long long last = (ve > vb) ? (unsigned long long)(inc_ea[ve - 1] / S) : 0ULL;
+  keys[i] = (last << 32) | (unsigned)i;
+  vals[i] = row;
+}
+__global__ void k_chunk_lower_bound(const unsigned long long *__restrict__ keys, int n, int chunk, int n_chunks,
+                                    int *ptr) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > n_chunks) return;
+  const unsigned long long target = (unsigned long long)k * (unsigned long long)chunk;
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if ((keys[mid] >> 32) < target)
+      lo = mid + 1;
+    else
+      hi = mid;
+  }
+  ptr[k] = (k == n_chunks) ? n : lo;
+}
+
+int build_completion_order(const tlfea_elem *h, int chunk, int **d_order, std::vector<int> *chunk_ptr) {
+  const int n = h->pat.n_coef, S = h->pat.S;
+  cudaStream_t st = h->stream;
+  int *d_morton = nullptr;
+  TL_TRY(build_row_order(h, &d_morton));
+  unsigned long long *k0 = nullptr, *k1 = nullptr;
+  int *v0 = nullptr, *d_ptr = nullptr;
+  TL_TRY(dmalloc(&k0, (size_t)n));
+  TL_TRY(dmalloc(&k1, (size_t)n));
+  TL_TRY(dmalloc(&v0, (size_t)n));
+  TL_TRY(dmalloc(d_order, (size_t)n));
+  TL_LAUNCH(k_completion_keys, blocks_for(n, 256), 256, 0, st, n, S, d_morton, h->pat.d_inc_ptr, h->pat.d_inc_ea, k0, v0);
+  size_t tmp_bytes = 0;
+  TL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k0, k1, v0, *d_order, n, 0, 64, st));
+  void *tmp = nullptr;
+  TL_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+  cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k0, k1, v0, *d_order, n, 0, 64, st);
+  g_launches.fetch_add(1);
+  const int n_chunks = (h->n_elem + chunk - 1) / chunk;
+  TL_TRY(dmalloc(&d_ptr, (size_t)n_chunks + 1));
+  TL_LAUNCH(k_chunk_lower_bound, blocks_for(n_chunks + 1, 256), 256, 0, st, k1, n, chunk, n_chunks, d_ptr);
+  chunk_ptr->resize(n_chunks + 1);
+  cudaMemcpyAsync(chunk_ptr->data(), d_ptr, (size_t)(n_chunks + 1) * sizeof(int), cudaMemcpyDeviceToHost, st);
+  cudaStreamSynchronize(st);
+  cudaFree(tmp);
+  cudaFree(k0);
+  cudaFree(k1);
+  cudaFree(v0);
+  cudaFree(d_ptr);
+  cudaFree(d_morton);
+  TL_CUDA(e);
+  return TLFEA_OK;
+}
+
 }  // namespace tlfea
