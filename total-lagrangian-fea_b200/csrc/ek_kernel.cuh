@@ -70,6 +70,7 @@ constexpr int EK_REC = 9;     // per Gauss point: M(6) | dV | pad(2); odd stride
 constexpr int EK_GQ = 31;     // stride of the per-(element, point) u / force-partial rows (30 used)
 constexpr int EK_VIS = 90;    // doubles of one visit record: K_ab, b = 0..9
 constexpr int EK_ELEM = 900;  // doubles of one element record: [a][b][9]
+constexpr int EK_LS = 73;     // staging stride per lane: 8 blocks x 9 (+1: odd => conflict-free lane-major stores)
 
 template <int G, bool DAMP>
 struct EKShape {
@@ -79,7 +80,7 @@ struct EKShape {
   static constexpr int EC_D = (G * 5 + 1) / 2 * 2;  // G*10 ints
   static constexpr int U_D = G * 5 * EK_GQ;         // u = F h per (element, point)
   static constexpr int REC_D = G * 5 * EK_REC;
-  static constexpr int K_D = 2 * EK_ELEM;           // records of the element pair in flight; also the force partials
+  static constexpr int K_D = 32 * EK_LS;            // lane-major block staging of the element pair in flight; also the force partials
   static constexpr int OFF_H = 0;
   static constexpr int OFF_DJ = OFF_H + 2 * H_D;
   static constexpr int OFF_X = OFF_DJ + 2 * DJ_D;
@@ -102,6 +103,17 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
   double *wb = ek_smem + (size_t)warp * Sh::WARP_D;
   double *s_u = wb + Sh::OFF_U, *s_rec = wb + Sh::OFF_REC, *s_k = wb + Sh::OFF_K;
   double *s_fp = s_k;  // force partials live in the record staging before the block step needs it
+  // record position (a, b, k) -> staging offset of the producing lane (tile, slot, k); built once per block
+  __shared__ uint16_t s_map[EK_ELEM];
+  for (int r = threadIdx.x; r < EK_ELEM; r += W * 32) {
+    const int blk = r / 9, k = r - blk * 9, ra = blk / 10, rb = blk - ra * 10;
+    const int I = ra >> 1, J = rb >> 1;
+    const int lo = min(I, J), hi = max(I, J);
+    const int tile_id = (lo == 0 ? 0 : lo == 1 ? 5 : lo == 2 ? 9 : lo == 3 ? 12 : 14) + (hi - lo);
+    const int t8 = (I <= J) ? ((ra & 1) * 2 + (rb & 1)) : (4 + (rb & 1) * 2 + (ra & 1));
+    s_map[r] = (uint16_t)(tile_id * EK_LS + t8 * 9 + k);
+  }
+  __syncthreads();
 
   const int n_groups = (p.n_elem + G - 1) / G;
   const int gstride = gridDim.x * W;
@@ -349,7 +361,7 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
         }
         // h K_ab + C_ab = c1 A + c2 A^T + c4 mu tr(A) I + G      (SVK.cuh:35-55, FEAT10DataFunc.cuh:695-762)
         if (on) {
-          double *ke = s_k + el2 * EK_ELEM;
+          double *ke = s_k + lane * EK_LS;
 #pragma unroll
           for (int ta = 0; ta < 2; ta++)
 #pragma unroll
@@ -366,12 +378,11 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
               k[6] = p.c1 * A[t][6] + p.c2 * A[t][2] + Gs[t][2];
               k[7] = p.c1 * A[t][7] + p.c2 * A[t][5] + Gs[t][4];
               k[8] = p.c1 * A[t][8] + p.c2 * A[t][8] + Gs[t][5] + dg;
-              const int aa = a1 + ta, bb = b1 + tb;
-              double *d1 = ke + (aa * 10 + bb) * 9;
+              double *d1 = ke + t * 9;
 #pragma unroll
               for (int i = 0; i < 9; i++) d1[i] = k[i];
               if (tI != tJ) {  // K_ba = K_ab^T
-                double *d2 = ke + (bb * 10 + aa) * 9;
+                double *d2 = ke + (4 + t) * 9;
 #pragma unroll
                 for (int i = 0; i < 3; i++)
 #pragma unroll
@@ -383,7 +394,10 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
         // the pair's records are contiguous in global memory: one coalesced burst
         const int npair = min(2, ne - pr);
         double *dst = p.stage + (int64_t)(e0 + pr) * EK_ELEM;
-        for (int i = lane; i < npair * EK_ELEM; i += 32) dst[i] = s_k[i];
+        for (int i = lane; i < npair * EK_ELEM; i += 32) {
+          const int second = (i >= EK_ELEM) ? 1 : 0;
+          dst[i] = s_k[s_map[i - second * EK_ELEM] + second * 15 * EK_LS];
+        }
         __syncwarp();
       }
     }

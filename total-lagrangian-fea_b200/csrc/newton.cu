@@ -275,7 +275,7 @@ struct EKCfg {
 };
 static EKCfg ek_cfg() {
   static EKCfg c = [] {
-    EKCfg t{6, 5};
+    EKCfg t{4, 6};
     const char *e = getenv("TLFEA_EK_CFG");  // "65" = groups of 6, 5 warps ... (tuning aid)
     if (e && strlen(e) == 2) t = EKCfg{e[0] - '0', e[1] - '0'};
     return t;
@@ -307,12 +307,11 @@ static int launch_ek_t(tlfea_elem *e, const EKArgs &a) {
 template <bool DAMP, bool TANGENT>
 static int launch_ek_cfg(tlfea_elem *e, const EKArgs &a) {
   const EKCfg c = ek_cfg();
-  if (DAMP) return launch_ek_t<4, 6, DAMP, TANGENT>(e, a);
+  if (DAMP) return launch_ek_t<4, 5, DAMP, TANGENT>(e, a);
   if (c.g == 6 && c.w == 4) return launch_ek_t<6, 4, DAMP, TANGENT>(e, a);
-  if (c.g == 4 && c.w == 6) return launch_ek_t<4, 6, DAMP, TANGENT>(e, a);
-  if (c.g == 4 && c.w == 7) return launch_ek_t<4, 7, DAMP, TANGENT>(e, a);
   if (c.g == 2 && c.w == 8) return launch_ek_t<2, 8, DAMP, TANGENT>(e, a);
-  return launch_ek_t<6, 5, DAMP, TANGENT>(e, a);
+  if (c.g == 4 && c.w == 5) return launch_ek_t<4, 5, DAMP, TANGENT>(e, a);
+  return launch_ek_t<4, 6, DAMP, TANGENT>(e, a);
 }
 
 static int ek_chunk_elems() {
