@@ -325,13 +325,16 @@ def main():
         tf = C.c_double(0)
         tlfea.lib.tlfea_fp64_peak(local, C.byref(tf))
         fp64 = tf.value
-    dom_ms = max(row_ms, 1e-9)
+    # two-phase assembly: gp_ms is the element kernel (ek_kernel), row_ms the row-reduce kernel (rk_kernel);
+    # the dominant one carries the roofline line, measured against the ALGORITHMIC bytes of the whole assembly
+    dom_is_row = row_ms >= gp_ms
+    dom_ms = max(row_ms if dom_is_row else gp_ms, 1e-9)
     achieved = algo_b / (dom_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "row2_kernel<10,5>" if s.TileStats()["n_tiles"] else "row_kernel<10,5,SVK>", "achieved": achieved, "peak": hbm_peak,
+    roofline = {"bound": "hbm", "kernel": "rk_kernel<10>" if dom_is_row else "ek_kernel<4,6,0,1>", "achieved": achieved, "peak": hbm_peak,
                 "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                "algorithmic_bytes_per_launch": algo_b, "kernel_ms": row_ms, "gp_kernel_ms": gp_ms,
-                "step_share": row_ms / max(ms_step, 1e-9)}
+                "algorithmic_bytes_per_launch": algo_b, "kernel_ms": dom_ms, "rk_kernel_ms": row_ms, "ek_kernel_ms": gp_ms,
+                "step_share": dom_ms / max(ms_step, 1e-9)}
     if fp64:
         fl = ALGO_FLOP_PER_GP * n_elem_l * 5
         roofline["fp64"] = {"achieved_tflops": fl / ((row_ms + gp_ms) * 1e-3) / 1e12, "peak_tflops": fp64,
