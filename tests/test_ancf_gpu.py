@@ -1,0 +1,179 @@
+"""GPU parity tests, ANCF3243 beam and ANCF3443 shell.
+
+Set-up path (B^-T, reference gradients, mass) is pinned by the reference's own known-answer mass matrices
+data/utest/mass_matrix_{2,3}_beam.csv (lib_utest/utest_3243.cc:74-112,159-197; tolerance 1e-4 there, 1e-9 here)
+and by quadrature invariants; the force / tangent kernels for S = 8 and S = 16 are compared with the oracle's
+generic restatement (compute_p, compute_internal_force, compute_hessian_assemble_csr twins:
+ANCF3243DataFunc.cuh:189-454,642-940, ANCF3443DataFunc.cuh:281-535,724-1033) on the same gradients, within
+1e-12 relative to the largest entry."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+E_MOD, NU, RHO, H_STEP = 7e8, 0.33, 2700.0, 1e-3
+
+GL = {
+    2: ([-0.57735026918962576, 0.57735026918962576], [1.0, 1.0]),
+    3: ([-0.77459666924148340, 0.0, 0.77459666924148340],
+        [0.55555555555555556, 0.88888888888888889, 0.55555555555555556]),
+    4: ([-0.8611363115940526, -0.3399810435848563, 0.3399810435848563, 0.8611363115940526],
+        [0.3478548451374538, 0.6521451548625461, 0.6521451548625461, 0.3478548451374538]),
+}
+
+
+def stiffness_weights(kind):
+    n = (3, 2, 2) if kind == 3243 else (4, 4, 3)
+    w = [GL[k][1] for k in n]
+    return np.array([w[0][q // (n[1] * n[2])] * w[1][(q // n[2]) % n[1]] * w[2][q % n[2]]
+                     for q in range(n[0] * n[1] * n[2])])
+
+
+def straight_beam(n_elem, L):
+    """GridMeshGenerator(n*L, 0, L, horizontal) of the reference's unit tests: nodes on the x axis,
+    coefficients [r, r_u = e_x, r_v = e_y, r_w = e_z]."""
+    nn = n_elem + 1
+    x = np.zeros(4 * nn); y = np.zeros(4 * nn); z = np.zeros(4 * nn)
+    for i in range(nn):
+        x[4 * i:4 * i + 4] = [i * L, 1.0, 0.0, 0.0]
+        y[4 * i:4 * i + 4] = [0.0, 0.0, 1.0, 0.0]
+        z[4 * i:4 * i + 4] = [0.0, 0.0, 0.0, 1.0]
+    conn = np.array([[i, i + 1] for i in range(n_elem)], dtype=np.int32)
+    return x, y, z, conn
+
+
+def plate(nx, ny, L, W):
+    """Flat ANCF3443 plate in the xy plane: corner order P1..P4 = (-,-), (+,-), (+,+), (-,+) (cpu_utils.cc:214-217)."""
+    nn = (nx + 1) * (ny + 1)
+    x = np.zeros(4 * nn); y = np.zeros(4 * nn); z = np.zeros(4 * nn)
+    for i in range(nx + 1):
+        for j in range(ny + 1):
+            n = i * (ny + 1) + j
+            x[4 * n:4 * n + 4] = [i * L, 1.0, 0.0, 0.0]
+            y[4 * n:4 * n + 4] = [j * W, 0.0, 1.0, 0.0]
+            z[4 * n:4 * n + 4] = [0.0, 0.0, 0.0, 1.0]
+    nid = lambda i, j: i * (ny + 1) + j
+    conn = np.array([[nid(i, j), nid(i + 1, j), nid(i + 1, j + 1), nid(i, j + 1)]
+                     for i in range(nx) for j in range(ny)], dtype=np.int32)
+    return x, y, z, conn
+
+
+def make(kind, x, y, z, conn, dims, model="svk", damp=False):
+    import tlfea
+
+    nn = x.shape[0] // 4
+    cls = tlfea.GPU_ANCF3243_Data if kind == 3243 else tlfea.GPU_ANCF3443_Data
+    d = cls(nn, conn.shape[0])
+    d.Initialize()
+    d.Setup(*dims, x, y, z, conn)
+    d.SetDensity(RHO)
+    if model == "svk":
+        d.SetSVK(E_MOD, NU)
+    else:
+        mu = E_MOD / (2 * (1 + NU)); K = E_MOD / (3 * (1 - 2 * NU))
+        d.SetMooneyRivlin(0.3 * mu, 0.2 * mu, 1.5 * K)
+    if damp:
+        d.SetDamping(1e5, 2e5)
+    d.CalcDsDuPre()
+    d.CalcMassMatrix()
+    s = tlfea.SyncedNewtonSolver(d, 0)
+    s.SetParameters(tlfea.SyncedNewtonParams(1e-4, 0.0, 1e-6, 1e14, 1, 1, H_STEP))
+    s.Setup()
+    s.AnalyzeHessianSparsity()
+    return d, s
+
+
+def dense_mass(d):
+    off, cols, vals = d.RetrieveMassCSRToCPU()
+    n = off.shape[0] - 1
+    M = np.zeros((n, n))
+    for i in range(n):
+        M[i, cols[off[i]:off[i + 1]]] = vals[off[i]:off[i + 1]]
+    return M
+
+
+@pytest.mark.parametrize("nb", [2, 3])
+def test_3243_mass_matrix_known_answer(nb):
+    """MassMatrix2Beams / MassMatrix3Beams of lib_utest/utest_3243.cc."""
+    L, W, H = 2.0, 1.0, 1.0
+    x, y, z, conn = straight_beam(nb, L)
+    d, _ = make(3243, x, y, z, conn, (L, W, H))
+    M = dense_mass(d)
+    ref = np.load(os.path.join(GOLDEN, f"ancf3243_mass_{nb}_beam.npy"))
+    assert M.shape == ref.shape
+    assert np.abs(M - ref).max() < 1e-4  # the reference's own tolerance (CSV has ~6 digits)
+    assert np.abs(M - M.T).max() < 1e-9 * np.abs(M).max()
+    assert np.linalg.det(M) > 0
+    assert abs(M[0::4, 0::4].sum() - RHO * nb * L * W * H) < 1e-9 * RHO * nb * L * W * H  # total mass
+
+
+@pytest.mark.parametrize("kind", [3243, 3443])
+def test_precompute_invariants(kind):
+    if kind == 3243:
+        dims = (0.5, 0.1, 0.1); x, y, z, conn = straight_beam(5, dims[0]); vol = 5 * 0.5 * 0.1 * 0.1
+    else:
+        dims = (0.4, 0.3, 0.05); x, y, z, conn = plate(3, 2, dims[0], dims[1]); vol = 6 * 0.4 * 0.3 * 0.05
+    d, s = make(kind, x, y, z, conn, dims)
+    detJ = d.RetrieveDetJToCPU().reshape(conn.shape[0], -1)
+    qw = stiffness_weights(kind)
+    assert abs((detJ * qw).sum() - vol) < 1e-12 * vol
+    M = dense_mass(d)
+    assert abs(M[0::4, 0::4].sum() - RHO * vol) < 1e-10 * RHO * vol
+    # at rest: F = I, P = 0, f_int = 0
+    s.AssembleForce()
+    f = d.RetrieveInternalForceToCPU()
+    assert np.abs(f).max() < 1e-12 * E_MOD  # rounding only (forces under load are ~E * area)
+
+
+@pytest.mark.parametrize("kind", [3243, 3443])
+@pytest.mark.parametrize("model,damp", [("svk", False), ("svk", True), ("mr", False)])
+def test_force_tangent_vs_oracle(kind, model, damp):
+    from oracle import oracle as orc
+
+    if kind == 3243:
+        dims = (0.5, 0.1, 0.1); x, y, z, conn = straight_beam(6, dims[0]); S = 8
+    else:
+        dims = (0.4, 0.3, 0.05); x, y, z, conn = plate(3, 3, dims[0], dims[1]); S = 16
+    d, s = make(kind, x, y, z, conn, dims, model, damp)
+    ne, nc = conn.shape[0], x.shape[0]
+    rng = np.random.Generator(np.random.PCG64(2234))
+    amp = np.tile([0.02 * dims[0], 0.02, 0.02, 0.02], nc // 4)
+    xd = x + amp * rng.uniform(-1, 1, nc); yd = y + amp * rng.uniform(-1, 1, nc); zd = z + amp * rng.uniform(-1, 1, nc)
+    v = 0.1 * rng.uniform(-1, 1, 3 * nc)
+    d.UpdatePositions(xd, yd, zd)
+    s.SetVelocityGuess(v)
+    s.Assemble()
+    f = d.RetrieveInternalForceToCPU()
+    H = s.RetrieveHessianValues()
+
+    ecoef = np.array([[4 * conn[e, a // 4] + a % 4 for a in range(S)] for e in range(ne)], dtype=np.int32)
+    Q = stiffness_weights(kind).shape[0]
+    gradN = d.RetrieveDsDuPreToCPU().reshape(ne, Q, 3 * S)
+    detJ = d.RetrieveDetJToCPU().reshape(ne, Q)
+    qw = stiffness_weights(kind)
+    eta, lam_d = (1e5, 2e5) if damp else (0.0, 0.0)
+    if model == "svk":
+        mat = orc.Material.svk(E_MOD, NU, eta, lam_d)
+    else:
+        mu = E_MOD / (2 * (1 + NU)); K = E_MOD / (3 * (1 - 2 * NU))
+        mat = orc.Material.mooney_rivlin(0.3 * mu, 0.2 * mu, 1.5 * K, eta, lam_d)
+    coords = np.stack([xd, yd, zd], axis=1)
+    if damp:
+        F, P, Fd, Pv = orc.compute_p(ecoef, coords, gradN, mat, v, want_visc=True)
+    else:
+        F, P = orc.compute_p(ecoef, coords, gradN, mat)
+    f_ref = orc.internal_force(ecoef, gradN, detJ, qw, P, nc)
+    off, cols, mvals = d.RetrieveMassCSRToCPU()
+    H_ref = np.zeros(9 * cols.shape[0])
+    orc.hessian_mass(off, cols, mvals, H_STEP, H_ref)
+    orc.tangent_assemble(ecoef, coords, gradN, detJ, qw, mat, H_STEP, off, cols, H_ref)
+    assert rel_err(f, f_ref) < TOL
+    assert rel_err(H, H_ref) < TOL
+    # bit-reproducible
+    s.Assemble()
+    assert np.array_equal(H, s.RetrieveHessianValues())
+    assert np.array_equal(f, d.RetrieveInternalForceToCPU())
