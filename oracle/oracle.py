@@ -285,3 +285,77 @@ class T10Oracle:
             J, _ = fixed_node_jacobians(fixed_nodes, self.nn)
             hessian_constraints(*J, h, alm_rho, self.off, self.cols, H)
         return H
+
+
+# --------------------------------------------------------------------------- ANCF set-up path
+_GL = {
+    2: ([-0.57735026918962576, 0.57735026918962576], [1.0, 1.0]),
+    3: ([-0.77459666924148340, 0.0, 0.77459666924148340],
+        [0.55555555555555556, 0.88888888888888889, 0.55555555555555556]),
+    -3: ([-0.7745966692414834, 0.0, 0.7745966692414834], [0.5555555555555556, 0.8888888888888888, 0.5555555555555556]),
+    4: ([-0.8611363115940526, -0.3399810435848563, 0.3399810435848563, 0.8611363115940526],
+        [0.3478548451374538, 0.6521451548625461, 0.6521451548625461, 0.3478548451374538]),
+    6: ([-0.93246951420315202, -0.66120938646626451, -0.23861918608319691, 0.23861918608319691,
+         0.66120938646626451, 0.93246951420315202],
+        [0.17132449237917034, 0.36076157304813861, 0.46791393457269104, 0.46791393457269104,
+         0.36076157304813861, 0.17132449237917034]),
+    7: ([-0.949107912342759, -0.741531185599394, -0.405845151377397, 0.0, 0.405845151377397, 0.741531185599394,
+         0.949107912342759],
+        [0.129484966168870, 0.279705391489277, 0.381830050505119, 0.417959183673469, 0.381830050505119,
+         0.279705391489277, 0.129484966168870]),
+}
+
+
+def ancf_rule(kind: int, mass: bool):
+    """(n[3], points[3][7], weights[3][7]) of lib_utils/quadrature_utils.h: stiffness 3x2x2 / 4x4x3,
+    mass 6x2x2 / 7x7x3."""
+    ax = {(3243, False): (3, 2, 2), (3243, True): (6, 2, 2), (3443, False): (4, 4, 3), (3443, True): (7, 7, -3)}[(kind, mass)]
+    n = np.array([abs(a) for a in ax], dtype=np.int32)
+    p = np.zeros((3, 7)); w = np.zeros((3, 7))
+    for k, a in enumerate(ax):
+        p[k, :abs(a)], w[k, :abs(a)] = _GL[a]
+    return n, p, w
+
+
+def ancf_stiffness_weights(kind: int):
+    n, _, w = ancf_rule(kind, False)
+    return np.array([w[0][q // (n[1] * n[2])] * w[1][(q // n[2]) % n[1]] * w[2][q % n[2]]
+                     for q in range(int(n.prod()))])
+
+
+def ancf_ecoef(kind: int, conn):
+    conn = np.asarray(conn)
+    S = 8 if kind == 3243 else 16
+    return np.array([[4 * conn[e, a // 4] + a % 4 for a in range(S)] for e in range(conn.shape[0])], dtype=np.int32)
+
+
+def ancf_binv(kind: int, L, W, H):
+    S = 8 if kind == 3243 else 16
+    L, W, H = (np.atleast_1d(np.asarray(a, dtype=np.float64)) for a in (L, W, H))
+    out = np.zeros((L.shape[0], S * S))
+    for e in range(L.shape[0]):
+        if lib().orc_ancf_binv(S, C.c_double(L[e]), C.c_double(W[e]), C.c_double(H[e]), _d(out[e])) != 0:
+            raise ValueError("singular B matrix")
+    return out
+
+
+def ancf_precompute(kind, ecoef, x, y, z, LWH, Binv):
+    ecoef = _i32(ecoef)
+    ne, S = ecoef.shape
+    n, p, _ = ancf_rule(kind, False)
+    Q = int(n.prod())
+    g = np.zeros((ne, Q, 3 * S)); dj = np.zeros((ne, Q))
+    x, y, z, LWH, Binv, p = _f64(x), _f64(y), _f64(z), _f64(LWH), _f64(Binv), _f64(p)
+    lib().orc_ancf_precompute(ne, S, _i(ecoef), _d(x), _d(y), _d(z), _d(LWH), _d(Binv), _i(n), _d(p), _d(g), _d(dj))
+    return g, dj
+
+
+def ancf_mass(kind, ecoef, x, y, z, LWH, Binv, rho, off, cols):
+    ecoef = _i32(ecoef)
+    ne, S = ecoef.shape
+    n, p, w = ancf_rule(kind, True)
+    vals = np.zeros(cols.shape[0])
+    x, y, z, LWH, Binv, p, w = _f64(x), _f64(y), _f64(z), _f64(LWH), _f64(Binv), _f64(p), _f64(w)
+    lib().orc_ancf_mass(ne, S, _i(ecoef), _d(x), _d(y), _d(z), _d(LWH), _d(Binv), _i(n), _d(p), _d(w),
+                        C.c_double(rho), _i(off), _i(cols), _d(vals))
+    return vals

@@ -736,3 +736,170 @@ void orc_set_num_threads(int n) {
   (void)n;
 #endif
 }
+
+/* ================================================================== */
+/* ANCF3243 / ANCF3443 set-up path                                    */
+/*   basis + derivatives  ANCF3243DataFunc.cuh:115-152, ANCF3443DataFunc.cuh:114-238 */
+/*   B^-T                 lib_utils/cpu_utils.cc:125-209, 211-441 (Eigen inverse -> Gauss-Jordan) */
+/*   precompute           ANCF3243Data.cu:102-198, ANCF3443Data.cu:96-182   */
+/*   mass                 ANCF3243Data.cu:200-288, ANCF3443Data.cu:184-254  */
+/* ================================================================== */
+static void ancf_b(int S, double u, double v, double w, double *b, double *bu,
+                   double *bv, double *bw) {
+  memset(bu, 0, S * sizeof(double));
+  memset(bv, 0, S * sizeof(double));
+  memset(bw, 0, S * sizeof(double));
+  if (S == 8) {
+    b[0] = 1.0; b[1] = u; b[2] = v; b[3] = w; b[4] = u * v; b[5] = u * w;
+    b[6] = u * u; b[7] = u * u * u;
+    bu[1] = 1.0; bu[4] = v; bu[5] = w; bu[6] = 2.0 * u; bu[7] = 3.0 * u * u;
+    bv[2] = 1.0; bv[4] = u;
+    bw[3] = 1.0; bw[5] = u;
+  } else {
+    b[0] = 1.0; b[1] = u; b[2] = v; b[3] = w; b[4] = u * v; b[5] = u * w;
+    b[6] = v * w; b[7] = u * v * w; b[8] = u * u; b[9] = v * v;
+    b[10] = (u * u) * v; b[11] = u * (v * v); b[12] = u * u * u;
+    b[13] = v * v * v; b[14] = (u * u * u) * v; b[15] = u * (v * v * v);
+    bu[1] = 1.0; bu[4] = v; bu[5] = w; bu[7] = v * w; bu[8] = 2.0 * u;
+    bu[10] = 2.0 * u * v; bu[11] = v * v; bu[12] = 3.0 * u * u;
+    bu[14] = 3.0 * u * u * v; bu[15] = v * v * v;
+    bv[2] = 1.0; bv[4] = u; bv[6] = w; bv[7] = u * w; bv[9] = 2.0 * v;
+    bv[10] = u * u; bv[11] = 2.0 * u * v; bv[13] = 3.0 * v * v;
+    bv[14] = u * u * u; bv[15] = 3.0 * u * v * v;
+    bw[3] = 1.0; bw[5] = u; bw[6] = v; bw[7] = u * v;
+  }
+}
+
+/* out: column-major S x S,  out[j*S+i] = (B^T)^-1 (i,j) */
+int orc_ancf_binv(int S, double L, double W, double H, double *out) {
+  (void)H;
+  double pu[4], pv[4];
+  int np = (S == 8) ? 2 : 4;
+  if (S == 8) {
+    pu[0] = -L / 2.0; pu[1] = L / 2.0; pv[0] = pv[1] = 0.0;
+  } else {
+    pu[0] = -L / 2.0; pv[0] = -W / 2.0; pu[1] = L / 2.0; pv[1] = -W / 2.0;
+    pu[2] = L / 2.0;  pv[2] = W / 2.0;  pu[3] = -L / 2.0; pv[3] = W / 2.0;
+  }
+  double a[16 * 16], inv[16 * 16]; /* a = B^T row-major */
+  for (int p = 0; p < np; p++) {
+    double b[16], bu[16], bv[16], bw[16];
+    ancf_b(S, pu[p], pv[p], 0.0, b, bu, bv, bw);
+    for (int c = 0; c < S; c++) {
+      a[c * S + 4 * p + 0] = b[c];
+      a[c * S + 4 * p + 1] = bu[c];
+      a[c * S + 4 * p + 2] = bv[c];
+      a[c * S + 4 * p + 3] = bw[c];
+    }
+  }
+  for (int i = 0; i < S * S; i++) inv[i] = 0.0;
+  for (int i = 0; i < S; i++) inv[i * S + i] = 1.0;
+  for (int c = 0; c < S; c++) {
+    int piv = c;
+    for (int r = c + 1; r < S; r++)
+      if (fabs(a[r * S + c]) > fabs(a[piv * S + c])) piv = r;
+    if (a[piv * S + c] == 0.0) return -1;
+    if (piv != c)
+      for (int k = 0; k < S; k++) {
+        double t = a[c * S + k]; a[c * S + k] = a[piv * S + k]; a[piv * S + k] = t;
+        t = inv[c * S + k]; inv[c * S + k] = inv[piv * S + k]; inv[piv * S + k] = t;
+      }
+    double d = 1.0 / a[c * S + c];
+    for (int k = 0; k < S; k++) { a[c * S + k] *= d; inv[c * S + k] *= d; }
+    for (int r = 0; r < S; r++) {
+      if (r == c) continue;
+      double f = a[r * S + c];
+      if (f == 0.0) continue;
+      for (int k = 0; k < S; k++) {
+        a[r * S + k] -= f * a[c * S + k];
+        inv[r * S + k] -= f * inv[c * S + k];
+      }
+    }
+  }
+  for (int i = 0; i < S; i++)
+    for (int j = 0; j < S; j++) out[j * S + i] = inv[i * S + j];
+  return 0;
+}
+
+static void ancf_shape(int S, const double *Binv, double L, double W, double H,
+                       double xi, double eta, double zeta, double *s,
+                       double *dxi, double *deta, double *dzeta) {
+  double b[16], bu[16], bv[16], bw[16];
+  ancf_b(S, 0.5 * L * xi, 0.5 * W * eta, 0.5 * H * zeta, b, bu, bv, bw);
+  for (int i = 0; i < S; i++) { bu[i] *= 0.5 * L; bv[i] *= 0.5 * W; bw[i] *= 0.5 * H; }
+  for (int i = 0; i < S; i++) {
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    for (int j = 0; j < S; j++) {
+      double m = Binv[j * S + i];
+      a0 += m * b[j]; a1 += m * bu[j]; a2 += m * bv[j]; a3 += m * bw[j];
+    }
+    s[i] = a0; dxi[i] = a1; deta[i] = a2; dzeta[i] = a3;
+  }
+}
+
+static void ancf_J(int S, const int *ec, const double *x, const double *y,
+                   const double *z, const double *dxi, const double *deta,
+                   const double *dzeta, double J[3][3]) {
+  for (int i = 0; i < 3; i++) J[i][0] = J[i][1] = J[i][2] = 0.0;
+  for (int a = 0; a < S; a++) {
+    double X[3] = {x[ec[a]], y[ec[a]], z[ec[a]]};
+    for (int i = 0; i < 3; i++) {
+      J[i][0] += X[i] * dxi[a];
+      J[i][1] += X[i] * deta[a];
+      J[i][2] += X[i] * dzeta[a];
+    }
+  }
+}
+
+/* rule: n[3], points p[3][7], weights w[3][7]; q -> (q/(n1*n2), (q/n2)%n1, q%n2) */
+void orc_ancf_precompute(int n_elem, int S, const int *ecoef, const double *x,
+                         const double *y, const double *z, const double *LWH,
+                         const double *Binv, const int *n, const double *pts,
+                         double *grad_N, double *detJ) {
+  const int Q = n[0] * n[1] * n[2];
+  for (int e = 0; e < n_elem; e++)
+    for (int q = 0; q < Q; q++) {
+      int ix = q / (n[1] * n[2]), ie = (q / n[2]) % n[1], iz = q % n[2];
+      double s[16], dxi[16], deta[16], dzeta[16], J[3][3], JT[3][3];
+      ancf_shape(S, Binv + (size_t)e * S * S, LWH[e * 3], LWH[e * 3 + 1],
+                 LWH[e * 3 + 2], pts[ix], pts[7 + ie], pts[14 + iz], s, dxi,
+                 deta, dzeta);
+      ancf_J(S, ecoef + (size_t)e * S, x, y, z, dxi, deta, dzeta, J);
+      detJ[(size_t)e * Q + q] = det3(J);
+      for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) JT[i][j] = J[j][i];
+      double *g = grad_N + ((size_t)e * Q + q) * 3 * S;
+      for (int a = 0; a < S; a++) {
+        double rhs[3] = {dxi[a], deta[a], dzeta[a]}, gr[3];
+        solve3(JT, rhs, gr);
+        g[a] = gr[0]; g[S + a] = gr[1]; g[2 * S + a] = gr[2];
+      }
+    }
+}
+
+void orc_ancf_mass(int n_elem, int S, const int *ecoef, const double *x,
+                   const double *y, const double *z, const double *LWH,
+                   const double *Binv, const int *n, const double *pts,
+                   const double *wts, double rho, const int *offsets,
+                   const int *columns, double *values) {
+  const int Q = n[0] * n[1] * n[2];
+  for (int e = 0; e < n_elem; e++) {
+    const int *ec = ecoef + (size_t)e * S;
+    for (int q = 0; q < Q; q++) {
+      int ix = q / (n[1] * n[2]), ie = (q / n[2]) % n[1], iz = q % n[2];
+      double weight = wts[ix] * wts[7 + ie] * wts[14 + iz];
+      double s[16], dxi[16], deta[16], dzeta[16], J[3][3];
+      ancf_shape(S, Binv + (size_t)e * S * S, LWH[e * 3], LWH[e * 3 + 1],
+                 LWH[e * 3 + 2], pts[ix], pts[7 + ie], pts[14 + iz], s, dxi,
+                 deta, dzeta);
+      ancf_J(S, ec, x, y, z, dxi, deta, dzeta, J);
+      double dj = det3(J);
+      for (int i = 0; i < S; i++)
+        for (int j = 0; j < S; j++) {
+          int rs = offsets[ec[i]], re = offsets[ec[i] + 1];
+          int p = bsearch_col(columns + rs, re - rs, ec[j]);
+          if (p >= 0) values[rs + p] += rho * s[i] * s[j] * weight * dj;
+        }
+    }
+  }
+}

@@ -177,3 +177,33 @@ def test_force_tangent_vs_oracle(kind, model, damp):
     s.Assemble()
     assert np.array_equal(H, s.RetrieveHessianValues())
     assert np.array_equal(f, d.RetrieveInternalForceToCPU())
+
+
+@pytest.mark.parametrize("kind", [3243, 3443])
+def test_setup_path_vs_oracle(kind):
+    """CalcDsDuPre / CalcMassMatrix / pattern against the oracle restatement on a curved configuration."""
+    from oracle import oracle as orc
+
+    if kind == 3243:
+        dims = (0.5, 0.1, 0.2); x, y, z, conn = straight_beam(5, dims[0])
+    else:
+        dims = (0.4, 0.3, 0.05); x, y, z, conn = plate(3, 2, dims[0], dims[1])
+    rng = np.random.Generator(np.random.PCG64(77))
+    nc = x.shape[0]
+    amp = np.tile([0.03 * dims[0], 0.03, 0.03, 0.03], nc // 4)
+    x = x + amp * rng.uniform(-1, 1, nc); y = y + amp * rng.uniform(-1, 1, nc); z = z + amp * rng.uniform(-1, 1, nc)
+    d, s = make(kind, x, y, z, conn, dims)
+    ne = conn.shape[0]
+    ec = orc.ancf_ecoef(kind, conn)
+    Binv = orc.ancf_binv(kind, [dims[0]] * ne, [dims[1]] * ne, [dims[2]] * ne)
+    LWH = np.tile(dims, (ne, 1))
+    g_ref, dj_ref = orc.ancf_precompute(kind, ec, x, y, z, LWH, Binv)
+    assert rel_err(d.RetrieveDsDuPreToCPU().reshape(g_ref.shape), g_ref) < TOL
+    assert rel_err(d.RetrieveDetJToCPU().reshape(dj_ref.shape), dj_ref) < TOL
+    off, cols, vals = d.RetrieveMassCSRToCPU()
+    off_ref, cols_ref = orc.coef_pattern(ec, nc)
+    assert np.array_equal(off, off_ref) and np.array_equal(cols, cols_ref)  # bit-exact
+    assert rel_err(vals, orc.ancf_mass(kind, ec, x, y, z, LWH, Binv, RHO, off, cols)) < TOL
+    ro, ci, _ = s.RetrieveHessianCSR(want_values=False)
+    ro_ref, ci_ref = orc.dof_pattern(off_ref, cols_ref)
+    assert np.array_equal(ro, ro_ref) and np.array_equal(ci, ci_ref)  # bit-exact

@@ -7,7 +7,9 @@ FP64 tolerance: 1e-12 relative to the largest entry (north_star), written at eac
 import numpy as np
 import pytest
 
-from conftest import rel_err
+import os
+
+from conftest import GOLDEN, rel_err
 from oracle import oracle as orc
 
 TOL = 1e-12
@@ -136,3 +138,65 @@ def test_rest_state_and_rigid_motion(o, golden_t10):
     Kd = _dense_from_csr(o, o.tangent(g["x"], mat, 1.0))
     t = np.tile([1.0, 0.0, 0.0], o.nn)
     assert np.abs(Kd @ t).max() < 1e-9 * np.abs(Kd).max()
+
+
+@pytest.mark.parametrize("nb", [2, 3])
+def test_oracle_ancf3243_mass_known_answer(nb):
+    """The oracle's ANCF set-up path (B^-T, shape functions, 6x2x2 mass rule) against the reference's
+    known-answer matrices data/utest/mass_matrix_{2,3}_beam.csv (lib_utest/utest_3243.cc:74-112,159-197)."""
+    from oracle import oracle as orc
+
+    L, W, H, rho = 2.0, 1.0, 1.0, 2700.0
+    nn = nb + 1
+    x = np.zeros(4 * nn); y = np.zeros(4 * nn); z = np.zeros(4 * nn)
+    for i in range(nn):
+        x[4 * i:4 * i + 4] = [i * L, 1, 0, 0]
+        y[4 * i:4 * i + 4] = [0, 0, 1, 0]
+        z[4 * i:4 * i + 4] = [0, 0, 0, 1]
+    conn = np.array([[i, i + 1] for i in range(nb)])
+    ec = orc.ancf_ecoef(3243, conn)
+    off, cols = orc.coef_pattern(ec, 4 * nn)
+    Binv = orc.ancf_binv(3243, [L] * nb, [W] * nb, [H] * nb)
+    vals = orc.ancf_mass(3243, ec, x, y, z, np.tile([L, W, H], (nb, 1)), Binv, rho, off, cols)
+    M = np.zeros((4 * nn, 4 * nn))
+    for i in range(4 * nn):
+        M[i, cols[off[i]:off[i + 1]]] = vals[off[i]:off[i + 1]]
+    ref = np.load(os.path.join(GOLDEN, f"ancf3243_mass_{nb}_beam.npy"))
+    assert np.abs(M - ref).max() < 1e-4  # the reference's tolerance; the CSV carries ~9 significant digits
+    assert np.abs(M - M.T).max() < 1e-9 * np.abs(M).max() and np.linalg.det(M) > 0
+
+
+@pytest.mark.parametrize("kind", [3243, 3443])
+def test_oracle_ancf_precompute_invariants(kind):
+    """sum detJ*w = volume, grad of the partition-of-unity position functions sums to zero, F = I at rest."""
+    from oracle import oracle as orc
+
+    if kind == 3243:
+        L, W, H = 0.5, 0.1, 0.2
+        nn = 4
+        conn = np.array([[i, i + 1] for i in range(nn - 1)])
+        pos = [(i * L, 0.0) for i in range(nn)]
+    else:
+        L, W, H = 0.4, 0.3, 0.05
+        pos = [(i * L, j * W) for i in range(3) for j in range(3)]
+        nid = lambda i, j: i * 3 + j
+        conn = np.array([[nid(i, j), nid(i + 1, j), nid(i + 1, j + 1), nid(i, j + 1)] for i in range(2) for j in range(2)])
+        nn = 9
+    x = np.zeros(4 * nn); y = np.zeros(4 * nn); z = np.zeros(4 * nn)
+    for n, (px, py) in enumerate(pos):
+        x[4 * n:4 * n + 4] = [px, 1, 0, 0]
+        y[4 * n:4 * n + 4] = [py, 0, 1, 0]
+        z[4 * n:4 * n + 4] = [0, 0, 0, 1]
+    ne = conn.shape[0]
+    ec = orc.ancf_ecoef(kind, conn)
+    Binv = orc.ancf_binv(kind, [L] * ne, [W] * ne, [H] * ne)
+    g, dj = orc.ancf_precompute(kind, ec, x, y, z, np.tile([L, W, H], (ne, 1)), Binv)
+    qw = orc.ancf_stiffness_weights(kind)
+    assert abs((dj * qw).sum() - ne * L * W * H) < 1e-12 * ne * L * W * H
+    S = ec.shape[1]
+    coords = np.stack([x, y, z], axis=1)
+    for e in range(ne):
+        for q in range(g.shape[1]):
+            h = g[e, q].reshape(3, S)  # h[j, a]
+            F = coords[ec[e]].T @ h.T
+            assert np.abs(F - np.eye(3)).max() < 1e-12
