@@ -232,6 +232,7 @@ def main():
     if world > 1:
         dist.barrier()
     import tlfea
+    from tlfea import partition
 
     launches0 = tlfea.lib.tlfea_launch_count()
     t_setup = time.perf_counter()
@@ -249,20 +250,8 @@ def main():
     halo = torch.zeros(max(world - 1, 1) * pn3, dtype=torch.float64, device=dev)
 
     def halo_sum():
-        """interface-plane f_int summed over the two ranks that share each plane (NCCL allreduce of
-        the compact interface vector: slot p holds the plane between rank p and p+1)."""
-        if world == 1:
-            return
-        halo.zero_()
-        if slab.has_left:
-            halo[(rank - 1) * pn3: rank * pn3] = f_int[:pn3]
-        if slab.has_right:
-            halo[rank * pn3:(rank + 1) * pn3] = f_int[-pn3:]
-        dist.all_reduce(halo)
-        if slab.has_left:
-            f_int[:pn3] = halo[(rank - 1) * pn3: rank * pn3]
-        if slab.has_right:
-            f_int[-pn3:] = halo[rank * pn3:(rank + 1) * pn3]
+        """interface-plane f_int summed over the two ranks that share each plane (tlfea/partition.py)"""
+        partition.halo_sum(f_int, slab, rank, world, halo, dist)
 
     def step():
         s.Assemble()

@@ -95,3 +95,22 @@ def perturb_global(slab: Slab, amplitude: float, seed: int) -> np.ndarray:
         u = (z >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
         out[:, c] = slab.X[:, c] + amplitude * (2.0 * u - 1.0)
     return out
+
+
+def halo_sum(f_int, slab: Slab, rank: int, world: int, halo, dist):
+    """Sum the interface-plane entries of a nodal vector (3 per node, torch tensor on any device) over the
+    two ranks sharing each plane: one all-reduce of the compact interface vector; slot p of `halo`
+    (length (world-1) * 3 * plane_nodes) holds the plane between rank p and p+1."""
+    if world == 1:
+        return
+    pn3 = 3 * slab.plane_nodes
+    halo.zero_()
+    if slab.has_left:
+        halo[(rank - 1) * pn3: rank * pn3] = f_int[:pn3]
+    if slab.has_right:
+        halo[rank * pn3:(rank + 1) * pn3] = f_int[-pn3:]
+    dist.all_reduce(halo)
+    if slab.has_left:
+        f_int[:pn3] = halo[(rank - 1) * pn3: rank * pn3]
+    if slab.has_right:
+        f_int[-pn3:] = halo[rank * pn3:(rank + 1) * pn3]
