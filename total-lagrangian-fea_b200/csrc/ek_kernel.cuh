@@ -7,24 +7,25 @@
 //   assemble_sparse_hessian_mass  SyncedNewton.cu:213-259
 //   svk_compute_tangent_block     SVK.cuh:35-55
 //
-// Phase E (ek_kernel, element-parallel, FP64-pipe work): ONE WARP PER ELEMENT.
-//   * a warp pulls groups of G consecutive elements; gradN / detJ / connectivity / nodal coordinates of
-//     the NEXT group are in flight (cp.async into a per-warp double buffer) while the current one computes;
-//   * Gauss-point step: lane = (element-in-group, q) builds F, P, and the 6 numbers of
+// Phase E (ek_kernel, element-parallel, FP64-pipe + shared-memory work): ONE WARP PER GROUP OF G ELEMENTS.
+//   * gradN / detJ / connectivity / nodal coordinates of the NEXT group are in flight (cp.async into a
+//     per-warp double buffer) while the current one computes;
+//   * Gauss-point step: lane = (element-in-group, q) builds F, P (SVK + Kelvin-Voigt), u_a = F h_a, the
+//     force partials P dV h_a and the 6 numbers of
 //       M_q = dV [ (h mu + eta) F F^T + h (lambda trE - mu) I ]          (symmetric 3x3)
-//     and leaves them in shared memory;
-//   * block step: lane = (a, g): shape function a and one third of the cyclic diagonals d of the
-//     SYMMETRIC element matrix.  K_ab for b = (a + d) mod 10, d = 0..5 covers all 55 unordered pairs
-//     exactly once (d = 5 only for a < 5).  h_a, u_a = F h_a stay in registers for all 5 points, the
-//     b-side operands are shared-memory reads with <= 10 distinct addresses per warp (one wavefront):
-//       A  = sum_q dV u_a u_b^T   (9 DFMA)      G = sum_q (h_a.h_b) M_q   (3 + 6 DFMA)
-//       K_ab = c1 A + c2 A^T + h mu tr(A) I + G
-//     18 DFMA per (pair, point) instead of the reference's ~170 flop;
-//   * the 55 blocks (495 doubles) go to a global staging record of the element through shared memory so the
-//     write is one contiguous 3 960-byte burst; element forces go to fe[e][a][3].
+//     and leaves them in shared memory; the element force is the fixed-order sum of its 5 point partials;
+//   * block step: two elements at a time, lane = (element, 2x2 tile (I,J), I <= J, of the symmetric 5x5
+//     tile grid of shape-function pairs): per Gauss point the lane loads h, u of its 2+2 shape functions
+//     and M_q once and updates 4 blocks
+//       A  += (dV u_a) u_b^T   (9 DFMA)      G += (h_a.h_b) M_q   (3 + 6 DFMA)
+//     (18 DFMA per (pair, point) instead of the reference's ~170 flop), then
+//       K_ab = c1 A + c2 A^T + h mu tr(A) I + G,   K_ba = K_ab^T;
+//   * the 100 blocks of an element go to its visit-major record [a][b][9] (7 200 B) through a lane-major
+//     shared-memory staging area, so the global write is one contiguous burst per element pair and every
+//     row visit of phase R reads 720 contiguous bytes; element forces go to fe[e][a][3].
 // Phase R (rk_kernel, row-parallel, HBM work): ONE WARP PER COEFFICIENT ROW of H.  The warp zero-fills the
 //   block row in shared memory with M/h on the 3x3 diagonals, adds the row's blocks of every incident element
-//   in ASCENDING ELEMENT ORDER (direct or transposed from the symmetric record), sums the nodal force in the
+//   in ASCENDING ELEMENT ORDER (three coalesced loads per visit record), sums the nodal force in the
 //   same order, and streams the finished 3 scalar CSR rows to H exactly once.
 // No atomics, no searches, fixed summation order => bit-reproducible results.
 #pragma once

@@ -85,6 +85,7 @@ def perturb_global(slab: Slab, amplitude: float, seed: int) -> np.ndarray:
     a counter-based hash of (seed, global node id, component) -> U(-1,1)."""
     gid = slab.node_gid.astype(np.uint64)
     out = np.empty_like(slab.X)
+    old = np.seterr(over="ignore")  # splitmix64 wraps modulo 2^64 by design
     for c in range(3):
         z = gid * np.uint64(3) + np.uint64(c) + np.uint64(seed) * np.uint64(0x9E3779B97F4A7C15)
         # splitmix64
@@ -94,6 +95,7 @@ def perturb_global(slab: Slab, amplitude: float, seed: int) -> np.ndarray:
         z = z ^ (z >> np.uint64(31))
         u = (z >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
         out[:, c] = slab.X[:, c] + amplitude * (2.0 * u - 1.0)
+    np.seterr(**old)
     return out
 
 
