@@ -428,7 +428,6 @@ struct RKArgs {
 };
 
 constexpr int RK_WARPS = 8;
-constexpr int RK_U = 5;  // visits in flight per warp
 constexpr int RK_T = 4;  // rows per ticket
 
 __global__ void k_row_desc(int n, const int *__restrict__ order, const int *__restrict__ off,
@@ -446,8 +445,9 @@ __global__ void k_row_desc(int n, const int *__restrict__ order, const int *__re
   desc[i] = d;
 }
 
-template <int S>
-__global__ void __launch_bounds__(RK_WARPS * 32, 3) rk_kernel(RKArgs p) {
+// RK_U = visits in flight per warp, MINB = resident blocks per SM the register budget is set for
+template <int S, int RK_U, int MINB>
+__global__ void __launch_bounds__(RK_WARPS * 32, MINB) rk_kernel(RKArgs p) {
   static_assert(S * 9 <= 96, "a visit record is read as three coalesced 32-double rows");
   constexpr int VIS = S * 9;
   extern __shared__ double rk_smem[];
@@ -486,13 +486,14 @@ __global__ void __launch_bounds__(RK_WARPS * 32, 3) rk_kernel(RKArgs p) {
       const int vb_r = __shfl_sync(0xffffffffu, dword, r * 8 + 3), nv_r = __shfl_sync(0xffffffffu, dword, r * 8 + 4);
       ea_r[r] = (lane < nv_r) ? p.inc_ea[vb_r + lane] : 0;
     }
-#pragma unroll
+#pragma unroll 1  // one copy of the row body: four unrolled copies overflow the instruction cache
   for (int r = 0; r < RK_T; r++) {
     if (tk * RK_T + r >= p.n_coef) break;
     const int row = __shfl_sync(0xffffffffu, dword, r * 8 + 0), rs = __shfl_sync(0xffffffffu, dword, r * 8 + 1);
     const int deg = __shfl_sync(0xffffffffu, dword, r * 8 + 2), vb = __shfl_sync(0xffffffffu, dword, r * 8 + 3);
     const int nvis = __shfl_sync(0xffffffffu, dword, r * 8 + 4);
-    const int ea_cur = ea_r[r];
+    static_assert(RK_T == 4, "select chain below");
+    const int ea_cur = (r == 0) ? ea_r[0] : (r == 1) ? ea_r[1] : (r == 2) ? ea_r[2] : ea_r[3];
     // Every global load of the row's first phase is issued before anything waits on one:
     // the first batch of block values + slots, the first 10 element forces, the mass row.
     double *fbuf = rowbuf + p.row_stride - 32;

@@ -275,7 +275,7 @@ struct EKCfg {
 };
 static EKCfg ek_cfg() {
   static EKCfg c = [] {
-    EKCfg t{4, 6};
+    EKCfg t{2, 8};
     const char *e = getenv("TLFEA_EK_CFG");  // "65" = groups of 6, 5 warps ... (tuning aid)
     if (e && strlen(e) == 2) t = EKCfg{e[0] - '0', e[1] - '0'};
     return t;
@@ -307,11 +307,11 @@ static int launch_ek_t(tlfea_elem *e, const EKArgs &a) {
 template <bool DAMP, bool TANGENT>
 static int launch_ek_cfg(tlfea_elem *e, const EKArgs &a) {
   const EKCfg c = ek_cfg();
-  if (DAMP) return launch_ek_t<4, 5, DAMP, TANGENT>(e, a);
+  if (DAMP) return launch_ek_t<2, 7, DAMP, TANGENT>(e, a);
   if (c.g == 6 && c.w == 4) return launch_ek_t<6, 4, DAMP, TANGENT>(e, a);
-  if (c.g == 2 && c.w == 8) return launch_ek_t<2, 8, DAMP, TANGENT>(e, a);
+  if (c.g == 4 && c.w == 6) return launch_ek_t<4, 6, DAMP, TANGENT>(e, a);
   if (c.g == 4 && c.w == 5) return launch_ek_t<4, 5, DAMP, TANGENT>(e, a);
-  return launch_ek_t<4, 6, DAMP, TANGENT>(e, a);
+  return launch_ek_t<2, 8, DAMP, TANGENT>(e, a);  // most warps per SM: the kernel is latency / LSU bound
 }
 
 static int ek_chunk_elems() {
@@ -389,9 +389,17 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   r.row_stride = ((e->pat.max_deg * 9 + 32 + 1) | 1);  // block row + 32 doubles for the force gather
   const size_t smem = (size_t)RK_WARPS * r.row_stride * sizeof(double);
   TL_CHECK(smem <= 220 * 1024, "coefficient row too long for the row-reduce kernel (max_deg=%d)", e->pat.max_deg);
-  if (smem > 48 * 1024)
-    TL_CUDA(cudaFuncSetAttribute(rk_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int per_sm = std::max(1, std::min(3, (int)((227 * 1024) / (smem + 2048))));
+  static const int rk_cfg = [] {
+    const char *v = getenv("TLFEA_RK_CFG");  // tuning aid: 0 = (U 5, 3 blocks/SM), 1 = (4, 4), 2 = (8, 2)
+    return v ? atoi(v) : 0;
+  }();
+  const int want_sm = rk_cfg == 1 ? 4 : (rk_cfg == 2 ? 2 : 3);
+  if (smem > 48 * 1024) {
+    TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  const int per_sm = std::max(1, std::min(want_sm, (int)((227 * 1024) / (smem + 2048))));
   const int n_chunks = (int)s->chunk_ptr.size() - 1;
   TL_CUDA(cudaMemsetAsync(s->d_tickets, 0, s->chunk_ptr.size() * sizeof(int), e->stream));
   for (int k = 0; k < n_chunks; k++) {
@@ -404,7 +412,13 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
     r.desc = static_cast<const RowDesc *>(s->d_rowdesc) + r0;
     r.counter = s->d_tickets + k;
     const int blocks = (nr + RK_WARPS * RK_T - 1) / (RK_WARPS * RK_T);
-    TL_LAUNCH((rk_kernel<10>), std::min(blocks, 148 * per_sm), RK_WARPS * 32, smem, e->stream, r);
+    const int grid = std::min(blocks, 148 * per_sm);
+    if (rk_cfg == 1)
+      TL_LAUNCH((rk_kernel<10, 4, 4>), grid, RK_WARPS * 32, smem, e->stream, r);
+    else if (rk_cfg == 2)
+      TL_LAUNCH((rk_kernel<10, 8, 2>), grid, RK_WARPS * 32, smem, e->stream, r);
+    else
+      TL_LAUNCH((rk_kernel<10, 5, 3>), grid, RK_WARPS * 32, smem, e->stream, r);
   }
   TL_CUDA(cudaGetLastError());
   if (s->profile) TL_CUDA(cudaEventRecord(s->ev[3], e->stream));
