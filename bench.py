@@ -206,7 +206,7 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=32, help="cells per edge of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--assembly", type=int, default=-1, help="0 row gather, 1 tiles, 2 row gather in tile order")
+    ap.add_argument("--assembly", type=int, default=-1, help="0 generic row gather, 1 element kernel + row reduce (default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
@@ -379,7 +379,7 @@ def main():
                        "gauss_points": gp_total, "nnz_H_sum_over_ranks": nnz_g, "material": "SVK E=7e8 nu=0.33",
                        "h": H_STEP, "partition": f"x-slabs x{world}, sub-assembled H, NCCL halo sum of f_int",
                        "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
-                       "setup_s": t_setup, "tiles": s.TileStats()},
+                       "setup_s": t_setup},
             "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all,
             "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
         }

@@ -194,15 +194,13 @@ double *tlfea_newton_devptr_g(tlfea_newton *s);
 int tlfea_newton_spmv(tlfea_newton *s, const double *d_x, double *d_y);
 /* sum of the CUDA-event time (ms) of assemble calls since the last reset, and their count */
 int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset);
-/* Assembly kernel selection: 1 (default) = spatial row tiles in shared memory where supported
- * (FEAT10 + SVK), 0 = warp-per-row gather.  Both are deterministic; results agree to rounding. */
+/* Assembly kernel selection: 1 (default) = element kernel + row reduce where supported (FEAT10 + SVK,
+ * csrc/ek_kernel.cuh), 0 = generic warp-per-row gather (all element types and materials).  Both are
+ * deterministic (no atomics); results agree to rounding. */
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode);
-/* phase cycle counters of the tile kernel (only filled by -DTK_TIMING builds): prologue, wait, (unused),
- * stage, barrier, prefetch issue, visits, write-out */
-int tlfea_newton_tile_timing(tlfea_newton *s, unsigned long long *out8, int reset);
-int tlfea_newton_tile_stats(tlfea_newton *s, int *n_tiles, int64_t *n_entries, int *max_rows, int *max_buf);
 /* per-kernel CUDA-event timing of the next assemble calls (0/1) */
 int tlfea_newton_set_profile(tlfea_newton *s, int on);
+/* element-phase, row-phase and remaining (constraint term) milliseconds accumulated while profiling */
 int tlfea_newton_kernel_ms(tlfea_newton *s, double *gp_ms, double *row_ms, double *other_ms);
 
 /* --------------------------------------------------------------- multi-GPU */

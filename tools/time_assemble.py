@@ -6,7 +6,7 @@ sys.path.insert(0, os.path.join(ROOT, "total-lagrangian-fea_b200"))
 import numpy as np, tlfea
 from tlfea import meshgen
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 48
-mode = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+mode = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 morton = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 X, E = meshgen.kuhn_block(n); x = meshgen.perturb(X, 0.05 / n, 1234)
 if morton:

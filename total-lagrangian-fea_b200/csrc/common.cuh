@@ -101,28 +101,6 @@ struct Pattern {
 
 int build_pattern(const int *d_ecoef, int n_elem, int S, int n_coef, cudaStream_t stream, Pattern *out);
 
-// Spatial row tiles for the tile assembly kernel (tiles.cu, tile_kernel.cuh).
-struct Tiles {
-  int n_tiles = 0;
-  int64_t n_entries = 0;          // (tile, element) incidences
-  int max_rows = 0, max_buf = 0;  // largest tile: rows, row-buffer doubles
-  int *d_trow = nullptr;          // [n_coef]       rows in tile (Morton) order
-  int *d_tile_ptr = nullptr;      // [n_tiles+1]    into d_trow
-  int *d_te_ptr = nullptr;        // [n_tiles+1]    into the entry arrays
-  int *d_te_elem = nullptr;       // [n_entries]    element id, ascending inside a tile
-  int batch = 0, warps = 0;       // elements staged per batch, warps per CTA (rows are owned by lrow % warps)
-  int n_batches = 0;
-  int *d_tb_ptr = nullptr;        // [n_tiles+1]    first global batch of a tile
-  int *d_vptr = nullptr;          // [n_batches*warps+1] visit list of (batch, warp)
-  unsigned *d_visit = nullptr;    // [n_visits]     elem-in-batch | a<<8 | local row<<16
-  int *d_vea = nullptr;           // [n_visits]     e*S+a of the visit
-  uint16_t *d_vslot = nullptr;    // [n_visits*S]   column slots of the visit's S blocks
-  int *d_trs = nullptr, *d_tdeg = nullptr;  // [n_coef] CSR row start / degree in tile order
-  int max_entries = 0;            // most elements incident to one tile
-  int *d_err = nullptr;           // [4] device error flags
-  void release();
-};
-
 }  // namespace tlfea
 
 enum { TL_MODEL_SVK = 0, TL_MODEL_MR = 1 };
@@ -170,7 +148,6 @@ struct tlfea_elem {
 };
 
 namespace tlfea {
-int build_tiles(const tlfea_elem *h, int budget_doubles, int max_rows, int batch, int warps, Tiles *out);
 int build_row_order(const tlfea_elem *h, int **d_order);
 int build_completion_order(const tlfea_elem *h, int chunk, int **d_order, std::vector<int> *chunk_ptr);
 }
@@ -178,9 +155,7 @@ int build_completion_order(const tlfea_elem *h, int chunk, int **d_order, std::v
 struct tlfea_newton {
   tlfea_elem *e = nullptr;
   int device = 0;
-  tlfea::Tiles tiles;
-  bool have_tiles = false;
-  int use_tiles = 4;  // assembly: 0 row gather, 1 tiles, 2 row gather in tile order, 3 staged row gather, 4 element kernel + row reduce (default where supported)
+  bool two_phase = true;  // element kernel + row reduce where supported (FEAT10 + SVK); else the generic row gather
   int n_constraints = 0;
   tlfea_newton_params prm{};
   bool analyzed = false, fixed_pattern = false;

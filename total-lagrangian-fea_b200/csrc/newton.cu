@@ -9,8 +9,6 @@
 
 #include "common.cuh"
 #include "kernels.cuh"
-#include "tile_kernel.cuh"
-#include "row2_kernel.cuh"
 #include "ek_kernel.cuh"
 
 namespace tlfea {
@@ -285,7 +283,7 @@ static EKCfg ek_cfg() {
 
 static bool ek_supported(const tlfea_newton *s) {
   const tlfea_elem *e = s->e;
-  return s->use_tiles == 4 && e->type == TLFEA_TYPE_T10 && e->model == TL_MODEL_SVK;
+  return s->two_phase && e->type == TLFEA_TYPE_T10 && e->model == TL_MODEL_SVK;
 }
 
 template <int G, int W, bool DAMP, bool TANGENT>
@@ -425,84 +423,6 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   return TLFEA_OK;
 }
 
-constexpr int TILE_WARPS = 8;
-// Two tilings: one big CTA per SM (large tiles, least element re-staging) or two smaller CTAs per SM
-// (more latency hiding).  TLFEA_TILE_CTAS=1|2 selects; the budget is the row-buffer size in doubles.
-struct TileCfg {
-  int ctas, batch, budget;
-};
-static TileCfg tile_cfg() {
-  static TileCfg c = [] {
-    TileCfg t{1, 12, 18000};
-    const char *e = getenv("TLFEA_TILE_CTAS");
-    if (e && atoi(e) == 2) t = TileCfg{2, 6, 7800};
-    const char *b = getenv("TLFEA_TILE_BUDGET");
-    if (b && atoi(b) > 0) t.budget = atoi(b);
-    return t;
-  }();
-  return c;
-}
-
-static bool tiles_supported(const tlfea_newton *s) {
-  return s->use_tiles && s->e->type == TLFEA_TYPE_T10 && s->e->model == TL_MODEL_SVK &&
-         s->e->pat.max_inc <= 255 && s->e->pat.max_deg * 9 <= tile_cfg().budget;
-}
-
-static int ensure_tiles(tlfea_newton *s) {
-  if (s->have_tiles) return TLFEA_OK;
-  const TileCfg c = tile_cfg();
-  TL_TRY(build_tiles(s->e, c.budget, TK_MAX_ROWS, c.batch, TILE_WARPS, &s->tiles));
-  TL_CHECK(s->tiles.max_entries <= TK_MAX_ENT, "tile with %d incident elements exceeds the kernel's list (%d)",
-           s->tiles.max_entries, TK_MAX_ENT);
-  s->have_tiles = true;
-  return TLFEA_OK;
-}
-
-template <int B, int CTAS>
-static int launch_tile_t(tlfea_newton *s, const TileArgs &a) {
-  const size_t smem = TileShape<10, 5, TILE_WARPS, B>::smem_bytes(a.buf_doubles);
-  TL_CUDA(cudaFuncSetAttribute(tile_kernel<10, 5, TILE_WARPS, B, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)smem));
-  TL_LAUNCH((tile_kernel<10, 5, TILE_WARPS, B, CTAS>), a.n_tiles, TILE_WARPS * 32, smem, s->e->stream, a);
-  TL_CUDA(cudaGetLastError());
-  return TLFEA_OK;
-}
-
-static int launch_tile(tlfea_newton *s, const RowArgs &r) {
-  const Tiles &t = s->tiles;
-  TileArgs a;
-  a.n_tiles = t.n_tiles;
-  a.trow = t.d_trow;
-  a.trs = t.d_trs;
-  a.tdeg = t.d_tdeg;
-  a.tile_ptr = t.d_tile_ptr;
-  a.te_ptr = t.d_te_ptr;
-  a.te_elem = t.d_te_elem;
-  a.tb_ptr = t.d_tb_ptr;
-  a.vptr = t.d_vptr;
-  a.visit = t.d_visit;
-  a.vea = t.d_vea;
-  a.vslot = t.d_vslot;
-  a.mass = r.mass;
-  a.rec = r.rec;
-  a.gradN = r.gradN;
-  a.detJ = r.detJ;
-  a.fe = r.fe;
-  a.qw = r.qw;
-  a.inv_h = r.inv_h;
-  a.c1 = r.c1;
-  a.c2 = r.c2;
-  a.c3 = r.c3;
-  a.c4 = r.c4;
-  a.mu = r.mu;
-  a.H = r.H;
-  a.f_int = r.f_int;
-  a.buf_doubles = tile_cfg().budget;
-  a.timing = reinterpret_cast<unsigned long long *>(t.d_err + 4);
-  if (tile_cfg().ctas == 2) return launch_tile_t<6, 2>(s, a);
-  return launch_tile_t<12, 1>(s, a);
-}
-
 static int do_assemble(tlfea_newton *s, bool tangent) {
   tlfea_elem *e = s->e;
   TL_CHECK(e->is_precomputed, "CalcDnDuPre/CalcDsDuPre must run before assembling");
@@ -564,28 +484,7 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
     const int grid = std::min(rows_blocks, 148 * 32);
     a.perm = nullptr;
     a.chunk = ROW_WARPS;
-    if (s->use_tiles == 2 && tiles_supported(s)) {  // row gather in Morton-tile order
-      TL_TRY(ensure_tiles(s));
-      a.perm = s->tiles.d_trow;
-      a.chunk = 64;
-    }
-    const int r2_passes = R2_GROUP * ((e->pat.max_inc + 2) / 3);
-    if (s->use_tiles == 3 && tiles_supported(s) && r2_passes <= 32) {  // row gather + cp.async operand staging
-      TL_TRY(ensure_tiles(s));
-      a.perm = s->tiles.d_trow;
-      using Sh = Row2Shape<10, 5>;
-      const int wd = Sh::warp_doubles(e->pat.max_deg), md = Sh::mrow_doubles(e->pat.max_deg);
-      const size_t smem2 = (size_t)R2_WARPS * wd * sizeof(double);
-      TL_CHECK(smem2 <= 220 * 1024, "row too long for the row2 kernel");
-      TL_CUDA(cudaFuncSetAttribute(row2_kernel<10, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-      const int n_chunks = (e->n_coef + R2_CHUNK - 1) / R2_CHUNK;
-      const int per_sm = std::max(1, (int)((227 * 1024) / (smem2 + 1024)));
-      TL_LAUNCH((row2_kernel<10, 5>), std::min(n_chunks, 148 * per_sm * 4), R2_WARPS * 32, smem2, e->stream, a, wd, md);
-      TL_CUDA(cudaGetLastError());
-    } else if (s->use_tiles == 1 && tiles_supported(s)) {
-      TL_TRY(ensure_tiles(s));
-      TL_TRY(launch_tile(s, a));
-    } else {
+    {
       switch (e->type) {
         case TLFEA_TYPE_T10: TL_TRY((launch_row_t<10, 5>(s, a, grid, smem, damp))); break;
         case TLFEA_TYPE_3243: TL_TRY((launch_row_t<8, 12>(s, a, grid, smem, damp))); break;
@@ -609,11 +508,6 @@ static int collect_timing(tlfea_newton *s, bool tangent) {
   TL_CUDA(cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]));
   s->ms_total += ms;
   s->calls++;
-  if (s->have_tiles && tangent) {
-    int flag = 0;
-    TL_CUDA(cudaMemcpy(&flag, s->tiles.d_err, sizeof(int), cudaMemcpyDeviceToHost));
-    if (flag) return fail(TLFEA_ERR_CUDA, "tile kernel: ordered-commit wait timed out (device flag %d)", flag);
-  }
   if (s->profile && tangent) {
     float a = 0, b = 0, c = 0;
     cudaEventElapsedTime(&a, s->ev[0], s->ev[2]);
@@ -730,7 +624,6 @@ int tlfea_newton_destroy(tlfea_newton *s) {
   if (s->d_rowdesc) cudaFree(s->d_rowdesc);
   s->d_rowdesc = nullptr;
   dfree(s->d_tickets);
-  s->tiles.release();
   dfree(s->d_v);
   dfree(s->d_v_prev);
   dfree(s->d_lambda);
@@ -1025,22 +918,8 @@ int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset
   return TLFEA_OK;
 }
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode) {
-  TL_CHECK(s && mode >= 0 && mode <= 4, "mode must be 0..4 (0 row gather, 1 tiles, 2 gather in tile order, 3 staged gather, 4 element kernel + row reduce)");
-  s->use_tiles = mode;
-  return TLFEA_OK;
-}
-int tlfea_newton_tile_timing(tlfea_newton *s, unsigned long long *out8, int reset) {
-  TL_CHECK(s && s->have_tiles && out8, "no tiles");
-  TL_CUDA(cudaMemcpy(out8, s->tiles.d_err + 4, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-  if (reset) TL_CUDA(cudaMemset(s->tiles.d_err + 4, 0, 8 * sizeof(unsigned long long)));
-  return TLFEA_OK;
-}
-int tlfea_newton_tile_stats(tlfea_newton *s, int *n_tiles, int64_t *n_entries, int *max_rows, int *max_buf) {
-  TL_CHECK(s, "null handle");
-  if (n_tiles) *n_tiles = s->have_tiles ? s->tiles.n_tiles : 0;
-  if (n_entries) *n_entries = s->have_tiles ? s->tiles.n_entries : 0;
-  if (max_rows) *max_rows = s->have_tiles ? s->tiles.max_rows : 0;
-  if (max_buf) *max_buf = s->have_tiles ? s->tiles.max_buf : 0;
+  TL_CHECK(s && (mode == 0 || mode == 1), "mode must be 0 (generic row gather) or 1 (element kernel + row reduce)");
+  s->two_phase = (mode == 1);
   return TLFEA_OK;
 }
 int tlfea_newton_set_profile(tlfea_newton *s, int on) {

@@ -113,8 +113,6 @@ _SIGS = {
     "tlfea_newton_spmv": (C.c_int, [c_vp, c_vp, c_vp]),
     "tlfea_newton_timing": (C.c_int, [c_vp, c_dp, c_ip, C.c_int]),
     "tlfea_newton_set_assembly": (C.c_int, [c_vp, C.c_int]),
-    "tlfea_newton_tile_timing": (C.c_int, [c_vp, C.POINTER(C.c_uint64), C.c_int]),
-    "tlfea_newton_tile_stats": (C.c_int, [c_vp, c_ip, c_i64p, c_ip, c_ip]),
     "tlfea_newton_set_profile": (C.c_int, [c_vp, C.c_int]),
     "tlfea_newton_kernel_ms": (C.c_int, [c_vp, c_dp, c_dp, c_dp]),
     "tlfea_dist_pack": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),

@@ -129,13 +129,8 @@ class SyncedNewtonSolver(SolverBase):
         return ms.value, calls.value
 
     def SetAssembly(self, mode: int):
-        """1 = spatial row tiles (default where supported), 0 = warp-per-row gather."""
+        """1 = element kernel + row reduce (default where supported: FEAT10 + SVK), 0 = generic warp-per-row gather."""
         check(lib.tlfea_newton_set_assembly(self._h, int(mode)))
-
-    def TileStats(self):
-        nt, mr, mb, ne = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int64(0)
-        check(lib.tlfea_newton_tile_stats(self._h, C.byref(nt), C.byref(ne), C.byref(mr), C.byref(mb)))
-        return {"n_tiles": nt.value, "n_entries": ne.value, "max_rows": mr.value, "max_buf": mb.value}
 
     def SetProfile(self, on: bool):
         check(lib.tlfea_newton_set_profile(self._h, int(on)))
