@@ -206,6 +206,7 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=32, help="cells per edge of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-newton", action="store_true")
     ap.add_argument("--assembly", type=int, default=-1, help="0 generic row gather, 1 element kernel + row reduce (default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -364,6 +365,28 @@ def main():
                "what": "UpdatePositions(host x,y,z) -> Assemble -> halo sum -> Residual ||g|| -> RetrieveInternalForceToCPU; "
                        "H stays device-resident for the solver, as in the reference"}
 
+    # ---- second half of the metric: Newton iterations / s, single GPU only.
+    # One inner iteration = force + H assembly, residual + norm, block-Jacobi PCG with a FIXED 50 iterations
+    # (cuDSS is not in this image), velocity / position update -- OneStepNewtonCuDSS, SyncedNewton.cu:1043-1119.
+    newton = None
+    if world == 1 and not args.no_newton:
+        s.SetParameters(tlfea.SyncedNewtonParams(1e-4, 0.0, 1e-6, ALM_RHO, 1, 2, H_STEP))
+        s.SetPCG(50, 0.0)
+        s.Solve()  # warm-up (allocates the PCG vectors)
+        d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+        s.Setup()
+        torch.cuda.synchronize()
+        n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0.record()
+        s.Solve()
+        n1.record()
+        torch.cuda.synchronize()
+        st = s.LastStats()
+        nms = n0.elapsed_time(n1)
+        newton = {"value": st["newton_iters"] / (nms * 1e-3), "unit": "Newton iterations/s", "newton_iters": st["newton_iters"],
+                  "pcg_iters": st["pcg_iters"], "ms_per_newton_iter": nms / max(st["newton_iters"], 1),
+                  "linear_solver": "block-Jacobi PCG, fixed 50 iterations per Newton iteration", "n_dofs": s.n_dofs}
+
     cpu_base = None
     if rank == 0 and not args.no_cpu_baseline:
         gps, threads, desc, dt = cpu_sample(args.cpu_n, 5)
@@ -381,7 +404,7 @@ def main():
                        "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
                        "setup_s": t_setup},
             "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all,
-            "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
+            "newton": newton, "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
         }
         print(json.dumps(line))
     if world > 1:
