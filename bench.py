@@ -320,8 +320,13 @@ def main():
     dom_is_row = row_ms >= gp_ms
     dom_ms = max(row_ms if dom_is_row else gp_ms, 1e-9)
     achieved = algo_b / (dom_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "rk_kernel<10>" if dom_is_row else "ek_kernel<4,6,0,1>", "achieved": achieved, "peak": hbm_peak,
-                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+    # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full on this workload (n = 119, one GPU):
+    # profiles/r1i_ncu_full_ek_rk_n119.txt.  Other sizes were not captured.
+    ncu_traffic = {("rk", 119): 91.930448e9 + 29.111833e9, ("ek", 119): 14.840199e9 + 75.169257e9}
+    traffic = ncu_traffic.get(("rk" if dom_is_row else "ek", args.n)) if world == 1 else None
+    roofline = {"bound": "hbm", "kernel": "rk_kernel<10,5,3>" if dom_is_row else "ek_kernel<2,8,0,1>", "achieved": achieved, "peak": hbm_peak,
+                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
+                "traffic_unit": "bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                 "algorithmic_bytes_per_launch": algo_b, "kernel_ms": dom_ms, "rk_kernel_ms": row_ms, "ek_kernel_ms": gp_ms,
                 "step_share": dom_ms / max(ms_step, 1e-9)}
