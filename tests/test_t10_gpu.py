@@ -226,3 +226,38 @@ def test_assembly_kernels_agree(mesh, damp):
     assert rel_err(H1[~big], H0[~big]) < 1e-14
     assert rel_err(H1[big], H0[big]) < 1e-14
     assert rel_err(f1, f0) < 1e-14
+
+
+@pytest.mark.parametrize("case", ["permuted", "odd_count", "unused_nodes", "single_element"])
+def test_general_numbering_and_ragged_meshes(case):
+    """Nothing in the path may depend on the structured numbering of the synthetic block: random element and
+    node renumbering, an odd element count (the element kernel works on pairs and groups), nodes that no element
+    touches (empty H rows), and a single element."""
+    from oracle import oracle as orc
+    from tlfea import meshgen
+
+    X, E = meshgen.kuhn_block(3)
+    rng = np.random.Generator(np.random.PCG64(99))
+    if case == "permuted":
+        pn = rng.permutation(X.shape[0])          # new id of old node
+        Xp = np.empty_like(X); Xp[pn] = X
+        E = pn[E][rng.permutation(E.shape[0])].astype(np.int32)
+        X = Xp
+    elif case == "odd_count":
+        E = E[:E.shape[0] - 5]                     # 157 elements
+    elif case == "unused_nodes":
+        E = E[rng.permutation(E.shape[0])[:40]]    # many nodes lose all their elements
+    else:
+        E = E[7:8]
+    x = meshgen.perturb(X, 0.05 / 3, 4321)
+    d, s = _make(X, np.ascontiguousarray(E))
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    s.Assemble()
+    o = orc.T10Oracle(np.ascontiguousarray(E), X)
+    mat = orc.Material.svk(E_MOD, NU)
+    f_ref, _, _ = o.force(x, mat)
+    H_ref = o.hessian(x, mat, H_STEP, RHO)
+    off, cols, _ = d.RetrieveMassCSRToCPU()
+    assert np.array_equal(off, o.off) and np.array_equal(cols, o.cols)
+    assert rel_err(d.RetrieveInternalForceToCPU(), f_ref) < TOL
+    assert rel_err(s.RetrieveHessianValues(), H_ref) < TOL
