@@ -261,3 +261,48 @@ def test_general_numbering_and_ragged_meshes(case):
     assert np.array_equal(off, o.off) and np.array_equal(cols, o.cols)
     assert rel_err(d.RetrieveInternalForceToCPU(), f_ref) < TOL
     assert rel_err(s.RetrieveHessianValues(), H_ref) < TOL
+
+
+def test_full_size_properties():
+    """Size-independent properties at a size the oracle cannot check in seconds (n = 40: 384 000 tets, 1.9 M Gauss
+    points): internal forces self-equilibrate (sum f = 0, sum x cross f = 0: frame indifference of SVK),
+    H is symmetric (y.Hz = z.Hy), K annihilates rigid translations (H t = (M/h) t), H is reproducible bit for bit."""
+    import torch
+    from tlfea import meshgen
+
+    n = 40
+    X, E = meshgen.kuhn_block(n)
+    x = meshgen.perturb(X, 0.05 / n, 1234)
+    d, s = _make(X, E)
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    s.Assemble()
+    f = d.RetrieveInternalForceToCPU().reshape(-1, 3)
+    scale = np.abs(f).sum()
+    assert np.abs(f.sum(axis=0)).max() < 1e-12 * scale
+    assert np.abs(np.cross(x, f).sum(axis=0)).max() < 1e-12 * scale
+    nd = 3 * X.shape[0]
+    g = torch.Generator(device="cpu").manual_seed(5)
+    y = torch.rand(nd, dtype=torch.float64, generator=g).cuda()
+    z = torch.rand(nd, dtype=torch.float64, generator=g).cuda()
+    Hy, Hz = torch.empty_like(y), torch.empty_like(z)
+    torch.cuda.synchronize()
+    s.SpMV(y.data_ptr(), Hy.data_ptr())
+    s.SpMV(z.data_ptr(), Hz.data_ptr())
+    d.Sync()
+    a, b = torch.dot(z, Hy).item(), torch.dot(y, Hz).item()
+    assert abs(a - b) < 1e-12 * abs(a)
+    # rigid translation: the tangent part vanishes, the mass part remains
+    t = torch.zeros(nd, dtype=torch.float64).cuda(); t[0::3] = 1.0
+    Ht = torch.empty_like(t)
+    torch.cuda.synchronize()
+    s.SpMV(t.data_ptr(), Ht.data_ptr())
+    d.Sync()
+    off, cols, mvals = d.RetrieveMassCSRToCPU()
+    row_sum = np.add.reduceat(mvals, off[:-1]) / H_STEP
+    ht = Ht.cpu().numpy().reshape(-1, 3)
+    hmax = np.abs(s.RetrieveHessianValues()).max()
+    assert np.abs(ht[:, 0] - row_sum).max() < 1e-11 * hmax
+    assert np.abs(ht[:, 1:]).max() < 1e-11 * hmax
+    H1 = s.RetrieveHessianValues()
+    s.Assemble()
+    assert np.array_equal(H1, s.RetrieveHessianValues())

@@ -132,6 +132,10 @@ class SyncedNewtonSolver(SolverBase):
         """1 = element kernel + row reduce (default where supported: FEAT10 + SVK), 0 = generic warp-per-row gather."""
         check(lib.tlfea_newton_set_assembly(self._h, int(mode)))
 
+    def SpMV(self, d_x: int, d_y: int):
+        """y = H x on the device with the assembled values; d_x, d_y are device pointers to 3*n_coef doubles."""
+        check(lib.tlfea_newton_spmv(self._h, C.c_void_p(int(d_x)), C.c_void_p(int(d_y))))
+
     def SetProfile(self, on: bool):
         check(lib.tlfea_newton_set_profile(self._h, int(on)))
 
