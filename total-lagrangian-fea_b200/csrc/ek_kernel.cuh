@@ -71,7 +71,18 @@ constexpr int EK_REC = 9;     // per Gauss point: M(6) | dV | pad(2); odd stride
 constexpr int EK_GQ = 31;     // stride of the per-(element, point) u / force-partial rows (30 used)
 constexpr int EK_VIS = 90;    // doubles of one visit record: K_ab, b = 0..9
 constexpr int EK_ELEM = 900;  // doubles of one element record: [a][b][9]
-constexpr int EK_LS = 73;     // staging stride per lane: 8 blocks x 9 (+1: odd => conflict-free lane-major stores)
+// Staging of one element's block records on the way to global memory.  A chunk (I, p) holds rows a = 2I, 2I+1 of
+// block columns b = 2p, 2p+1 as [a & 1][18 doubles].  Chunk bases are chosen so that, per half warp (the unit the
+// shared-memory pipe serves for 64-bit accesses), the 15 tiles of an element store to 15 distinct banks -- direct
+// and transposed -- and a row of 90 doubles reads back linearly without conflicts: base(I, p) = 3 I + 2 p (mod 16),
+// except chunk (4, 4) which sits one bank lower (found by exhaustive search; 134 wavefronts per element against
+// 132 ideal).
+constexpr int EK_CRS = 195;                 // stride of a row-pair region (186 used), = 3 (mod 16)
+constexpr int EK_CX = 193;                  // offset of the exception chunk (4, 4) in its region
+constexpr int EK_ES = 4 * EK_CRS + EK_CX + 36;  // staged element
+__host__ __device__ constexpr int ek_chunk_off(int I, int p) {
+  return I * EK_CRS + ((I == 4 && p == 4) ? EK_CX : 18 * p + 96 * (p & 1));
+}
 
 template <int G, bool DAMP>
 struct EKShape {
@@ -81,7 +92,7 @@ struct EKShape {
   static constexpr int EC_D = (G * 5 + 1) / 2 * 2;  // G*10 ints
   static constexpr int U_D = G * 5 * EK_GQ;         // u = F h per (element, point)
   static constexpr int REC_D = G * 5 * EK_REC;
-  static constexpr int K_D = 32 * EK_LS;            // lane-major block staging of the element pair in flight; also the force partials
+  static constexpr int K_D = 2 * EK_ES;             // chunked staging of the element pair in flight; also the force partials
   static constexpr int OFF_H = 0;
   static constexpr int OFF_DJ = OFF_H + 2 * H_D;
   static constexpr int OFF_X = OFF_DJ + 2 * DJ_D;
@@ -104,18 +115,6 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
   double *wb = ek_smem + (size_t)warp * Sh::WARP_D;
   double *s_u = wb + Sh::OFF_U, *s_rec = wb + Sh::OFF_REC, *s_k = wb + Sh::OFF_K;
   double *s_fp = s_k;  // force partials live in the record staging before the block step needs it
-  // record position (a, b, k) -> staging offset of the producing lane (tile, slot, k); built once per block
-  __shared__ uint16_t s_map[EK_ELEM];
-  for (int r = threadIdx.x; r < EK_ELEM; r += W * 32) {
-    const int blk = r / 9, k = r - blk * 9, ra = blk / 10, rb = blk - ra * 10;
-    const int I = ra >> 1, J = rb >> 1;
-    const int lo = min(I, J), hi = max(I, J);
-    const int tile_id = (lo == 0 ? 0 : lo == 1 ? 5 : lo == 2 ? 9 : lo == 3 ? 12 : 14) + (hi - lo);
-    const int t8 = (I <= J) ? ((ra & 1) * 2 + (rb & 1)) : (4 + (rb & 1) * 2 + (ra & 1));
-    s_map[r] = (uint16_t)(tile_id * EK_LS + t8 * 9 + k);
-  }
-  __syncthreads();
-
   const int n_groups = (p.n_elem + G - 1) / G;
   const int gstride = gridDim.x * W;
   const int g_first = blockIdx.x * W + warp;
@@ -165,10 +164,10 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
   cp_async_commit();
 
   // block step: lane = (element of the pair, 2x2 tile (I, J), I <= J, of the 5x5 tile grid)
-  const int el2 = (lane >= 15) ? 1 : 0;
-  int tile = lane - 15 * el2;
-  if (tile > 14) tile = 14;  // lanes 30, 31 shadow the last tile and never store
-  const bool lane_on = lane < 30;
+  const int el2 = lane >> 4;  // one element per half warp
+  int tile = lane & 15;
+  const bool lane_on = tile < 15;
+  if (tile > 14) tile = 14;  // lanes 15, 31 shadow the last tile and never store
   int tI, tJ;
   if (tile < 5) {
     tI = 0; tJ = tile;
@@ -182,6 +181,18 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
     tI = 4; tJ = 4;
   }
   const int a1 = 2 * tI, b1 = 2 * tJ;
+  const int st_d = el2 * EK_ES + ek_chunk_off(tI, tJ);  // staging chunk of the tile, and of its transpose
+  const int st_t = el2 * EK_ES + ek_chunk_off(tJ, tI);
+  // copy-out: lane reads positions lane, lane + 32, lane + 64 of a 90-double record row
+  int cp_off[3], cp_x2;
+  {
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const int pos = lane + 32 * j, pp = pos / 18;
+      cp_off[j] = 18 * pp + 96 * (pp & 1) + (pos - 18 * pp);
+    }
+    cp_x2 = (lane + 64) / 18 == 4 ? EK_CX + (lane + 64 - 72) : cp_off[2];
+  }
 
   int it = 0;
   for (int grp = g_first; grp < n_groups; grp += gstride, it++) {
@@ -362,7 +373,6 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
         }
         // h K_ab + C_ab = c1 A + c2 A^T + c4 mu tr(A) I + G      (SVK.cuh:35-55, FEAT10DataFunc.cuh:695-762)
         if (on) {
-          double *ke = s_k + lane * EK_LS;
 #pragma unroll
           for (int ta = 0; ta < 2; ta++)
 #pragma unroll
@@ -379,11 +389,11 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
               k[6] = p.c1 * A[t][6] + p.c2 * A[t][2] + Gs[t][2];
               k[7] = p.c1 * A[t][7] + p.c2 * A[t][5] + Gs[t][4];
               k[8] = p.c1 * A[t][8] + p.c2 * A[t][8] + Gs[t][5] + dg;
-              double *d1 = ke + t * 9;
+              double *d1 = s_k + st_d + ta * 18 + tb * 9;
 #pragma unroll
               for (int i = 0; i < 9; i++) d1[i] = k[i];
               if (tI != tJ) {  // K_ba = K_ab^T
-                double *d2 = ke + (4 + t) * 9;
+                double *d2 = s_k + st_t + tb * 18 + ta * 9;
 #pragma unroll
                 for (int i = 0; i < 3; i++)
 #pragma unroll
@@ -395,9 +405,19 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
         // the pair's records are contiguous in global memory: one coalesced burst
         const int npair = min(2, ne - pr);
         double *dst = p.stage + (int64_t)(e0 + pr) * EK_ELEM;
-        for (int i = lane; i < npair * EK_ELEM; i += 32) {
-          const int second = (i >= EK_ELEM) ? 1 : 0;
-          dst[i] = s_k[s_map[i - second * EK_ELEM] + second * 15 * EK_LS];
+        for (int e = 0; e < npair; e++) {
+          const double *se = s_k + e * EK_ES;
+          double *de = dst + e * EK_ELEM + lane;
+#pragma unroll
+          for (int I = 0; I < 5; I++)
+#pragma unroll
+            for (int ta = 0; ta < 2; ta++) {
+              const double *sr = se + I * EK_CRS + ta * 18;
+              double *dr = de + (2 * I + ta) * EK_VIS;
+              dr[0] = sr[cp_off[0]];
+              dr[32] = sr[cp_off[1]];
+              if (lane < 26) dr[64] = sr[I == 4 ? cp_x2 : cp_off[2]];
+            }
         }
         __syncwarp();
       }

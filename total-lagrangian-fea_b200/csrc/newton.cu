@@ -305,7 +305,8 @@ static int launch_ek_t(tlfea_elem *e, const EKArgs &a) {
 template <bool DAMP, bool TANGENT>
 static int launch_ek_cfg(tlfea_elem *e, const EKArgs &a) {
   const EKCfg c = ek_cfg();
-  if (DAMP) return launch_ek_t<2, 7, DAMP, TANGENT>(e, a);
+  if (DAMP) return launch_ek_t<2, 8, DAMP, TANGENT>(e, a);
+  if (c.g == 2 && c.w == 9) return launch_ek_t<2, 9, DAMP, TANGENT>(e, a);
   if (c.g == 6 && c.w == 4) return launch_ek_t<6, 4, DAMP, TANGENT>(e, a);
   if (c.g == 4 && c.w == 6) return launch_ek_t<4, 6, DAMP, TANGENT>(e, a);
   if (c.g == 4 && c.w == 5) return launch_ek_t<4, 5, DAMP, TANGENT>(e, a);
