@@ -67,8 +67,31 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 #endif
 
+// TMA bulk copy (cp.async.bulk) of a contiguous global range into shared memory, completion on an mbarrier.
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+  const unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(b), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load(void *smem, const void *gmem, unsigned bytes, uint64_t *bar) {
+  const unsigned b = (unsigned)__cvta_generic_to_shared(bar), s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(b), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(s),
+               "l"(gmem), "r"(bytes), "r"(b)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
+  const unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+  asm volatile(
+      "{\n.reg .pred p;\nWAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}\n" ::"r"(b),
+      "r"(parity)
+      : "memory");
+}
+
 constexpr int EK_REC = 9;     // per Gauss point: M(6) | dV | pad(2); odd stride => conflict-free lane writes
-constexpr int EK_GQ = 31;     // stride of the per-(element, point) u / force-partial rows (30 used)
+constexpr int EK_GQ = 33;     // stride of the per-(element, point) u / force-partial rows (30 used); = 1 (mod 16)
 constexpr int EK_VIS = 90;    // doubles of one visit record: K_ab, b = 0..9
 constexpr int EK_ELEM = 900;  // doubles of one element record: [a][b][9]
 // Staging of one element's block records on the way to global memory.  A chunk (I, p) holds rows a = 2I, 2I+1 of
@@ -115,6 +138,12 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
   double *wb = ek_smem + (size_t)warp * Sh::WARP_D;
   double *s_u = wb + Sh::OFF_U, *s_rec = wb + Sh::OFF_REC, *s_k = wb + Sh::OFF_K;
   double *s_fp = s_k;  // force partials live in the record staging before the block step needs it
+  __shared__ uint64_t s_bar[W][2];  // per warp, per buffer: the bulk copy of gradN has landed
+  if (lane == 0) {
+    mbar_init(&s_bar[warp][0], 1);
+    mbar_init(&s_bar[warp][1], 1);
+  }
+  __syncwarp();
   const int n_groups = (p.n_elem + G - 1) / G;
   const int gstride = gridDim.x * W;
   const int g_first = blockIdx.x * W + warp;
@@ -134,7 +163,7 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
     const int ne = min(G, p.n_elem - e0);
     double *dh = wb + Sh::OFF_H + buf * Sh::H_D;
     const double *sh = p.gradN + (int64_t)e0 * 150;
-    for (int i = lane; i < ne * 75; i += 32) cp_async16(dh + 2 * i, sh + 2 * i);
+    if (lane == 0) bulk_load(dh, sh, ne * 1200u, &s_bar[warp][buf]);  // one TMA bulk copy: gradN of the group
     double *dj = wb + Sh::OFF_DJ + buf * Sh::DJ_D;
     const double *sj = p.detJ + (int64_t)e0 * 5;
     for (int i = lane; i < ne * 5; i += 32) cp_async8(dj + i, sj + i);
@@ -198,6 +227,7 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
   for (int grp = g_first; grp < n_groups; grp += gstride, it++) {
     const int buf = it & 1;
     cp_async_wait_all();
+    mbar_wait(&s_bar[warp][buf], (it >> 1) & 1);
     __syncwarp();
     // next group's data (its connectivity landed with the wait above) and the one after's connectivity
     issue_ec(grp + 2 * gstride, buf);
@@ -292,11 +322,13 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
       double *uq = s_u + lane * EK_GQ;
 #pragma unroll
       for (int aa = 0; aa < 10; aa++) {
-        const double ha[3] = {hq[aa], hq[10 + aa], hq[20 + aa]};
+        int ar = aa + rot;  // same rotation as above keeps the gradN reads and these stores conflict-free
+        if (ar >= 10) ar -= 10;
+        const double ha[3] = {hq[ar], hq[10 + ar], hq[20 + ar]};
 #pragma unroll
         for (int i = 0; i < 3; i++) {
-          fpq[aa * 3 + i] = P[i][0] * ha[0] + P[i][1] * ha[1] + P[i][2] * ha[2];
-          if (TANGENT) uq[i * 10 + aa] = F[i][0] * ha[0] + F[i][1] * ha[1] + F[i][2] * ha[2];
+          fpq[ar * 3 + i] = P[i][0] * ha[0] + P[i][1] * ha[1] + P[i][2] * ha[2];
+          if (TANGENT) uq[i * 10 + ar] = F[i][0] * ha[0] + F[i][1] * ha[1] + F[i][2] * ha[2];
         }
       }
       if (TANGENT) {

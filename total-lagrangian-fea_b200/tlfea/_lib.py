@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libtlfea_b200.so")
+LIB_PATH = os.environ.get("TLFEA_LIB", os.path.join(os.path.dirname(_HERE), "lib", "libtlfea_b200.so"))  # TLFEA_LIB: A/B builds
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int)
