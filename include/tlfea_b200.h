@@ -99,6 +99,9 @@ int tlfea_elem_set_mooney_rivlin(tlfea_elem *h, double mu10, double mu01, double
 int tlfea_elem_set_external_force(tlfea_elem *h, const double *f_ext, int n);
 /* SetNodalFixed(VectorXi)  FEAT10Data.cu:728-749 (a second call is an error, as in the reference) */
 int tlfea_elem_set_nodal_fixed(tlfea_elem *h, const int *fixed_nodes, int n_fixed);
+/* UpdateNodalFixed (FEAT10Data.cu:751-839): replace the pinned set.  A solver already bound to the element keeps
+ * working if the number of pinned nodes is unchanged (its constraint slots are re-derived on the next call). */
+int tlfea_elem_update_nodal_fixed(tlfea_elem *h, const int *fixed_nodes, int n_fixed);
 /* SetLinearConstraintsCSR(offsets,columns,values,rhs)  ANCF3243Data.cuh:810-940: rows = constraints, cols = DOFs */
 int tlfea_elem_set_linear_constraints_csr(tlfea_elem *h, int n_constraints, const int *offsets, const int *columns,
                                           const double *values, const double *rhs);
@@ -125,7 +128,9 @@ int tlfea_elem_n_coef(const tlfea_elem *h);        /* get_n_coef() */
 int tlfea_elem_n_shape(const tlfea_elem *h);
 int tlfea_elem_n_qp(const tlfea_elem *h);
 int tlfea_elem_n_constraint(const tlfea_elem *h);
-int64_t tlfea_elem_mass_nnz(const tlfea_elem *h);
+int64_t tlfea_elem_mass_nnz(const tlfea_elem *h); /* with linear CSR constraints: an upper bound (the stored pattern
+                                                    * also holds the J^T J couplings; get_mass_csr filters them, and
+                                                    * offsets[n_coef] is the exact count) */
 
 /* Retrieve*ToCPU  FEAT10Data.cu:603-726; out buffers are caller-allocated */
 int tlfea_elem_get_internal_force(tlfea_elem *h, double *out, int n);                    /* 3*n_coef */

@@ -55,6 +55,40 @@ struct ElementBase {
   void SetNodalFixed(const std::vector<int> &nodes) {
     TLFEA_OR_DIE(tlfea_elem_set_nodal_fixed(d_data, nodes.data(), (int)nodes.size()));
   }
+  void UpdateNodalFixed(const std::vector<int> &nodes) {
+    TLFEA_OR_DIE(tlfea_elem_update_nodal_fixed(d_data, nodes.data(), (int)nodes.size()));
+  }
+  void SetLinearConstraintsCSR(const std::vector<int> &offsets, const std::vector<int> &columns,
+                               const std::vector<double> &values, const std::vector<double> &rhs) {
+    TLFEA_OR_DIE(tlfea_elem_set_linear_constraints_csr(d_data, (int)offsets.size() - 1, offsets.data(), columns.data(),
+                                                       values.data(), rhs.data()));
+  }
+  void UpdateConstraintTargets(const std::vector<double> &x, const std::vector<double> &y,
+                               const std::vector<double> &z) {
+    TLFEA_OR_DIE(tlfea_elem_update_constraint_targets(d_data, x.data(), y.data(), z.data(), (int)x.size()));
+  }
+  void RetrieveMassCSRToCPU(std::vector<int> &offsets, std::vector<int> &columns, std::vector<double> &values) {
+    const int64_t nnz = tlfea_elem_mass_nnz(d_data);
+    offsets.assign((size_t)get_n_coef() + 1, 0);
+    columns.assign((size_t)(nnz > 0 ? nnz : 0), 0);
+    values.assign(columns.size(), 0.0);
+    if (nnz < 0) return;
+    TLFEA_OR_DIE(tlfea_elem_get_mass_csr(d_data, offsets.data(), columns.data(), values.data()));
+    columns.resize((size_t)offsets.back());
+    values.resize((size_t)offsets.back());
+  }
+  void RetrieveDeformationGradientToCPU(std::vector<double> &F) {
+    F.resize((size_t)get_n_beam() * tlfea_elem_n_qp(d_data) * 9);
+    TLFEA_OR_DIE(tlfea_elem_get_F(d_data, F.data(), (int64_t)F.size()));
+  }
+  void RetrievePFromFToCPU(std::vector<double> &P) {
+    P.resize((size_t)get_n_beam() * tlfea_elem_n_qp(d_data) * 9);
+    TLFEA_OR_DIE(tlfea_elem_get_P(d_data, P.data(), (int64_t)P.size()));
+  }
+  void RetrieveDetJToCPU(std::vector<double> &detJ) {
+    detJ.resize((size_t)get_n_beam() * tlfea_elem_n_qp(d_data));
+    TLFEA_OR_DIE(tlfea_elem_get_detJ(d_data, detJ.data(), (int64_t)detJ.size()));
+  }
   void UpdatePositions(const std::vector<double> &x, const std::vector<double> &y, const std::vector<double> &z) {
     TLFEA_OR_DIE(tlfea_elem_update_positions(d_data, x.data(), y.data(), z.data(), (int)x.size()));
   }
@@ -83,6 +117,51 @@ struct GPU_FEAT10_Data : ElementBase {
                                       z.data(), conn_colmajor.data()));
   }
   void CalcDnDuPre() { TLFEA_OR_DIE(tlfea_elem_precompute(d_data)); }
+  void BuildMassCSRPattern() { TLFEA_OR_DIE(tlfea_elem_build_mass_pattern(d_data)); }
+};
+
+// ANCF3243Data.cuh:434-440 ctor (n_nodes, n_elem); Setup(L, W, H, x12, y12, z12, connectivity row-major [n_elem][2]).
+// The Gauss tables the reference passes to Setup are compile-time constants of the library (quadrature_utils.h).
+struct GPU_ANCF3243_Data : ElementBase {
+  GPU_ANCF3243_Data(int num_nodes, int num_elements, int device = 0) {
+    type = TYPE_3243;
+    TLFEA_OR_DIE(tlfea_elem_create(TLFEA_TYPE_3243, num_elements, num_nodes, device, &d_data));
+  }
+  void Initialize() {}
+  void Setup(const std::vector<double> &L, const std::vector<double> &W, const std::vector<double> &H,
+             const std::vector<double> &x, const std::vector<double> &y, const std::vector<double> &z,
+             const std::vector<int> &conn_rowmajor) {
+    TLFEA_OR_DIE(tlfea_elem_setup_3243(d_data, L.data(), W.data(), H.data(), x.data(), y.data(), z.data(),
+                                       conn_rowmajor.data()));
+  }
+  void Setup(double L, double W, double H, const std::vector<double> &x, const std::vector<double> &y,
+             const std::vector<double> &z, const std::vector<int> &conn_rowmajor) {  // uniform beam overload
+    const size_t n = (size_t)get_n_beam();
+    Setup(std::vector<double>(n, L), std::vector<double>(n, W), std::vector<double>(n, H), x, y, z, conn_rowmajor);
+  }
+  void CalcDsDuPre() { TLFEA_OR_DIE(tlfea_elem_precompute(d_data)); }
+  void BuildMassCSRPattern() { TLFEA_OR_DIE(tlfea_elem_build_mass_pattern(d_data)); }
+};
+
+// ANCF3443Data.cuh:445-455 ctor (n_nodes, n_elem); connectivity column-major [4][n_elem].
+struct GPU_ANCF3443_Data : ElementBase {
+  GPU_ANCF3443_Data(int num_nodes, int num_elements, int device = 0) {
+    type = TYPE_3443;
+    TLFEA_OR_DIE(tlfea_elem_create(TLFEA_TYPE_3443, num_elements, num_nodes, device, &d_data));
+  }
+  void Initialize() {}
+  void Setup(const std::vector<double> &L, const std::vector<double> &W, const std::vector<double> &H,
+             const std::vector<double> &x, const std::vector<double> &y, const std::vector<double> &z,
+             const std::vector<int> &conn_colmajor) {
+    TLFEA_OR_DIE(tlfea_elem_setup_3443(d_data, L.data(), W.data(), H.data(), x.data(), y.data(), z.data(),
+                                       conn_colmajor.data()));
+  }
+  void Setup(double L, double W, double H, const std::vector<double> &x, const std::vector<double> &y,
+             const std::vector<double> &z, const std::vector<int> &conn_colmajor) {
+    const size_t n = (size_t)get_n_beam();
+    Setup(std::vector<double>(n, L), std::vector<double>(n, W), std::vector<double>(n, H), x, y, z, conn_colmajor);
+  }
+  void CalcDsDuPre() { TLFEA_OR_DIE(tlfea_elem_precompute(d_data)); }
   void BuildMassCSRPattern() { TLFEA_OR_DIE(tlfea_elem_build_mass_pattern(d_data)); }
 };
 

@@ -55,3 +55,32 @@ def test_product_never_imports_oracle():
             if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 txt = open(os.path.join(dp, fn)).read()
                 assert "oracle" not in txt.lower() or fn == "README.md", f"{fn} mentions the oracle"
+
+
+def test_cpp_shim_compiles_and_links_against_the_abi(tmp_path):
+    """include/tlfea_shim.hpp (reference class names forwarding to the C ABI) builds with a plain host compiler and
+    every symbol it uses resolves in libtlfea_b200.so (no run: there is no GPU here)."""
+    import os
+    import shutil
+    import subprocess
+
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.join(root, "total-lagrangian-fea_b200", "lib")
+    src = tmp_path / "driver.cc"
+    src.write_text(
+        '#include "tlfea_shim.hpp"\n'
+        "int main(int argc, char **) {\n"
+        "  if (argc < 99) return 0;  // link check only\n"
+        "  GPU_FEAT10_Data t(1, 10); GPU_ANCF3243_Data b(3, 2); GPU_ANCF3443_Data p(4, 1);\n"
+        "  SyncedNewtonSolver s(&t, 0); SyncedNewtonParams prm{1e-4, 0, 1e-6, 1e14, 5, 10, 1e-3};\n"
+        "  s.SetParameters(&prm); s.Setup(); s.AnalyzeHessianSparsity(); s.Solve();\n"
+        "  std::vector<double> f; t.RetrieveInternalForceToCPU(f); b.CalcDsDuPre(); p.CalcMassMatrix();\n"
+        "  std::vector<int> o, c; std::vector<double> v; b.RetrieveMassCSRToCPU(o, c, v); b.UpdateNodalFixed(o);\n"
+        "  return (int)f.size();\n}\n")
+    exe = tmp_path / "driver"
+    subprocess.check_call([gxx, "-std=c++17", "-I", os.path.join(root, "include"), str(src), "-o", str(exe),
+                           "-L", lib_dir, "-ltlfea_b200", "-Wl,-rpath," + lib_dir, "-Wl,--unresolved-symbols=ignore-in-shared-libs"])
+    assert subprocess.call([str(exe)], env=dict(os.environ, LD_LIBRARY_PATH=lib_dir)) == 0

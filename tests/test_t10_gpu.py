@@ -306,3 +306,32 @@ def test_full_size_properties():
     H1 = s.RetrieveHessianValues()
     s.Assemble()
     assert np.array_equal(H1, s.RetrieveHessianValues())
+
+
+def test_update_nodal_fixed_moves_the_penalty_entries(mesh):
+    """UpdateNodalFixed (FEAT10Data.cu:751-839) under a live solver: same count, different pinned set."""
+    from oracle import oracle as orc
+
+    X, E, x, v = mesh
+    face0 = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
+    face1 = np.nonzero(X[:, 0] == X[:, 0].max())[0].astype(np.int32)
+    assert len(face0) == len(face1)
+    d, s = _make(X, E, fixed=face0)
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    o = orc.T10Oracle(E, X)
+    mat = _mat(orc, "svk", False)
+    for fixed in (face0, face1, face0):
+        d.UpdateNodalFixed(fixed)
+        s.Assemble()
+        H_ref = o.hessian(x, mat, H_STEP, RHO, fixed, 1e14)
+        H = s.RetrieveHessianValues()
+        big = np.abs(H_ref) > 0.5 * H_STEP**2 * 1e14
+        assert big.sum() == 3 * len(fixed)
+        assert np.array_equal(np.abs(H) > 0.5 * H_STEP**2 * 1e14, big)
+        assert rel_err(H[big], H_ref[big]) < TOL and rel_err(H[~big], H_ref[~big]) < TOL
+        d.CalcConstraintData()
+        c = d.RetrieveConstraintDataToCPU()
+        assert rel_err(c, (x - X)[fixed].reshape(-1)) < TOL
+    with pytest.raises(Exception):  # a different count cannot be absorbed by the bound solver
+        d.UpdateNodalFixed(face0[:-1])
+        s.Assemble()

@@ -99,7 +99,8 @@ struct Pattern {
   }
 };
 
-int build_pattern(const int *d_ecoef, int n_elem, int S, int n_coef, cudaStream_t stream, Pattern *out);
+int build_pattern(const int *d_ecoef, int n_elem, int S, int n_coef, cudaStream_t st, Pattern *out,
+                  const unsigned long long *h_extra = nullptr, int64_t n_extra = 0);
 
 }  // namespace tlfea
 
@@ -111,6 +112,9 @@ struct tlfea_elem {
   cudaStream_t stream = nullptr;
   bool own_stream = true;
   bool is_setup = false, is_precomputed = false, is_pattern = false, is_mass = false;
+  int cons_version = 0;               // bumped by UpdateNodalFixed: solvers refresh their constraint slots
+  bool pat_extra = false;             // the pattern also holds J^T J couplings of linear constraints
+  std::vector<int> h_j_off, h_j_cols;  // host copy of the constraint Jacobian structure
 
   int *d_conn = nullptr;    // caller layout (reference layout), n_elem * nodes_per_elem
   int nodes_per_elem = 0;
@@ -171,6 +175,7 @@ struct tlfea_newton {
   double *d_v = nullptr, *d_v_prev = nullptr, *d_lambda = nullptr, *d_g = nullptr, *d_dv = nullptr, *d_r = nullptr;
   double *d_xp = nullptr, *d_yp = nullptr, *d_zp = nullptr;
   // constraint term h^2 rho J^T J as a (slot, coefficient) list with unique slots
+  int cons_version_seen = 0;
   int64_t n_cons_slots = 0;
   int64_t *d_cons_slot = nullptr;
   double *d_cons_val = nullptr;

@@ -263,7 +263,24 @@ int launch_gp(tlfea_elem *h, const double *v, double *rec, double *fe, double *F
 int ensure_pattern(tlfea_elem *h) {
   if (h->is_pattern) return TLFEA_OK;
   TL_CHECK(h->is_setup, "element must be set up before building the pattern");
-  TL_TRY(build_pattern(h->d_ecoef, h->n_elem, h->S, h->n_coef, h->stream, &h->pat));
+  // General linear constraints couple the coefficients of a constraint row through h^2 rho J^T J: the reference
+  // widens the Hessian pattern with those pairs (SyncedNewton.cu:556-801).  Here the H pattern is 9x the
+  // coefficient pattern, so the pairs join the adjacency keys; the mass getter filters them out again.
+  std::vector<unsigned long long> extra;
+  if (h->cons_mode == TL_CONS_LINEAR_CSR) {
+    std::vector<int> row;
+    for (int c = 0; c < h->n_constraint; c++) {
+      row.clear();
+      for (int k = h->h_j_off[c]; k < h->h_j_off[c + 1]; k++) row.push_back(h->h_j_cols[k] / 3);
+      std::sort(row.begin(), row.end());
+      row.erase(std::unique(row.begin(), row.end()), row.end());
+      for (int a : row)
+        for (int b : row) extra.push_back(((unsigned long long)(unsigned)a << 32) | (unsigned)b);
+    }
+  }
+  h->pat_extra = !extra.empty();
+  TL_TRY(build_pattern(h->d_ecoef, h->n_elem, h->S, h->n_coef, h->stream, &h->pat, extra.data(),
+                       (int64_t)extra.size()));
   TL_TRY(dmalloc(&h->d_mass, (size_t)h->pat.nnz));
   TL_CUDA(cudaMemsetAsync(h->d_mass, 0, (size_t)h->pat.nnz * sizeof(double), h->stream));
   h->is_pattern = true;
@@ -509,6 +526,23 @@ int tlfea_elem_set_nodal_fixed(tlfea_elem *h, const int *fixed, int n_fixed) {
   return TLFEA_OK;
 }
 
+// UpdateNodalFixed (FEAT10Data.cu:751-839): replace the pinned set; buffers are re-made when the count changes.
+// A solver bound to this element re-derives its constraint slots on the next call (same count required).
+int tlfea_elem_update_nodal_fixed(tlfea_elem *h, const int *fixed, int n_fixed) {
+  TL_CHECK(h, "null handle");
+  if (h->cons_mode == TL_CONS_NONE) return tlfea_elem_set_nodal_fixed(h, fixed, n_fixed);
+  TL_CHECK(h->cons_mode == TL_CONS_FIXED_NODES, "UpdateNodalFixed needs fixed-node constraints");
+  TL_CUDA(cudaSetDevice(h->device));
+  TL_CUDA(cudaStreamSynchronize(h->stream));
+  dfree(h->d_fixed);
+  dfree(h->d_constraint);
+  h->d_fixed = nullptr;
+  h->d_constraint = nullptr;
+  h->cons_mode = TL_CONS_NONE;
+  h->cons_version++;
+  return tlfea_elem_set_nodal_fixed(h, fixed, n_fixed);
+}
+
 int tlfea_elem_set_linear_constraints_csr(tlfea_elem *h, int n_c, const int *off, const int *cols,
                                           const double *vals, const double *rhs) {
   TL_CHECK(h && off && cols && vals && rhs, "null input");
@@ -549,6 +583,19 @@ int tlfea_elem_set_linear_constraints_csr(tlfea_elem *h, int n_c, const int *off
   TL_CUDA(cudaMemcpy(h->d_jt_vals, t_vals.data(), (size_t)nnz * sizeof(double), cudaMemcpyHostToDevice));
   TL_CUDA(cudaMemset(h->d_constraint, 0, (size_t)n_c * sizeof(double)));
   h->cons_mode = TL_CONS_LINEAR_CSR;
+  h->h_j_off.assign(off, off + n_c + 1);
+  h->h_j_cols.assign(cols, cols + nnz);
+  if (h->is_pattern) {  // pattern was built before the constraints arrived: rebuild it with the J^T J couplings
+    const bool had_mass = h->is_mass;
+    TL_CUDA(cudaStreamSynchronize(h->stream));
+    h->pat.release();
+    h->pat = Pattern();
+    dfree(h->d_mass);
+    h->d_mass = nullptr;
+    h->is_pattern = h->is_mass = false;
+    TL_TRY(ensure_pattern(h));
+    if (had_mass) TL_TRY(tlfea_elem_calc_mass(h));
+  }
   return TLFEA_OK;
 }
 
@@ -736,9 +783,39 @@ int tlfea_elem_get_detJ(tlfea_elem *h, double *out, int64_t n) {
 }
 int tlfea_elem_get_mass_csr(tlfea_elem *h, int *off, int *cols, double *vals) {
   TL_CHECK(h && h->is_pattern, "mass pattern has not been built");
-  if (off) TL_TRY(d2h(h, off, h->pat.d_off, ((size_t)h->n_coef + 1) * sizeof(int)));
-  if (cols) TL_TRY(d2h(h, cols, h->pat.d_cols, (size_t)h->pat.nnz * sizeof(int)));
-  if (vals) TL_TRY(d2h(h, vals, h->d_mass, (size_t)h->pat.nnz * sizeof(double)));
+  if (!h->pat_extra) {
+    if (off) TL_TRY(d2h(h, off, h->pat.d_off, ((size_t)h->n_coef + 1) * sizeof(int)));
+    if (cols) TL_TRY(d2h(h, cols, h->pat.d_cols, (size_t)h->pat.nnz * sizeof(int)));
+    if (vals) TL_TRY(d2h(h, vals, h->d_mass, (size_t)h->pat.nnz * sizeof(double)));
+    return TLFEA_OK;
+  }
+  // the stored pattern also holds constraint couplings: hand out the element adjacency only (BuildMassCSRPattern)
+  std::vector<int> xo(h->n_coef + 1), xc(h->pat.nnz), ec((size_t)h->n_elem * h->S);
+  std::vector<double> xv(h->pat.nnz, 0.0);
+  TL_TRY(d2h(h, xo.data(), h->pat.d_off, xo.size() * sizeof(int)));
+  TL_TRY(d2h(h, xc.data(), h->pat.d_cols, xc.size() * sizeof(int)));
+  TL_TRY(d2h(h, xv.data(), h->d_mass, xv.size() * sizeof(double)));
+  TL_TRY(d2h(h, ec.data(), h->d_ecoef, ec.size() * sizeof(int)));
+  std::vector<char> keep(h->pat.nnz, 0);
+  for (int e = 0; e < h->n_elem; e++)
+    for (int a = 0; a < h->S; a++) {
+      const int i = ec[(size_t)e * h->S + a];
+      for (int b = 0; b < h->S; b++) {
+        const int j = ec[(size_t)e * h->S + b];
+        keep[std::lower_bound(xc.begin() + xo[i], xc.begin() + xo[i + 1], j) - xc.begin()] = 1;
+      }
+    }
+  int n = 0;
+  for (int i = 0; i < h->n_coef; i++) {
+    if (off) off[i] = n;
+    for (int k = xo[i]; k < xo[i + 1]; k++)
+      if (keep[k]) {
+        if (cols) cols[n] = xc[k];
+        if (vals) vals[n] = xv[k];
+        n++;
+      }
+  }
+  if (off) off[h->n_coef] = n;
   return TLFEA_OK;
 }
 int tlfea_elem_get_constraint(tlfea_elem *h, double *out, int n) {

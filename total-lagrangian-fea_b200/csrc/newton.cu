@@ -424,6 +424,30 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   return TLFEA_OK;
 }
 
+// slots of the h^2 rho J^T J diagonal entries of pinned nodes (J = selection rows)
+static int fixed_cons_slots(tlfea_newton *s) {
+  tlfea_elem *e = s->e;
+  TL_CHECK(s->n_constraints == e->n_constraint, "n_constraints (%d) != element constraints (%d)", s->n_constraints,
+           e->n_constraint);
+  dfree(s->d_cons_slot);
+  dfree(s->d_cons_val);
+  s->d_cons_slot = nullptr;
+  s->d_cons_val = nullptr;
+  s->n_cons_slots = 3 * (int64_t)e->n_fixed;
+  TL_TRY(dmalloc(&s->d_cons_slot, (size_t)std::max<int64_t>(s->n_cons_slots, 1)));
+  TL_TRY(dmalloc(&s->d_cons_val, (size_t)std::max<int64_t>(s->n_cons_slots, 1)));
+  if (e->n_fixed > 0)
+    TL_LAUNCH(k_fixed_cons_slots, blocks_for(3 * e->n_fixed, 256), 256, 0, e->stream, e->n_fixed, e->d_fixed,
+              e->pat.d_off, e->pat.d_cols, s->d_cons_slot, s->d_cons_val);
+  s->cons_version_seen = e->cons_version;
+  return TLFEA_OK;
+}
+static int refresh_constraints(tlfea_newton *s) {  // the element's pinned set changed (UpdateNodalFixed)
+  if (!s->analyzed || s->n_constraints == 0 || s->cons_version_seen == s->e->cons_version) return TLFEA_OK;
+  TL_CHECK(s->e->cons_mode == TL_CONS_FIXED_NODES, "constraint kind changed under a live solver");
+  return fixed_cons_slots(s);
+}
+
 static int do_assemble(tlfea_newton *s, bool tangent) {
   tlfea_elem *e = s->e;
   TL_CHECK(e->is_precomputed, "CalcDnDuPre/CalcDsDuPre must run before assembling");
@@ -434,6 +458,7 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
   }
   TL_CUDA(cudaSetDevice(e->device));
   TL_TRY(ensure_pattern(e));
+  TL_TRY(refresh_constraints(s));
   const bool damp = (e->eta != 0.0 || e->lambda_d != 0.0);
   TL_CUDA(cudaEventRecord(s->ev[0], e->stream));
   if (ek_supported(s)) {
@@ -531,6 +556,7 @@ static int compute_residual(tlfea_newton *s) {
   const double h = s->prm.time_step;
   TL_CHECK(h > 0.0, "time_step must be positive (SetParameters)");
   TL_CHECK(e->is_mass, "CalcMassMatrix must run before the residual");
+  TL_TRY(refresh_constraints(s));
   TL_TRY(eval_constraints(s));
   const bool lin = (s->n_constraints > 0 && e->cons_mode == TL_CONS_LINEAR_CSR);
   TL_LAUNCH(k_grad_L, blocks_for((int64_t)e->n_coef * 3, 256), 256, 0, e->stream, e->n_coef, e->pat.d_off,
@@ -677,12 +703,7 @@ int tlfea_newton_analyze_sparsity(tlfea_newton *s) {
     TL_CHECK(s->n_constraints == e->n_constraint, "n_constraints (%d) != element constraints (%d)", s->n_constraints,
              e->n_constraint);
     if (e->cons_mode == TL_CONS_FIXED_NODES) {
-      s->n_cons_slots = 3 * (int64_t)e->n_fixed;
-      TL_TRY(dmalloc(&s->d_cons_slot, (size_t)s->n_cons_slots));
-      TL_TRY(dmalloc(&s->d_cons_val, (size_t)s->n_cons_slots));
-      if (e->n_fixed > 0)
-        TL_LAUNCH(k_fixed_cons_slots, blocks_for(3 * e->n_fixed, 256), 256, 0, e->stream, e->n_fixed, e->d_fixed,
-                  e->pat.d_off, e->pat.d_cols, s->d_cons_slot, s->d_cons_val);
+      TL_TRY(fixed_cons_slots(s));
     } else {
       // general linear constraints: J^T J on the host (small systems), merged per slot in row order
       std::vector<int> off(e->n_coef + 1), cols(e->pat.nnz);
@@ -700,7 +721,8 @@ int tlfea_newton_analyze_sparsity(tlfea_newton *s) {
             const int di = jcols[a], dj = jcols[b], ci = di / 3, cj = dj / 3;
             const int rs = off[ci], deg = off[ci + 1] - rs;
             auto it = std::lower_bound(cols.begin() + rs, cols.begin() + rs + deg, cj);
-            // the reference silently drops entries outside the pattern (SyncedNewton.cu:336)
+            // every (ci, cj) of a constraint row is in the pattern (ensure_pattern adds the J^T J couplings);
+            // an entry outside it would be dropped as the reference does (SyncedNewton.cu:336)
             if (it == cols.begin() + rs + deg || *it != cj) continue;
             const int pos = (int)(it - (cols.begin() + rs));
             entries.emplace_back(9 * (int64_t)rs + (int64_t)(di % 3) * 3 * deg + 3 * pos + dj % 3,

@@ -97,7 +97,8 @@ static int sort_keys(unsigned long long *d_in, unsigned long long *d_out, int64_
   return TLFEA_OK;
 }
 
-int build_pattern(const int *d_ecoef, int n_elem, int S, int n_coef, cudaStream_t st, Pattern *out) {
+int build_pattern(const int *d_ecoef, int n_elem, int S, int n_coef, cudaStream_t st, Pattern *out,
+                  const unsigned long long *h_extra, int64_t n_extra) {
   Pattern p;
   p.n_coef = n_coef;
   p.S = S;
@@ -107,11 +108,15 @@ int build_pattern(const int *d_ecoef, int n_elem, int S, int n_coef, cudaStream_
 
   // ---- adjacency: sorted unique (i,j)
   {
-    int64_t total = (int64_t)n_elem * S * S;
+    const int64_t n_pairs = (int64_t)n_elem * S * S;
+    const int64_t total = n_pairs + n_extra;  // extra (i, j) couplings: the J^T J fill of linear constraints
     unsigned long long *k0 = nullptr, *k1 = nullptr;
     TL_TRY(dmalloc(&k0, (size_t)total));
     TL_TRY(dmalloc(&k1, (size_t)total));
-    TL_LAUNCH(k_pair_keys, blocks_for(total, 256), 256, 0, st, d_ecoef, total, S, k0);
+    TL_LAUNCH(k_pair_keys, blocks_for(n_pairs, 256), 256, 0, st, d_ecoef, n_pairs, S, k0);
+    if (n_extra > 0)
+      TL_CUDA(cudaMemcpyAsync(k0 + n_pairs, h_extra, (size_t)n_extra * sizeof(unsigned long long),
+                              cudaMemcpyHostToDevice, st));
     TL_TRY(sort_keys(k0, k1, total, 32 + coef_bits, st));
     int64_t *d_num = nullptr;
     TL_TRY(dmalloc(&d_num, 1));

@@ -58,6 +58,7 @@ _SIGS = {
     "tlfea_elem_set_mooney_rivlin": (C.c_int, [c_vp, C.c_double, C.c_double, C.c_double]),
     "tlfea_elem_set_external_force": (C.c_int, [c_vp, c_dp, C.c_int]),
     "tlfea_elem_set_nodal_fixed": (C.c_int, [c_vp, c_ip, C.c_int]),
+    "tlfea_elem_update_nodal_fixed": (C.c_int, [c_vp, c_ip, C.c_int]),
     "tlfea_elem_set_linear_constraints_csr": (C.c_int, [c_vp, C.c_int, c_ip, c_ip, c_dp, c_dp]),
     "tlfea_elem_update_positions": (C.c_int, [c_vp, c_dp, c_dp, c_dp, C.c_int]),
     "tlfea_elem_update_constraint_targets": (C.c_int, [c_vp, c_dp, c_dp, c_dp, C.c_int]),

@@ -99,6 +99,10 @@ class ElementBase:
         fx = _i32(fixed_nodes)
         check(lib.tlfea_elem_set_nodal_fixed(self._h, _i(fx), fx.shape[0]))
 
+    def UpdateNodalFixed(self, fixed_nodes):
+        f = _i32(fixed_nodes)
+        check(lib.tlfea_elem_update_nodal_fixed(self._h, _i(f), f.shape[0]))
+
     def SetLinearConstraintsCSR(self, offsets, columns, values, rhs):
         o, c, v, r = _i32(offsets), _i32(columns), _f64(values), _f64(rhs)
         check(lib.tlfea_elem_set_linear_constraints_csr(self._h, o.shape[0] - 1, _i(o), _i(c), _d(v), _d(r)))
@@ -177,7 +181,8 @@ class ElementBase:
         cols = np.empty(nnz, dtype=np.int32)
         vals = np.empty(nnz)
         check(lib.tlfea_elem_get_mass_csr(self._h, _i(off), _i(cols), _d(vals)))
-        return off, cols, vals
+        n = int(off[-1])  # < nnz when the stored pattern also holds constraint couplings
+        return off, cols[:n], vals[:n]
 
     def RetrieveConstraintDataToCPU(self):
         n = lib.tlfea_elem_n_constraint(self._h)
