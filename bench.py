@@ -341,6 +341,7 @@ def main():
     e2e = None
     if not args.no_e2e:
         hx = [torch.from_numpy(np.ascontiguousarray(x[:, k])).pin_memory().numpy() for k in range(3)]
+        hf = torch.empty(3 * n_nodes_l, dtype=torch.float64).pin_memory().numpy()  # caller's result buffer
         h2d = 3 * n_nodes_l * 8
         d2h = 3 * n_nodes_l * 8 + 8
 
@@ -349,7 +350,7 @@ def main():
             s.Assemble()
             halo_sum()
             ng = s.Residual()                         # D2H scalar ||g|| (SyncedNewton.cu:1063-1064)
-            f = d.RetrieveInternalForceToCPU()        # D2H of the step's result
+            f = d.RetrieveInternalForceToCPU(hf)      # D2H of the step's result into the caller's buffer
             return ng, f
 
         for _ in range(2):

@@ -142,8 +142,11 @@ class ElementBase:
         check(lib.tlfea_elem_sync(self._h))
 
     # ---- retrieval -----------------------------------------------------
-    def RetrieveInternalForceToCPU(self):
-        out = np.empty(3 * self.n_coef)
+    def RetrieveInternalForceToCPU(self, out=None):
+        """out: caller's buffer like the reference's VectorXd& (a pinned one makes the copy a plain DMA)."""
+        if out is None:
+            out = np.empty(3 * self.n_coef)
+        assert out.dtype == np.float64 and out.flags.c_contiguous and out.shape[0] == 3 * self.n_coef
         check(lib.tlfea_elem_get_internal_force(self._h, _d(out), out.shape[0]))
         return out
 
