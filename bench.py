@@ -54,10 +54,43 @@ class ClockSampler:
 
     def __init__(self, gpu_index: int):
         self.idx = gpu_index
+        self.thread = None
         self.proc = None
         self.path = None
 
+    def _nvml_loop(self):
+        import pynvml as nv
+        bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        while True:
+            try:
+                self.n_sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.n_pw.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for nm, b in bits.items():
+                    if r & b:
+                        self.n_reasons.add(nm)
+            except Exception:
+                pass
+            if self.halt.wait(0.004):  # at least one sample even for a timed region of a few ms
+                break
+
     def start(self):
+        # in-process NVML first (a sample every 4 ms: the 8-GPU timed region lasts ~60 ms, shorter than the
+        # start-up of an nvidia-smi child); the nvidia-smi recipe is the fallback
+        try:
+            import threading
+
+            import pynvml as nv
+            nv.nvmlInit()
+            self.h = nv.nvmlDeviceGetHandleByIndex(self.idx)
+            self.n_max = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+            self.n_sm, self.n_pw, self.n_reasons = [], [], set()
+            self.halt = threading.Event()
+            self.thread = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.thread = None
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
@@ -70,6 +103,13 @@ class ClockSampler:
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if getattr(self, "thread", None) is not None:
+            self.halt.set()
+            self.thread.join(timeout=2)
+            if self.n_sm:
+                out.update(sm_mhz=float(np.median(self.n_sm)), sm_max_mhz=self.n_max, reasons=sorted(self.n_reasons),
+                           samples=len(self.n_sm), power_w_max=max(self.n_pw) if self.n_pw else None, source="nvml")
+            return out
         if self.proc is None:
             return out
         self.proc.terminate()
@@ -193,7 +233,7 @@ def run_reference(args):
         "e2e": {"value": gps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    _emit(line)
 
 
 def main():
@@ -412,11 +452,28 @@ def main():
             "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all,
             "newton": newton, "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
         }
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+def _emit(line: dict):
+    """The contract is ONE JSON line on stdout: everything else a library prints there (NCCL's version banner)
+    was sent to stderr by _quiet_stdout()."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
+def _quiet_stdout():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
 if __name__ == "__main__":
+    _quiet_stdout()
     main()
