@@ -202,13 +202,14 @@ def test_newton_step_converges(golden_t10):
     assert st["norm_c"] < 1e-6, st
 
 
+@pytest.mark.parametrize("model", ["svk", "mr"])
 @pytest.mark.parametrize("damp", [False, True])
-def test_assembly_kernels_agree(mesh, damp):
+def test_assembly_kernels_agree(mesh, damp, model):
     """The two deterministic assembly paths (1: element kernel + row reduce, 0: generic warp-per-row gather)
     give the same H and f_int to rounding, and each is bit-reproducible."""
     X, E, x, v = mesh
     fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
-    d, s = _make(X, E, "svk", damp, fixed)
+    d, s = _make(X, E, model, damp, fixed)
     d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
     s.SetVelocityGuess(v.reshape(-1))
     s.SetAssembly(1)
@@ -223,12 +224,13 @@ def test_assembly_kernels_agree(mesh, damp):
     s.Assemble()
     assert np.array_equal(H0, s.RetrieveHessianValues())
     big = np.abs(H0) > 0.5 * H_STEP**2 * 1e14
-    assert rel_err(H1[~big], H0[~big]) < 1e-14
-    assert rel_err(H1[big], H0[big]) < 1e-14
-    assert rel_err(f1, f0) < 1e-14
+    tol = 1e-14 if model == "svk" else 1e-13  # the MR tensor entries cancel to ~1e-2 of their terms
+    assert rel_err(H1[~big], H0[~big]) < tol
+    assert rel_err(H1[big], H0[big]) < tol
+    assert rel_err(f1, f0) < tol
 
 
-@pytest.mark.parametrize("case", ["permuted", "odd_count", "unused_nodes", "single_element"])
+@pytest.mark.parametrize("case", ["permuted", "odd_count", "odd_count_mr", "unused_nodes", "single_element"])
 def test_general_numbering_and_ragged_meshes(case):
     """Nothing in the path may depend on the structured numbering of the synthetic block: random element and
     node renumbering, an odd element count (the element kernel works on pairs and groups), nodes that no element
@@ -243,18 +245,19 @@ def test_general_numbering_and_ragged_meshes(case):
         Xp = np.empty_like(X); Xp[pn] = X
         E = pn[E][rng.permutation(E.shape[0])].astype(np.int32)
         X = Xp
-    elif case == "odd_count":
+    elif case.startswith("odd_count"):
         E = E[:E.shape[0] - 5]                     # 157 elements
     elif case == "unused_nodes":
         E = E[rng.permutation(E.shape[0])[:40]]    # many nodes lose all their elements
     else:
         E = E[7:8]
     x = meshgen.perturb(X, 0.05 / 3, 4321)
-    d, s = _make(X, np.ascontiguousarray(E))
+    model = "mr" if case.endswith("_mr") else "svk"
+    d, s = _make(X, np.ascontiguousarray(E), model)
     d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
     s.Assemble()
     o = orc.T10Oracle(np.ascontiguousarray(E), X)
-    mat = orc.Material.svk(E_MOD, NU)
+    mat = _mat(orc, model, False)
     f_ref, _, _ = o.force(x, mat)
     H_ref = o.hessian(x, mat, H_STEP, RHO)
     off, cols, _ = d.RetrieveMassCSRToCPU()

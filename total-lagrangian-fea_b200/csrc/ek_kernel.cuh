@@ -30,6 +30,7 @@
 // No atomics, no searches, fixed summation order => bit-reproducible results.
 #pragma once
 #include "common.cuh"
+#include "kernels.cuh"  // MRState / mr_state
 
 namespace tlfea {
 
@@ -49,6 +50,7 @@ struct EKArgs {
   QuadW qw;
   double lambda, mu, eta, lambda_d;
   double c1, c2, c3, c4;  // c1 = h lambda + lambda_d, c2 = c3 = h mu + eta, c4 = h
+  double mu10, mu01, kappa;  // Mooney-Rivlin (MODEL == TL_MODEL_MR)
   double *fe;             // [n_elem][10][3]
   double *stage;          // [n_elem][10][10][9] visit-major block records, or nullptr (force only)
 };
@@ -107,14 +109,18 @@ __host__ __device__ constexpr int ek_chunk_off(int I, int p) {
   return I * EK_CRS + ((I == 4 && p == 4) ? EK_CX : 18 * p + 96 * (p & 1));
 }
 
-template <int G, bool DAMP>
+constexpr int EK_GQM = 35;  // Mooney-Rivlin: stride of the force-partial rows, lane = (element, point, row i); = 3 (mod 16)
+constexpr int EK_TS = 83;   // Mooney-Rivlin: stride of the per-point tangent tensor T[j][k][l][i] (81 used); = 3 (mod 16)
+
+template <int G, bool DAMP, int MODEL = TL_MODEL_SVK>
 struct EKShape {
   static constexpr int H_D = G * 150;               // gradN of a group
   static constexpr int DJ_D = (G * 5 + 1) / 2 * 2;  // detJ of a group
   static constexpr int X_D = G * 30;                // nodal coordinates [el][a][3]
   static constexpr int EC_D = (G * 5 + 1) / 2 * 2;  // G*10 ints
-  static constexpr int U_D = G * 5 * EK_GQ;         // u = F h per (element, point)
-  static constexpr int REC_D = G * 5 * EK_REC;
+  static constexpr bool MR = (MODEL == TL_MODEL_MR);
+  static constexpr int U_D = MR ? G * 5 * EK_TS : G * 5 * EK_GQ;  // u = F h per (element, point); MR: tensor T
+  static constexpr int REC_D = MR ? 0 : G * 5 * EK_REC;
   static constexpr int K_D = 2 * EK_ES;             // chunked staging of the element pair in flight; also the force partials
   static constexpr int OFF_H = 0;
   static constexpr int OFF_DJ = OFF_H + 2 * H_D;
@@ -125,13 +131,15 @@ struct EKShape {
   static constexpr int OFF_REC = OFF_U + (U_D + 1) / 2 * 2;
   static constexpr int OFF_K = OFF_REC + (REC_D + 1) / 2 * 2;
   static constexpr int WARP_D = OFF_K + K_D;
-  static_assert(G * 5 * EK_GQ <= K_D, "force partials alias the record staging");
+  static_assert(G * 5 * EK_GQM <= K_D, "force partials alias the record staging");
   static constexpr size_t smem_bytes(int warps) { return (size_t)warps * WARP_D * sizeof(double); }
 };
 
-template <int G, int W, bool DAMP, bool TANGENT>
+template <int G, int W, bool DAMP, bool TANGENT, int MODEL = TL_MODEL_SVK>
 __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
-  using Sh = EKShape<G, DAMP>;
+  using Sh = EKShape<G, DAMP, MODEL>;
+  constexpr bool MR = (MODEL == TL_MODEL_MR);
+  static_assert(!MR || G == 2, "the Mooney-Rivlin Gauss-point step maps lane = (element, point, row): G * 15 <= 32");
   static_assert(G * 5 <= 32 && G % 2 == 0, "a group is G*5 Gauss-point lanes and G/2 element pairs");
   extern __shared__ __align__(16) double ek_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -240,8 +248,118 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
     const double *s_dj = wb + Sh::OFF_DJ + buf * Sh::DJ_D;
     const double *s_x = wb + Sh::OFF_X + buf * Sh::X_D;
 
-    // ------------------------------------------------------------ Gauss-point step
-    if (lane < ne * 5) {
+    // ------------------------------------------------------------ Gauss-point step, Mooney-Rivlin
+    // lane = (element, point, row i): F and the invariants are computed by the three lanes of a point, the force
+    // partials and the tangent tensor are split by row.  T[i][J][k][L] = h dV dP_iJ/dF_kL (MooneyRivlin.cuh:193-223)
+    // + the Kelvin-Voigt block (FEAT10DataFunc.cuh:695-762) written in the same form:
+    //   lambda_d u_a u_b^T + eta u_b u_a^T + eta (h_a.h_b) F F^T = sum_JL h_a[J] dV (lambda_d F_iJ F_kL + eta F_kJ F_iL
+    //   + eta d_JL (FF^T)_ik) h_b[L], so the block step is one contraction K_ab[i][k] = sum_JL h_a[J] T[i][J][k][L] h_b[L].
+    if (MR && lane < ne * 15) {
+      const int idx = lane / 3, part = lane - 3 * idx;
+      const int el = idx / 5, q = idx - el * 5;
+      const double *hq = s_h + el * 150 + q * 30;
+      const double *xe = s_x + el * 30;
+      double F[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
+      double Fd[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
+#pragma unroll
+      for (int aa = 0; aa < 10; aa++) {
+        const double xa[3] = {xe[aa * 3], xe[aa * 3 + 1], xe[aa * 3 + 2]};
+        const double ha[3] = {hq[aa], hq[10 + aa], hq[20 + aa]};
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+          for (int j = 0; j < 3; j++) F[i][j] += xa[i] * ha[j];
+        if (DAMP) {
+          const double *ve = wb + Sh::OFF_V + buf * Sh::X_D + el * 30;
+          const double va[3] = {ve[aa * 3], ve[aa * 3 + 1], ve[aa * 3 + 2]};
+#pragma unroll
+          for (int i = 0; i < 3; i++)
+#pragma unroll
+            for (int j = 0; j < 3; j++) Fd[i][j] += va[i] * ha[j];
+        }
+      }
+      const double dV = s_dj[idx] * p.qw.w[q];
+      MRState m;
+      mr_state(F, p.mu10, p.mu01, p.kappa, m);
+      double term1[3][3], term2[3][3], P[3][3];
+#pragma unroll
+      for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+          term1[i][j] = F[i][j] - (m.I1 / 3.0) * m.Fit[i][j];
+          term2[i][j] = m.I1 * F[i][j] - m.FC[i][j] - (2.0 * m.I2 / 3.0) * m.Fit[i][j];
+          P[i][j] = m.t1 * term1[i][j] + m.t2 * term2[i][j] + m.t3 * m.Fit[i][j];
+        }
+      if (DAMP) {
+        double Ed[3][3];
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+          for (int j = 0; j < 3; j++) {
+            double a1 = 0.0, a2 = 0.0;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+              a1 += Fd[k][i] * F[k][j];
+              a2 += F[k][i] * Fd[k][j];
+            }
+            Ed[i][j] = 0.5 * (a1 + a2);
+          }
+        const double trEd = Ed[0][0] + Ed[1][1] + Ed[2][2];
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+          for (int j = 0; j < 3; j++) {
+            double sv = 0.0;
+#pragma unroll
+            for (int k = 0; k < 3; k++)
+              sv += F[i][k] * (2.0 * p.eta * Ed[k][j] + ((k == j) ? p.lambda_d * trEd : 0.0));
+            P[i][j] += sv;
+          }
+      }
+      // this lane's row i = part of everything indexed by i
+      double Pi[3], Fi[3], Fiti[3], FFTi[3], t1i[3], t2i[3], dk[3];
+#pragma unroll
+      for (int j = 0; j < 3; j++) {
+        Pi[j] = dV * (part == 0 ? P[0][j] : (part == 1 ? P[1][j] : P[2][j]));
+        Fi[j] = part == 0 ? F[0][j] : (part == 1 ? F[1][j] : F[2][j]);
+        Fiti[j] = part == 0 ? m.Fit[0][j] : (part == 1 ? m.Fit[1][j] : m.Fit[2][j]);
+        FFTi[j] = part == 0 ? m.FFT[0][j] : (part == 1 ? m.FFT[1][j] : m.FFT[2][j]);
+        t1i[j] = part == 0 ? term1[0][j] : (part == 1 ? term1[1][j] : term1[2][j]);
+        t2i[j] = part == 0 ? term2[0][j] : (part == 1 ? term2[1][j] : term2[2][j]);
+        dk[j] = (part == j) ? 1.0 : 0.0;
+      }
+      double *fpq = s_fp + idx * EK_GQM;
+#pragma unroll
+      for (int aa = 0; aa < 10; aa++)
+        fpq[aa * 3 + part] = Pi[0] * hq[aa] + Pi[1] * hq[10 + aa] + Pi[2] * hq[20 + aa];
+      if (TANGENT) {
+        double *sT = s_u + idx * EK_TS + part;
+        const double hdV = p.c4 * dV;
+        const double kt3 = p.kappa * (2.0 * m.J - 1.0) * m.J;
+#pragma unroll
+        for (int j = 0; j < 3; j++)
+#pragma unroll
+          for (int k = 0; k < 3; k++)
+#pragma unroll
+            for (int l = 0; l < 3; l++) {
+              const double djl = (j == l) ? 1.0 : 0.0;
+              const double dFit = -Fiti[l] * m.Fit[k][j];
+              const double dt1 = (-2.0 / 3.0) * m.t1 * m.Fit[k][l];
+              const double dt2 = (-4.0 / 3.0) * m.t2 * m.Fit[k][l];
+              const double dt3 = kt3 * m.Fit[k][l];
+              const double dT1 = dk[k] * djl - (2.0 / 3.0) * F[k][l] * Fiti[j] + (m.I1 / 3.0) * Fiti[l] * m.Fit[k][j];
+              const double dT2 = 2.0 * F[k][l] * Fi[j] + m.I1 * dk[k] * djl -
+                                 (dk[k] * m.C[l][j] + Fi[l] * F[k][j] + djl * FFTi[k]) -
+                                 (4.0 / 3.0) * (m.I1 * F[k][l] - m.FC[k][l]) * Fiti[j] +
+                                 (2.0 * m.I2 / 3.0) * Fiti[l] * m.Fit[k][j];
+              double t = hdV * (dt1 * t1i[j] + m.t1 * dT1 + dt2 * t2i[j] + m.t2 * dT2 + dt3 * Fiti[j] + m.t3 * dFit);
+              if (DAMP) t += dV * (p.lambda_d * Fi[j] * F[k][l] + p.eta * (F[k][j] * Fi[l] + djl * FFTi[k]));
+              sT[((j * 3 + k) * 3 + l) * 3] = t;
+            }
+      }
+    }
+    // ------------------------------------------------------------ Gauss-point step, SVK
+    if (!MR && lane < ne * 5) {
       const int el = lane / 5, q = lane - el * 5;
       const int rot = lane >> 3;  // lanes 8 apart would hit the same banks: rotate their a order
       const double *hq = s_h + el * 150 + q * 30;
@@ -348,9 +466,9 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
     // element forces: sum of the 5 point partials in fixed order, one coalesced 240-byte row per element
     for (int el = 0; el < ne; el++) {
       if (lane < 30) {
-        const double *fq = s_fp + el * 5 * EK_GQ + lane;
-        p.fe[(int64_t)(e0 + el) * 30 + lane] =
-            (((fq[0] + fq[EK_GQ]) + fq[2 * EK_GQ]) + fq[3 * EK_GQ]) + fq[4 * EK_GQ];
+        constexpr int FS = MR ? EK_GQM : EK_GQ;
+        const double *fq = s_fp + el * 5 * FS + lane;
+        p.fe[(int64_t)(e0 + el) * 30 + lane] = (((fq[0] + fq[FS]) + fq[2 * FS]) + fq[3 * FS]) + fq[4 * FS];
       }
     }
     __syncwarp();
@@ -363,7 +481,7 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
         const double *he = s_h + el * 150;
         const double *ue = s_u + el * 5 * EK_GQ;
         const double *re = s_rec + el * 5 * EK_REC;
-        double A[4][9], Gs[4][6];
+        double A[4][9], Gs[4][6];  // SVK accumulators; Mooney-Rivlin accumulates the finished blocks in A
 #pragma unroll
         for (int t = 0; t < 4; t++) {
 #pragma unroll
@@ -371,8 +489,39 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
 #pragma unroll
           for (int i = 0; i < 6; i++) Gs[t][i] = 0.0;
         }
+        if (MR) {
+          // K_ab[i][k] += sum_J h_a[J] (sum_L T[i][J][k][L] h_b[L]): 3 loads + 10 DFMA per (i, J, k) for the 2x2 tile
+          const double *Te = s_u + el * 5 * EK_TS;
+#pragma unroll 1
+          for (int q = 0; q < 5; q++) {
+            const double *hq = he + q * 30, *Tq = Te + q * EK_TS;
+            double ha[2][3], hb[2][3];
 #pragma unroll
-        for (int q = 0; q < 5; q++) {
+            for (int j = 0; j < 3; j++) {
+              ha[0][j] = hq[j * 10 + a1];
+              ha[1][j] = hq[j * 10 + a1 + 1];
+              hb[0][j] = hq[j * 10 + b1];
+              hb[1][j] = hq[j * 10 + b1 + 1];
+            }
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+              for (int j = 0; j < 3; j++)
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                  const double t0 = Tq[((j * 3 + k) * 3 + 0) * 3 + i], t1 = Tq[((j * 3 + k) * 3 + 1) * 3 + i],
+                               t2 = Tq[((j * 3 + k) * 3 + 2) * 3 + i];
+                  const double s0 = t0 * hb[0][0] + t1 * hb[0][1] + t2 * hb[0][2];
+                  const double s1 = t0 * hb[1][0] + t1 * hb[1][1] + t2 * hb[1][2];
+                  A[0][i * 3 + k] += ha[0][j] * s0;
+                  A[1][i * 3 + k] += ha[0][j] * s1;
+                  A[2][i * 3 + k] += ha[1][j] * s0;
+                  A[3][i * 3 + k] += ha[1][j] * s1;
+                }
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < (MR ? 0 : 5); q++) {
           const double *hq = he + q * 30, *uq = ue + q * EK_GQ, *rq = re + q * EK_REC;
           const double dV = rq[6];
           double ha[2][3], hb[2][3], ua[2][3], ub[2][3], M[6];
@@ -412,6 +561,10 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
               const int t = ta * 2 + tb;
               const double dg = p.c4 * p.mu * (A[t][0] + A[t][4] + A[t][8]);
               double k[9];
+              if (MR) {
+#pragma unroll
+                for (int i = 0; i < 9; i++) k[i] = A[t][i];
+              } else {
               k[0] = p.c1 * A[t][0] + p.c2 * A[t][0] + Gs[t][0] + dg;
               k[1] = p.c1 * A[t][1] + p.c2 * A[t][3] + Gs[t][1];
               k[2] = p.c1 * A[t][2] + p.c2 * A[t][6] + Gs[t][2];
@@ -421,6 +574,7 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
               k[6] = p.c1 * A[t][6] + p.c2 * A[t][2] + Gs[t][2];
               k[7] = p.c1 * A[t][7] + p.c2 * A[t][5] + Gs[t][4];
               k[8] = p.c1 * A[t][8] + p.c2 * A[t][8] + Gs[t][5] + dg;
+              }
               double *d1 = s_k + st_d + ta * 18 + tb * 9;
 #pragma unroll
               for (int i = 0; i < 9; i++) d1[i] = k[i];

@@ -283,34 +283,33 @@ static EKCfg ek_cfg() {
 
 static bool ek_supported(const tlfea_newton *s) {
   const tlfea_elem *e = s->e;
-  return s->two_phase && e->type == TLFEA_TYPE_T10 && e->model == TL_MODEL_SVK;
+  return s->two_phase && e->type == TLFEA_TYPE_T10;  // SVK and Mooney-Rivlin, with or without Kelvin-Voigt damping
 }
 
-template <int G, int W, bool DAMP, bool TANGENT>
+template <int G, int W, bool DAMP, bool TANGENT, int MODEL>
 static int launch_ek_t(tlfea_elem *e, const EKArgs &a) {
-  const size_t smem = EKShape<G, DAMP>::smem_bytes(W);
+  const size_t smem = EKShape<G, DAMP, MODEL>::smem_bytes(W);
   TL_CHECK(smem <= 227 * 1024, "element kernel configuration needs %zu bytes of shared memory", smem);
   static thread_local int attr_dev = -1;  // the opt-in is per function and device: set it once
   if (attr_dev != e->device) {
-    TL_CUDA(cudaFuncSetAttribute(ek_kernel<G, W, DAMP, TANGENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TL_CUDA(cudaFuncSetAttribute(ek_kernel<G, W, DAMP, TANGENT, MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem));
     attr_dev = e->device;
   }
   const int n_groups = (a.n_elem + G - 1) / G;
   const int grid = std::max(1, std::min(148, (n_groups + W - 1) / W));
-  TL_LAUNCH((ek_kernel<G, W, DAMP, TANGENT>), grid, W * 32, smem, e->stream, a);
+  TL_LAUNCH((ek_kernel<G, W, DAMP, TANGENT, MODEL>), grid, W * 32, smem, e->stream, a);
   TL_CUDA(cudaGetLastError());
   return TLFEA_OK;
 }
 
 template <bool DAMP, bool TANGENT>
 static int launch_ek_cfg(tlfea_elem *e, const EKArgs &a) {
+  // Mooney-Rivlin keeps an 81-entry tangent tensor per Gauss point in shared memory: 7 warps fit
+  if (e->model == TL_MODEL_MR) return launch_ek_t<2, 7, DAMP, TANGENT, TL_MODEL_MR>(e, a);
   const EKCfg c = ek_cfg();
-  if (DAMP) return launch_ek_t<2, 8, DAMP, TANGENT>(e, a);
-  if (c.g == 2 && c.w == 9) return launch_ek_t<2, 9, DAMP, TANGENT>(e, a);
-  if (c.g == 6 && c.w == 4) return launch_ek_t<6, 4, DAMP, TANGENT>(e, a);
-  if (c.g == 4 && c.w == 6) return launch_ek_t<4, 6, DAMP, TANGENT>(e, a);
-  if (c.g == 4 && c.w == 5) return launch_ek_t<4, 5, DAMP, TANGENT>(e, a);
-  return launch_ek_t<2, 8, DAMP, TANGENT>(e, a);  // most warps per SM: the kernel is latency / LSU bound
+  if (!DAMP && c.g == 2 && c.w == 9) return launch_ek_t<2, 9, DAMP, TANGENT, TL_MODEL_SVK>(e, a);
+  return launch_ek_t<2, 8, DAMP, TANGENT, TL_MODEL_SVK>(e, a);  // most warps per SM: the kernel is latency / LSU bound
 }
 
 static int ek_chunk_elems() {
@@ -359,6 +358,9 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   a.c2 = h * e->mu + e->eta;
   a.c3 = h * e->mu + e->eta;
   a.c4 = h;
+  a.mu10 = e->mu10;
+  a.mu01 = e->mu01;
+  a.kappa = e->kappa;
   auto launch_e = [&](int e0, int ne) -> int {
     a.n_elem = ne;
     a.ecoef = e->d_ecoef + (int64_t)e0 * 10;
