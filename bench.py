@@ -246,6 +246,7 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=32, help="cells per edge of the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-variants", action="store_true", help="skip the damped / Mooney-Rivlin assembles")
     ap.add_argument("--no-newton", action="store_true")
     ap.add_argument("--assembly", type=int, default=-1, help="0 generic row gather, 1 element kernel + row reduce (default)")
     args = ap.parse_args()
@@ -433,6 +434,36 @@ def main():
                   "pcg_iters": st["pcg_iters"], "ms_per_newton_iter": nms / max(st["newton_iters"], 1),
                   "linear_solver": "block-Jacobi PCG, fixed 50 iterations per Newton iteration", "n_dofs": s.n_dofs}
 
+    # ---- the other two runs SURVEY.md 8(d) names on the same mesh: Kelvin-Voigt damping and Mooney-Rivlin
+    variants = None
+    if world == 1 and not args.no_variants:
+        mu, bulk = E_MOD / (2 * (1 + NU)), E_MOD / (3 * (1 - 2 * NU))
+        vel = 0.1 * np.random.Generator(np.random.PCG64(1235)).uniform(-1, 1, size=s.n_dofs)
+
+        def timed_assemble(reps=5):
+            for _ in range(2):
+                s.Assemble()
+            torch.cuda.synchronize()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for _ in range(reps):
+                s.Assemble()
+            a1.record()
+            torch.cuda.synchronize()
+            ms = a0.elapsed_time(a1) / reps
+            return {"ms_per_step": ms, "value": gp_total / (ms * 1e-3), "unit": UNIT}
+
+        d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+        s.SetVelocityGuess(vel)
+        variants = {}
+        d.SetDamping(1e5, 1e5)
+        variants["svk_kelvin_voigt_eta1e5_lambda1e5"] = timed_assemble()
+        d.SetDamping(0.0, 0.0)
+        d.SetMooneyRivlin(0.3 * mu, 0.2 * mu, 1.5 * bulk)
+        variants["mooney_rivlin_0.3mu_0.2mu_1.5K"] = timed_assemble()
+        d.SetSVK(E_MOD, NU)
+        s.SetVelocityGuess(np.zeros(s.n_dofs))
+
     cpu_base = None
     if rank == 0 and not args.no_cpu_baseline:
         gps, threads, desc, dt = cpu_sample(args.cpu_n, 5)
@@ -450,7 +481,7 @@ def main():
                        "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
                        "setup_s": t_setup},
             "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all,
-            "newton": newton, "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
+            "newton": newton, "variants": variants, "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
         }
         _emit(line)
     if world > 1:
