@@ -134,13 +134,15 @@ __global__ void __launch_bounds__(256) k_spmv(int n_coef, const int *__restrict_
   const int rs = off[row], deg = off[row + 1] - rs;
   const int64_t base = 9 * (int64_t)rs;
   double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-  for (int s = lane; s < deg; s += 32) {
-    const int64_t j = 3 * (int64_t)cols[rs + s];
-    const double x0 = x[j], x1 = x[j + 1], x2 = x[j + 2];
-    const double *h0 = H + base + 3 * s, *h1 = h0 + 3 * deg, *h2 = h1 + 3 * deg;
-    s0 += h0[0] * x0 + h0[1] * x1 + h0[2] * x2;
-    s1 += h1[0] * x0 + h1[1] * x1 + h1[2] * x2;
-    s2 += h2[0] * x0 + h2[1] * x1 + h2[2] * x2;
+  // the three scalar rows of the block row are contiguous runs of 3*deg doubles: lane-linear (coalesced) reads,
+  // x gathered per (column, component)
+  const double *h0 = H + base, *h1 = h0 + 3 * deg, *h2 = h1 + 3 * deg;
+  for (int t = lane; t < 3 * deg; t += 32) {
+    const int sl = t / 3;
+    const double xv = x[3 * (int64_t)cols[rs + sl] + (t - 3 * sl)];
+    s0 += h0[t] * xv;
+    s1 += h1[t] * xv;
+    s2 += h2[t] * xv;
   }
   for (int o = 16; o > 0; o >>= 1) {
     s0 += __shfl_xor_sync(0xffffffffu, s0, o);
@@ -154,9 +156,10 @@ __global__ void __launch_bounds__(256) k_spmv(int n_coef, const int *__restrict_
   }
 }
 
-// z = D^-1 r with D the 3x3 diagonal blocks of H (block-Jacobi)
-__global__ void k_block_jacobi(int n_coef, const int *__restrict__ off, const int *__restrict__ cols,
-                               const double *__restrict__ H, const double *__restrict__ r, double *z) {
+// block-Jacobi preconditioner: Dinv = inverse of the 3x3 diagonal blocks of H, built once per linear solve
+// (layout [9][n_coef] so the apply kernel reads it coalesced); identity where the block is singular
+__global__ void k_block_jacobi_setup(int n_coef, const int *__restrict__ off, const int *__restrict__ cols,
+                                     const double *__restrict__ H, double *__restrict__ Dinv) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_coef) return;
   const int rs = off[i], deg = off[i + 1] - rs;
@@ -176,17 +179,32 @@ __global__ void k_block_jacobi(int n_coef, const int *__restrict__ off, const in
   const double a = h0[0], b = h0[1], c = h0[2], d = h1[0], e = h1[1], f = h1[2], g = h2[0], hh = h2[1], k = h2[2];
   const double A = e * k - f * hh, B = -(d * k - f * g), C = d * hh - e * g;
   const double det = a * A + b * B + c * C;
-  const double r0 = r[3 * (int64_t)i], r1 = r[3 * (int64_t)i + 1], r2 = r[3 * (int64_t)i + 2];
-  if (fabs(det) < 1e-300) {
-    z[3 * (int64_t)i] = r0;
-    z[3 * (int64_t)i + 1] = r1;
-    z[3 * (int64_t)i + 2] = r2;
-    return;
+  double m[9] = {1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0};
+  if (deg > 0 && fabs(det) >= 1e-300) {
+    const double id = 1.0 / det;
+    m[0] = A * id;
+    m[1] = -(b * k - c * hh) * id;
+    m[2] = (b * f - c * e) * id;
+    m[3] = B * id;
+    m[4] = (a * k - c * g) * id;
+    m[5] = -(a * f - c * d) * id;
+    m[6] = C * id;
+    m[7] = -(a * hh - b * g) * id;
+    m[8] = (a * e - b * d) * id;
   }
-  const double id = 1.0 / det;
-  z[3 * (int64_t)i] = (A * r0 + (-(b * k - c * hh)) * r1 + (b * f - c * e) * r2) * id;
-  z[3 * (int64_t)i + 1] = (B * r0 + (a * k - c * g) * r1 + (-(a * f - c * d)) * r2) * id;
-  z[3 * (int64_t)i + 2] = (C * r0 + (-(a * hh - b * g)) * r1 + (a * e - b * d) * r2) * id;
+#pragma unroll
+  for (int q = 0; q < 9; q++) Dinv[(int64_t)q * n_coef + i] = m[q];
+}
+// z = Dinv r
+__global__ void k_block_jacobi(int n_coef, const double *__restrict__ Dinv, const double *__restrict__ r, double *z) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_coef) return;
+  const double r0 = r[3 * (int64_t)i], r1 = r[3 * (int64_t)i + 1], r2 = r[3 * (int64_t)i + 2];
+  const double *m = Dinv + i;
+  const int64_t n = n_coef;
+  z[3 * (int64_t)i] = m[0] * r0 + m[n] * r1 + m[2 * n] * r2;
+  z[3 * (int64_t)i + 1] = m[3 * n] * r0 + m[4 * n] * r1 + m[5 * n] * r2;
+  z[3 * (int64_t)i + 2] = m[6 * n] * r0 + m[7 * n] * r1 + m[8 * n] * r2;
 }
 
 __global__ void k_pcg_update_xr(int64_t n, const double *scal, const double *p, const double *Ap, double *x,
@@ -579,7 +597,9 @@ static int pcg_solve(tlfea_newton *s, int *iters_out) {
   double *x = s->d_dv, *r = s->d_r, *z = s->d_pcg[0], *p = s->d_pcg[1], *Ap = s->d_pcg[2];
   const unsigned gb = blocks_for(n, 256), nb = blocks_for(e->n_coef, 256), sb = blocks_for((int64_t)e->n_coef * 32, 256);
   TL_CUDA(cudaMemsetAsync(x, 0, n * sizeof(double), e->stream));
-  TL_LAUNCH(k_block_jacobi, nb, 256, 0, e->stream, e->n_coef, e->pat.d_off, e->pat.d_cols, s->d_H, r, z);
+  double *Dinv = s->d_pcg[3];
+  TL_LAUNCH(k_block_jacobi_setup, nb, 256, 0, e->stream, e->n_coef, e->pat.d_off, e->pat.d_cols, s->d_H, Dinv);
+  TL_LAUNCH(k_block_jacobi, nb, 256, 0, e->stream, e->n_coef, Dinv, r, z);
   TL_CUDA(cudaMemcpyAsync(p, z, n * sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
   TL_TRY(dot(s, r, z, s->d_scal + 0));  // rz
   double r0 = 0;
@@ -593,7 +613,7 @@ static int pcg_solve(tlfea_newton *s, int *iters_out) {
       double rn = 0;
       TL_TRY(norm2(s, r, n, &rn));
       if (rn <= s->pcg_rel_tol * r0) break;
-      TL_LAUNCH(k_block_jacobi, nb, 256, 0, e->stream, e->n_coef, e->pat.d_off, e->pat.d_cols, s->d_H, r, z);
+      TL_LAUNCH(k_block_jacobi, nb, 256, 0, e->stream, e->n_coef, Dinv, r, z);
       TL_TRY(dot(s, r, z, s->d_scal + 2));
       TL_LAUNCH(k_pcg_update_p, gb, 256, 0, e->stream, n, s->d_scal, z, p);
       TL_LAUNCH(k_copy_scalar, 1, 1, 0, e->stream, s->d_scal + 0, s->d_scal + 2);
@@ -798,8 +818,8 @@ int tlfea_newton_solve_step(tlfea_newton *s) {
   if (!s->analyzed) TL_TRY(tlfea_newton_analyze_sparsity(s));
   const int64_t n = 3 * (int64_t)e->n_coef;
   const size_t cb = (size_t)e->n_coef * sizeof(double);
-  for (int i = 0; i < 3; i++)
-    if (!s->d_pcg[i]) TL_TRY(dmalloc(&s->d_pcg[i], (size_t)n));
+  for (int i = 0; i < 4; i++)  // z, p, Ap, and the inverse diagonal blocks (9 per coefficient = 3n)
+    if (!s->d_pcg[i]) TL_TRY(dmalloc(&s->d_pcg[i], (size_t)n * (i == 3 ? 3 : 1)));
   const double h = s->prm.time_step;
   // update_pos_prev  (SyncedNewton.cu:1035)
   TL_CUDA(cudaMemcpyAsync(s->d_xp, e->d_x, cb, cudaMemcpyDeviceToDevice, e->stream));
