@@ -216,6 +216,29 @@ int tlfea_newton_kernel_ms(tlfea_newton *s, double *gp_ms, double *row_ms, doubl
 int tlfea_dist_pack(tlfea_newton *s, const double *d_vec, const int *d_idx, int n, double *d_buf);
 int tlfea_dist_unpack(tlfea_newton *s, double *d_vec, const int *d_idx, int n, const double *d_buf);
 
+/* Distributed Newton/Krylov building blocks (north_star: "distributed Newton/Krylov residual norms use allreduce").
+ * Every rank owns a sub-assembled H; between these calls the host side halo-sums interface entries of the vector
+ * the op names and all-reduces the 4 partial scalars at TLFEA_KVEC_SCAL (r.z, p.Ap, new r.z, r.r | g.g), which
+ * stay in device memory: alpha and beta are formed on the device.  Replaces the single-GPU cuDSS solve of
+ * OneStepNewtonCuDSS (SyncedNewton.cu:995-1029,1103-1119) for the partitioned mesh. */
+enum {
+  TLFEA_KOP_SAVE_POSITIONS = 0, /* x_prev = x (start of a time step) */
+  TLFEA_KOP_RESIDUAL = 1,       /* local g; halo-sum the vector at tlfea_newton_devptr_g afterwards */
+  TLFEA_KOP_NORM_G = 2,         /* scal[3] = g.g over owned DOFs */
+  TLFEA_KOP_BEGIN = 3,          /* r = -g, dv = 0, raw 3x3 diagonal blocks -> KVEC_DIAG [n_coef][9]; halo-sum DIAG */
+  TLFEA_KOP_PRECOND = 4,        /* invert the blocks, z = Dinv r, p = z, scal[0] = r.z, scal[3] = r.r */
+  TLFEA_KOP_SPMV = 5,           /* Ap = H_local p; halo-sum KVEC_AP */
+  TLFEA_KOP_PAP = 6,            /* scal[1] = p.Ap */
+  TLFEA_KOP_UPDATE_XR = 7,      /* dv += alpha p, r -= alpha Ap, z = Dinv r, scal[2] = r.z, scal[3] = r.r */
+  TLFEA_KOP_UPDATE_P = 8,       /* p = z + beta p, scal[0] = scal[2] */
+  TLFEA_KOP_APPLY = 9           /* v += dv, x = x_prev + h v */
+};
+enum { TLFEA_KVEC_Z = 0, TLFEA_KVEC_P = 1, TLFEA_KVEC_AP = 2, TLFEA_KVEC_DIAG = 3, TLFEA_KVEC_R = 4, TLFEA_KVEC_DV = 5,
+       TLFEA_KVEC_SCAL = 6 };
+int tlfea_newton_set_owned_range(tlfea_newton *s, int64_t dof_lo, int64_t dof_hi); /* dot products count [lo, hi) */
+int tlfea_newton_krylov_op(tlfea_newton *s, int op);
+double *tlfea_newton_devptr_krylov(tlfea_newton *s, int which);
+
 /* FP64 FMA peak micro-benchmark (roofline denominator for the tangent kernel): TFLOP/s */
 int tlfea_fp64_peak(int device, double *tflops);
 

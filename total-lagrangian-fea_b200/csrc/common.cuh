@@ -176,6 +176,7 @@ struct tlfea_newton {
   double *d_xp = nullptr, *d_yp = nullptr, *d_zp = nullptr;
   // constraint term h^2 rho J^T J as a (slot, coefficient) list with unique slots
   int cons_version_seen = 0;
+  int64_t own_lo = 0, own_hi = -1;  // DOF range owned by this rank (dot products of the distributed solve)
   int64_t n_cons_slots = 0;
   int64_t *d_cons_slot = nullptr;
   double *d_cons_val = nullptr;

@@ -195,6 +195,58 @@ __global__ void k_block_jacobi_setup(int n_coef, const int *__restrict__ off, co
 #pragma unroll
   for (int q = 0; q < 9; q++) Dinv[(int64_t)q * n_coef + i] = m[q];
 }
+// distributed solve: raw diagonal blocks [n_coef][9] (interface nodes are completed by a halo sum before inversion)
+__global__ void k_diag_extract(int n_coef, const int *__restrict__ off, const int *__restrict__ cols,
+                               const double *__restrict__ H, double *__restrict__ diag) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_coef) return;
+  const int rs = off[i], deg = off[i + 1] - rs;
+  int lo = 0, hi = deg - 1, pos = -1;
+  while (lo <= hi) {
+    int mid = (lo + hi) >> 1, c = cols[rs + mid];
+    if (c == i) {
+      pos = mid;
+      break;
+    }
+    if (c < i)
+      lo = mid + 1;
+    else
+      hi = mid - 1;
+  }
+  double *o = diag + 9 * (int64_t)i;
+  if (pos < 0) {
+#pragma unroll
+    for (int q = 0; q < 9; q++) o[q] = 0.0;
+    return;
+  }
+  const double *h0 = H + 9 * (int64_t)rs + 3 * pos, *h1 = h0 + 3 * deg, *h2 = h1 + 3 * deg;
+  o[0] = h0[0], o[1] = h0[1], o[2] = h0[2];
+  o[3] = h1[0], o[4] = h1[1], o[5] = h1[2];
+  o[6] = h2[0], o[7] = h2[1], o[8] = h2[2];
+}
+__global__ void k_diag_invert(int n_coef, const double *__restrict__ diag, double *__restrict__ Dinv) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_coef) return;
+  const double *o = diag + 9 * (int64_t)i;
+  const double a = o[0], b = o[1], c = o[2], d = o[3], e = o[4], f = o[5], g = o[6], hh = o[7], k = o[8];
+  const double A = e * k - f * hh, B = -(d * k - f * g), C = d * hh - e * g;
+  const double det = a * A + b * B + c * C;
+  double m[9] = {1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0};
+  if (fabs(det) >= 1e-300) {
+    const double id = 1.0 / det;
+    m[0] = A * id;
+    m[1] = -(b * k - c * hh) * id;
+    m[2] = (b * f - c * e) * id;
+    m[3] = B * id;
+    m[4] = (a * k - c * g) * id;
+    m[5] = -(a * f - c * d) * id;
+    m[6] = C * id;
+    m[7] = -(a * hh - b * g) * id;
+    m[8] = (a * e - b * d) * id;
+  }
+#pragma unroll
+  for (int q = 0; q < 9; q++) Dinv[(int64_t)q * n_coef + i] = m[q];
+}
 // z = Dinv r
 __global__ void k_block_jacobi(int n_coef, const double *__restrict__ Dinv, const double *__restrict__ r, double *z) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -259,6 +311,16 @@ static int dot(tlfea_newton *s, const double *a, const double *b, double *d_out)
   const int64_t n = 3 * (int64_t)s->e->n_coef;
   double *partial = s->d_scal + 8;
   TL_LAUNCH(k_dot_partial, DOT_BLOCKS, 256, 0, s->e->stream, n, a, b, partial);
+  TL_LAUNCH(k_dot_final, 1, 1024, 0, s->e->stream, DOT_BLOCKS, partial, d_out);
+  return TLFEA_OK;
+}
+
+// partial dot over the DOF range this rank owns (distributed solve: shared DOFs are counted once)
+static int dot_owned(tlfea_newton *s, const double *a, const double *b, double *d_out) {
+  const int64_t n = 3 * (int64_t)s->e->n_coef;
+  const int64_t lo = std::max<int64_t>(0, s->own_lo), hi = (s->own_hi < 0) ? n : std::min<int64_t>(n, s->own_hi);
+  double *partial = s->d_scal + 8;
+  TL_LAUNCH(k_dot_partial, DOT_BLOCKS, 256, 0, s->e->stream, std::max<int64_t>(hi - lo, 0), a + lo, b + lo, partial);
   TL_LAUNCH(k_dot_final, 1, 1024, 0, s->e->stream, DOT_BLOCKS, partial, d_out);
   return TLFEA_OK;
 }
@@ -949,6 +1011,99 @@ int tlfea_newton_spmv(tlfea_newton *s, const double *d_x, double *d_y) {
             e->pat.d_cols, s->d_H, d_x, d_y);
   TL_CUDA(cudaGetLastError());
   return TLFEA_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Distributed Newton/Krylov building blocks.  Every rank holds a sub-assembled H and consistent copies of the
+// vectors; the host side (tlfea/dist_newton.py) completes interface entries with a halo sum and the partial
+// scalars with an all-reduce between these calls.  Scalars live in device memory (scal[0] = r.z, [1] = p.Ap,
+// [2] = new r.z, [3] = r.r or g.g): alpha and beta are formed on the device, so an iteration needs no host sync.
+// ---------------------------------------------------------------------------------------------
+int tlfea_newton_set_owned_range(tlfea_newton *s, int64_t dof_lo, int64_t dof_hi) {
+  TL_CHECK(s, "null handle");
+  s->own_lo = dof_lo;
+  s->own_hi = dof_hi;
+  return TLFEA_OK;
+}
+
+int tlfea_newton_krylov_op(tlfea_newton *s, int op) {
+  TL_CHECK(s && s->analyzed, "AnalyzeHessianSparsity must run first");
+  tlfea_elem *e = s->e;
+  TL_CUDA(cudaSetDevice(e->device));
+  const int64_t n = 3 * (int64_t)e->n_coef;
+  for (int i = 0; i < 5; i++)  // z, p, Ap, inverse diagonal blocks, raw diagonal blocks
+    if (!s->d_pcg[i]) TL_TRY(dmalloc(&s->d_pcg[i], (size_t)n * (i >= 3 ? 3 : 1)));
+  double *x = s->d_dv, *r = s->d_r, *z = s->d_pcg[0], *p = s->d_pcg[1], *Ap = s->d_pcg[2], *Dinv = s->d_pcg[3],
+         *diag = s->d_pcg[4];
+  const unsigned gb = blocks_for(n, 256), nb = blocks_for(e->n_coef, 256);
+  const double h = s->prm.time_step;
+  switch (op) {
+    case TLFEA_KOP_SAVE_POSITIONS: {  // update_pos_prev (SyncedNewton.cu:1035)
+      const size_t cb = (size_t)e->n_coef * sizeof(double);
+      TL_CUDA(cudaMemcpyAsync(s->d_xp, e->d_x, cb, cudaMemcpyDeviceToDevice, e->stream));
+      TL_CUDA(cudaMemcpyAsync(s->d_yp, e->d_y, cb, cudaMemcpyDeviceToDevice, e->stream));
+      TL_CUDA(cudaMemcpyAsync(s->d_zp, e->d_z, cb, cudaMemcpyDeviceToDevice, e->stream));
+      break;
+    }
+    case TLFEA_KOP_RESIDUAL:  // local g from the rank's own f_int, mass and f_ext: halo-sum g afterwards
+      TL_TRY(compute_residual(s));
+      break;
+    case TLFEA_KOP_NORM_G:
+      TL_TRY(dot_owned(s, s->d_g, s->d_g, s->d_scal + 3));
+      break;
+    case TLFEA_KOP_BEGIN:  // r = -g, dv = 0, raw diagonal blocks of the local H
+      TL_LAUNCH(k_neg_copy, gb, 256, 0, e->stream, n, s->d_g, r);
+      TL_CUDA(cudaMemsetAsync(x, 0, n * sizeof(double), e->stream));
+      TL_LAUNCH(k_diag_extract, nb, 256, 0, e->stream, e->n_coef, e->pat.d_off, e->pat.d_cols, s->d_H, diag);
+      break;
+    case TLFEA_KOP_PRECOND:  // after the halo sum of the diagonal blocks
+      TL_LAUNCH(k_diag_invert, nb, 256, 0, e->stream, e->n_coef, diag, Dinv);
+      TL_LAUNCH(k_block_jacobi, nb, 256, 0, e->stream, e->n_coef, Dinv, r, z);
+      TL_CUDA(cudaMemcpyAsync(p, z, n * sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
+      TL_TRY(dot_owned(s, r, z, s->d_scal + 0));
+      TL_TRY(dot_owned(s, r, r, s->d_scal + 3));
+      break;
+    case TLFEA_KOP_SPMV:  // Ap = H_local p: halo-sum Ap afterwards
+      TL_LAUNCH(k_spmv, blocks_for((int64_t)e->n_coef * 32, 256), 256, 0, e->stream, e->n_coef, e->pat.d_off,
+                e->pat.d_cols, s->d_H, p, Ap);
+      break;
+    case TLFEA_KOP_PAP:
+      TL_TRY(dot_owned(s, p, Ap, s->d_scal + 1));
+      break;
+    case TLFEA_KOP_UPDATE_XR:  // alpha = r.z / p.Ap; dv += alpha p; r -= alpha Ap; z = Dinv r
+      TL_LAUNCH(k_pcg_update_xr, gb, 256, 0, e->stream, n, s->d_scal, p, Ap, x, r);
+      TL_LAUNCH(k_block_jacobi, nb, 256, 0, e->stream, e->n_coef, Dinv, r, z);
+      TL_TRY(dot_owned(s, r, z, s->d_scal + 2));
+      TL_TRY(dot_owned(s, r, r, s->d_scal + 3));
+      break;
+    case TLFEA_KOP_UPDATE_P:  // beta = new r.z / old r.z; p = z + beta p
+      TL_LAUNCH(k_pcg_update_p, gb, 256, 0, e->stream, n, s->d_scal, z, p);
+      TL_LAUNCH(k_copy_scalar, 1, 1, 0, e->stream, s->d_scal + 0, s->d_scal + 2);
+      break;
+    case TLFEA_KOP_APPLY:  // v += dv; x = x_prev + h v   (SyncedNewton.cu:1116-1119)
+      TL_LAUNCH(k_axpy, gb, 256, 0, e->stream, n, 1.0, x, s->d_v);
+      TL_LAUNCH(k_update_pos, nb, 256, 0, e->stream, e->n_coef, s->d_xp, s->d_yp, s->d_zp, s->d_v, h, e->d_x, e->d_y,
+                e->d_z);
+      break;
+    default:
+      return fail(TLFEA_ERR_INVALID, "unknown Krylov op %d", op);
+  }
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
+double *tlfea_newton_devptr_krylov(tlfea_newton *s, int which) {
+  if (!s) return nullptr;
+  switch (which) {
+    case TLFEA_KVEC_Z: return s->d_pcg[0];
+    case TLFEA_KVEC_P: return s->d_pcg[1];
+    case TLFEA_KVEC_AP: return s->d_pcg[2];
+    case TLFEA_KVEC_DIAG: return s->d_pcg[4];
+    case TLFEA_KVEC_R: return s->d_r;
+    case TLFEA_KVEC_DV: return s->d_dv;
+    case TLFEA_KVEC_SCAL: return s->d_scal;
+    default: return nullptr;
+  }
 }
 
 int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset) {

@@ -111,6 +111,9 @@ _SIGS = {
     "tlfea_newton_devptr_v": (c_vp, [c_vp]),
     "tlfea_newton_devptr_hessian_values": (c_vp, [c_vp]),
     "tlfea_newton_devptr_g": (c_vp, [c_vp]),
+    "tlfea_newton_set_owned_range": (C.c_int, [c_vp, C.c_int64, C.c_int64]),
+    "tlfea_newton_krylov_op": (C.c_int, [c_vp, C.c_int]),
+    "tlfea_newton_devptr_krylov": (C.c_void_p, [c_vp, C.c_int]),
     "tlfea_newton_spmv": (C.c_int, [c_vp, c_vp, c_vp]),
     "tlfea_newton_timing": (C.c_int, [c_vp, c_dp, c_ip, C.c_int]),
     "tlfea_newton_set_assembly": (C.c_int, [c_vp, C.c_int]),
