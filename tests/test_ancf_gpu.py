@@ -177,6 +177,14 @@ def test_force_tangent_vs_oracle(kind, model, damp):
     s.Assemble()
     assert np.array_equal(H, s.RetrieveHessianValues())
     assert np.array_equal(f, d.RetrieveInternalForceToCPU())
+    # the two assembly paths (element kernel + row reduce for SVK; generic row gather) agree, and so does force-only
+    s.SetAssembly(0)
+    s.Assemble()
+    assert rel_err(s.RetrieveHessianValues(), H) < 1e-13
+    assert rel_err(d.RetrieveInternalForceToCPU(), f) < 1e-13
+    s.SetAssembly(1)
+    s.AssembleForce()
+    assert rel_err(d.RetrieveInternalForceToCPU(), f) < 1e-13
 
 
 @pytest.mark.parametrize("kind", [3243, 3443])

@@ -654,20 +654,20 @@ __global__ void k_row_desc(int n, const int *__restrict__ order, const int *__re
 // RK_U = visits in flight per warp, MINB = resident blocks per SM the register budget is set for
 template <int S, int RK_U, int MINB>
 __global__ void __launch_bounds__(RK_WARPS * 32, MINB) rk_kernel(RKArgs p) {
-  static_assert(S * 9 <= 96, "a visit record is read as three coalesced 32-double rows");
   constexpr int VIS = S * 9;
+  constexpr int NK = (VIS + 31) / 32;  // a visit record is read as NK coalesced 32-double rows (3 for S <= 10)
   extern __shared__ double rk_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *rowbuf = rk_smem + (size_t)warp * p.row_stride;
   // lane l adds doubles l, l+32, l+64 of every visit record: block b = idx / 9, entry idx % 9
-  int lb[3], lk[3];
+  int lb[NK], lk[NK];
 #pragma unroll
-  for (int k = 0; k < 3; k++) {
+  for (int k = 0; k < NK; k++) {
     const int idx = min(lane + 32 * k, VIS - 1);
     lb[k] = idx / 9;
     lk[k] = idx - 9 * lb[k];
   }
-  const bool on2 = lane + 64 < VIS;
+  const bool on2 = lane + 32 * (NK - 1) < VIS;  // the last row of a record may be partial
 
   // Dynamic schedule: a warp draws tickets of RK_T consecutive rows (processing order) from a global counter,
   // so every resident warp works at the same frontier of the Morton order and the element records the
@@ -703,8 +703,8 @@ __global__ void __launch_bounds__(RK_WARPS * 32, MINB) rk_kernel(RKArgs p) {
     // Every global load of the row's first phase is issued before anything waits on one:
     // the first batch of block values + slots, the first 10 element forces, the mass row.
     double *fbuf = rowbuf + p.row_stride - 32;
-    double val[RK_U][3];
-    unsigned sl[RK_U][3];
+    double val[RK_U][NK];
+    unsigned sl[RK_U][NK];
     auto load_batch = [&](int v0) {
 #pragma unroll
       for (int u = 0; u < RK_U; u++) {
@@ -714,13 +714,14 @@ __global__ void __launch_bounds__(RK_WARPS * 32, MINB) rk_kernel(RKArgs p) {
           const int ea = (v < 32) ? ea_s : p.inc_ea[vb + v];
           const double *src = p.stage + (int64_t)ea * VIS + lane;  // record of visit (e, a): [b][9], contiguous
           const uint16_t *ss = p.slot + (int64_t)(vb + v) * S;
-          val[u][0] = src[0];
-          val[u][1] = src[32];
-          sl[u][0] = ss[lb[0]];
-          sl[u][1] = ss[lb[1]];
+#pragma unroll
+          for (int k = 0; k < NK - 1; k++) {
+            val[u][k] = src[32 * k];
+            sl[u][k] = ss[lb[k]];
+          }
           if (on2) {
-            val[u][2] = src[64];
-            sl[u][2] = ss[lb[2]];
+            val[u][NK - 1] = src[32 * (NK - 1)];
+            sl[u][NK - 1] = ss[lb[NK - 1]];
           }
         }
       }
@@ -776,9 +777,9 @@ __global__ void __launch_bounds__(RK_WARPS * 32, MINB) rk_kernel(RKArgs p) {
 #pragma unroll
       for (int u = 0; u < RK_U; u++) {
         if (v0 + u < nvis) {
-          rowbuf[sl[u][0] * 9 + lk[0]] += val[u][0];
-          rowbuf[sl[u][1] * 9 + lk[1]] += val[u][1];
-          if (on2) rowbuf[sl[u][2] * 9 + lk[2]] += val[u][2];
+#pragma unroll
+          for (int k = 0; k < NK - 1; k++) rowbuf[sl[u][k] * 9 + lk[k]] += val[u][k];
+          if (on2) rowbuf[sl[u][NK - 1] * 9 + lk[NK - 1]] += val[u][NK - 1];
         }
         __syncwarp();
       }

@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 #include "ek_kernel.cuh"
+#include "ancf_ek.cuh"
 
 namespace tlfea {
 int launch_gp(tlfea_elem *h, const double *v, double *rec, double *fe, double *F_out, double *P_out);
@@ -363,7 +364,9 @@ static EKCfg ek_cfg() {
 
 static bool ek_supported(const tlfea_newton *s) {
   const tlfea_elem *e = s->e;
-  return s->two_phase && e->type == TLFEA_TYPE_T10;  // SVK and Mooney-Rivlin, with or without Kelvin-Voigt damping
+  if (!s->two_phase) return false;
+  if (e->type == TLFEA_TYPE_T10) return true;  // SVK and Mooney-Rivlin, with or without Kelvin-Voigt damping
+  return e->model == TL_MODEL_SVK;             // ANCF: SVK (+ damping); Mooney-Rivlin stays on the generic path
 }
 
 template <int G, int W, bool DAMP, bool TANGENT, int MODEL>
@@ -392,6 +395,23 @@ static int launch_ek_cfg(tlfea_elem *e, const EKArgs &a) {
   return launch_ek_t<2, 8, DAMP, TANGENT, TL_MODEL_SVK>(e, a);  // most warps per SM: the kernel is latency / LSU bound
 }
 
+template <int S, int Q, int EPB, bool DAMP, bool TANGENT>
+static int launch_aek_t(tlfea_elem *e, const AEKArgs &a) {
+  using Sh = AEKShape<S, Q, EPB, DAMP>;
+  static_assert(Sh::SMEM <= 48 * 1024, "fits the default dynamic shared memory limit");
+  const int n_groups = (a.n_elem + EPB - 1) / EPB;
+  const int per_sm = std::max(1, std::min((int)((227 * 1024) / (Sh::SMEM + 1024)), 2048 / Sh::THREADS));
+  const int grid = std::max(1, std::min(n_groups, 148 * per_sm));
+  TL_LAUNCH((aek_kernel<S, Q, EPB, DAMP, TANGENT>), grid, Sh::THREADS, Sh::SMEM, e->stream, a);
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+template <bool DAMP, bool TANGENT>
+static int launch_aek(tlfea_elem *e, const AEKArgs &a) {
+  if (e->type == TLFEA_TYPE_3243) return launch_aek_t<8, 12, 7, DAMP, TANGENT>(e, a);
+  return launch_aek_t<16, 48, 1, DAMP, TANGENT>(e, a);
+}
+
 static int ek_chunk_elems() {
   static int c = [] {
     const char *e = getenv("TLFEA_EK_CHUNK");  // elements per interleaved E/R chunk (0 = two full passes)
@@ -407,8 +427,9 @@ static int ek_chunk_elems() {
 static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   tlfea_elem *e = s->e;
   const double h = s->prm.time_step;
-  if (tangent && !s->d_stage)
-    TL_TRY(dmalloc(&s->d_stage, (size_t)e->n_elem * EK_ELEM));
+  const bool t10 = (e->type == TLFEA_TYPE_T10);
+  const int64_t rec = (int64_t)e->S * e->S * 9;  // doubles of one element's block records [a][b][9]
+  if (tangent && !s->d_stage) TL_TRY(dmalloc(&s->d_stage, (size_t)e->n_elem * rec));
   if (tangent && !s->d_rowdesc) {
     int chunk = ek_chunk_elems();
     if (chunk <= 0 || chunk >= e->n_elem) chunk = e->n_elem;
@@ -441,7 +462,30 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   a.mu10 = e->mu10;
   a.mu01 = e->mu01;
   a.kappa = e->kappa;
+  AEKArgs aa;
+  aa.x = e->d_x;
+  aa.y = e->d_y;
+  aa.z = e->d_z;
+  aa.v = damp ? s->d_v : nullptr;
+  aa.qw = e->qw;
+  aa.lambda = e->lambda;
+  aa.mu = e->mu;
+  aa.eta = e->eta;
+  aa.lambda_d = e->lambda_d;
+  aa.c1 = a.c1;
+  aa.c2 = a.c2;
+  aa.c4 = h;
   auto launch_e = [&](int e0, int ne) -> int {
+    if (!t10) {
+      aa.n_elem = ne;
+      aa.ecoef = e->d_ecoef + (int64_t)e0 * e->S;
+      aa.gradN = e->d_gradN + (int64_t)e0 * e->Q * 3 * e->S;
+      aa.detJ = e->d_detJ + (int64_t)e0 * e->Q;
+      aa.fe = e->d_fe + (int64_t)e0 * e->S * 3;
+      aa.stage = tangent ? s->d_stage + (int64_t)e0 * rec : nullptr;
+      if (tangent) return damp ? launch_aek<true, true>(e, aa) : launch_aek<false, true>(e, aa);
+      return damp ? launch_aek<true, false>(e, aa) : launch_aek<false, false>(e, aa);
+    }
     a.n_elem = ne;
     a.ecoef = e->d_ecoef + (int64_t)e0 * 10;
     a.gradN = e->d_gradN + (int64_t)e0 * 150;
@@ -479,6 +523,8 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
     TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TL_CUDA(cudaFuncSetAttribute(rk_kernel<8, 5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    TL_CUDA(cudaFuncSetAttribute(rk_kernel<16, 3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
   const int per_sm = std::max(1, std::min(want_sm, (int)((227 * 1024) / (smem + 2048))));
   const int n_chunks = (int)s->chunk_ptr.size() - 1;
@@ -494,7 +540,11 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
     r.counter = s->d_tickets + k;
     const int blocks = (nr + RK_WARPS * RK_T - 1) / (RK_WARPS * RK_T);
     const int grid = std::min(blocks, 148 * per_sm);
-    if (rk_cfg == 1)
+    if (e->type == TLFEA_TYPE_3243)
+      TL_LAUNCH((rk_kernel<8, 5, 3>), grid, RK_WARPS * 32, smem, e->stream, r);
+    else if (e->type == TLFEA_TYPE_3443)
+      TL_LAUNCH((rk_kernel<16, 3, 3>), grid, RK_WARPS * 32, smem, e->stream, r);
+    else if (rk_cfg == 1)
       TL_LAUNCH((rk_kernel<10, 4, 4>), grid, RK_WARPS * 32, smem, e->stream, r);
     else if (rk_cfg == 2)
       TL_LAUNCH((rk_kernel<10, 8, 2>), grid, RK_WARPS * 32, smem, e->stream, r);
