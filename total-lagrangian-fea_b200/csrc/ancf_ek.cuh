@@ -49,7 +49,7 @@ struct AEKShape {
 };
 
 template <int S, int Q, int EPB, bool DAMP, bool TANGENT>
-__global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS) aek_kernel(AEKArgs p) {
+__global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 5 : 4) aek_kernel(AEKArgs p) {
   using Sh = AEKShape<S, Q, EPB, DAMP>;
   constexpr int T = Sh::THREADS, HS = Sh::HS, RS = Sh::RS, NP = Sh::NPAIR;
   extern __shared__ __align__(16) double aek_smem[];
