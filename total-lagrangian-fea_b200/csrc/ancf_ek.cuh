@@ -43,8 +43,10 @@ struct AEKShape {
   static constexpr int H_D = Q * HS;             // per element
   static constexpr int STG_D = S * RS;           // per element; aliases gradN + u after the block step
   static_assert(STG_D <= 2 * H_D, "block staging must fit in the gradN + u region");
-  static constexpr int M_D = Q * 7, P_D = Q * 9, X_D = S * 3;
-  static constexpr int ELEM_D = 2 * H_D + M_D + P_D + X_D * (DAMP ? 2 : 1);
+  static constexpr int M_D = Q * 8, P_D = Q * 9, X_D = S * 3;  // M_q padded to 8: four 16-byte loads in the block step
+  static constexpr int H2_D = (2 * H_D + 1) / 2 * 2;            // keeps M 16-byte aligned
+  // odd element stride: the lanes of a warp that belong to different elements must not share banks
+  static constexpr int ELEM_D = (EPB > 1) ? ((H2_D + M_D + P_D + X_D * (DAMP ? 2 : 1) + 1) | 3) - 1 : H2_D + M_D + P_D + X_D * (DAMP ? 2 : 1);
   static constexpr size_t SMEM = (size_t)EPB * ELEM_D * sizeof(double);
 };
 
@@ -80,7 +82,7 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 
       for (int i = tid; i < ne * S; i += T) {
         const int el = i / S, a = i - el * S;
         const int c = p.ecoef[(int64_t)(e0 + el) * S + a];
-        double *sx = aek_smem + el * Sh::ELEM_D + 2 * Sh::H_D + Sh::M_D + Sh::P_D;
+        double *sx = aek_smem + el * Sh::ELEM_D + Sh::H2_D + Sh::M_D + Sh::P_D;
         sx[a * 3 + 0] = p.x[c];
         sx[a * 3 + 1] = p.y[c];
         sx[a * 3 + 2] = p.z[c];
@@ -98,7 +100,7 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 
       double *se = aek_smem + el * Sh::ELEM_D;
       const double *hq = se + q * HS;
       double *uq = se + Sh::H_D + q * HS;
-      const double *sx = se + 2 * Sh::H_D + Sh::M_D + Sh::P_D;
+      const double *sx = se + Sh::H2_D + Sh::M_D + Sh::P_D;
       double F[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
       double Fd[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
 #pragma unroll 4
@@ -160,7 +162,7 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 
             P[i][j] += sv;
           }
       }
-      double *sP = se + 2 * Sh::H_D + Sh::M_D + q * 9;
+      double *sP = se + Sh::H2_D + Sh::M_D + q * 9;
 #pragma unroll
       for (int i = 0; i < 3; i++)
 #pragma unroll
@@ -172,7 +174,7 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 
 #pragma unroll
           for (int i = 0; i < 3; i++) uq[i * S + a] = F[i][0] * ha[0] + F[i][1] * ha[1] + F[i][2] * ha[2];
         }
-        double *sM = se + 2 * Sh::H_D + q * 7;
+        double *sM = se + Sh::H2_D + q * 8;
         const double sI = p.c4 * dV * (p.lambda * trE - p.mu);
         const double cf = p.c2 * dV;
         sM[0] = cf * FFT[0][0] + sI;
@@ -189,7 +191,7 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 
     if (tid < ne * 3 * S) {
       const int el = tid / (3 * S), r = tid - el * 3 * S, a = r / 3, i = r - 3 * a;
       const double *se = aek_smem + el * Sh::ELEM_D;
-      const double *sP = se + 2 * Sh::H_D + Sh::M_D;
+      const double *sP = se + Sh::H2_D + Sh::M_D;
       double f = 0.0;
       for (int q = 0; q < Q; q++) {
         const double *hq = se + q * HS;
@@ -206,8 +208,11 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 
         double A[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, G[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll 2
         for (int q = 0; q < Q; q++) {
-          const double *hq = se + q * HS, *uq = se + Sh::H_D + q * HS, *mq = se + 2 * Sh::H_D + q * 7;
-          const double dV = mq[6];
+          const double *hq = se + q * HS, *uq = se + Sh::H_D + q * HS;
+          const double2 *m2 = reinterpret_cast<const double2 *>(se + Sh::H2_D + q * 8);  // same address in every lane
+          const double2 m01 = m2[0], m23 = m2[1], m45 = m2[2], m67 = m2[3];
+          const double mq[6] = {m01.x, m01.y, m23.x, m23.y, m45.x, m45.y};
+          const double dV = m67.x;
           const double hab = hq[pa] * hq[pb] + hq[S + pa] * hq[S + pb] + hq[2 * S + pa] * hq[2 * S + pb];
           const double ua[3] = {uq[pa] * dV, uq[S + pa] * dV, uq[2 * S + pa] * dV};
           const double ub[3] = {uq[pb], uq[S + pb], uq[2 * S + pb]};
