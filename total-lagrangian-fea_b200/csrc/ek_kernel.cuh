@@ -1,4 +1,5 @@
-// ek_kernel.cuh -- two-phase deterministic assembly for FEAT10 (S = 10, Q = 5), SVK (+ Kelvin-Voigt).
+// ek_kernel.cuh -- two-phase deterministic assembly for FEAT10 (S = 10, Q = 5): SVK or Mooney-Rivlin, each with
+// optional Kelvin-Voigt damping.  The row-reduce kernel at the end of the file also serves the ANCF elements.
 //
 // Reference behaviour replaced (file:line relative to the reference root):
 //   compute_p                     FEAT10DataFunc.cuh:85-293
@@ -6,10 +7,12 @@
 //   compute_hessian_assemble_csr  FEAT10DataFunc.cuh:512-791   (900 binary searches + 900 FP64 atomics per thread)
 //   assemble_sparse_hessian_mass  SyncedNewton.cu:213-259
 //   svk_compute_tangent_block     SVK.cuh:35-55
+//   mr_compute_P / mr_compute_tangent_tensor  MooneyRivlin.cuh:45-225
 //
 // Phase E (ek_kernel, element-parallel, FP64-pipe + shared-memory work): ONE WARP PER GROUP OF G ELEMENTS.
-//   * gradN / detJ / connectivity / nodal coordinates of the NEXT group are in flight (cp.async into a
-//     per-warp double buffer) while the current one computes;
+//   * gradN (one TMA bulk copy per group, per-warp mbarrier) and detJ / connectivity / gathered nodal
+//     coordinates (cp.async) of the NEXT group are in flight into a per-warp double buffer while the current
+//     one computes;
 //   * Gauss-point step: lane = (element-in-group, q) builds F, P (SVK + Kelvin-Voigt), u_a = F h_a, the
 //     force partials P dV h_a and the 6 numbers of
 //       M_q = dV [ (h mu + eta) F F^T + h (lambda trE - mu) I ]          (symmetric 3x3)
@@ -20,12 +23,16 @@
 //       A  += (dV u_a) u_b^T   (9 DFMA)      G += (h_a.h_b) M_q   (3 + 6 DFMA)
 //     (18 DFMA per (pair, point) instead of the reference's ~170 flop), then
 //       K_ab = c1 A + c2 A^T + h mu tr(A) I + G,   K_ba = K_ab^T;
-//   * the 100 blocks of an element go to its visit-major record [a][b][9] (7 200 B) through a lane-major
-//     shared-memory staging area, so the global write is one contiguous burst per element pair and every
-//     row visit of phase R reads 720 contiguous bytes; element forces go to fe[e][a][3].
+//   * the 100 blocks of an element go to its visit-major record [a][b][9] (7 200 B) through a chunked
+//     shared-memory staging area laid out so that tile stores and row reads are bank-conflict free (see
+//     ek_chunk_off), so the global write is a sequence of coalesced 720-byte rows and every row visit of
+//     phase R reads 720 contiguous bytes; element forces go to fe[e][a][3];
+//   * Mooney-Rivlin: the Gauss-point step runs on lanes (element, q, row i) and leaves the 81-entry tensor
+//     T = h dV dP/dF (+ the Kelvin-Voigt block in the same form) per point; the block step is the contraction
+//     K_ab[i][k] = sum_J h_a[J] (sum_L T[i][J][k][L] h_b[L]).
 // Phase R (rk_kernel, row-parallel, HBM work): ONE WARP PER COEFFICIENT ROW of H.  The warp zero-fills the
 //   block row in shared memory with M/h on the 3x3 diagonals, adds the row's blocks of every incident element
-//   in ASCENDING ELEMENT ORDER (three coalesced loads per visit record), sums the nodal force in the
+//   in ASCENDING ELEMENT ORDER (ceil(9S/32) coalesced loads per visit record), sums the nodal force in the
 //   same order, and streams the finished 3 scalar CSR rows to H exactly once.
 // No atomics, no searches, fixed summation order => bit-reproducible results.
 #pragma once
