@@ -235,6 +235,10 @@ enum {
 };
 enum { TLFEA_KVEC_Z = 0, TLFEA_KVEC_P = 1, TLFEA_KVEC_AP = 2, TLFEA_KVEC_DIAG = 3, TLFEA_KVEC_R = 4, TLFEA_KVEC_DV = 5,
        TLFEA_KVEC_SCAL = 6 };
+/* 3x3 diagonal blocks of the assembled H, out[n_coef][9] row-major (n = 9*n_coef): the per-node Hessian block of the
+ * reference's VBD sweep (vbd_accumulate_residual_and_hessian_diag, FEAT10DataFunc.cuh:295-395); together with
+ * tlfea_newton_get_g it feeds VBD / block-Jacobi consumers without re-integrating the elements. */
+int tlfea_newton_get_diag_blocks(tlfea_newton *s, double *out, int64_t n);
 int tlfea_newton_set_owned_range(tlfea_newton *s, int64_t dof_lo, int64_t dof_hi); /* dot products count [lo, hi) */
 int tlfea_newton_krylov_op(tlfea_newton *s, int op);
 double *tlfea_newton_devptr_krylov(tlfea_newton *s, int which);

@@ -338,3 +338,24 @@ def test_update_nodal_fixed_moves_the_penalty_entries(mesh):
     with pytest.raises(Exception):  # a different count cannot be absorbed by the bound solver
         d.UpdateNodalFixed(face0[:-1])
         s.Assemble()
+
+
+def test_diag_blocks_match_the_assembled_hessian(mesh):
+    """tlfea_newton_get_diag_blocks: the per-node 3x3 blocks a VBD sweep needs are exactly H's diagonal blocks."""
+    import scipy.sparse as sp
+
+    X, E, x, v = mesh
+    fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
+    d, s = _make(X, E, "svk", False, fixed)
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    s.Assemble()
+    ro, ci, va = s.RetrieveHessianCSR()
+    A = sp.csr_matrix((va, ci, ro), shape=(s.n_dofs, s.n_dofs)).tobsr(blocksize=(3, 3))
+    D = s.RetrieveHessianDiagBlocks()
+    nn = X.shape[0]
+    ref = np.zeros((nn, 3, 3))
+    for i in range(nn):
+        for k in range(A.indptr[i], A.indptr[i + 1]):
+            if A.indices[k] == i:
+                ref[i] = A.data[k]
+    assert np.array_equal(D, ref)

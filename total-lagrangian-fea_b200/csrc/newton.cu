@@ -1142,6 +1142,25 @@ int tlfea_newton_krylov_op(tlfea_newton *s, int op) {
   return TLFEA_OK;
 }
 
+// 3x3 diagonal blocks of the assembled H, [n_coef][9] row-major: what the reference's VBD sweep builds per node
+// (vbd_accumulate_residual_and_hessian_diag, FEAT10DataFunc.cuh:295-395) -- here they are a by-product of the
+// deterministic assembly, so the VBD / block-Jacobi consumers read them instead of re-integrating.
+int tlfea_newton_get_diag_blocks(tlfea_newton *s, double *out, int64_t n) {
+  TL_CHECK(s && s->analyzed && out, "AnalyzeHessianSparsity / Assemble must run first");
+  tlfea_elem *e = s->e;
+  TL_CHECK(n == 9 * (int64_t)e->n_coef, "size mismatch: need 9 * n_coef doubles");
+  TL_CUDA(cudaSetDevice(e->device));
+  double *d_tmp = nullptr;
+  TL_TRY(dmalloc(&d_tmp, (size_t)n));
+  TL_LAUNCH(k_diag_extract, blocks_for(e->n_coef, 256), 256, 0, e->stream, e->n_coef, e->pat.d_off, e->pat.d_cols, s->d_H,
+            d_tmp);
+  cudaError_t err = cudaMemcpyAsync(out, d_tmp, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, e->stream);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(e->stream);
+  cudaFree(d_tmp);
+  TL_CUDA(err);
+  return TLFEA_OK;
+}
+
 double *tlfea_newton_devptr_krylov(tlfea_newton *s, int which) {
   if (!s) return nullptr;
   switch (which) {

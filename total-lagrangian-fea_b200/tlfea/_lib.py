@@ -111,6 +111,7 @@ _SIGS = {
     "tlfea_newton_devptr_v": (c_vp, [c_vp]),
     "tlfea_newton_devptr_hessian_values": (c_vp, [c_vp]),
     "tlfea_newton_devptr_g": (c_vp, [c_vp]),
+    "tlfea_newton_get_diag_blocks": (C.c_int, [c_vp, c_dp, C.c_int64]),
     "tlfea_newton_set_owned_range": (C.c_int, [c_vp, C.c_int64, C.c_int64]),
     "tlfea_newton_krylov_op": (C.c_int, [c_vp, C.c_int]),
     "tlfea_newton_devptr_krylov": (C.c_void_p, [c_vp, C.c_int]),

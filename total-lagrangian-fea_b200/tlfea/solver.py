@@ -100,6 +100,12 @@ class SyncedNewtonSolver(SolverBase):
             None if ci is None else ci.ctypes.data_as(c_ip), None if va is None else _d(va)))
         return ro, ci, va
 
+    def RetrieveHessianDiagBlocks(self):
+        """[n_coef, 3, 3]: the per-node diagonal blocks of H (VBD / block-Jacobi consumers)."""
+        out = np.empty(3 * self.n_dofs)
+        check(lib.tlfea_newton_get_diag_blocks(self._h, _d(out), out.shape[0]))
+        return out.reshape(-1, 3, 3)
+
     def RetrieveHessianValues(self):
         va = np.empty(self.nnz())
         check(lib.tlfea_newton_get_hessian_csr(self._h, None, None, _d(va)))
