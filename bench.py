@@ -492,7 +492,7 @@ def main():
         s.SetVelocityGuess(np.zeros(s.n_dofs))
 
     cpu_base = None
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:  # the contract: rank 0, N = 1 only
         gps, threads, desc, dt = cpu_sample(args.cpu_n, 5)
         cpu_base = {"value": gps, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc,
                     "seconds_per_pass": dt}
