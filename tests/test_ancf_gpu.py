@@ -215,3 +215,43 @@ def test_setup_path_vs_oracle(kind):
     ro, ci, _ = s.RetrieveHessianCSR(want_values=False)
     ro_ref, ci_ref = orc.dof_pattern(off_ref, cols_ref)
     assert np.array_equal(ro, ro_ref) and np.array_equal(ci, ci_ref)  # bit-exact
+
+
+@pytest.mark.parametrize("kind", [3243, 3443])
+def test_reference_prototype_vectors(kind):
+    """GPU set-up, mass, SVK force and tangent against vectors produced by the reference's own numpy prototypes
+    (test-scripts/3243-beam/f-form-3243-nesterov.py, test-scripts/3443-shell/f-form-3443-nesterov.py;
+    tests/golden/make_golden_ancf.py): consistent mass, internal force of a perturbed configuration, and the exact
+    derivative of the prototype's force as the tangent.  1e-11: the prototypes' quadrature tables carry 15 digits."""
+    g = dict(np.load(os.path.join(GOLDEN, f"ancf{kind}_proto.npz")))
+    dims = (float(g["L"]), float(g["W"]), float(g["H"]))
+    conn = np.ascontiguousarray(g["conn"], dtype=np.int32)
+    import tlfea
+
+    nc = g["x"].shape[0]
+    cls = tlfea.GPU_ANCF3243_Data if kind == 3243 else tlfea.GPU_ANCF3443_Data
+    d = cls(nc // 4, conn.shape[0])
+    d.Initialize()
+    d.Setup(*dims, g["x_ref"], g["y_ref"], g["z_ref"], conn)
+    d.SetDensity(float(g["rho"]))
+    d.SetSVK(float(g["Emod"]), float(g["nu"]))
+    d.CalcDsDuPre()
+    d.CalcMassMatrix()
+    h = 1.0
+    s = tlfea.SyncedNewtonSolver(d, 0)
+    s.SetParameters(tlfea.SyncedNewtonParams(1e-4, 0.0, 1e-6, 1e14, 1, 1, h))
+    s.Setup()
+    s.AnalyzeHessianSparsity()
+    M = dense_mass(d)
+    assert rel_err(M, g["M"]) < 1e-11
+    d.UpdatePositions(g["x"], g["y"], g["z"])
+    for mode in (1, 0):  # element kernel + row reduce, generic row gather
+        s.SetAssembly(mode)
+        s.Assemble()
+        assert rel_err(d.RetrieveInternalForceToCPU(), g["f_int"]) < 1e-11
+        ro, ci, Hv = s.RetrieveHessianCSR()
+        Hd = np.zeros((3 * nc, 3 * nc))
+        for r in range(3 * nc):
+            Hd[r, ci[ro[r]:ro[r + 1]]] = Hv[ro[r]:ro[r + 1]]
+        # H = M/h (x) I3 + h K_t with h = 1
+        assert rel_err(Hd - np.kron(M, np.eye(3)), g["K_t"]) < 1e-11

@@ -200,3 +200,47 @@ def test_oracle_ancf_precompute_invariants(kind):
             h = g[e, q].reshape(3, S)  # h[j, a]
             F = coords[ec[e]].T @ h.T
             assert np.abs(F - np.eye(3)).max() < 1e-12
+
+
+@pytest.mark.parametrize("kind", [3243, 3443])
+def test_oracle_ancf_matches_reference_prototype(kind):
+    """The oracle's ANCF path (B^-T, reference gradients, detJ, consistent mass, SVK P, internal force) against
+    the reference's own numpy prototypes test-scripts/3243-beam/f-form-3243-nesterov.py and
+    test-scripts/3443-shell/f-form-3443-nesterov.py (golden: tests/golden/make_golden_ancf.py).  The prototypes
+    integrate in (u,v,w) with ds/du and det * LWH/8, the CUDA code (and the oracle) in (xi,eta,zeta) with
+    J^-T ds/dxi: the two must give the same physical force and mass."""
+    g = dict(np.load(os.path.join(GOLDEN, f"ancf{kind}_proto.npz")))
+    conn = g["conn"]
+    ne, nc = conn.shape[0], g["x"].shape[0]
+    L, W, H = float(g["L"]), float(g["W"]), float(g["H"])
+    ec = orc.ancf_ecoef(kind, conn)
+    S = ec.shape[1]
+    Binv = orc.ancf_binv(kind, [L] * ne, [W] * ne, [H] * ne)
+    # B^-1 of the prototype is inv(B) with B's columns the node rows; the oracle stores B^-T row-major or its
+    # transpose -- compare as a set of shape functions through the mass matrix and the force below, and directly
+    # up to transposition here
+    Bo = Binv[0].reshape(S, S)
+    assert min(rel_err(Bo, g["B_inv"]), rel_err(Bo.T, g["B_inv"])) < 1e-12
+    LWH = np.tile([L, W, H], (ne, 1))
+    off, cols = orc.coef_pattern(ec, nc)
+    vals = orc.ancf_mass(kind, ec, g["x_ref"], g["y_ref"], g["z_ref"], LWH, Binv, float(g["rho"]), off, cols)
+    M = np.zeros((nc, nc))
+    for i in range(nc):
+        M[i, cols[off[i]:off[i + 1]]] = vals[off[i]:off[i + 1]]
+    assert rel_err(M, g["M"]) < 1e-11  # the prototype's quadrature tables carry 15 digits
+    gradN, detJ = orc.ancf_precompute(kind, ec, g["x_ref"], g["y_ref"], g["z_ref"], LWH, Binv)
+    qw = orc.ancf_stiffness_weights(kind)
+    mat = orc.Material.svk(float(g["Emod"]), float(g["nu"]))
+    coords = np.stack([g["x"], g["y"], g["z"]], axis=1)
+    _, P = orc.compute_p(ec, coords, gradN, mat)
+    f = orc.internal_force(ec, gradN, detJ, qw, P, nc)
+    assert rel_err(f, g["f_int"]) < 1e-11
+    # consistent tangent against the exact derivative of the prototype's force (Richardson-extrapolated central
+    # differences of a cubic polynomial): h * K_t assembled with h = 1 into an empty H
+    ro, ci = orc.dof_pattern(off, cols)
+    Hv = np.zeros(ci.shape[0])
+    orc.tangent_assemble(ec, coords, gradN, detJ, qw, mat, 1.0, off, cols, Hv)
+    K = np.zeros((3 * nc, 3 * nc))
+    for r in range(3 * nc):
+        K[r, ci[ro[r]:ro[r + 1]]] = Hv[ro[r]:ro[r + 1]]
+    assert rel_err(K, g["K_t"]) < 1e-11
