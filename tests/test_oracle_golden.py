@@ -244,3 +244,82 @@ def test_oracle_ancf_matches_reference_prototype(kind):
     for r in range(3 * nc):
         K[r, ci[ro[r]:ro[r + 1]]] = Hv[ro[r]:ro[r + 1]]
     assert rel_err(K, g["K_t"]) < 1e-11
+
+
+def _mr_energy(F, c1, c2, kappa):
+    """psi = C1 (I1bar - 3) + C2 (I2bar - 3) + kappa/2 (J - 1)^2, the compressible Mooney-Rivlin energy the
+    reference validates against (test-scripts/validation/fenics/beam_dynamic_backward_euler.py:332-342; its
+    P = d psi / d F, :345, is what MooneyRivlin.cuh:45-111 writes out).  Works for complex F (complex step)."""
+    Cm = F.T @ F
+    I1 = np.trace(Cm)
+    I2 = 0.5 * (I1 * I1 - np.trace(Cm @ Cm))
+    J = (F[0, 0] * (F[1, 1] * F[2, 2] - F[1, 2] * F[2, 1]) - F[0, 1] * (F[1, 0] * F[2, 2] - F[1, 2] * F[2, 0])
+         + F[0, 2] * (F[1, 0] * F[2, 1] - F[1, 1] * F[2, 0]))
+    return c1 * (J ** (-2.0 / 3.0) * I1 - 3.0) + c2 * (J ** (-4.0 / 3.0) * I2 - 3.0) + 0.5 * kappa * (J - 1.0) ** 2
+
+
+def _mr_P_complex_step(F, c1, c2, kappa):
+    """d psi / d F by the complex-step derivative: exact to rounding, no subtractive cancellation."""
+    P = np.zeros((3, 3), dtype=F.dtype)
+    hcs = 1e-30
+    for i in range(3):
+        for j in range(3):
+            Fc = F.astype(np.complex128 if F.dtype == np.float64 else F.dtype).copy()
+            Fc[i, j] += 1j * hcs
+            P[i, j] = _mr_energy(Fc, c1, c2, kappa).imag / hcs
+    return P
+
+
+def test_mooney_rivlin_pinned_to_the_reference_energy(o, golden_t10):
+    """Mooney-Rivlin has no numpy prototype in the reference; what the reference does state is the strain energy
+    its FEniCS validation differentiates.  P of the oracle (mr_compute_P, MooneyRivlin.cuh:45-111) must be
+    d psi / d F, and the element tangent (mr_compute_tangent_tensor, :113-225, contracted as in
+    FEAT10DataFunc.cuh:612-659) must be d^2 psi / d F^2 contracted with the shape gradients."""
+    g = golden_t10
+    mu = float(g["mu"])
+    bulk = float(g["Emod"]) / (3 * (1 - 2 * float(g["nu"])))
+    c1, c2, kappa = 0.3 * mu, 0.2 * mu, 1.5 * bulk
+    mat = orc.Material.mooney_rivlin(c1, c2, kappa)
+    x = g["x"]
+    f, F, P = o.force(x, mat)
+    scale = np.abs(P).max()
+    ne, Q = F.shape[:2]
+    Pref = np.zeros_like(P)
+    for e in range(ne):
+        for q in range(Q):
+            Fm = F[e, q].reshape(3, 3)
+            # the reference stores 3x3 matrices column-major or row-major consistently for F and P: detect once
+            Pref[e, q] = _mr_P_complex_step(Fm, c1, c2, kappa).reshape(9)
+    if np.abs(P - Pref).max() > 1e-6 * scale:  # other storage order
+        for e in range(ne):
+            for q in range(Q):
+                Pref[e, q] = _mr_P_complex_step(F[e, q].reshape(3, 3).T, c1, c2, kappa).T.reshape(9)
+    assert np.abs(P - Pref).max() < 1e-12 * scale
+
+    # element tangent: A_iJkL = d P_iJ / d F_kL by Richardson-extrapolated central differences of the
+    # complex-step gradient (truncation O(d^4), rounding ~1e-13), K_ab[i,k] = sum_q dV h_a[J] A_iJkL h_b[L]
+    def grad(Fm):
+        return _mr_P_complex_step(Fm, c1, c2, kappa)
+
+    def dP(Fm, k, l, dd):
+        Fp, Fn = Fm.copy(), Fm.copy()
+        Fp[k, l] += dd
+        Fn[k, l] -= dd
+        return (grad(Fp) - grad(Fn)) / (2 * dd)
+
+    coords = x
+    dd = 2.0 ** -9
+    for e in (0, 17, ne - 1):
+        ec = o.ecoef[e]
+        K_ref = np.zeros((30, 30))
+        for q in range(Q):
+            hN = o.grad_N[e, q].reshape(3, 10)  # h[J, a]
+            Fm = sum(np.outer(coords[ec[a]], hN[:, a]) for a in range(10))
+            A = np.zeros((3, 3, 3, 3))
+            for k in range(3):
+                for l in range(3):
+                    A[:, :, k, l] = (4.0 * dP(Fm, k, l, dd) - dP(Fm, k, l, 2 * dd)) / 3.0
+            dV = o.detJ[e, q] * o.qw[q]
+            K_ref += dV * np.einsum("Ja,iJkL,Lb->aibk", hN, A, hN).reshape(30, 30)
+        K = orc.element_tangent(ec, coords, o.grad_N[e], o.detJ[e], o.qw, mat)
+        assert rel_err(K, K_ref) < 1e-10
