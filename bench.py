@@ -202,6 +202,92 @@ def cpu_sample(n_cpu: int, reps: int):
     return E.shape[0] * 5 / dt, orc.num_threads(), f"kuhn block n={n_cpu} ({E.shape[0]} tets) x {reps} passes", dt
 
 
+def ancf_config(kind: int, shape, torch, fp64_peak, reps=5):
+    """The ANCF configurations of BASELINE.json on one GPU: C3 = ANCF3443 plate 1000 x 1000 (L = W = 1e-2,
+    H = 1e-3, one edge clamped), and the ANCF3243 chain of beam_sag scaled to 1M elements.  SVK, same assemble
+    (f_int + H = M/h + h K_t + h^2 rho J^T J) timed with CUDA events, then two Newton iterations with the fixed
+    50-iteration block-Jacobi PCG.  Algorithmic flop per element: SURVEY.md 8d (0.94 Mflop for 3443, 63 kflop
+    for 3243; both FP64-bound)."""
+    import tlfea
+    from tlfea import meshgen
+
+    t0 = time.perf_counter()
+    if kind == 3443:
+        nx, ny = shape
+        L, W, H = 1e-2, 1e-2, 1e-3
+        x, y, z, conn = meshgen.ancf_plate(nx, ny, L, W)
+        d = tlfea.GPU_ANCF3443_Data(x.shape[0] // 4, conn.shape[0])
+        Q, flop_elem, name = 48, 0.94e6, f"ancf3443_plate_{nx}x{ny}_svk"
+        fixed_nodes = np.arange(ny + 1)  # edge i = 0
+    else:
+        (nx,) = shape
+        L, W, H = 0.5, 0.1, 0.1
+        x, y, z, conn = meshgen.ancf_chain(nx, L)
+        d = tlfea.GPU_ANCF3243_Data(x.shape[0] // 4, conn.shape[0])
+        Q, flop_elem, name = 12, 63e3, f"ancf3243_chain_{nx}_svk"
+        fixed_nodes = np.arange(1)
+    fixed = (4 * fixed_nodes[:, None] + np.arange(4)[None, :]).ravel().astype(np.int32)
+    d.Initialize()
+    d.Setup(L, W, H, x, y, z, conn)
+    d.SetDensity(RHO0)
+    d.SetSVK(E_MOD, NU)
+    d.SetNodalFixed(fixed)
+    d.CalcDsDuPre()
+    d.CalcMassMatrix()
+    s = tlfea.SyncedNewtonSolver(d, 3 * len(fixed))
+    s.SetParameters(tlfea.SyncedNewtonParams(1e-4, 0.0, 1e-6, ALM_RHO, 1, 2, H_STEP))
+    s.Setup()
+    s.AnalyzeHessianSparsity()
+    s.SetFixedSparsityPattern(True)
+    xd, yd, zd = meshgen.ancf_perturb(x, y, z, L, 2234)
+    d.UpdatePositions(xd, yd, zd)
+    d.SetStream(torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    setup_s = time.perf_counter() - t0
+    for _ in range(3):
+        s.Assemble()
+    torch.cuda.synchronize()
+    s.Timing(reset=True)
+    s.SetProfile(True)
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record()
+    for _ in range(reps):
+        s.Assemble()
+    a1.record()
+    torch.cuda.synchronize()
+    kms = s.KernelMs()
+    s.SetProfile(False)
+    ms = a0.elapsed_time(a1) / reps
+    ne = conn.shape[0]
+    out = {"workload": name, "n_elem": int(ne), "gauss_points": int(ne * Q), "n_dofs": int(s.n_dofs), "nnz_H": int(s.nnz()),
+           "ms_per_step": ms, "value": ne * Q / (ms * 1e-3), "unit": UNIT, "element_kernel_ms": kms["gp_ms"] / reps,
+           "row_reduce_kernel_ms": kms["row_ms"] / reps, "setup_s": setup_s,
+           "l2_policy": "gradN and H are far larger than the 126 MB L2"}
+    if fp64_peak:
+        tf = flop_elem * ne / (ms * 1e-3) / 1e12
+        out["fp64"] = {"achieved_tflops": tf, "peak_tflops": fp64_peak, "frac": tf / fp64_peak,
+                       "algorithmic_flop_per_element": flop_elem}
+    s.SetPCG(50, 0.0)
+    s.Solve()  # warm-up (allocates the PCG vectors)
+    d.UpdatePositions(xd, yd, zd)
+    s.Setup()
+    torch.cuda.synchronize()
+    n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0.record()
+    s.Solve()
+    n1.record()
+    torch.cuda.synchronize()
+    st = s.LastStats()
+    nms = n0.elapsed_time(n1)
+    out["newton"] = {"value": st["newton_iters"] / (nms * 1e-3), "unit": "Newton iterations/s",
+                     "newton_iters": st["newton_iters"], "pcg_iters": st["pcg_iters"],
+                     "ms_per_newton_iter": nms / max(st["newton_iters"], 1),
+                     "linear_solver": "block-Jacobi PCG, fixed 50 iterations per Newton iteration"}
+    s.Destroy()
+    d.Destroy()
+    return name, out
+
+
 class _DevArray:
     """Borrowed device pointer -> torch tensor (no copy) through __cuda_array_interface__."""
 
@@ -248,6 +334,9 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-variants", action="store_true", help="skip the damped / Mooney-Rivlin assembles")
     ap.add_argument("--no-newton", action="store_true")
+    ap.add_argument("--no-ancf", action="store_true", help="skip the ANCF3443 plate / ANCF3243 chain configurations")
+    ap.add_argument("--plate", type=int, default=1000, help="ANCF3443 plate: elements per edge (1000 -> 1M elements)")
+    ap.add_argument("--chain", type=int, default=1000000, help="ANCF3243 chain: elements")
     ap.add_argument("--assembly", type=int, default=-1, help="0 generic row gather, 1 element kernel + row reduce (default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -497,6 +586,21 @@ def main():
         cpu_base = {"value": gps, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc,
                     "seconds_per_pass": dt}
 
+    # ---- the ANCF configurations of BASELINE.json (C3 plate, 1M-element beam chain) on the same GPU, after the
+    # FEAT10 problem has been freed (it holds ~125 GB)
+    other = None
+    if world == 1 and not args.no_ancf:
+        del f_int
+        s.Destroy()
+        d.Destroy()
+        other = {}
+        for kind, shape in ((3443, (args.plate, args.plate)), (3243, (args.chain,))):
+            try:
+                name, res = ancf_config(kind, shape, torch, fp64)
+                other[name] = res
+            except Exception as ex:  # the headline line must still be printed
+                other[f"ancf{kind}"] = {"error": repr(ex)}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -508,7 +612,7 @@ def main():
                        "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
                        "setup_s": t_setup},
             "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all,
-            "newton": newton, "variants": variants, "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
+            "newton": newton, "variants": variants, "other_configs": other, "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
         }
         _emit(line)
     if world > 1:

@@ -41,6 +41,35 @@
 
 namespace tlfea {
 
+// Cache hints on the streams that are touched exactly once (A/B switch: -DTLFEA_HINTS=mask at build time).
+//   bit 0: visit records are read by the row-reduce kernel with ld.global.cs (evict-first)
+//   bit 1: finished H rows leave the row-reduce kernel with st.global.cs
+//   bit 2: the element kernel writes its records with st.global.cs
+#ifndef TLFEA_HINTS
+#define TLFEA_HINTS 0
+#endif
+__device__ __forceinline__ double rec_load(const double *p) {
+#if TLFEA_HINTS & 1
+  return __ldcs(p);
+#else
+  return *p;
+#endif
+}
+__device__ __forceinline__ void row_store(double *p, double v) {
+#if TLFEA_HINTS & 2
+  __stcs(p, v);
+#else
+  *p = v;
+#endif
+}
+__device__ __forceinline__ void rec_store(double *p, double v) {
+#if TLFEA_HINTS & 4
+  __stcs(p, v);
+#else
+  *p = v;
+#endif
+}
+
 template <int S>
 struct SymLayout {
   static constexpr int D = S / 2;               // diagonals d = 0..D-1 are stored for every a
@@ -607,9 +636,9 @@ __global__ void __launch_bounds__(W * 32, 1) ek_kernel(EKArgs p) {
             for (int ta = 0; ta < 2; ta++) {
               const double *sr = se + I * EK_CRS + ta * 18;
               double *dr = de + (2 * I + ta) * EK_VIS;
-              dr[0] = sr[cp_off[0]];
-              dr[32] = sr[cp_off[1]];
-              if (lane < 26) dr[64] = sr[I == 4 ? cp_x2 : cp_off[2]];
+              rec_store(dr, sr[cp_off[0]]);
+              rec_store(dr + 32, sr[cp_off[1]]);
+              if (lane < 26) rec_store(dr + 64, sr[I == 4 ? cp_x2 : cp_off[2]]);
             }
         }
         __syncwarp();
@@ -723,11 +752,11 @@ __global__ void __launch_bounds__(RK_WARPS * 32, MINB) rk_kernel(RKArgs p) {
           const uint16_t *ss = p.slot + (int64_t)(vb + v) * S;
 #pragma unroll
           for (int k = 0; k < NK - 1; k++) {
-            val[u][k] = src[32 * k];
+            val[u][k] = rec_load(src + 32 * k);
             sl[u][k] = ss[lb[k]];
           }
           if (on2) {
-            val[u][NK - 1] = src[32 * (NK - 1)];
+            val[u][NK - 1] = rec_load(src + 32 * (NK - 1));
             sl[u][NK - 1] = ss[lb[NK - 1]];
           }
         }
@@ -800,7 +829,7 @@ __global__ void __launch_bounds__(RK_WARPS * 32, MINB) rk_kernel(RKArgs p) {
       double *out = p.H + base + (int64_t)d * rowlen;
       for (int c = lane; c < rowlen; c += 32) {  // c = 3*s + e
         const int sl = c / 3, e2 = c - 3 * sl;
-        out[c] = rowbuf[sl * 9 + d * 3 + e2];
+        row_store(out + c, rowbuf[sl * 9 + d * 3 + e2]);
       }
     }
     __syncwarp();

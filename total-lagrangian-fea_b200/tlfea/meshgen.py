@@ -81,3 +81,38 @@ def read_tetgen(node_file: str, ele_file: str):
     E = np.zeros((ne, 10), dtype=np.int32)
     E[eid - ebase] = (raw - nbase)[:, [0, 1, 2, 3, 6, 7, 9, 5, 8, 4]]
     return X, E
+
+
+def ancf_plate(nx: int, ny: int, L: float, W: float):
+    """Flat ANCF3443 plate of nx x ny elements in the xy plane (config C3: 1000 x 1000, L = W = 1e-2, H = 1e-3).
+    Node (i, j) -> id i*(ny+1)+j with coefficients [r, r_u = e_x, r_v = e_y, r_w = e_z]; element corners in the
+    reference's order P1..P4 = (-,-), (+,-), (+,+), (-,+) (cpu_utils.cc:214-217).  Returns x, y, z ([4 nn]), conn."""
+    ii, jj = np.meshgrid(np.arange(nx + 1), np.arange(ny + 1), indexing="ij")
+    nn = (nx + 1) * (ny + 1)
+    x = np.zeros((nn, 4)); y = np.zeros((nn, 4)); z = np.zeros((nn, 4))
+    x[:, 0] = ii.ravel() * L; x[:, 1] = 1.0
+    y[:, 0] = jj.ravel() * W; y[:, 2] = 1.0
+    z[:, 3] = 1.0
+    ci, cj = (a.ravel() for a in np.meshgrid(np.arange(nx), np.arange(ny), indexing="ij"))
+    nid = lambda i, j: i * (ny + 1) + j  # noqa: E731
+    conn = np.stack([nid(ci, cj), nid(ci + 1, cj), nid(ci + 1, cj + 1), nid(ci, cj + 1)], axis=1).astype(np.int32)
+    return x.ravel(), y.ravel(), z.ravel(), conn
+
+
+def ancf_chain(n_elem: int, L: float):
+    """Straight ANCF3243 beam of n_elem elements along x (GridMeshGenerator's horizontal line, beam_sag layout)."""
+    nn = n_elem + 1
+    x = np.zeros((nn, 4)); y = np.zeros((nn, 4)); z = np.zeros((nn, 4))
+    x[:, 0] = np.arange(nn) * L; x[:, 1] = 1.0
+    y[:, 2] = 1.0
+    z[:, 3] = 1.0
+    conn = np.stack([np.arange(n_elem), np.arange(n_elem) + 1], axis=1).astype(np.int32)
+    return x.ravel(), y.ravel(), z.ravel(), conn
+
+
+def ancf_perturb(x, y, z, L: float, seed: int, pos: float = 0.05, grad: float = 0.02):
+    """SURVEY.md 8d recipe: position slots moved by pos*L*U(-1,1), gradient slots by grad*U(-1,1), PCG64(seed)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    n = x.shape[0]
+    amp = np.tile([pos * L, grad, grad, grad], n // 4)
+    return tuple(a + amp * rng.uniform(-1.0, 1.0, n) for a in (x, y, z))

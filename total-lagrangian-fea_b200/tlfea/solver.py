@@ -37,11 +37,16 @@ class SyncedNewtonSolver(SolverBase):
         check(lib.tlfea_newton_create(data._h, int(n_constraints), C.byref(self._h)))
         self.n_dofs = lib.tlfea_newton_n_dofs(self._h)
 
+    def Destroy(self):
+        """Frees H, the staging records and the Krylov vectors (the reference frees in the destructor,
+        SyncedNewton.cuh:151-204)."""
+        if self._h:
+            lib.tlfea_newton_destroy(self._h)
+            self._h = _lib.c_vp()
+
     def __del__(self):
         try:
-            if self._h:
-                lib.tlfea_newton_destroy(self._h)
-                self._h = _lib.c_vp()
+            self.Destroy()
         except Exception:
             pass
 
