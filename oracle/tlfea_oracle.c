@@ -7,11 +7,22 @@
  * and bench.py's cpu_baseline / --impl reference legs may load this library.
  * The product (libtlfea_b200.so) never links, loads or calls it.
  *
- * Parity pin: cross-checked against the reference's own numpy prototypes
- * (test-scripts/T10-tets/f-form-T10-beam-newton.py, ...-newton-damped.py)
- * imported in place by oracle/ref_proto.py; resulting fixtures are committed
- * in tests/golden/.  The reference's C++/CUDA cannot be built here (needs
- * Eigen, cuDSS, Bazel, a GPU) so there is no oracle/_ref binary.
+ * Parity pin (tests/test_oracle_golden.py; fixtures committed in tests/golden/
+ * with the scripts that made them):
+ *   FEAT10 precompute, mass, SVK and Kelvin-Voigt force + tangent: the reference's
+ *     numpy prototypes test-scripts/T10-tets/f-form-T10-beam-newton.py and
+ *     ...-newton-damped.py, imported in place (oracle/ref_proto.py);
+ *   ANCF3243 / ANCF3443 B^-1, mass, SVK force + tangent: the prototypes
+ *     test-scripts/3243-beam/f-form-3243-nesterov.py and
+ *     test-scripts/3443-shell/f-form-3443-nesterov.py run in place up to their
+ *     time loop (tests/golden/make_golden_ancf.py), plus the known-answer
+ *     matrices data/utest/mass_matrix_{2,3}_beam.csv;
+ *   Mooney-Rivlin P and element tangent: the strain energy stated in
+ *     test-scripts/validation/fenics/beam_dynamic_backward_euler.py:332-345.
+ * Parity unpinned: Kelvin-Voigt and Mooney-Rivlin on the ANCF elements (same
+ * S/Q-generic code as the pinned FEAT10 cases, no reference fixture).
+ * The reference's C++/CUDA cannot be built here (needs Eigen, cuDSS, Bazel, a
+ * GPU) so there is no oracle/_ref binary.
  *
  * Layout conventions restated from the reference (SURVEY.md section 7,
  * "Exact reference semantics"):
