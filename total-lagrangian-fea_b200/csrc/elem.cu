@@ -421,11 +421,21 @@ static int upload_coords(tlfea_elem *h, const double *x, const double *y, const 
   return TLFEA_OK;
 }
 
+// An out-of-range node id would only show up as an illegal address deep inside a kernel (the reference does not
+// check either): refuse it here, where the caller can still be told which entry is wrong.
+static int check_node_ids(const int *conn, int64_t n, int n_nodes) {
+  for (int64_t i = 0; i < n; i++)
+    TL_CHECK(conn[i] >= 0 && conn[i] < n_nodes, "connectivity entry %lld = %d is outside [0, %d)", (long long)i,
+             conn[i], n_nodes);
+  return TLFEA_OK;
+}
+
 int tlfea_elem_setup_t10(tlfea_elem *h, const double *qx, const double *qy, const double *qz, const double *qw,
                          const double *x, const double *y, const double *z, const int *conn) {
   TL_CHECK(h && h->type == TLFEA_TYPE_T10, "handle is not FEAT10");
   TL_CHECK(!h->is_setup, "GPU_FEAT10_Data is already set up.");
   TL_CHECK(qx && qy && qz && qw && x && y && z && conn, "null input");
+  TL_TRY(check_node_ids(conn, (int64_t)h->n_elem * 10, h->n_nodes));
   TL_CUDA(cudaSetDevice(h->device));
   for (int q = 0; q < 5; q++) {
     h->t10_q[0][q] = qx[q];
@@ -450,6 +460,7 @@ int tlfea_elem_setup_3243(tlfea_elem *h, const double *L, const double *W, const
   TL_CHECK(h && h->type == TLFEA_TYPE_3243, "handle is not ANCF3243");
   TL_CHECK(!h->is_setup, "GPU_ANCF3243_Data is already set up.");
   TL_CHECK(L && W && H && x && y && z && conn, "null input");
+  TL_TRY(check_node_ids(conn, (int64_t)h->n_elem * 2, h->n_nodes));
   TL_CUDA(cudaSetDevice(h->device));
   TL_TRY(upload_coords(h, x, y, z, true));
   TL_TRY(ancf_setup(h, L, W, H, conn));
@@ -462,6 +473,7 @@ int tlfea_elem_setup_3443(tlfea_elem *h, const double *L, const double *W, const
   TL_CHECK(h && h->type == TLFEA_TYPE_3443, "handle is not ANCF3443");
   TL_CHECK(!h->is_setup, "GPU_ANCF3443_Data is already set up.");
   TL_CHECK(L && W && H && x && y && z && conn, "null input");
+  TL_TRY(check_node_ids(conn, (int64_t)h->n_elem * 4, h->n_nodes));
   TL_CUDA(cudaSetDevice(h->device));
   TL_TRY(upload_coords(h, x, y, z, true));
   TL_TRY(ancf_setup(h, L, W, H, conn));
