@@ -172,6 +172,18 @@ int tlfea_newton_set_fixed_pattern(tlfea_newton *s, int fixed);
 int tlfea_newton_assemble(tlfea_newton *s);
 /* force half only (what AdamW/Nesterov consume): SyncedNewton.cu:1046-1052 */
 int tlfea_newton_assemble_force(tlfea_newton *s);
+/* The same unit from HOST buffers, with the copies overlapped with the kernels:
+ *   begin = UpdatePositions(x,y,z) (FEAT10Data.cuh:672-712) + tlfea_newton_assemble.  The coordinates go up in chunks
+ *           on a copy stream and the element kernel starts on each element chunk as soon as the coordinates it reads
+ *           have landed; then f_int is summed.  Returns without waiting (the H rows are reduced by end).  Between
+ *           begin and end the caller may work on f_int on the element's stream (the interface halo sum of a
+ *           partitioned mesh) but must not touch H.  x, y, z (n = n_coef each; pinned memory
+ *           for a truly asynchronous copy) must stay valid until end returns.
+ *   end   = tlfea_newton_residual (if norm_g) + RetrieveInternalForceToCPU into f_int[n = 3 n_coef] (if f_int) on the
+ *           main stream, then the H rows are reduced on a second stream WHILE f_int and ||g|| travel back to the host;
+ *           returns when f_int, ||g|| AND H are complete. */
+int tlfea_newton_assemble_host_begin(tlfea_newton *s, const double *x, const double *y, const double *z, int n);
+int tlfea_newton_assemble_host_end(tlfea_newton *s, double *f_int, int n, double *norm_g);
 /* constraints_eval + compute_grad_l + ||g||  SyncedNewton.cu:1056-1064; writes ||g||_2 to *norm_g */
 int tlfea_newton_residual(tlfea_newton *s, double *norm_g);
 /* One implicit step: OneStepNewtonCuDSS (SyncedNewton.cu:909-1394) with the

@@ -359,3 +359,57 @@ def test_diag_blocks_match_the_assembled_hessian(mesh):
             if A.indices[k] == i:
                 ref[i] = A.data[k]
     assert np.array_equal(D, ref)
+
+
+@pytest.mark.parametrize("model,damp,permute", [("svk", False, False), ("svk", True, False), ("mr", False, False),
+                                                ("svk", False, True)])
+def test_host_pipelined_assemble_matches_the_plain_sequence(model, damp, permute):
+    """tlfea_newton_assemble_host_begin/_end (chunked H2D overlapped with the element kernel, H rows reduced on a
+    second stream while f_int goes back to the host) against UpdatePositions + Assemble + Residual +
+    RetrieveInternalForceToCPU: bit-identical H, f_int and ||g||, also when the node numbering is scrambled (every
+    element chunk then needs every coordinate chunk) and when it is called repeatedly with changing positions."""
+    import torch
+    from tlfea import meshgen
+
+    X, E = meshgen.kuhn_block(6)
+    if permute:
+        perm = np.random.Generator(np.random.PCG64(7)).permutation(X.shape[0])
+        inv = np.empty_like(perm)
+        inv[perm] = np.arange(X.shape[0])
+        X, E = X[perm], inv[E].astype(np.int32)
+    fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
+    d, s = _make(X, E, model, damp, fixed)
+    if damp:
+        s.SetVelocityGuess(0.1 * np.random.Generator(np.random.PCG64(1235)).uniform(-1, 1, size=3 * X.shape[0]))
+    pinned = [torch.empty(X.shape[0], dtype=torch.float64).pin_memory().numpy() for _ in range(3)]
+    out = torch.empty(3 * X.shape[0], dtype=torch.float64).pin_memory().numpy()
+    for seed in (1234, 99, 5):
+        x = meshgen.perturb(X, 0.05 / 6, seed)
+        d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+        s.Assemble()
+        ng_ref = s.Residual()
+        f_ref = d.RetrieveInternalForceToCPU()
+        H_ref = s.RetrieveHessianValues()
+        d.UpdatePositions(X[:, 0], X[:, 1], X[:, 2])  # make sure the pipelined call really uploads
+        for k in range(3):
+            pinned[k][:] = x[:, k]
+        ng, f = s.AssembleFromHost(pinned[0], pinned[1], pinned[2], out)
+        assert ng == ng_ref
+        assert np.array_equal(f, f_ref)
+        assert np.array_equal(s.RetrieveHessianValues(), H_ref)
+        gx, gy, gz = d.RetrievePositionToCPU()
+        assert np.array_equal(gx, x[:, 0]) and np.array_equal(gz, x[:, 2])
+    # pageable host arrays work too (the copy is then staged by the driver)
+    ng2, f2 = s.AssembleFromHost(x[:, 0].copy(), x[:, 1].copy(), x[:, 2].copy())
+    assert ng2 == ng_ref and np.array_equal(f2, f_ref)
+    # generic row-gather path: same call, no overlap, same numbers as its own plain sequence
+    s.SetAssembly(0)
+    s.Assemble()
+    H0, f0 = s.RetrieveHessianValues(), d.RetrieveInternalForceToCPU()
+    ng0, f0b = s.AssembleFromHost(pinned[0], pinned[1], pinned[2])
+    assert np.array_equal(f0b, f0) and np.array_equal(s.RetrieveHessianValues(), H0)
+    # misuse: end without begin
+    import tlfea
+
+    with pytest.raises(tlfea.TlfeaError):
+        s.AssembleFromHostEnd()

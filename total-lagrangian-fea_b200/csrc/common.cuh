@@ -188,6 +188,13 @@ struct tlfea_newton {
   double pcg_rel_tol = 1e-8;
   int last_newton = 0, last_pcg = 0;
   double last_norm_g = 0, last_norm_c = 0;
+  // pipelined host-buffer step (tlfea_newton_assemble_host_begin / _end): copy stream, row-reduce stream,
+  // events 0..15 = coordinate chunk k is on the device, 16 = tail of the main stream, 17 = residual kernels queued,
+  // 18 = H rows done
+  cudaStream_t st_copy = nullptr, st_rows = nullptr;
+  cudaEvent_t ev_pipe[19] = {};
+  std::vector<int> pipe_need;  // last coordinate chunk the element chunk j reads
+  bool pipe_open = false, pipe_overlapped = false;
   // timing
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   double ms_total = 0;

@@ -820,7 +820,7 @@ __global__ void __launch_bounds__(RK_WARPS * 32, MINB) rk_kernel(RKArgs p) {
         __syncwarp();
       }
     }
-    if (lane < 3) p.f_int[(int64_t)row * 3 + lane] = f;
+    if (lane < 3 && p.f_int) p.f_int[(int64_t)row * 3 + lane] = f;  // nullptr: a separate force gather owns f_int
     // stream the finished block row out as three scalar CSR rows of length 3*deg
     const int64_t base = 9 * (int64_t)rs;
     const int rowlen = 3 * deg;

@@ -420,62 +420,100 @@ static int ek_chunk_elems() {
   return c;
 }
 
-// Schedule: the element range is cut into chunks; for chunk k the element kernel writes the chunk's block
-// records and the row-reduce kernel immediately consumes them for the rows that chunk completes, while the
-// records are still dirty in L2 (row order = completion order, see build_completion_order).  With a mesh whose
-// element numbering is spatially coherent nearly every record read of phase R is an L2 hit.
-static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
-  tlfea_elem *e = s->e;
-  const double h = s->prm.time_step;
-  const bool t10 = (e->type == TLFEA_TYPE_T10);
-  const int64_t rec = (int64_t)e->S * e->S * 9;  // doubles of one element's block records [a][b][9]
-  if (tangent && !s->d_stage) TL_TRY(dmalloc(&s->d_stage, (size_t)e->n_elem * rec));
-  if (tangent && !s->d_rowdesc) {
-    int chunk = ek_chunk_elems();
-    if (chunk <= 0 || chunk >= e->n_elem) chunk = e->n_elem;
-    s->ek_chunk = chunk;
-    int *d_order = nullptr;
-    TL_TRY(build_completion_order(e, chunk, &d_order, &s->chunk_ptr));
-    RowDesc *desc = nullptr;
-    TL_TRY(dmalloc(&desc, (size_t)e->n_coef));
-    TL_LAUNCH(k_row_desc, blocks_for(e->n_coef, 256), 256, 0, e->stream, e->n_coef, d_order, e->pat.d_off,
-              e->pat.d_inc_ptr, desc);
-    TL_CUDA(cudaStreamSynchronize(e->stream));
-    cudaFree(d_order);
-    s->d_rowdesc = desc;
-    TL_TRY(dmalloc(&s->d_tickets, s->chunk_ptr.size()));
-  }
+// Arguments and launch helpers of the two-phase assembly, shared by the plain schedule (assemble_ek) and the
+// pipelined host-buffer schedule (assemble_host_begin).
+struct EkPlan {
+  tlfea_newton *s = nullptr;
+  bool tangent = true, damp = false, t10 = true;
+  int64_t rec = 0;
   EKArgs a;
-  a.x = e->d_x;
-  a.y = e->d_y;
-  a.z = e->d_z;
-  a.v = damp ? s->d_v : nullptr;
-  a.qw = e->qw;
-  a.lambda = e->lambda;
-  a.mu = e->mu;
-  a.eta = e->eta;
-  a.lambda_d = e->lambda_d;
-  a.c1 = h * e->lambda + e->lambda_d;
-  a.c2 = h * e->mu + e->eta;
-  a.c3 = h * e->mu + e->eta;
-  a.c4 = h;
-  a.mu10 = e->mu10;
-  a.mu01 = e->mu01;
-  a.kappa = e->kappa;
   AEKArgs aa;
-  aa.x = e->d_x;
-  aa.y = e->d_y;
-  aa.z = e->d_z;
-  aa.v = damp ? s->d_v : nullptr;
-  aa.qw = e->qw;
-  aa.lambda = e->lambda;
-  aa.mu = e->mu;
-  aa.eta = e->eta;
-  aa.lambda_d = e->lambda_d;
-  aa.c1 = a.c1;
-  aa.c2 = a.c2;
-  aa.c4 = h;
-  auto launch_e = [&](int e0, int ne) -> int {
+  RKArgs r;
+  size_t smem = 0;
+  int per_sm = 1, rk_cfg = 0;
+
+  int init(tlfea_newton *s_, bool tangent_, bool damp_) {
+    s = s_, tangent = tangent_, damp = damp_;
+    tlfea_elem *e = s->e;
+    const double h = s->prm.time_step;
+    t10 = (e->type == TLFEA_TYPE_T10);
+    rec = (int64_t)e->S * e->S * 9;  // doubles of one element's block records [a][b][9]
+    if (tangent && !s->d_stage) TL_TRY(dmalloc(&s->d_stage, (size_t)e->n_elem * rec));
+    if (tangent && !s->d_rowdesc) {
+      int chunk = ek_chunk_elems();
+      if (chunk <= 0 || chunk >= e->n_elem) chunk = e->n_elem;
+      s->ek_chunk = chunk;
+      int *d_order = nullptr;
+      TL_TRY(build_completion_order(e, chunk, &d_order, &s->chunk_ptr));
+      RowDesc *desc = nullptr;
+      TL_TRY(dmalloc(&desc, (size_t)e->n_coef));
+      TL_LAUNCH(k_row_desc, blocks_for(e->n_coef, 256), 256, 0, e->stream, e->n_coef, d_order, e->pat.d_off,
+                e->pat.d_inc_ptr, desc);
+      TL_CUDA(cudaStreamSynchronize(e->stream));
+      cudaFree(d_order);
+      s->d_rowdesc = desc;
+      TL_TRY(dmalloc(&s->d_tickets, s->chunk_ptr.size()));
+    }
+    a.x = e->d_x;
+    a.y = e->d_y;
+    a.z = e->d_z;
+    a.v = damp ? s->d_v : nullptr;
+    a.qw = e->qw;
+    a.lambda = e->lambda;
+    a.mu = e->mu;
+    a.eta = e->eta;
+    a.lambda_d = e->lambda_d;
+    a.c1 = h * e->lambda + e->lambda_d;
+    a.c2 = h * e->mu + e->eta;
+    a.c3 = h * e->mu + e->eta;
+    a.c4 = h;
+    a.mu10 = e->mu10;
+    a.mu01 = e->mu01;
+    a.kappa = e->kappa;
+    aa.x = e->d_x;
+    aa.y = e->d_y;
+    aa.z = e->d_z;
+    aa.v = damp ? s->d_v : nullptr;
+    aa.qw = e->qw;
+    aa.lambda = e->lambda;
+    aa.mu = e->mu;
+    aa.eta = e->eta;
+    aa.lambda_d = e->lambda_d;
+    aa.c1 = a.c1;
+    aa.c2 = a.c2;
+    aa.c4 = h;
+    if (!tangent) return TLFEA_OK;
+    r.inc_ea = e->pat.d_inc_ea;
+    r.slot = e->pat.d_slot;
+    r.mass = e->d_mass;
+    r.stage = s->d_stage;
+    r.fe = e->d_fe;
+    r.inv_h = 1.0 / h;
+    r.H = s->d_H;
+    r.f_int = e->d_f_int;
+    r.row_stride = ((e->pat.max_deg * 9 + 32 + 1) | 1);  // block row + 32 doubles for the force gather
+    smem = (size_t)RK_WARPS * r.row_stride * sizeof(double);
+    TL_CHECK(smem <= 220 * 1024, "coefficient row too long for the row-reduce kernel (max_deg=%d)", e->pat.max_deg);
+    static const int cfg = [] {
+      const char *v = getenv("TLFEA_RK_CFG");  // tuning aid: 0 = (U 5, 3 blocks/SM), 1 = (4, 4), 2 = (8, 2)
+      return v ? atoi(v) : 0;
+    }();
+    rk_cfg = cfg;
+    const int want_sm = rk_cfg == 1 ? 4 : (rk_cfg == 2 ? 2 : 3);
+    if (smem > 48 * 1024) {
+      TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      TL_CUDA(cudaFuncSetAttribute(rk_kernel<8, 5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      TL_CUDA(cudaFuncSetAttribute(rk_kernel<16, 3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    per_sm = std::max(1, std::min(want_sm, (int)((227 * 1024) / (smem + 2048))));
+    return TLFEA_OK;
+  }
+
+  // element kernel over elements [e0, e0 + ne) on the element's stream
+  int elems(int e0, int ne) {
+    tlfea_elem *e = s->e;
     if (!t10) {
       aa.n_elem = ne;
       aa.ecoef = e->d_ecoef + (int64_t)e0 * e->S;
@@ -494,62 +532,55 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
     a.stage = tangent ? s->d_stage + (int64_t)e0 * EK_ELEM : nullptr;
     if (tangent) return damp ? launch_ek_cfg<true, true>(e, a) : launch_ek_cfg<false, true>(e, a);
     return damp ? launch_ek_cfg<true, false>(e, a) : launch_ek_cfg<false, false>(e, a);
-  };
-  if (!tangent) {
-    TL_TRY(launch_e(0, e->n_elem));
-    if (s->profile) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
-    TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)e->n_coef * 3, 128), 128, 0, e->stream, e->n_coef,
-              e->pat.d_inc_ptr, e->pat.d_inc_ea, e->d_fe, e->d_f_int, 0);
-    return TLFEA_OK;
   }
-  RKArgs r;
-  r.inc_ea = e->pat.d_inc_ea;
-  r.slot = e->pat.d_slot;
-  r.mass = e->d_mass;
-  r.stage = s->d_stage;
-  r.fe = e->d_fe;
-  r.inv_h = 1.0 / h;
-  r.H = s->d_H;
-  r.f_int = e->d_f_int;
-  r.row_stride = ((e->pat.max_deg * 9 + 32 + 1) | 1);  // block row + 32 doubles for the force gather
-  const size_t smem = (size_t)RK_WARPS * r.row_stride * sizeof(double);
-  TL_CHECK(smem <= 220 * 1024, "coefficient row too long for the row-reduce kernel (max_deg=%d)", e->pat.max_deg);
-  static const int rk_cfg = [] {
-    const char *v = getenv("TLFEA_RK_CFG");  // tuning aid: 0 = (U 5, 3 blocks/SM), 1 = (4, 4), 2 = (8, 2)
-    return v ? atoi(v) : 0;
-  }();
-  const int want_sm = rk_cfg == 1 ? 4 : (rk_cfg == 2 ? 2 : 3);
-  if (smem > 48 * 1024) {
-    TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    TL_CUDA(cudaFuncSetAttribute(rk_kernel<10, 8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    TL_CUDA(cudaFuncSetAttribute(rk_kernel<8, 5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    TL_CUDA(cudaFuncSetAttribute(rk_kernel<16, 3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  }
-  const int per_sm = std::max(1, std::min(want_sm, (int)((227 * 1024) / (smem + 2048))));
-  const int n_chunks = (int)s->chunk_ptr.size() - 1;
-  TL_CUDA(cudaMemsetAsync(s->d_tickets, 0, s->chunk_ptr.size() * sizeof(int), e->stream));
-  for (int k = 0; k < n_chunks; k++) {
-    const int e0 = k * s->ek_chunk, ne = std::min(s->ek_chunk, e->n_elem - e0);
-    TL_TRY(launch_e(e0, ne));
-    if (s->profile && k == n_chunks - 1) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
+
+  // row-reduce kernel over the rows completed by element chunk k, on stream st; with_force = false leaves f_int
+  // to a separate force gather (pipelined schedule)
+  int rows(int k, cudaStream_t st, bool with_force) {
+    tlfea_elem *e = s->e;
     const int r0 = s->chunk_ptr[k], nr = s->chunk_ptr[k + 1] - r0;
-    if (nr <= 0) continue;
+    if (nr <= 0) return TLFEA_OK;
+    r.f_int = with_force ? e->d_f_int : nullptr;
     r.n_coef = nr;
     r.desc = static_cast<const RowDesc *>(s->d_rowdesc) + r0;
     r.counter = s->d_tickets + k;
     const int blocks = (nr + RK_WARPS * RK_T - 1) / (RK_WARPS * RK_T);
     const int grid = std::min(blocks, 148 * per_sm);
     if (e->type == TLFEA_TYPE_3243)
-      TL_LAUNCH((rk_kernel<8, 5, 3>), grid, RK_WARPS * 32, smem, e->stream, r);
+      TL_LAUNCH((rk_kernel<8, 5, 3>), grid, RK_WARPS * 32, smem, st, r);
     else if (e->type == TLFEA_TYPE_3443)
-      TL_LAUNCH((rk_kernel<16, 3, 3>), grid, RK_WARPS * 32, smem, e->stream, r);
+      TL_LAUNCH((rk_kernel<16, 3, 3>), grid, RK_WARPS * 32, smem, st, r);
     else if (rk_cfg == 1)
-      TL_LAUNCH((rk_kernel<10, 4, 4>), grid, RK_WARPS * 32, smem, e->stream, r);
+      TL_LAUNCH((rk_kernel<10, 4, 4>), grid, RK_WARPS * 32, smem, st, r);
     else if (rk_cfg == 2)
-      TL_LAUNCH((rk_kernel<10, 8, 2>), grid, RK_WARPS * 32, smem, e->stream, r);
+      TL_LAUNCH((rk_kernel<10, 8, 2>), grid, RK_WARPS * 32, smem, st, r);
     else
-      TL_LAUNCH((rk_kernel<10, 5, 3>), grid, RK_WARPS * 32, smem, e->stream, r);
+      TL_LAUNCH((rk_kernel<10, 5, 3>), grid, RK_WARPS * 32, smem, st, r);
+    return TLFEA_OK;
+  }
+};
+
+// Schedule: the element range is cut into chunks; for chunk k the element kernel writes the chunk's block
+// records and the row-reduce kernel consumes them for the rows that chunk completes (row order = completion
+// order, see build_completion_order).  Default: one chunk = two full passes.
+static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
+  tlfea_elem *e = s->e;
+  EkPlan pl;
+  TL_TRY(pl.init(s, tangent, damp));
+  if (!tangent) {
+    TL_TRY(pl.elems(0, e->n_elem));
+    if (s->profile) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
+    TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)e->n_coef * 3, 128), 128, 0, e->stream, e->n_coef,
+              e->pat.d_inc_ptr, e->pat.d_inc_ea, e->d_fe, e->d_f_int, 0);
+    return TLFEA_OK;
+  }
+  const int n_chunks = (int)s->chunk_ptr.size() - 1;
+  TL_CUDA(cudaMemsetAsync(s->d_tickets, 0, s->chunk_ptr.size() * sizeof(int), e->stream));
+  for (int k = 0; k < n_chunks; k++) {
+    const int e0 = k * s->ek_chunk, ne = std::min(s->ek_chunk, e->n_elem - e0);
+    TL_TRY(pl.elems(e0, ne));
+    if (s->profile && k == n_chunks - 1) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
+    TL_TRY(pl.rows(k, e->stream, true));
   }
   TL_CUDA(cudaGetLastError());
   if (s->profile) TL_CUDA(cudaEventRecord(s->ev[3], e->stream));
@@ -736,6 +767,169 @@ static int pcg_solve(tlfea_newton *s, int *iters_out) {
   return TLFEA_OK;
 }
 
+// ---------------------------------------------------------------------------
+// Pipelined host-buffer step: H2D of the coordinates in PIPE_K chunks on a copy stream, the element kernel in
+// PIPE_K element chunks on the main stream (chunk j starts as soon as the last coordinate chunk it reads has
+// landed), then the row reduce on its own stream while the main stream gathers f_int, evaluates the residual
+// and copies f_int back to the host.
+// ---------------------------------------------------------------------------
+constexpr int PIPE_MAX = 16, PIPE_EV_TAIL = 16, PIPE_EV_RES = 17, PIPE_EV_ROWS = 18;
+static const int PIPE_K = [] {
+  const char *v = getenv("TLFEA_PIPE_K");  // coordinate / element chunks of the pipelined host-buffer step
+  const int k = v ? atoi(v) : 8;
+  return std::min(std::max(k, 1), PIPE_MAX);
+}();
+
+struct PipeBounds {
+  int b[PIPE_MAX + 1];
+};
+__global__ void k_chunk_max_coef(int64_t n_entries, int S, const int *__restrict__ ecoef, PipeBounds eb, int nk,
+                                 int *out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_entries) return;
+  const int el = (int)(i / S);
+  int j = 0;
+  for (int k = 1; k < nk; k++) j += (el >= eb.b[k]);
+  atomicMax(out + j, ecoef[i]);
+}
+
+static void pipe_bounds(int n, bool even, int *b) {
+  for (int k = 0; k <= PIPE_K; k++) {
+    int64_t v = (int64_t)n * k / PIPE_K;
+    if (even && k < PIPE_K) v &= ~(int64_t)1;
+    b[k] = (int)v;
+  }
+}
+
+static int pipe_prepare(tlfea_newton *s) {
+  tlfea_elem *e = s->e;
+  if (!s->st_copy) TL_CUDA(cudaStreamCreateWithFlags(&s->st_copy, cudaStreamNonBlocking));
+  if (!s->st_rows) TL_CUDA(cudaStreamCreateWithFlags(&s->st_rows, cudaStreamNonBlocking));
+  for (auto &ev : s->ev_pipe)
+    if (!ev) TL_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  if (s->pipe_need.empty()) {
+    int eb[PIPE_MAX + 1], cb[PIPE_MAX + 1];
+    pipe_bounds(e->n_elem, true, eb);
+    pipe_bounds(e->n_coef, false, cb);
+    int *d_max = nullptr;
+    TL_TRY(dmalloc(&d_max, (size_t)PIPE_MAX));
+    TL_CUDA(cudaMemsetAsync(d_max, 0, PIPE_K * sizeof(int), e->stream));
+    const int64_t n_entries = (int64_t)e->n_elem * e->S;
+    PipeBounds pb;
+    for (int k = 0; k <= PIPE_K; k++) pb.b[k] = eb[k];
+    TL_LAUNCH(k_chunk_max_coef, blocks_for(n_entries, 256), 256, 0, e->stream, n_entries, e->S, e->d_ecoef, pb, PIPE_K,
+              d_max);
+    int h_max[PIPE_MAX];
+    TL_CUDA(cudaMemcpyAsync(h_max, d_max, PIPE_K * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    TL_CUDA(cudaStreamSynchronize(e->stream));
+    dfree(d_max);
+    s->pipe_need.assign(PIPE_K, PIPE_K - 1);
+    for (int j = 0; j < PIPE_K; j++) {
+      int k = 0;
+      while (k < PIPE_K - 1 && h_max[j] >= cb[k + 1]) k++;
+      s->pipe_need[j] = k;
+    }
+  }
+  return TLFEA_OK;
+}
+
+static int assemble_host_begin(tlfea_newton *s, const double *hx, const double *hy, const double *hz) {
+  tlfea_elem *e = s->e;
+  TL_CHECK(!s->pipe_open, "assemble_host_begin called twice without assemble_host_end");
+  TL_CHECK(e->is_precomputed, "CalcDnDuPre/CalcDsDuPre must run before assembling");
+  TL_CHECK(s->analyzed, "AnalyzeHessianSparsity must run before assembling");
+  TL_CHECK(e->is_mass, "CalcMassMatrix must run before assembling H = M/h + ...");
+  TL_CHECK(s->prm.time_step > 0.0, "time_step must be positive (SetParameters)");
+  TL_CUDA(cudaSetDevice(e->device));
+  TL_TRY(ensure_pattern(e));
+  TL_TRY(refresh_constraints(s));
+  const bool damp = (e->eta != 0.0 || e->lambda_d != 0.0);
+  bool overlap = ek_supported(s);
+  EkPlan pl;
+  if (overlap) {
+    TL_TRY(pl.init(s, true, damp));
+    overlap = (s->chunk_ptr.size() == 2);  // the interleaved E/R chunk schedule (tuning aid) keeps the plain order
+  }
+  if (!overlap) {  // generic row-gather path: same result, no overlap
+    TL_TRY(tlfea_elem_update_positions(e, hx, hy, hz, e->n_coef));
+    TL_TRY(do_assemble(s, true));
+    s->pipe_open = true;
+    s->pipe_overlapped = false;
+    return TLFEA_OK;
+  }
+  TL_TRY(pipe_prepare(s));
+  cudaStream_t m = e->stream, c = s->st_copy;
+  int eb[PIPE_MAX + 1], cb[PIPE_MAX + 1];
+  pipe_bounds(e->n_elem, true, eb);
+  pipe_bounds(e->n_coef, false, cb);
+  // the copies may not overtake work already queued on the main stream that still reads the old coordinates
+  TL_CUDA(cudaEventRecord(s->ev_pipe[PIPE_EV_TAIL], m));
+  TL_CUDA(cudaStreamWaitEvent(c, s->ev_pipe[PIPE_EV_TAIL], 0));
+  for (int k = 0; k < PIPE_K; k++) {
+    const size_t off = (size_t)cb[k], bytes = (size_t)(cb[k + 1] - cb[k]) * sizeof(double);
+    if (bytes) {
+      TL_CUDA(cudaMemcpyAsync(e->d_x + off, hx + off, bytes, cudaMemcpyHostToDevice, c));
+      TL_CUDA(cudaMemcpyAsync(e->d_y + off, hy + off, bytes, cudaMemcpyHostToDevice, c));
+      TL_CUDA(cudaMemcpyAsync(e->d_z + off, hz + off, bytes, cudaMemcpyHostToDevice, c));
+    }
+    TL_CUDA(cudaEventRecord(s->ev_pipe[k], c));
+  }
+  int waited = -1;
+  for (int j = 0; j < PIPE_K; j++) {
+    while (waited < s->pipe_need[j]) TL_CUDA(cudaStreamWaitEvent(m, s->ev_pipe[++waited], 0));
+    if (eb[j + 1] > eb[j]) TL_TRY(pl.elems(eb[j], eb[j + 1] - eb[j]));
+  }
+  while (waited < PIPE_K - 1) TL_CUDA(cudaStreamWaitEvent(m, s->ev_pipe[++waited], 0));
+  // the nodal forces (same ascending-element order as the row reduce); the H rows are reduced by _end, AFTER the
+  // small residual kernels have gone through: the row-reduce kernel is persistent and leaves no room on the SMs
+  TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)e->n_coef * 3, 128), 128, 0, m, e->n_coef, e->pat.d_inc_ptr,
+            e->pat.d_inc_ea, e->d_fe, e->d_f_int, 0);
+  TL_CUDA(cudaGetLastError());
+  s->pipe_open = true;
+  s->pipe_overlapped = true;
+  return TLFEA_OK;
+}
+
+static int assemble_host_end(tlfea_newton *s, double *h_f_int, double *norm_g) {
+  tlfea_elem *e = s->e;
+  TL_CHECK(s->pipe_open, "assemble_host_end without assemble_host_begin");
+  TL_CUDA(cudaSetDevice(e->device));
+  s->pipe_open = false;
+  cudaStream_t m = e->stream, rw = s->st_rows;
+  const int64_t n = 3 * (int64_t)e->n_coef;
+  // residual and its norm: kernels only, nothing waits yet
+  if (norm_g) {
+    TL_TRY(compute_residual(s));
+    double *partial = s->d_scal + 8;
+    TL_LAUNCH(k_dot_partial, DOT_BLOCKS, 256, 0, m, n, s->d_g, s->d_g, partial);
+    TL_LAUNCH(k_dot_final, 1, 1024, 0, m, DOT_BLOCKS, partial, s->d_scal + 4);
+  }
+  if (s->pipe_overlapped) {  // H rows on their own stream, behind everything queued on the main stream so far
+    EkPlan pl;
+    TL_TRY(pl.init(s, true, (e->eta != 0.0 || e->lambda_d != 0.0)));
+    TL_CUDA(cudaEventRecord(s->ev_pipe[PIPE_EV_RES], m));
+    TL_CUDA(cudaStreamWaitEvent(rw, s->ev_pipe[PIPE_EV_RES], 0));
+    TL_CUDA(cudaMemsetAsync(s->d_tickets, 0, s->chunk_ptr.size() * sizeof(int), rw));
+    TL_TRY(pl.rows(0, rw, false));
+    if (s->n_cons_slots > 0) {
+      TL_LAUNCH(k_add_constraint_term, blocks_for(s->n_cons_slots, 256), 256, 0, rw, s->n_cons_slots, s->d_cons_slot,
+                s->d_cons_val, s->prm.time_step * s->prm.time_step * s->prm.rho, s->d_H);
+    }
+    TL_CUDA(cudaEventRecord(s->ev_pipe[PIPE_EV_ROWS], rw));
+  }
+  // the copies back to the host run on the copy engines while the rows are reduced
+  if (norm_g) TL_CUDA(cudaMemcpyAsync(s->h_scal, s->d_scal + 4, sizeof(double), cudaMemcpyDeviceToHost, m));
+  if (h_f_int) TL_CUDA(cudaMemcpyAsync(h_f_int, e->d_f_int, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, m));
+  TL_CUDA(cudaStreamSynchronize(m));
+  if (norm_g) *norm_g = std::sqrt(s->h_scal[0]);
+  if (s->pipe_overlapped) {  // H is complete, and later main-stream work is ordered after it
+    TL_CUDA(cudaEventSynchronize(s->ev_pipe[PIPE_EV_ROWS]));
+    TL_CUDA(cudaStreamWaitEvent(m, s->ev_pipe[PIPE_EV_ROWS], 0));
+  }
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
 }  // namespace tlfea
 
 using namespace tlfea;
@@ -797,6 +991,10 @@ int tlfea_newton_destroy(tlfea_newton *s) {
   dfree(s->d_cons_slot);
   dfree(s->d_cons_val);
   for (auto &p : s->d_pcg) dfree(p);
+  if (s->st_copy) cudaStreamDestroy(s->st_copy);
+  if (s->st_rows) cudaStreamDestroy(s->st_rows);
+  for (auto &ev : s->ev_pipe)
+    if (ev) cudaEventDestroy(ev);
   dfree(s->d_scal);
   if (s->h_scal) cudaFreeHost(s->h_scal);
   for (auto &ev : s->ev)
@@ -906,6 +1104,18 @@ int tlfea_newton_assemble_force(tlfea_newton *s) {
   TL_CHECK(s, "null handle");
   TL_TRY(do_assemble(s, false));
   return collect_timing(s, false);
+}
+
+int tlfea_newton_assemble_host_begin(tlfea_newton *s, const double *x, const double *y, const double *z, int n) {
+  TL_CHECK(s && x && y && z, "null input");
+  TL_CHECK(n == s->e->n_coef, "Position vector size mismatch.");
+  return assemble_host_begin(s, x, y, z);
+}
+
+int tlfea_newton_assemble_host_end(tlfea_newton *s, double *f_int, int n, double *norm_g) {
+  TL_CHECK(s, "null handle");
+  TL_CHECK(!f_int || n == 3 * s->e->n_coef, "size mismatch");
+  return assemble_host_end(s, f_int, norm_g);
 }
 
 int tlfea_newton_residual(tlfea_newton *s, double *norm_g) {

@@ -98,6 +98,8 @@ _SIGS = {
     "tlfea_newton_assemble": (C.c_int, [c_vp]),
     "tlfea_newton_assemble_force": (C.c_int, [c_vp]),
     "tlfea_newton_residual": (C.c_int, [c_vp, c_dp]),
+    "tlfea_newton_assemble_host_begin": (C.c_int, [c_vp, c_dp, c_dp, c_dp, C.c_int]),
+    "tlfea_newton_assemble_host_end": (C.c_int, [c_vp, c_dp, C.c_int, c_dp]),
     "tlfea_newton_solve_step": (C.c_int, [c_vp]),
     "tlfea_newton_last_stats": (C.c_int, [c_vp, c_ip, c_ip, c_dp, c_dp]),
     "tlfea_newton_set_pcg": (C.c_int, [c_vp, C.c_int, C.c_double]),

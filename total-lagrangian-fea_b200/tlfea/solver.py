@@ -78,6 +78,29 @@ class SyncedNewtonSolver(SolverBase):
     def AssembleForce(self):
         check(lib.tlfea_newton_assemble_force(self._h))
 
+    def AssembleFromHostBegin(self, x, y, z):
+        """UpdatePositions(x, y, z) + Assemble with the H2D copies overlapped with the element kernel
+        (tlfea_newton_assemble_host_begin).  Returns without waiting; x, y, z must stay alive (and unchanged)
+        until AssembleFromHostEnd returns -- pass pinned float64 arrays for a truly asynchronous copy."""
+        n = self.data.n_coef
+        self._pipe_in = tuple(np.ascontiguousarray(a, dtype=np.float64) for a in (x, y, z))
+        check(lib.tlfea_newton_assemble_host_begin(self._h, *(_d(a) for a in self._pipe_in), n))
+
+    def AssembleFromHostEnd(self, out=None, want_norm=True):
+        """Residual() + RetrieveInternalForceToCPU(out) while H is still being reduced; returns (||g||, f_int)
+        once f_int, ||g|| and H are all complete."""
+        n = 3 * self.data.n_coef
+        if out is None:
+            out = np.empty(n)
+        ng = C.c_double(0.0)
+        check(lib.tlfea_newton_assemble_host_end(self._h, _d(out), n, C.byref(ng) if want_norm else None))
+        self._pipe_in = None
+        return ng.value, out
+
+    def AssembleFromHost(self, x, y, z, out=None):
+        self.AssembleFromHostBegin(x, y, z)
+        return self.AssembleFromHostEnd(out)
+
     def Residual(self) -> float:
         out = C.c_double(0.0)
         check(lib.tlfea_newton_residual(self._h, C.byref(out)))
