@@ -255,3 +255,27 @@ def test_reference_prototype_vectors(kind):
             Hd[r, ci[ro[r]:ro[r + 1]]] = Hv[ro[r]:ro[r + 1]]
         # H = M/h (x) I3 + h K_t with h = 1
         assert rel_err(Hd - np.kron(M, np.eye(3)), g["K_t"]) < 1e-11
+
+
+@pytest.mark.parametrize("kind", [3243, 3443])
+def test_host_pipelined_assemble_matches_the_plain_sequence(kind):
+    """tlfea_newton_assemble_host_begin/_end on the ANCF elements (element kernel in chunks under the chunked H2D,
+    rows reduced under the D2H): bit-identical to UpdatePositions + Assemble + Residual + Retrieve."""
+    if kind == 3243:
+        dims = (0.5, 0.1, 0.1); x, y, z, conn = straight_beam(37, dims[0])
+    else:
+        dims = (0.4, 0.3, 0.05); x, y, z, conn = plate(5, 4, dims[0], dims[1])
+    d, s = make(kind, x, y, z, conn, dims, "svk", True)
+    nc = x.shape[0]
+    rng = np.random.Generator(np.random.PCG64(11))
+    amp = np.tile([0.02 * dims[0], 0.02, 0.02, 0.02], nc // 4)
+    s.SetVelocityGuess(0.1 * rng.uniform(-1, 1, 3 * nc))
+    for _ in range(2):
+        xd = x + amp * rng.uniform(-1, 1, nc); yd = y + amp * rng.uniform(-1, 1, nc); zd = z + amp * rng.uniform(-1, 1, nc)
+        d.UpdatePositions(xd, yd, zd)
+        s.Assemble()
+        ng_ref, f_ref, H_ref = s.Residual(), d.RetrieveInternalForceToCPU(), s.RetrieveHessianValues()
+        d.UpdatePositions(x, y, z)
+        ng, f = s.AssembleFromHost(xd, yd, zd)
+        assert ng == ng_ref and np.array_equal(f, f_ref)
+        assert np.array_equal(s.RetrieveHessianValues(), H_ref)
