@@ -29,9 +29,29 @@ __global__ void k_grad_L(int n_coef, const int *__restrict__ off, const int *__r
   if (tid >= (int64_t)n_coef * 3) return;
   const int ni = (int)(tid / 3), di = (int)(tid % 3);
   double res = 0.0;
-  for (int idx = off[ni]; idx < off[ni + 1]; idx++) {
+  // (M (v - v_prev)) / h, summed in the reference order; the loads of four entries are issued together (the
+  // gathers depend on the column loads: one entry at a time leaves the memory system idle), the adds stay in order
+  const int r0 = off[ni], r1 = off[ni + 1];
+  int idx = r0;
+  for (; idx + 4 <= r1; idx += 4) {
+    int64_t tj[4];
+    double m[4], a[4], b[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      tj[k] = (int64_t)cols[idx + k] * 3 + di;
+      m[k] = mass[idx + k];
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      a[k] = v[tj[k]];
+      b[k] = v_prev[tj[k]];
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) res += m[k] * (a[k] - b[k]) * inv_h;
+  }
+  for (; idx < r1; idx++) {
     const int64_t tj = (int64_t)cols[idx] * 3 + di;
-    res += mass[idx] * (v[tj] - v_prev[tj]) * inv_h;  // (M (v - v_prev)) / h, reference order
+    res += mass[idx] * (v[tj] - v_prev[tj]) * inv_h;
   }
   res -= (-f_int[tid]);
   res -= f_ext[tid];
@@ -790,7 +810,15 @@ __global__ void k_chunk_max_coef(int64_t n_entries, int S, const int *__restrict
   const int el = (int)(i / S);
   int j = 0;
   for (int k = 1; k < nk; k++) j += (el >= eb.b[k]);
-  atomicMax(out + j, ecoef[i]);
+  // one atomic per warp where the warp sits inside one chunk (nearly always)
+  const unsigned act = __activemask();
+  const int j0 = __shfl_sync(act, j, __ffs(act) - 1);
+  if (__all_sync(act, j == j0)) {
+    const int mx = __reduce_max_sync(act, ecoef[i]);
+    if ((threadIdx.x & 31) == __ffs(act) - 1) atomicMax(out + j, mx);
+  } else {
+    atomicMax(out + j, ecoef[i]);
+  }
 }
 
 static void pipe_bounds(int n, bool even, int *b) {
