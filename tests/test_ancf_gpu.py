@@ -130,7 +130,7 @@ def test_precompute_invariants(kind):
 
 
 @pytest.mark.parametrize("kind", [3243, 3443])
-@pytest.mark.parametrize("model,damp", [("svk", False), ("svk", True), ("mr", False)])
+@pytest.mark.parametrize("model,damp", [("svk", False), ("svk", True), ("mr", False), ("mr", True)])
 def test_force_tangent_vs_oracle(kind, model, damp):
     from oracle import oracle as orc
 

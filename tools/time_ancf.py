@@ -25,8 +25,12 @@ else:
 x, y, z = x.ravel(), y.ravel(), z.ravel()
 rng = np.random.Generator(np.random.PCG64(2234))
 amp = np.tile([0.05 * L, 0.02, 0.02, 0.02], nn)
-d.Setup(L, W, H, x, y, z, conn); d.SetDensity(2700.); d.SetSVK(7e8, 0.33); d.CalcDsDuPre(); d.CalcMassMatrix()
+d.Setup(L, W, H, x, y, z, conn); d.SetDensity(2700.); d.SetSVK(7e8, 0.33)
+if os.environ.get("TLFEA_MAT", "svk") == "mr":  # 0.3 mu, 0.2 mu, 1.5 K
+    mu, K = 7e8 / (2 * 1.33), 7e8 / (3 * (1 - 0.66)); d.SetMooneyRivlin(0.3 * mu, 0.2 * mu, 1.5 * K)
+d.CalcDsDuPre(); d.CalcMassMatrix()
 s = tlfea.SyncedNewtonSolver(d, 0); s.SetParameters(tlfea.SyncedNewtonParams(1e-4, 0, 1e-6, 1e14, 1, 1, 1e-3)); s.Setup(); s.AnalyzeHessianSparsity()
+s.SetAssembly(int(os.environ.get("TLFEA_MODE", "1")))
 d.UpdatePositions(x + amp * rng.uniform(-1, 1, 4 * nn), y + amp * rng.uniform(-1, 1, 4 * nn), z + amp * rng.uniform(-1, 1, 4 * nn))
 setup_s = time.time() - t0
 for i in range(2): s.Assemble()

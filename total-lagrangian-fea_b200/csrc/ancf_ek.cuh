@@ -15,8 +15,15 @@
 // the Gauss-point step (thread = (element, q)), the force step (thread = (element, a, i)) and the block step
 // (thread = (element, pair)); finished blocks are staged as [a][b][9] and leave as one contiguous burst per element
 // -- the visit-major record the row-reduce kernel (rk_kernel) consumes.  No atomics, fixed summation order.
+//
+// Mooney-Rivlin (MODEL = TL_MODEL_MR; MooneyRivlin.cuh:45-225): the Gauss-point step runs on threads (element, q, row i)
+// and leaves, per point, P dV and the 81-entry tensor T[i][k][J][L] = h dV dP_iJ/dF_kL with the Kelvin-Voigt block
+// folded in (same form as the FEAT10 kernel, ek_kernel.cuh); the block step is the contraction
+// K_ab[i][k] = sum_J h_a[J] (sum_L T[i][k][J][L] h_b[L]) -- T is read by every thread at the same address (broadcast),
+// so a (pair, point) costs 45 shared-memory wavefronts + 6 operand loads against 22 for SVK.
 #pragma once
 #include "common.cuh"
+#include "kernels.cuh"  // MRState / mr_state
 
 namespace tlfea {
 
@@ -29,30 +36,39 @@ struct AEKArgs {
   QuadW qw;
   double lambda, mu, eta, lambda_d;
   double c1, c2, c4;             // c1 = h lambda + lambda_d, c2 = h mu + eta, c4 = h
+  double mu10, mu01, kappa;      // Mooney-Rivlin (MODEL == TL_MODEL_MR)
   double *fe;                    // [n_elem][S][3]
   double *stage;                 // [n_elem][S][S][9] or nullptr (force only)
 };
 
-template <int S, int Q, int EPB, bool DAMP>
+template <int S, int Q, int EPB, bool DAMP, int MODEL = TL_MODEL_SVK>
 struct AEKShape {
+  static constexpr bool MR = (MODEL == TL_MODEL_MR);
   static constexpr int NPAIR = S * (S + 1) / 2;
   static constexpr int HS = 3 * S + 1;           // padded stride of a Gauss point's gradN / u row (odd: lanes = q)
   static constexpr int RS = 9 * S + 1;           // padded stride of a staged block row (odd: lanes = b)
+  static constexpr int TS = 90;                  // Mooney-Rivlin: T of one point, 9 groups (i,k) of [J][L] padded to 10
+  static constexpr int GPT = MR ? EPB * Q * 3 : EPB * Q;  // threads of the Gauss-point step
   static constexpr int WORK = (EPB * NPAIR > EPB * 3 * S ? EPB * NPAIR : EPB * 3 * S);
-  static constexpr int THREADS = ((WORK > EPB * Q ? WORK : EPB * Q) + 31) / 32 * 32;
+  static constexpr int THREADS = ((WORK > GPT ? WORK : GPT) + 31) / 32 * 32;
   static constexpr int H_D = Q * HS;             // per element
-  static constexpr int STG_D = S * RS;           // per element; aliases gradN + u after the block step
-  static_assert(STG_D <= 2 * H_D, "block staging must fit in the gradN + u region");
+  static constexpr int U_D = MR ? Q * TS : Q * HS;  // u rows (SVK) or the tangent tensors (Mooney-Rivlin)
+  static constexpr int STG_D = S * RS;           // per element; aliases gradN + u / T after the block step
+  static_assert(STG_D <= H_D + U_D, "block staging must fit in the gradN + u region");
+  static_assert(H_D % 2 == 0, "the region after gradN must stay 16-byte aligned");
   static constexpr int M_D = Q * 8, P_D = Q * 9, X_D = S * 3;  // M_q padded to 8: four 16-byte loads in the block step
-  static constexpr int H2_D = (2 * H_D + 1) / 2 * 2;            // keeps M 16-byte aligned
+  static constexpr int H2_D = (H_D + U_D + 1) / 2 * 2;          // keeps M 16-byte aligned
   // odd element stride: the lanes of a warp that belong to different elements must not share banks
   static constexpr int ELEM_D = (EPB > 1) ? ((H2_D + M_D + P_D + X_D * (DAMP ? 2 : 1) + 1) | 3) - 1 : H2_D + M_D + P_D + X_D * (DAMP ? 2 : 1);
   static constexpr size_t SMEM = (size_t)EPB * ELEM_D * sizeof(double);
+  static constexpr int MINB = MR ? (S == 16 ? 3 : 4) : (S == 16 ? 5 : 4);
 };
 
-template <int S, int Q, int EPB, bool DAMP, bool TANGENT>
-__global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 5 : 4) aek_kernel(AEKArgs p) {
-  using Sh = AEKShape<S, Q, EPB, DAMP>;
+template <int S, int Q, int EPB, bool DAMP, bool TANGENT, int MODEL = TL_MODEL_SVK>
+__global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP, MODEL>::THREADS, AEKShape<S, Q, EPB, DAMP, MODEL>::MINB)
+    aek_kernel(AEKArgs p) {
+  using Sh = AEKShape<S, Q, EPB, DAMP, MODEL>;
+  constexpr bool MR = Sh::MR;
   constexpr int T = Sh::THREADS, HS = Sh::HS, RS = Sh::RS, NP = Sh::NPAIR;
   extern __shared__ __align__(16) double aek_smem[];
   const int tid = threadIdx.x;
@@ -94,8 +110,110 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 
       }
     }
     __syncthreads();
-    // ---- Gauss-point step: thread = (element, q)
-    if (tid < ne * Q) {
+    // ---- Gauss-point step, Mooney-Rivlin: thread = (element, q, row i)
+    if (MR && tid < ne * Q * 3) {
+      const int idx = tid / 3, part = tid - 3 * idx;
+      const int el = idx / Q, q = idx - el * Q;
+      double *se = aek_smem + el * Sh::ELEM_D;
+      const double *hq = se + q * HS;
+      const double *sx = se + Sh::H2_D + Sh::M_D + Sh::P_D;
+      double F[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
+      double Fd[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
+#pragma unroll 4
+      for (int a = 0; a < S; a++) {
+        const double ha[3] = {hq[a], hq[S + a], hq[2 * S + a]};
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+          for (int j = 0; j < 3; j++) F[i][j] += sx[a * 3 + i] * ha[j];
+        if (DAMP) {
+#pragma unroll
+          for (int i = 0; i < 3; i++)
+#pragma unroll
+            for (int j = 0; j < 3; j++) Fd[i][j] += sx[Sh::X_D + a * 3 + i] * ha[j];
+        }
+      }
+      const double dV = p.detJ[(int64_t)(e0 + el) * Q + q] * p.qw.w[q];
+      MRState m;
+      mr_state(F, p.mu10, p.mu01, p.kappa, m);
+      double term1[3][3], term2[3][3], P[3][3];
+#pragma unroll
+      for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+          term1[i][j] = F[i][j] - (m.I1 / 3.0) * m.Fit[i][j];
+          term2[i][j] = m.I1 * F[i][j] - m.FC[i][j] - (2.0 * m.I2 / 3.0) * m.Fit[i][j];
+          P[i][j] = m.t1 * term1[i][j] + m.t2 * term2[i][j] + m.t3 * m.Fit[i][j];
+        }
+      if (DAMP) {  // P_vis = F (2 eta Edot + lambda_d tr(Edot) I), Edot = sym(Fdot^T F)
+        double Ed[3][3];
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+          for (int j = 0; j < 3; j++) {
+            double a1 = 0.0, a2 = 0.0;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+              a1 += Fd[k][i] * F[k][j];
+              a2 += F[k][i] * Fd[k][j];
+            }
+            Ed[i][j] = 0.5 * (a1 + a2);
+          }
+        const double trEd = Ed[0][0] + Ed[1][1] + Ed[2][2];
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+          for (int j = 0; j < 3; j++) {
+            double sv = 0.0;
+#pragma unroll
+            for (int k = 0; k < 3; k++)
+              sv += F[i][k] * (2.0 * p.eta * Ed[k][j] + ((k == j) ? p.lambda_d * trEd : 0.0));
+            P[i][j] += sv;
+          }
+      }
+      // this thread's row i = part of everything indexed by i
+      double Fi[3], Fiti[3], FFTi[3], t1i[3], t2i[3], dk[3];
+      double *sP = se + Sh::H2_D + Sh::M_D + q * 9;
+#pragma unroll
+      for (int j = 0; j < 3; j++) {
+        sP[part * 3 + j] = dV * (part == 0 ? P[0][j] : (part == 1 ? P[1][j] : P[2][j]));
+        Fi[j] = part == 0 ? F[0][j] : (part == 1 ? F[1][j] : F[2][j]);
+        Fiti[j] = part == 0 ? m.Fit[0][j] : (part == 1 ? m.Fit[1][j] : m.Fit[2][j]);
+        FFTi[j] = part == 0 ? m.FFT[0][j] : (part == 1 ? m.FFT[1][j] : m.FFT[2][j]);
+        t1i[j] = part == 0 ? term1[0][j] : (part == 1 ? term1[1][j] : term1[2][j]);
+        t2i[j] = part == 0 ? term2[0][j] : (part == 1 ? term2[1][j] : term2[2][j]);
+        dk[j] = (part == j) ? 1.0 : 0.0;
+      }
+      if (TANGENT) {
+        // T[i][k][J][L] = h dV dP_iJ/dF_kL (MooneyRivlin.cuh:193-223) + dV (lambda_d F_iJ F_kL + eta F_kJ F_iL
+        // + eta d_JL (FF^T)_ik)  (Kelvin-Voigt, ANCF3243DataFunc.cuh:843-917), groups (i,k) of 9 padded to 10
+        double *sT = se + Sh::H_D + q * Sh::TS + part * 30;
+        const double hdV = p.c4 * dV;
+        const double kt3 = p.kappa * (2.0 * m.J - 1.0) * m.J;
+#pragma unroll
+        for (int j = 0; j < 3; j++)
+#pragma unroll
+          for (int k = 0; k < 3; k++)
+#pragma unroll
+            for (int l = 0; l < 3; l++) {
+              const double djl = (j == l) ? 1.0 : 0.0;
+              const double dFit = -Fiti[l] * m.Fit[k][j];
+              const double dt1 = (-2.0 / 3.0) * m.t1 * m.Fit[k][l];
+              const double dt2 = (-4.0 / 3.0) * m.t2 * m.Fit[k][l];
+              const double dt3 = kt3 * m.Fit[k][l];
+              const double dT1 = dk[k] * djl - (2.0 / 3.0) * F[k][l] * Fiti[j] + (m.I1 / 3.0) * Fiti[l] * m.Fit[k][j];
+              const double dT2 = 2.0 * F[k][l] * Fi[j] + m.I1 * dk[k] * djl -
+                                 (dk[k] * m.C[l][j] + Fi[l] * F[k][j] + djl * FFTi[k]) -
+                                 (4.0 / 3.0) * (m.I1 * F[k][l] - m.FC[k][l]) * Fiti[j] +
+                                 (2.0 * m.I2 / 3.0) * Fiti[l] * m.Fit[k][j];
+              double t = hdV * (dt1 * t1i[j] + m.t1 * dT1 + dt2 * t2i[j] + m.t2 * dT2 + dt3 * Fiti[j] + m.t3 * dFit);
+              if (DAMP) t += dV * (p.lambda_d * Fi[j] * F[k][l] + p.eta * (F[k][j] * Fi[l] + djl * FFTi[k]));
+              sT[k * 10 + j * 3 + l] = t;
+            }
+      }
+    }
+    // ---- Gauss-point step, SVK: thread = (element, q)
+    if (!MR && tid < ne * Q) {
       const int el = tid / Q, q = tid - el * Q;
       double *se = aek_smem + el * Sh::ELEM_D;
       const double *hq = se + q * HS;
@@ -203,7 +321,27 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP>::THREADS, S == 16 ? 
       // ---- block step: thread = (element, pair a <= b)
       double k[9];
       const bool on = pel < ne;
-      if (on) {
+      if (on && MR) {
+        const double *se = aek_smem + pel * Sh::ELEM_D;
+#pragma unroll
+        for (int i = 0; i < 9; i++) k[i] = 0.0;
+#pragma unroll 1
+        for (int q = 0; q < Q; q++) {
+          const double *hq = se + q * HS;
+          const double2 *t2 = reinterpret_cast<const double2 *>(se + Sh::H_D + q * Sh::TS);  // same address in every lane
+          const double ha[3] = {hq[pa], hq[S + pa], hq[2 * S + pa]};
+          const double hb[3] = {hq[pb], hq[S + pb], hq[2 * S + pb]};
+#pragma unroll
+          for (int g = 0; g < 9; g++) {  // group g = (i, k): T[J][L] in 10 doubles
+            const double2 v0 = t2[g * 5], v1 = t2[g * 5 + 1], v2 = t2[g * 5 + 2], v3 = t2[g * 5 + 3], v4 = t2[g * 5 + 4];
+            const double w0 = v0.x * hb[0] + v0.y * hb[1] + v1.x * hb[2];
+            const double w1 = v1.y * hb[0] + v2.x * hb[1] + v2.y * hb[2];
+            const double w2 = v3.x * hb[0] + v3.y * hb[1] + v4.x * hb[2];
+            k[g] += ha[0] * w0 + ha[1] * w1 + ha[2] * w2;
+          }
+        }
+      }
+      if (on && !MR) {
         const double *se = aek_smem + pel * Sh::ELEM_D;
         double A[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, G[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll 2

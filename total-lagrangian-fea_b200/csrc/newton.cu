@@ -383,10 +383,8 @@ static EKCfg ek_cfg() {
 }
 
 static bool ek_supported(const tlfea_newton *s) {
-  const tlfea_elem *e = s->e;
   if (!s->two_phase) return false;
-  if (e->type == TLFEA_TYPE_T10) return true;  // SVK and Mooney-Rivlin, with or without Kelvin-Voigt damping
-  return e->model == TL_MODEL_SVK;             // ANCF: SVK (+ damping); Mooney-Rivlin stays on the generic path
+  return true;  // every element type, SVK and Mooney-Rivlin, with or without Kelvin-Voigt damping
 }
 
 template <int G, int W, bool DAMP, bool TANGENT, int MODEL>
@@ -415,21 +413,28 @@ static int launch_ek_cfg(tlfea_elem *e, const EKArgs &a) {
   return launch_ek_t<2, 8, DAMP, TANGENT, TL_MODEL_SVK>(e, a);  // most warps per SM: the kernel is latency / LSU bound
 }
 
-template <int S, int Q, int EPB, bool DAMP, bool TANGENT>
+template <int S, int Q, int EPB, bool DAMP, bool TANGENT, int MODEL>
 static int launch_aek_t(tlfea_elem *e, const AEKArgs &a) {
-  using Sh = AEKShape<S, Q, EPB, DAMP>;
-  static_assert(Sh::SMEM <= 48 * 1024, "fits the default dynamic shared memory limit");
+  using Sh = AEKShape<S, Q, EPB, DAMP, MODEL>;
+  static_assert(Sh::SMEM <= 227 * 1024, "fits the shared memory of one SM");
+  if (Sh::SMEM > 48 * 1024)
+    TL_CUDA(cudaFuncSetAttribute(aek_kernel<S, Q, EPB, DAMP, TANGENT, MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)Sh::SMEM));
   const int n_groups = (a.n_elem + EPB - 1) / EPB;
   const int per_sm = std::max(1, std::min((int)((227 * 1024) / (Sh::SMEM + 1024)), 2048 / Sh::THREADS));
   const int grid = std::max(1, std::min(n_groups, 148 * per_sm));
-  TL_LAUNCH((aek_kernel<S, Q, EPB, DAMP, TANGENT>), grid, Sh::THREADS, Sh::SMEM, e->stream, a);
+  TL_LAUNCH((aek_kernel<S, Q, EPB, DAMP, TANGENT, MODEL>), grid, Sh::THREADS, Sh::SMEM, e->stream, a);
   TL_CUDA(cudaGetLastError());
   return TLFEA_OK;
 }
 template <bool DAMP, bool TANGENT>
 static int launch_aek(tlfea_elem *e, const AEKArgs &a) {
-  if (e->type == TLFEA_TYPE_3243) return launch_aek_t<8, 12, 7, DAMP, TANGENT>(e, a);
-  return launch_aek_t<16, 48, 1, DAMP, TANGENT>(e, a);
+  if (e->model == TL_MODEL_MR) {  // 3 elements per CTA for the beam: the tangent tensors take 90 doubles per point
+    if (e->type == TLFEA_TYPE_3243) return launch_aek_t<8, 12, 3, DAMP, TANGENT, TL_MODEL_MR>(e, a);
+    return launch_aek_t<16, 48, 1, DAMP, TANGENT, TL_MODEL_MR>(e, a);
+  }
+  if (e->type == TLFEA_TYPE_3243) return launch_aek_t<8, 12, 7, DAMP, TANGENT, TL_MODEL_SVK>(e, a);
+  return launch_aek_t<16, 48, 1, DAMP, TANGENT, TL_MODEL_SVK>(e, a);
 }
 
 static int ek_chunk_elems() {
@@ -502,6 +507,9 @@ struct EkPlan {
     aa.c1 = a.c1;
     aa.c2 = a.c2;
     aa.c4 = h;
+    aa.mu10 = e->mu10;
+    aa.mu01 = e->mu01;
+    aa.kappa = e->kappa;
     if (!tangent) return TLFEA_OK;
     r.inc_ea = e->pat.d_inc_ea;
     r.slot = e->pat.d_slot;
