@@ -267,6 +267,20 @@ def ancf_config(kind: int, shape, torch, fp64_peak, reps=5):
         tf = flop_elem * ne / (ms * 1e-3) / 1e12
         out["fp64"] = {"achieved_tflops": tf, "peak_tflops": fp64_peak, "frac": tf / fp64_peak,
                        "algorithmic_flop_per_element": flop_elem}
+    # same mesh under the compressible Mooney-Rivlin law (0.3 mu, 0.2 mu, 1.5 K: test_feat10_bunny_newton.cc:120-126)
+    mu, bulk = E_MOD / (2 * (1 + NU)), E_MOD / (3 * (1 - 2 * NU))
+    d.SetMooneyRivlin(0.3 * mu, 0.2 * mu, 1.5 * bulk)
+    for _ in range(2):
+        s.Assemble()
+    torch.cuda.synchronize()
+    a0.record()
+    for _ in range(3):
+        s.Assemble()
+    a1.record()
+    torch.cuda.synchronize()
+    ms_mr = a0.elapsed_time(a1) / 3
+    out["mooney_rivlin_0.3mu_0.2mu_1.5K"] = {"ms_per_step": ms_mr, "value": ne * Q / (ms_mr * 1e-3), "unit": UNIT}
+    d.SetSVK(E_MOD, NU)
     s.SetPCG(50, 0.0)
     s.Solve()  # warm-up (allocates the PCG vectors)
     d.UpdatePositions(xd, yd, zd)
