@@ -19,8 +19,8 @@
 // Mooney-Rivlin (MODEL = TL_MODEL_MR; MooneyRivlin.cuh:45-225): the Gauss-point step runs on threads (element, q, row i)
 // and leaves, per point, P dV and the 81-entry tensor T[i][k][J][L] = h dV dP_iJ/dF_kL with the Kelvin-Voigt block
 // folded in (same form as the FEAT10 kernel, ek_kernel.cuh); the block step is the contraction
-// K_ab[i][k] = sum_J h_a[J] (sum_L T[i][k][J][L] h_b[L]) -- T is read by every thread at the same address (broadcast),
-// so a (pair, point) costs 45 shared-memory wavefronts + 6 operand loads against 22 for SVK.
+// K_ab[i][k] = sum_J h_a[J] W_b[i][k][J] with W_b = sum_L T[i][k][J][L] h_b[L] formed once per (point, column b) and
+// shared by all rows a: 27 DFMA per (pair, point).
 #pragma once
 #include "common.cuh"
 #include "kernels.cuh"  // MRState / mr_state
@@ -58,8 +58,14 @@ struct AEKShape {
   static_assert(H_D % 2 == 0, "the region after gradN must stay 16-byte aligned");
   static constexpr int M_D = Q * 8, P_D = Q * 9, X_D = S * 3;  // M_q padded to 8: four 16-byte loads in the block step
   static constexpr int H2_D = (H_D + U_D + 1) / 2 * 2;          // keeps M 16-byte aligned
+  // Mooney-Rivlin block step: W_b = T h_b of QB points at a time, [point][27][b] (b fastest: the pairs of a warp read
+  // consecutive addresses), shared by every row a of column b
+  static constexpr int QB = 3;
+  static_assert(Q % QB == 0, "point batches");
+  static constexpr int OFF_W = H2_D + M_D + P_D + X_D * (DAMP ? 2 : 1);
+  static constexpr int W_D = MR ? QB * 27 * S : 0;
   // odd element stride: the lanes of a warp that belong to different elements must not share banks
-  static constexpr int ELEM_D = (EPB > 1) ? ((H2_D + M_D + P_D + X_D * (DAMP ? 2 : 1) + 1) | 3) - 1 : H2_D + M_D + P_D + X_D * (DAMP ? 2 : 1);
+  static constexpr int ELEM_D = (EPB > 1) ? ((OFF_W + W_D + 1) | 3) - 1 : OFF_W + W_D;
   static constexpr size_t SMEM = (size_t)EPB * ELEM_D * sizeof(double);
   static constexpr int MINB = MR ? (S == 16 ? 3 : 4) : (S == 16 ? 5 : 4);
 };
@@ -321,24 +327,40 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP, MODEL>::THREADS, AEK
       // ---- block step: thread = (element, pair a <= b)
       double k[9];
       const bool on = pel < ne;
-      if (on && MR) {
-        const double *se = aek_smem + pel * Sh::ELEM_D;
+      if (MR) {
+        // K_ab[i][k] = sum_q sum_J h_a[J] W_b[i][k][J],  W_b[i][k][J] = sum_L T[i][k][J][L] h_b[L]: W_b does not depend
+        // on the row a, so it is formed once per (point, b) for QB points at a time (phase 1, thread = (point, group
+        // (i,k), b)) and every pair of column b reads it (phase 2, thread = pair): 27 DFMA per (pair, point) instead of 108
 #pragma unroll
         for (int i = 0; i < 9; i++) k[i] = 0.0;
+        constexpr int QB = Sh::QB, ITEMS = QB * 9 * S;
 #pragma unroll 1
-        for (int q = 0; q < Q; q++) {
-          const double *hq = se + q * HS;
-          const double2 *t2 = reinterpret_cast<const double2 *>(se + Sh::H_D + q * Sh::TS);  // same address in every lane
-          const double ha[3] = {hq[pa], hq[S + pa], hq[2 * S + pa]};
-          const double hb[3] = {hq[pb], hq[S + pb], hq[2 * S + pb]};
-#pragma unroll
-          for (int g = 0; g < 9; g++) {  // group g = (i, k): T[J][L] in 10 doubles
-            const double2 v0 = t2[g * 5], v1 = t2[g * 5 + 1], v2 = t2[g * 5 + 2], v3 = t2[g * 5 + 3], v4 = t2[g * 5 + 4];
-            const double w0 = v0.x * hb[0] + v0.y * hb[1] + v1.x * hb[2];
-            const double w1 = v1.y * hb[0] + v2.x * hb[1] + v2.y * hb[2];
-            const double w2 = v3.x * hb[0] + v3.y * hb[1] + v4.x * hb[2];
-            k[g] += ha[0] * w0 + ha[1] * w1 + ha[2] * w2;
+        for (int q0 = 0; q0 < Q; q0 += QB) {
+          for (int it = tid; it < ne * ITEMS; it += T) {
+            const int el = it / ITEMS, r = it - el * ITEMS, qq = r / (9 * S), r2 = r - qq * 9 * S, g = r2 / S, b = r2 - g * S;
+            const double *se = aek_smem + el * Sh::ELEM_D;
+            const double *hq = se + (q0 + qq) * HS;
+            const double2 *t2 = reinterpret_cast<const double2 *>(se + Sh::H_D + (q0 + qq) * Sh::TS + g * 10);
+            const double2 v0 = t2[0], v1 = t2[1], v2 = t2[2], v3 = t2[3], v4 = t2[4];
+            const double h0 = hq[b], h1 = hq[S + b], h2 = hq[2 * S + b];
+            double *w = aek_smem + el * Sh::ELEM_D + Sh::OFF_W + (qq * 27 + g * 3) * S + b;
+            w[0] = v0.x * h0 + v0.y * h1 + v1.x * h2;
+            w[S] = v1.y * h0 + v2.x * h1 + v2.y * h2;
+            w[2 * S] = v3.x * h0 + v3.y * h1 + v4.x * h2;
           }
+          __syncthreads();
+          if (on) {
+            const double *se = aek_smem + pel * Sh::ELEM_D;
+#pragma unroll
+            for (int qq = 0; qq < QB; qq++) {
+              const double *hq = se + (q0 + qq) * HS;
+              const double *w = se + Sh::OFF_W + qq * 27 * S + pb;
+              const double ha0 = hq[pa], ha1 = hq[S + pa], ha2 = hq[2 * S + pa];
+#pragma unroll
+              for (int g = 0; g < 9; g++) k[g] += ha0 * w[(g * 3) * S] + ha1 * w[(g * 3 + 1) * S] + ha2 * w[(g * 3 + 2) * S];
+            }
+          }
+          __syncthreads();  // the next batch overwrites W
         }
       }
       if (on && !MR) {
