@@ -49,7 +49,9 @@ struct AEKShape {
   static constexpr int RS = 9 * S + 1;           // padded stride of a staged block row (odd: lanes = b)
   static constexpr int TS = 90;                  // Mooney-Rivlin: T of one point, 9 groups (i,k) of [J][L] padded to 10
   static constexpr int GPT = MR ? EPB * Q * 3 : EPB * Q;  // threads of the Gauss-point step
-  static constexpr int WORK = (EPB * NPAIR > EPB * 3 * S ? EPB * NPAIR : EPB * 3 * S);
+  static constexpr int NT2 = (S / 2) * (S / 2 + 1);       // Mooney-Rivlin block step: tiles of two rows (2t, 2t+1) x column b >= 2t
+  static constexpr int BLK = MR ? EPB * NT2 : EPB * NPAIR;
+  static constexpr int WORK = (BLK > EPB * 3 * S ? BLK : EPB * 3 * S);
   static constexpr int THREADS = ((WORK > GPT ? WORK : GPT) + 31) / 32 * 32;
   static constexpr int H_D = Q * HS;             // per element
   static constexpr int U_D = MR ? Q * TS : Q * HS;  // u rows (SVK) or the tangent tensors (Mooney-Rivlin)
@@ -88,6 +90,16 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP, MODEL>::THREADS, AEK
     }
     pa = a;
     pb = a + r;
+  }
+  if (MR) {  // thread = (element, row pair t, column b >= 2t), b fastest: the lanes of a warp read consecutive W_b
+    pel = tid / Sh::NT2;
+    int r = tid - pel * Sh::NT2, t = 0;
+    while (r >= S - 2 * t) {
+      r -= S - 2 * t;
+      t++;
+    }
+    pa = 2 * t;      // rows pa and pa + 1 (the second one only where pa + 1 <= pb)
+    pb = 2 * t + r;
   }
   const int n_groups = (p.n_elem + EPB - 1) / EPB;
   for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
@@ -325,15 +337,18 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP, MODEL>::THREADS, AEK
     }
     if (TANGENT) {
       // ---- block step: thread = (element, pair a <= b)
-      double k[9];
+      double k[9], k1[9];  // k1: second row of a Mooney-Rivlin tile
       const bool on = pel < ne;
+      const bool on1 = MR && on && pa + 1 <= pb;
       if (MR) {
         // K_ab[i][k] = sum_q sum_J h_a[J] W_b[i][k][J],  W_b[i][k][J] = sum_L T[i][k][J][L] h_b[L]: W_b does not depend
         // on the row a, so it is formed once per (point, b) for QB points at a time (phase 1, thread = (point, group
-        // (i,k), b)) and every pair of column b reads it (phase 2, thread = pair): 27 DFMA per (pair, point) instead of 108
+        // (i,k), b)) and every pair of column b reads it (phase 2, thread = two rows x column b): 27 DFMA per (pair, point)
+        // instead of 108
 #pragma unroll
-        for (int i = 0; i < 9; i++) k[i] = 0.0;
+        for (int i = 0; i < 9; i++) k[i] = 0.0, k1[i] = 0.0;
         constexpr int QB = Sh::QB, ITEMS = QB * 9 * S;
+        const int pa1 = min(pa + 1, S - 1);
 #pragma unroll 1
         for (int q0 = 0; q0 < Q; q0 += QB) {
           for (int it = tid; it < ne * ITEMS; it += T) {
@@ -356,8 +371,13 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP, MODEL>::THREADS, AEK
               const double *hq = se + (q0 + qq) * HS;
               const double *w = se + Sh::OFF_W + qq * 27 * S + pb;
               const double ha0 = hq[pa], ha1 = hq[S + pa], ha2 = hq[2 * S + pa];
+              const double hc0 = hq[pa1], hc1 = hq[S + pa1], hc2 = hq[2 * S + pa1];
 #pragma unroll
-              for (int g = 0; g < 9; g++) k[g] += ha0 * w[(g * 3) * S] + ha1 * w[(g * 3 + 1) * S] + ha2 * w[(g * 3 + 2) * S];
+              for (int g = 0; g < 9; g++) {  // one read of W_b serves both rows of the tile
+                const double w0 = w[(g * 3) * S], w1 = w[(g * 3 + 1) * S], w2 = w[(g * 3 + 2) * S];
+                k[g] += ha0 * w0 + ha1 * w1 + ha2 * w2;
+                k1[g] += hc0 * w0 + hc1 * w1 + hc2 * w2;
+              }
             }
           }
           __syncthreads();  // the next batch overwrites W
@@ -406,6 +426,18 @@ __global__ void __launch_bounds__(AEKShape<S, Q, EPB, DAMP, MODEL>::THREADS, AEK
           for (int i = 0; i < 3; i++)
 #pragma unroll
             for (int c = 0; c < 3; c++) d2[c * 3 + i] = k[i * 3 + c];
+        }
+        if (on1) {
+          double *e1 = st + (pa + 1) * RS + pb * 9;
+#pragma unroll
+          for (int i = 0; i < 9; i++) e1[i] = k1[i];
+          if (pa + 1 != pb) {
+            double *e2 = st + pb * RS + (pa + 1) * 9;
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+              for (int c = 0; c < 3; c++) e2[c * 3 + i] = k1[i * 3 + c];
+          }
         }
       }
       __syncthreads();
