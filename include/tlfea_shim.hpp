@@ -191,4 +191,15 @@ struct SyncedNewtonSolver : SolverBase {
   void SetFixedSparsityPattern(bool fixed) { TLFEA_OR_DIE(tlfea_newton_set_fixed_pattern(s, fixed ? 1 : 0)); }
   void Solve() override { TLFEA_OR_DIE(tlfea_newton_solve_step(s)); }
   double *GetVelocityGuessDevicePtr() { return tlfea_newton_devptr_v(s); }
+  // Not in the reference: the per-iteration kernels driven from host buffers (UpdatePositions + force / tangent
+  // assembly + residual norm + RetrieveInternalForceToCPU) with the PCIe copies hidden under the kernels.
+  // x, y, z (n_coef each) must stay valid until AssembleFromHostEnd returns; f_int holds 3 * n_coef doubles.
+  void AssembleFromHostBegin(const double *x, const double *y, const double *z, int n_coef) {
+    TLFEA_OR_DIE(tlfea_newton_assemble_host_begin(s, x, y, z, n_coef));
+  }
+  double AssembleFromHostEnd(double *f_int, int n_dofs) {
+    double norm_g = 0.0;
+    TLFEA_OR_DIE(tlfea_newton_assemble_host_end(s, f_int, n_dofs, &norm_g));
+    return norm_g;
+  }
 };
