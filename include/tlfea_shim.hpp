@@ -191,6 +191,8 @@ struct SyncedNewtonSolver : SolverBase {
   void SetFixedSparsityPattern(bool fixed) { TLFEA_OR_DIE(tlfea_newton_set_fixed_pattern(s, fixed ? 1 : 0)); }
   void Solve() override { TLFEA_OR_DIE(tlfea_newton_solve_step(s)); }
   double *GetVelocityGuessDevicePtr() { return tlfea_newton_devptr_v(s); }
+  // Not in the reference: settings of the block-Jacobi PCG that stands in for the cuDSS solve
+  void SetPCG(int max_iters, double rel_tol) { TLFEA_OR_DIE(tlfea_newton_set_pcg(s, max_iters, rel_tol)); }
   // Not in the reference: the per-iteration kernels driven from host buffers (UpdatePositions + force / tangent
   // assembly + residual norm + RetrieveInternalForceToCPU) with the PCIe copies hidden under the kernels.
   // x, y, z (n_coef each) must stay valid until AssembleFromHostEnd returns; f_int holds 3 * n_coef doubles.

@@ -84,3 +84,8 @@ def test_cpp_shim_compiles_and_links_against_the_abi(tmp_path):
     subprocess.check_call([gxx, "-std=c++17", "-I", os.path.join(root, "include"), str(src), "-o", str(exe),
                            "-L", lib_dir, "-ltlfea_b200", "-Wl,-rpath," + lib_dir, "-Wl,--unresolved-symbols=ignore-in-shared-libs"])
     assert subprocess.call([str(exe)], env=dict(os.environ, LD_LIBRARY_PATH=lib_dir)) == 0
+    # the beam_sag example driver builds against the same header and library
+    ex = tmp_path / "beam_sag"
+    subprocess.check_call([gxx, "-std=c++17", "-I", os.path.join(root, "include"), os.path.join(root, "examples", "beam_sag.cc"),
+                           "-o", str(ex), "-L", lib_dir, "-ltlfea_b200", "-Wl,-rpath," + lib_dir,
+                           "-Wl,--unresolved-symbols=ignore-in-shared-libs"])

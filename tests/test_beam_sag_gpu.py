@@ -118,3 +118,53 @@ def test_beam_sag_newton_steps_match_cpu_restatement():
         tip = gz[4 * N_EL]
         assert tip > tip_prev  # the tip keeps moving up under the +z load
         tip_prev = tip
+
+
+def test_cpp_driver_through_the_shim_matches_the_python_mirror(tmp_path):
+    """examples/beam_sag.cc -- the beam_sag driver written in host C++ against the reference's class names
+    (include/tlfea_shim.hpp over the C ABI) -- is compiled with g++, run on the GPU, and must print the tip
+    positions the Python mirror produces for the same calls (same library, same operations: same bits)."""
+    import os
+    import shutil
+    import subprocess
+
+    import tlfea
+
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.join(root, "total-lagrangian-fea_b200", "lib")
+    exe = tmp_path / "beam_sag"
+    subprocess.check_call([gxx, "-std=c++17", "-O1", "-I", os.path.join(root, "include"),
+                           os.path.join(root, "examples", "beam_sag.cc"), "-o", str(exe), "-L", lib_dir, "-ltlfea_b200",
+                           "-Wl,-rpath," + lib_dir, "-Wl,--unresolved-symbols=ignore-in-shared-libs"])
+    out = subprocess.check_output([str(exe), str(N_STEPS)], env=dict(os.environ, LD_LIBRARY_PATH=lib_dir), text=True)
+    tips_cpp = [float(ln.split()[3]) for ln in out.splitlines() if ln.startswith("step")]
+    assert len(tips_cpp) == N_STEPS
+
+    x, y, z, conn = _mesh()
+    f_ext = np.zeros(3 * x.shape[0])
+    f_ext[3 * (4 * N_EL) + 2] = FZ
+    d = tlfea.GPU_ANCF3243_Data(N_EL + 1, N_EL)
+    d.Initialize()
+    d.SetExternalForce(f_ext)
+    d.Setup(L, W, H, x, y, z, conn)
+    d.SetDensity(RHO)
+    d.SetDamping(ETA, LAMD)
+    d.SetSVK(E_MOD, NU)
+    d.SetNodalFixed(np.arange(4, dtype=np.int32))
+    d.CalcDsDuPre()
+    d.CalcMassMatrix()
+    d.CalcConstraintData()
+    s = tlfea.SyncedNewtonSolver(d, 12)
+    s.SetParameters(tlfea.SyncedNewtonParams(*PRM))
+    s.Setup()
+    s.AnalyzeHessianSparsity()
+    s.SetFixedSparsityPattern(True)
+    s.SetPCG(20000, 1e-13)
+    for k in range(N_STEPS):
+        s.Solve()
+        tip = d.RetrievePositionToCPU()[2][4 * N_EL]
+        assert tip == tips_cpp[k], (k, tip, tips_cpp[k])
+    assert tips_cpp[-1] > tips_cpp[0] > 0.0
