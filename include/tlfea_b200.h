@@ -258,6 +258,17 @@ double *tlfea_newton_devptr_krylov(tlfea_newton *s, int which);
 /* FP64 FMA peak micro-benchmark (roofline denominator for the tangent kernel): TFLOP/s */
 int tlfea_fp64_peak(int device, double *tflops);
 
+/* Test hooks for the single-pass FEAT10 assembly plan (csrc/patch_plan.cuh; new design, no reference line):
+ * the plan is pure host data, built without a GPU, so the CPU test-suite can replay the kernel's summation
+ * order.  ecoef is [n_elem][10] row-major coefficient ids; off/cols the coefficient-level CSR pattern. */
+int tlfea_debug_patch_plan_build(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y,
+                                 const double *z, const int *off, const int *cols, int W, void **plan_out);
+/* sizes[8] = patches, colours, elements, rows, entries, sources, uncovered pattern blocks, sum of local blocks */
+int tlfea_debug_patch_plan_sizes(void *plan, int64_t *sizes);
+int tlfea_debug_patch_plan_copy(void *plan, int *color_ptr, void *desc, void *elems, void *rows, uint32_t *ent,
+                                uint16_t *src, int64_t *uncovered);
+int tlfea_debug_patch_plan_free(void *plan);
+
 #ifdef __cplusplus
 }
 #endif

@@ -125,6 +125,11 @@ _SIGS = {
     "tlfea_dist_pack": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
     "tlfea_dist_unpack": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
     "tlfea_fp64_peak": (C.c_int, [C.c_int, c_dp]),
+    "tlfea_debug_patch_plan_build": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_dp, c_ip, c_ip, C.c_int,
+                                               C.POINTER(c_vp)]),
+    "tlfea_debug_patch_plan_sizes": (C.c_int, [c_vp, c_i64p]),
+    "tlfea_debug_patch_plan_copy": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "tlfea_debug_patch_plan_free": (C.c_int, [c_vp]),
 }
 
 if not os.path.exists(LIB_PATH):
