@@ -211,10 +211,17 @@ double *tlfea_newton_devptr_g(tlfea_newton *s);
 int tlfea_newton_spmv(tlfea_newton *s, const double *d_x, double *d_y);
 /* sum of the CUDA-event time (ms) of assemble calls since the last reset, and their count */
 int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset);
-/* Assembly kernel selection: 1 (default) = element kernel + row reduce where supported (FEAT10 + SVK,
- * csrc/ek_kernel.cuh), 0 = generic warp-per-row gather (all element types and materials).  Both are
- * deterministic (no atomics); results agree to rounding. */
+/* Assembly kernel selection: 2 (default) = single-pass patch assembly for FEAT10 (csrc/pk_kernel.cuh: on-chip
+ * accumulation per patch, in-place update of H colour by colour) and the two-phase path for the ANCF elements;
+ * 1 = element kernel + row reduce for every element type (csrc/ek_kernel.cuh, csrc/ancf_ek.cuh); 0 = generic
+ * warp-per-row gather.  All are deterministic (no atomics); results agree to rounding. */
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode);
+/* Warps (= sub-patches) per patch of the single-pass assembly: 4 (two CTAs per SM, default) or 8.  Takes effect
+ * when the plan is (re)built, i.e. before the first assemble.  New design, no reference line. */
+int tlfea_newton_set_patch_warps(tlfea_newton *s, int warps);
+/* out[8] = patches, colours, warps per patch, sum over patches of their distinct node pairs, bytes of write-out
+ * lists, pattern blocks no element touches, 0, 0 (valid after the first FEAT10 assemble in mode 2) */
+int tlfea_newton_patch_stats(tlfea_newton *s, int64_t *out);
 /* per-kernel CUDA-event timing of the next assemble calls (0/1) */
 int tlfea_newton_set_profile(tlfea_newton *s, int on);
 /* element-phase, row-phase and remaining (constraint term) milliseconds accumulated while profiling */
@@ -263,10 +270,10 @@ int tlfea_fp64_peak(int device, double *tflops);
  * order.  ecoef is [n_elem][10] row-major coefficient ids; off/cols the coefficient-level CSR pattern. */
 int tlfea_debug_patch_plan_build(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y,
                                  const double *z, const int *off, const int *cols, int W, void **plan_out);
-/* sizes[8] = patches, colours, elements, rows, entries, sources, uncovered pattern blocks, sum of local blocks */
+/* sizes[8] = patches, colours, elements, rows, blob bytes, largest patch blob, uncovered pattern blocks, sum of local blocks */
 int tlfea_debug_patch_plan_sizes(void *plan, int64_t *sizes);
-int tlfea_debug_patch_plan_copy(void *plan, int *color_ptr, void *desc, void *elems, void *rows, uint32_t *ent,
-                                uint16_t *src, int64_t *uncovered);
+int tlfea_debug_patch_plan_copy(void *plan, int *color_ptr, void *desc, void *elems, int *row_node, int64_t *row_ptr,
+                                void *blob, int64_t *uncovered);
 int tlfea_debug_patch_plan_free(void *plan);
 
 #ifdef __cplusplus

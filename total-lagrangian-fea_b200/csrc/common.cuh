@@ -112,6 +112,7 @@ struct tlfea_elem {
   cudaStream_t stream = nullptr;
   bool own_stream = true;
   bool is_setup = false, is_precomputed = false, is_pattern = false, is_mass = false;
+  int mass_version = 0;               // bumped by CalcMassMatrix: cached copies of the mass values refresh
   int cons_version = 0;               // bumped by UpdateNodalFixed: solvers refresh their constraint slots
   bool pat_extra = false;             // the pattern also holds J^T J couplings of linear constraints
   std::vector<int> h_j_off, h_j_cols;  // host copy of the constraint Jacobian structure
@@ -151,15 +152,24 @@ struct tlfea_elem {
   int64_t j_nnz = 0;
 };
 
+struct tlfea_newton;
 namespace tlfea {
 int build_row_order(const tlfea_elem *h, int **d_order);
 int build_completion_order(const tlfea_elem *h, int chunk, int **d_order, std::vector<int> *chunk_ptr);
+int patch_prepare(tlfea_newton *s);
+int patch_assemble(tlfea_newton *s, bool tangent, bool damp);
+void patch_release(tlfea_newton *s);
+int patch_stats(tlfea_newton *s, int64_t *out);
 }
 
 struct tlfea_newton {
   tlfea_elem *e = nullptr;
   int device = 0;
-  bool two_phase = true;  // element kernel + row reduce where supported (FEAT10 + SVK); else the generic row gather
+  // 0 = generic row gather, 1 = element kernel + row reduce (two-phase), 2 = single-pass patch assembly for FEAT10
+  // (pk_kernel.cuh; the ANCF elements use the two-phase path)
+  int asm_mode = 2;
+  void *patch = nullptr;  // PatchPlanDev (patch_asm.cu)
+  int pk_w = 0;           // warps per patch (0 = TLFEA_PK_W or 4)
   int n_constraints = 0;
   tlfea_newton_params prm{};
   bool analyzed = false, fixed_pattern = false;

@@ -672,7 +672,7 @@ struct RKArgs {
 constexpr int RK_WARPS = 8;
 constexpr int RK_T = 4;  // rows per ticket
 
-__global__ void k_row_desc(int n, const int *__restrict__ order, const int *__restrict__ off,
+static __global__ void k_row_desc(int n, const int *__restrict__ order, const int *__restrict__ off,
                            const int *__restrict__ inc_ptr, RowDesc *desc) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;

@@ -688,6 +688,7 @@ int tlfea_elem_calc_mass(tlfea_elem *h) {
   TL_CUDA(cudaStreamSynchronize(h->stream));
   cudaFree(Me);
   h->is_mass = true;
+  h->mass_version++;
   return TLFEA_OK;
 }
 

@@ -383,8 +383,19 @@ static EKCfg ek_cfg() {
 }
 
 static bool ek_supported(const tlfea_newton *s) {
-  if (!s->two_phase) return false;
-  return true;  // every element type, SVK and Mooney-Rivlin, with or without Kelvin-Voigt damping
+  return s->asm_mode >= 1;  // every element type, SVK and Mooney-Rivlin, with or without Kelvin-Voigt damping
+}
+static bool pk_selected(const tlfea_newton *s) { return s->asm_mode == 2 && s->e->type == TLFEA_TYPE_T10; }
+
+// single-pass patch assembly (pk_kernel.cuh) + the ordered nodal force gather
+static int assemble_pk(tlfea_newton *s, bool tangent, bool damp) {
+  tlfea_elem *e = s->e;
+  TL_TRY(patch_assemble(s, tangent, damp));
+  if (s->profile) TL_CUDA(cudaEventRecord(s->ev[2], e->stream));
+  TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)e->n_coef * 3, 128), 128, 0, e->stream, e->n_coef,
+            e->pat.d_inc_ptr, e->pat.d_inc_ea, e->d_fe, e->d_f_int, 0);
+  if (s->profile) TL_CUDA(cudaEventRecord(s->ev[3], e->stream));
+  return TLFEA_OK;
 }
 
 template <int G, int W, bool DAMP, bool TANGENT, int MODEL>
@@ -653,7 +664,10 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
   const bool damp = (e->eta != 0.0 || e->lambda_d != 0.0);
   TL_CUDA(cudaEventRecord(s->ev[0], e->stream));
   if (ek_supported(s)) {
-    TL_TRY(assemble_ek(s, tangent, damp));
+    if (pk_selected(s))
+      TL_TRY(assemble_pk(s, tangent, damp));
+    else
+      TL_TRY(assemble_ek(s, tangent, damp));
     if (tangent && s->n_cons_slots > 0) {
       TL_LAUNCH(k_add_constraint_term, blocks_for(s->n_cons_slots, 256), 256, 0, e->stream, s->n_cons_slots,
                 s->d_cons_slot, s->d_cons_val, s->prm.time_step * s->prm.time_step * s->prm.rho, s->d_H);
@@ -880,7 +894,7 @@ static int assemble_host_begin(tlfea_newton *s, const double *hx, const double *
   TL_TRY(ensure_pattern(e));
   TL_TRY(refresh_constraints(s));
   const bool damp = (e->eta != 0.0 || e->lambda_d != 0.0);
-  bool overlap = ek_supported(s);
+  bool overlap = ek_supported(s) && !pk_selected(s);
   EkPlan pl;
   if (overlap) {
     TL_TRY(pl.init(s, true, damp));
@@ -1009,6 +1023,7 @@ int tlfea_newton_destroy(tlfea_newton *s) {
     cudaStreamSynchronize(s->e->stream);
   else
     cudaDeviceSynchronize();  // the element handle went first: its stream is gone
+  patch_release(s);
   dfree(s->d_H);
   dfree(s->d_gp);
   dfree(s->d_stage);
@@ -1433,9 +1448,21 @@ int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset
   return TLFEA_OK;
 }
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode) {
-  TL_CHECK(s && (mode == 0 || mode == 1), "mode must be 0 (generic row gather) or 1 (element kernel + row reduce)");
-  s->two_phase = (mode == 1);
+  TL_CHECK(s && mode >= 0 && mode <= 2,
+           "mode must be 0 (generic row gather), 1 (element kernel + row reduce) or 2 (single-pass patches, FEAT10)");
+  s->asm_mode = mode;
   return TLFEA_OK;
+}
+int tlfea_newton_set_patch_warps(tlfea_newton *s, int warps) {
+  TL_CHECK(s && (warps == 4 || warps == 8), "warps per patch must be 4 or 8");
+  if (s->pk_w != warps) patch_release(s);
+  s->pk_w = warps;
+  return TLFEA_OK;
+}
+int tlfea_newton_patch_stats(tlfea_newton *s, int64_t *out) {
+  TL_CHECK(s && out, "null input");
+  for (int i = 0; i < 8; i++) out[i] = 0;
+  return patch_stats(s, out);
 }
 int tlfea_newton_set_profile(tlfea_newton *s, int on) {
   TL_CHECK(s, "null handle");

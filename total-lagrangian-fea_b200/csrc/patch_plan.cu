@@ -3,7 +3,9 @@
 #include "patch_plan.cuh"
 
 #include <algorithm>
+#include <climits>
 #include <cmath>
+#include <cstdint>
 #include <cstring>
 
 #include "../../include/tlfea_b200.h"
@@ -40,18 +42,57 @@ struct SubPatch {
   int begin = 0, end = 0;  // range in the sorted element order
 };
 
+struct EntL {
+  int64_t habs;   // 9*off[i] + 3*slot
+  int64_t g;      // global pattern block
+  int rowlen;
+  uint16_t src;
+  bool first;
+};
 struct PatchLocal {
   std::vector<PElem> elems;
   int sub_ptr[PK_MAXW + 1] = {0};
   int n_sub = 0;
-  std::vector<PRow> rows;
-  std::vector<uint32_t> ent;
-  std::vector<int64_t> ent_g;  // global pattern block of each entry
-  std::vector<uint16_t> src;
-  std::vector<int> nodes;      // sorted distinct coefficient ids
+  std::vector<int> nodes;  // distinct coefficient ids (ascending)
+  std::vector<EntL> ent;
+  std::vector<uint32_t> ops;  // merge ops, round by round
+  int round_end[8] = {0};
   int color = -1;
   bool bad = false;
 };
+
+// Accumulator slots of a sub-patch's blocks.  The 15 lanes of a half warp add their t-th block at the same time:
+// the adds are bank-conflict free when those 15 slots differ modulo 16 (a block is 9 doubles = odd stride).
+// Greedy: blocks in order of first use take the residue class that collides least with the sets they belong to.
+void assign_slots(int nb, const std::vector<std::vector<int>> &sets, std::vector<int> &slot) {
+  std::vector<std::vector<int>> member((size_t)nb);
+  for (size_t q = 0; q < sets.size(); q++)
+    for (int b : sets[q]) member[(size_t)b].push_back((int)q);
+  std::vector<uint16_t> used(sets.size(), 0);  // residues taken per set
+  int cap[16], fill[16] = {0};
+  for (int r = 0; r < 16; r++) cap[r] = (PK_CAPU - r + 15) / 16;
+  slot.assign((size_t)nb, -1);
+  std::vector<int> order;
+  std::vector<char> seen((size_t)nb, 0);
+  for (auto &st : sets)
+    for (int b : st)
+      if (!seen[(size_t)b]) seen[(size_t)b] = 1, order.push_back(b);
+  for (int b = 0; b < nb; b++)
+    if (!seen[(size_t)b]) order.push_back(b);
+  for (int b : order) {
+    int best = -1, best_cost = 1 << 30;
+    for (int r = 0; r < 16; r++) {
+      if (fill[r] >= cap[r]) continue;
+      int cost = 0;
+      for (int q : member[(size_t)b]) cost += (used[(size_t)q] >> r) & 1;
+      cost = cost * 64 + fill[r];  // ties: the emptiest class
+      if (cost < best_cost) best_cost = cost, best = r;
+    }
+    slot[(size_t)b] = best + 16 * fill[best];
+    fill[best]++;
+    for (int q : member[(size_t)b]) used[(size_t)q] |= (uint16_t)(1u << best);
+  }
+}
 
 }  // namespace
 
@@ -166,8 +207,8 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
       PatchLocal P;
       P.n_sub = ns;
       struct Tup {
-        int i, j;
-        uint16_t s;
+        uint64_t key;
+        uint16_t s;  // accumulator block address: warp << 8 | slot
       };
       std::vector<Tup> tups;
       for (int w = 0; w < ns; w++) {
@@ -181,6 +222,28 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
         }
         std::sort(blocks.begin(), blocks.end());
         blocks.erase(std::unique(blocks.begin(), blocks.end()), blocks.end());
+        // the block sets that are added simultaneously: (element, t = ta*2+tb) over the 15 tiles
+        std::vector<std::vector<int>> sets;
+        std::vector<int> bidx((size_t)(S.end - S.begin) * 60, -1);
+        for (int i = S.begin; i < S.end; i++) {
+          const int *ec = ecoef + (size_t)order[i].second * 10;
+          for (int tt = 0; tt < 4; tt++) {
+            std::vector<int> st;
+            for (int t = 0; t < 15; t++) {
+              int I, J;
+              tile_ij(t, &I, &J);
+              if (I == J && tt == 2) continue;
+              const int a = 2 * I + (tt >> 1), b = 2 * J + (tt & 1);
+              const int bi = (int)(std::lower_bound(blocks.begin(), blocks.end(), upper_key(ec[a], ec[b])) -
+                                   blocks.begin());
+              bidx[(size_t)(i - S.begin) * 60 + t * 4 + tt] = bi;
+              st.push_back(bi);
+            }
+            sets.push_back(std::move(st));
+          }
+        }
+        std::vector<int> slot;
+        assign_slots((int)blocks.size(), sets, slot);
         for (int i = S.begin; i < S.end; i++) {
           const int e = order[i].second;
           const int *ec = ecoef + (size_t)e * 10;
@@ -192,62 +255,56 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
             int I, J;
             tile_ij(t, &I, &J);
             uint32_t word = 0;
-            for (int ta = 0; ta < 2; ta++)
-              for (int tb = 0; tb < 2; tb++) {
-                const int a = 2 * I + ta, b = 2 * J + tb, bit = t * 4 + ta * 2 + tb;
-                uint32_t u = 255;
-                if (!(I == J && ta == 1 && tb == 0)) {
-                  const uint64_t k = upper_key(ec[a], ec[b]);
-                  u = (uint32_t)(std::lower_bound(blocks.begin(), blocks.end(), k) - blocks.begin());
-                  if (ec[a] > ec[b]) pe.tr[bit >> 5] |= 1u << (bit & 31);
-                }
-                word |= u << (8 * (ta * 2 + tb));
+            for (int tt = 0; tt < 4; tt++) {
+              const int a = 2 * I + (tt >> 1), b = 2 * J + (tt & 1), bit = t * 4 + tt;
+              uint32_t u = 255;
+              if (!(I == J && tt == 2)) {
+                u = (uint32_t)slot[(size_t)bidx[(size_t)(i - S.begin) * 60 + t * 4 + tt]];
+                if (ec[a] > ec[b]) pe.tr[bit >> 5] |= 1u << (bit & 31);
               }
+              word |= u << (8 * tt);
+            }
             pe.blk4[t] = word;
           }
           P.elems.push_back(pe);
         }
-        for (size_t u = 0; u < blocks.size(); u++) {
-          const int i = (int)(blocks[u] >> 32), j = (int)(blocks[u] & 0xffffffffu);
-          tups.push_back({i, j, (uint16_t)(u | (w << 8))});
-          if (i != j) tups.push_back({j, i, (uint16_t)(u | (w << 8) | (1u << 11))});
-        }
+        for (size_t u = 0; u < blocks.size(); u++) tups.push_back({blocks[u], (uint16_t)(slot[u] | (w << 8))});
       }
       P.sub_ptr[ns] = (int)P.elems.size();
       for (int w = ns; w < PK_MAXW; w++) P.sub_ptr[w + 1] = P.sub_ptr[ns];
+      // pairs held by several warps: reduced into the lowest warp's block, one extra warp per round
       std::sort(tups.begin(), tups.end(), [](const Tup &a, const Tup &b) {
-        if (a.i != b.i) return a.i < b.i;
-        if (a.j != b.j) return a.j < b.j;
-        return (a.s & 0x7ff) < (b.s & 0x7ff);  // warp, then block: the combine order
+        return a.key != b.key ? a.key < b.key : a.s < b.s;
       });
+      std::vector<std::vector<uint32_t>> rounds(8);
       for (size_t k = 0; k < tups.size();) {
-        const int i = tups[k].i;
-        PRow r;
-        std::memset(&r, 0, sizeof(r));
-        r.node = i;
-        r.hbase = 9 * (int64_t)off[i];
-        const int deg = off[i + 1] - off[i];
-        r.rowlen = 3 * deg;
-        r.mass_base = off[i];
-        r.ent_begin = (int)P.ent.size();
-        P.nodes.push_back(i);
-        while (k < tups.size() && tups[k].i == i) {
-          const int j = tups[k].j;
-          size_t k2 = k;
-          while (k2 < tups.size() && tups[k2].i == i && tups[k2].j == j) k2++;
-          const int nsrc = (int)(k2 - k);
-          const int *cb = cols + off[i], *ce = cb + deg;
-          const int *it = std::lower_bound(cb, ce, j);
+        size_t k2 = k;
+        while (k2 < tups.size() && tups[k2].key == tups[k].key) k2++;
+        if (k2 - k > 8) P.bad = true;
+        for (size_t q = k + 1; q < k2 && q - k <= 7; q++)
+          rounds[q - k - 1].push_back((uint32_t)tups[k].s | ((uint32_t)tups[q].s << 16));
+        const int i = (int)(tups[k].key >> 32), j = (int)(tups[k].key & 0xffffffffu);
+        for (int side = 0; side < (i == j ? 1 : 2); side++) {
+          const int r = side ? j : i, c = side ? i : j;
+          const int deg = off[r + 1] - off[r];
+          const int *cb = cols + off[r], *ce = cb + deg;
+          const int *it = std::lower_bound(cb, ce, c);
           const int slot = (int)(it - cb);
-          if (it == ce || *it != j || slot > PK_MAX_SLOT || nsrc > 8 || P.src.size() > 32767) P.bad = true;
-          P.ent.push_back((uint32_t)slot | ((uint32_t)(nsrc - 1) << 14) | ((uint32_t)P.src.size() << 17));
-          P.ent_g.push_back((int64_t)off[i] + slot);
-          for (size_t q = k; q < k2; q++) P.src.push_back(tups[q].s);
-          k = k2;
+          if (it == ce || *it != c || 3 * deg > PK_MAX_ROWLEN) P.bad = true;
+          P.ent.push_back({9 * (int64_t)off[r] + 3 * slot, (int64_t)off[r] + slot, 3 * deg,
+                           (uint16_t)(tups[k].s | (side ? 0x800u : 0u)), false});
+          P.nodes.push_back(r);
         }
-        r.n_ent = (int)P.ent.size() - r.ent_begin;
-        P.rows.push_back(r);
+        k = k2;
       }
+      for (int r = 0; r < 7; r++) {
+        P.ops.insert(P.ops.end(), rounds[r].begin(), rounds[r].end());
+        P.round_end[r] = (int)P.ops.size();
+      }
+      P.round_end[7] = (int)P.ops.size();
+      std::sort(P.ent.begin(), P.ent.end(), [](const EntL &a, const EntL &b) { return a.habs < b.habs; });
+      std::sort(P.nodes.begin(), P.nodes.end());
+      P.nodes.erase(std::unique(P.nodes.begin(), P.nodes.end()), P.nodes.end());
       any_bad = any_bad || P.bad;
       plist.push_back(std::move(P));
     }
@@ -308,56 +365,78 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
 #pragma omp parallel for schedule(dynamic, 64)
     for (int q = R.color_ptr[c]; q < R.color_ptr[c + 1]; q++) {
       PatchLocal &P = *pl[perm[q]];
-      for (size_t k = 0; k < P.ent.size(); k++) {
-        uint8_t &cv = covered[(size_t)P.ent_g[k]];
+      for (auto &en : P.ent) {
+        uint8_t &cv = covered[(size_t)en.g];
         if (!cv) {
           cv = 1;
-          P.ent[k] |= PK_ENT_FIRST;
+          en.first = true;
         }
       }
+      // first touches first, then (row, column): entry k < n_first starts from the mass term
+      std::stable_sort(P.ent.begin(), P.ent.end(), [](const EntL &a, const EntL &b) { return a.first > b.first; });
     }
   }
   for (int64_t g = 0; g < nnz; g++)
     if (!covered[(size_t)g]) R.uncovered.push_back(g);
   std::vector<uint8_t>().swap(covered);
 
-  std::vector<int64_t> e_off((size_t)np + 1, 0), r_off((size_t)np + 1, 0), n_off((size_t)np + 1, 0),
-      s_off((size_t)np + 1, 0);
+  std::vector<int64_t> e_off((size_t)np + 1, 0), b_off((size_t)np + 1, 0), r_off((size_t)np + 1, 0);
+  int64_t sum_local = 0;
+  int max_blob = 0;
+  bool span_bad = false;
   for (int q = 0; q < np; q++) {
     const PatchLocal &P = *pl[perm[q]];
+    int nf = 0;
+    for (auto &en : P.ent) nf += en.first;
+    const BlobLayout L((int)P.ent.size(), nf, (int)P.ops.size());
     e_off[q + 1] = e_off[q] + (int64_t)P.elems.size();
-    r_off[q + 1] = r_off[q] + (int64_t)P.rows.size();
-    n_off[q + 1] = n_off[q] + (int64_t)P.ent.size();
-    s_off[q + 1] = s_off[q] + (int64_t)P.src.size();
+    b_off[q + 1] = b_off[q] + L.total;
+    r_off[q + 1] = r_off[q] + (int64_t)P.nodes.size();
+    sum_local += (int64_t)P.ent.size();
+    max_blob = std::max(max_blob, L.total);
   }
-  if (n_off[np] > 2147483647LL || s_off[np] > 2147483647LL)
-    return failm(TLFEA_ERR_UNSUPPORTED, "patch plan: entry list exceeds int32");
+  if (b_off[np] / 16 > 4294967295LL) return failm(TLFEA_ERR_UNSUPPORTED, "patch plan: blob exceeds 64 GB");
   R.desc.resize((size_t)np);
   R.elems.resize((size_t)e_off[np]);
-  R.rows.resize((size_t)r_off[np]);
-  R.ent.resize((size_t)n_off[np]);
-  R.src.resize((size_t)s_off[np]);
-  R.sum_local_blocks = n_off[np];
-#pragma omp parallel for schedule(dynamic, 64)
+  R.blob.assign((size_t)b_off[np], 0);
+  R.row_node.resize((size_t)r_off[np]);
+  R.row_ptr.assign(r_off.begin(), r_off.end());
+  R.sum_local_blocks = sum_local;
+  R.max_blob_bytes = max_blob;
+#pragma omp parallel for schedule(dynamic, 64) reduction(|| : span_bad)
   for (int q = 0; q < np; q++) {
     const PatchLocal &P = *pl[perm[q]];
+    int nf = 0;
+    int64_t hmin = INT64_MAX, hmax = 0;
+    for (auto &en : P.ent) nf += en.first, hmin = std::min(hmin, en.habs), hmax = std::max(hmax, en.habs);
+    if (P.ent.empty()) hmin = 0;
+    span_bad = span_bad || (hmax - hmin > 4294967295LL);
+    const BlobLayout L((int)P.ent.size(), nf, (int)P.ops.size());
     PatchDesc d;
     std::memset(&d, 0, sizeof(d));
     for (int w = 0; w <= PK_MAXW; w++) d.sub_ptr[w] = (int)e_off[q] + P.sub_ptr[w];
-    d.row_begin = (int)r_off[q];
-    d.n_rows = (int)P.rows.size();
-    d.src_base = (int)s_off[q];
     d.n_sub = P.n_sub;
+    d.n_ent = (int)P.ent.size();
+    d.n_first = nf;
+    d.n_merge = (int)P.ops.size();
+    d.blob_off = (uint32_t)(b_off[q] / 16);
+    d.hbase = hmin;
     R.desc[q] = d;
     std::copy(P.elems.begin(), P.elems.end(), R.elems.begin() + e_off[q]);
-    for (size_t k = 0; k < P.rows.size(); k++) {
-      PRow r = P.rows[k];
-      r.ent_begin += (int)n_off[q];
-      R.rows[(size_t)r_off[q] + k] = r;
+    std::copy(P.nodes.begin(), P.nodes.end(), R.row_node.begin() + r_off[q]);
+    unsigned char *bl = R.blob.data() + b_off[q];
+    std::memcpy(bl, P.round_end, 32);
+    if (!P.ops.empty()) std::memcpy(bl + L.ops, P.ops.data(), P.ops.size() * sizeof(uint32_t));
+    PEnt *ent = reinterpret_cast<PEnt *>(bl + L.ent);
+    for (size_t k = 0; k < P.ent.size(); k++) {
+      const EntL &en = P.ent[k];
+      ent[k].hoff = (uint32_t)(en.habs - hmin);
+      ent[k].rowlen = (uint16_t)en.rowlen;
+      ent[k].src = en.src;
     }
-    std::copy(P.ent.begin(), P.ent.end(), R.ent.begin() + n_off[q]);
-    std::copy(P.src.begin(), P.src.end(), R.src.begin() + s_off[q]);
+    // the mass section is filled on the device from the assembled mass values
   }
+  if (span_bad) return failm(TLFEA_ERR_UNSUPPORTED, "patch plan: a patch spans more than 2^32 entries of H");
   return TLFEA_OK;
 }
 
@@ -391,24 +470,24 @@ int tlfea_debug_patch_plan_sizes(void *plan, int64_t *sizes) {
   sizes[0] = p->n_patches;
   sizes[1] = p->n_colors;
   sizes[2] = (int64_t)p->elems.size();
-  sizes[3] = (int64_t)p->rows.size();
-  sizes[4] = (int64_t)p->ent.size();
-  sizes[5] = (int64_t)p->src.size();
+  sizes[3] = (int64_t)p->row_node.size();
+  sizes[4] = (int64_t)p->blob.size();
+  sizes[5] = p->max_blob_bytes;
   sizes[6] = (int64_t)p->uncovered.size();
   sizes[7] = p->sum_local_blocks;
   return TLFEA_OK;
 }
 
-int tlfea_debug_patch_plan_copy(void *plan, int *color_ptr, void *desc, void *elems, void *rows, uint32_t *ent,
-                                uint16_t *src, int64_t *uncovered) {
+int tlfea_debug_patch_plan_copy(void *plan, int *color_ptr, void *desc, void *elems, int *row_node, int64_t *row_ptr,
+                                void *blob, int64_t *uncovered) {
   TL_CHECK(plan, "null input");
   auto *p = static_cast<tlfea::PatchPlanHost *>(plan);
   if (color_ptr) std::memcpy(color_ptr, p->color_ptr.data(), p->color_ptr.size() * sizeof(int));
   if (desc) std::memcpy(desc, p->desc.data(), p->desc.size() * sizeof(tlfea::PatchDesc));
   if (elems) std::memcpy(elems, p->elems.data(), p->elems.size() * sizeof(tlfea::PElem));
-  if (rows) std::memcpy(rows, p->rows.data(), p->rows.size() * sizeof(tlfea::PRow));
-  if (ent) std::memcpy(ent, p->ent.data(), p->ent.size() * sizeof(uint32_t));
-  if (src) std::memcpy(src, p->src.data(), p->src.size() * sizeof(uint16_t));
+  if (row_node) std::memcpy(row_node, p->row_node.data(), p->row_node.size() * sizeof(int));
+  if (row_ptr) std::memcpy(row_ptr, p->row_ptr.data(), p->row_ptr.size() * sizeof(int64_t));
+  if (blob) std::memcpy(blob, p->blob.data(), p->blob.size());
   if (uncovered) std::memcpy(uncovered, p->uncovered.data(), p->uncovered.size() * sizeof(int64_t));
   return TLFEA_OK;
 }

@@ -20,7 +20,7 @@ namespace tlfea {
 
 constexpr int PK_CAPU = 216;    // 3x3 blocks per warp accumulator (a Kuhn cell of 6 tets needs 210)
 constexpr int PK_MAXW = 8;      // sub-patches (= warps) per patch
-constexpr int PK_MAX_SLOT = 8191;
+constexpr int PK_MAX_ROWLEN = 65535;
 
 struct PElem {          // 128 bytes, one per element, in processing order
   int elem;             // element id in the caller's numbering (rows of gradN, detJ, fe)
@@ -33,30 +33,43 @@ struct PElem {          // 128 bytes, one per element, in processing order
 };
 static_assert(sizeof(PElem) == 128, "PElem is fetched as eight 16-byte pieces");
 
-struct PRow {           // 32 bytes, one per patch-local coefficient row
-  int64_t hbase;        // 9*off[i]: start of the row's three scalar CSR rows in H
-  int rowlen;           // 3*deg(i)
-  int mass_base;        // off[i]
-  int ent_begin;        // first entry of the row in ent[]
-  int n_ent;
-  int node;
-  int pad;
+// Everything the write-out of a patch reads sits in one contiguous, 16-byte aligned BLOB so that it arrives by a
+// single TMA bulk copy into scratch shared memory:
+//   round_end int[8] | merge ops uint32[n_merge] | entries PEnt[n_ent] | mass double[n_first]
+// (sections padded to 16 bytes).
+//   * merge op (dst | src << 16): accumulator block src is added to accumulator block dst.  A node pair that
+//     several warps of the patch hold is first reduced into the block of the lowest warp, one extra warp per
+//     ROUND (ops of round r: [round_end[r-1], round_end[r]); within a round every dst is distinct).
+//   * entry: one 3x3 block of H (both orientations of a pair are separate entries), ordered (first touch before
+//     later touch, then row, then column).  Entry k < n_first starts from M_ij/h (mass[k], refreshed on the
+//     device when the mass changes), the others from the value already in H.
+//   accumulator block address (16 bits): bits 0-7 block, 8-10 warp; entry src adds bit 11 = read transposed.
+struct PEnt {            // 8 bytes
+  uint32_t hoff;         // offset (doubles) of H(3i, 3j) from the patch's hbase: 9*off[i] + 3*slot - hbase
+  uint16_t rowlen;       // 3*deg(i): distance between the three scalar rows of the block row
+  uint16_t src;
 };
-static_assert(sizeof(PRow) == 32, "PRow layout");
+static_assert(sizeof(PEnt) == 8, "PEnt layout");
 
-struct PatchDesc {      // 64 bytes
+struct PatchDesc {       // 64 bytes
   int sub_ptr[PK_MAXW + 1];  // PElem range of sub-patch w: [sub_ptr[w], sub_ptr[w+1])
-  int row_begin, n_rows;     // PRow range
-  int src_base;              // the patch's sources start here in src[]
   int n_sub;
-  int pad[3];
+  int n_ent, n_first, n_merge;
+  uint32_t blob_off;         // in 16-byte units
+  int64_t hbase;
 };
 static_assert(sizeof(PatchDesc) == 64, "PatchDesc layout");
 
-// entry word: bits 0-12 slot of column j in row i, 13 first touch of this H block (start from M_ij/h instead of
-// the value in memory), 14-16 number of sources - 1, 17-31 offset of the first source relative to src_base
-// source word: bits 0-7 accumulator block, 8-10 warp, 11 read transposed (row id > column id)
-constexpr uint32_t PK_ENT_FIRST = 1u << 13;
+__host__ __device__ inline int pk_al16(int b) { return (b + 15) & ~15; }
+struct BlobLayout {
+  int ops, ent, mass, total;  // byte offsets; round_end sits at 0
+  __host__ __device__ BlobLayout(int n_ent, int n_first, int n_merge) {
+    ops = 32;
+    ent = ops + pk_al16(n_merge * 4);
+    mass = ent + pk_al16(n_ent * 8);
+    total = mass + pk_al16(n_first * 8);
+  }
+};
 
 struct PatchPlanHost {
   int W = 0;
@@ -64,9 +77,10 @@ struct PatchPlanHost {
   std::vector<int> color_ptr;  // launch c runs patches [color_ptr[c], color_ptr[c+1])
   std::vector<PatchDesc> desc;
   std::vector<PElem> elems;
-  std::vector<PRow> rows;
-  std::vector<uint32_t> ent;
-  std::vector<uint16_t> src;
+  std::vector<unsigned char> blob;  // all patches, each 16-byte aligned
+  std::vector<int> row_node;        // host only: coefficient ids of every patch, patch by patch (tests)
+  std::vector<int64_t> row_ptr;     // host only: patch q's ids are row_node[row_ptr[q] .. row_ptr[q+1])
+  int max_blob_bytes = 0;
   std::vector<int64_t> uncovered;  // pattern blocks that no element touches (constraint couplings, unused nodes)
   int64_t sum_local_blocks = 0;    // sum over patches of their distinct node pairs (in-place update traffic)
 };

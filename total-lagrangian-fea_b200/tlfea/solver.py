@@ -166,6 +166,17 @@ class SyncedNewtonSolver(SolverBase):
         """1 = element kernel + row reduce (default where supported: FEAT10 + SVK), 0 = generic warp-per-row gather."""
         check(lib.tlfea_newton_set_assembly(self._h, int(mode)))
 
+    def SetPatchWarps(self, warps: int):
+        check(lib.tlfea_newton_set_patch_warps(self._h, int(warps)))
+
+    def PatchStats(self):
+        import numpy as np
+
+        out = np.zeros(8, dtype=np.int64)
+        check(lib.tlfea_newton_patch_stats(self._h, out.ctypes.data_as(C.POINTER(C.c_int64))))
+        return dict(patches=int(out[0]), colours=int(out[1]), warps=int(out[2]), local_blocks=int(out[3]),
+                    list_bytes=int(out[4]), uncovered=int(out[5]))
+
     def SpMV(self, d_x: int, d_y: int):
         """y = H x on the device with the assembled values; d_x, d_y are device pointers to 3*n_coef doubles."""
         check(lib.tlfea_newton_spmv(self._h, C.c_void_p(int(d_x)), C.c_void_p(int(d_y))))
