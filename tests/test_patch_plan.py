@@ -9,7 +9,7 @@ import pytest
 from conftest import rel_err
 
 PELEM = np.dtype([("elem", "<i4"), ("pad0", "<i4"), ("node", "<i4", (10,)), ("blk4", "<u4", (15,)),
-                  ("tr", "<u4", (2,)), ("pad1", "<i4", (3,))])
+                  ("tr", "<u4", (2,)), ("first", "<u4", (2,)), ("pad1", "<i4")])
 PENT = np.dtype([("hoff", "<u4"), ("rowlen", "<u2"), ("src", "<u2")])
 PDESC = np.dtype([("sub_ptr", "<i4", (9,)), ("n_sub", "<i4"), ("n_ent", "<i4"), ("n_first", "<i4"), ("n_merge", "<i4"),
                   ("blob_off", "<u4"), ("hbase", "<i8")])
@@ -67,7 +67,7 @@ def replay(plan, Ke, mass_of_hpos, h, nnz):
     for c in range(len(cp) - 1):
         for p in range(cp[c], cp[c + 1]):
             d = desc[p]
-            acc = np.zeros((8, CAPU, 3, 3))
+            acc = np.full((8, CAPU, 3, 3), np.nan)  # never zero-filled: the first touch of a block stores
             for w in range(d["n_sub"]):
                 for k in range(d["sub_ptr"][w], d["sub_ptr"][w + 1]):
                     pe = el[k]
@@ -84,7 +84,9 @@ def replay(plan, Ke, mass_of_hpos, h, nnz):
                                 tr = (int(pe["tr"][bit >> 5]) >> (bit & 31)) & 1
                                 blk = K[3 * a:3 * a + 3, 3 * b:3 * b + 3]
                                 assert u < CAPU
-                                acc[w, u] += blk.T if tr else blk
+                                fs = (int(pe["first"][bit >> 5]) >> (bit & 31)) & 1
+                                assert fs == int(np.isnan(acc[w, u]).all())
+                                acc[w, u] = (0.0 if fs else acc[w, u]) + (blk.T if tr else blk)
             round_end, ops, ent = patch_sections(plan, d)
             lo = 0
             for r in range(7):

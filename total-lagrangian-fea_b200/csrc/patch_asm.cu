@@ -37,6 +37,22 @@ void patch_release(tlfea_newton *s) {
   s->patch = nullptr;
 }
 
+static int sm_count(int device) {
+  static thread_local int dev = -1, n = 148;
+  if (dev != device) {
+    cudaDeviceProp pr;
+    if (cudaGetDeviceProperties(&pr, device) == cudaSuccess) n = pr.multiProcessorCount;
+    dev = device;
+  }
+  return n;
+}
+
+// bytes of write-out lists a patch may have: the scratch area of the kernel configuration that will run it
+static int blob_limit(int W, int model) {
+  if (model == TL_MODEL_MR) return std::min(PKShape<false, TL_MODEL_MR>::scratch_bytes(W), PKShape<true, TL_MODEL_MR>::scratch_bytes(W));
+  return std::min(PKShape<false, TL_MODEL_SVK>::scratch_bytes(W), PKShape<true, TL_MODEL_SVK>::scratch_bytes(W));
+}
+
 int patch_warps() {
   static int w = [] {
     const char *e = getenv("TLFEA_PK_W");  // warps (= sub-patches) per patch: 4 (two CTAs per SM) or 8
@@ -64,7 +80,7 @@ int patch_prepare(tlfea_newton *s) {
   PatchPlanHost hp;
   std::string err;
   const int rc = build_patch_plan(e->n_elem, e->n_coef, ecoef.data(), x.data(), y.data(), z.data(), off.data(),
-                                  cols.data(), W, &hp, &err);
+                                  cols.data(), W, blob_limit(W, e->model), &hp, &err);
   if (rc != TLFEA_OK) return fail(rc, "%s", err.c_str());
   auto *pp = new PatchPlanDev();
   s->patch = pp;
@@ -99,8 +115,8 @@ static int launch_pk_t(tlfea_elem *e, const PatchPlanDev *pp, PKArgs a, int p0, 
   using Sh = PKShape<DAMP, MODEL>;
   constexpr size_t smem = Sh::smem_bytes(W);
   static_assert(smem <= 227 * 1024, "patch kernel configuration exceeds the shared memory of one SM");
-  TL_CHECK(pp->max_blob <= Sh::stage_bytes(W), "patch write-out lists (%d bytes) exceed the staging area (%d bytes)",
-           pp->max_blob, Sh::stage_bytes(W));
+  TL_CHECK(pp->max_blob <= Sh::scratch_bytes(W), "patch write-out lists (%d bytes) exceed the scratch area (%d bytes)",
+           pp->max_blob, Sh::scratch_bytes(W));
   static thread_local int attr_dev = -1;
   if (attr_dev != e->device) {
     TL_CUDA(cudaFuncSetAttribute(pk_kernel<W, DAMP, TANGENT, MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -109,7 +125,11 @@ static int launch_pk_t(tlfea_elem *e, const PatchPlanDev *pp, PKArgs a, int p0, 
   }
   if (np <= 0) return TLFEA_OK;
   a.desc = pp->d_desc + p0;
-  TL_LAUNCH((pk_kernel<W, DAMP, TANGENT, MODEL>), np, W * 32, smem, e->stream, a);
+  a.n_patches = np;
+  // persistent CTAs, as many as fit the SMs at once: each walks its patches with the prefetch stream running
+  const int per_sm = std::max(1, std::min((int)((228 * 1024) / (smem + 1024)), 2048 / (W * 32)));
+  const int grid = std::min(np, per_sm * sm_count(e->device));
+  TL_LAUNCH((pk_kernel<W, DAMP, TANGENT, MODEL>), grid, W * 32, smem, e->stream, a);
   return TLFEA_OK;
 }
 
@@ -160,6 +180,10 @@ int patch_assemble(tlfea_newton *s, bool tangent, bool damp) {
   a.mu01 = e->mu01;
   a.kappa = e->kappa;
   a.inv_h = tangent ? 1.0 / h : 0.0;
+  {
+    static const int dbg = [] { const char *v = getenv("TLFEA_PK_DEBUG"); return v ? atoi(v) : 0; }();
+    a.debug = dbg;
+  }
   a.fe = e->d_fe;
   a.H = s->d_H;
   if (!tangent) {  // no shared output: every patch in one launch

@@ -97,7 +97,7 @@ void assign_slots(int nb, const std::vector<std::vector<int>> &sets, std::vector
 }  // namespace
 
 int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y, const double *z,
-                     const int *off, const int *cols, int W, PatchPlanHost *out, std::string *err) {
+                     const int *off, const int *cols, int W, int blob_limit, PatchPlanHost *out, std::string *err) {
   auto failm = [&](int code, const char *m) {
     if (err) *err = m;
     return code;
@@ -202,8 +202,9 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
     subs.push_back(sp);
 
     auto &plist = per_oct[o];
-    for (size_t s0 = 0; s0 < subs.size(); s0 += W) {
-      const int ns = (int)std::min<size_t>(W, subs.size() - s0);
+    for (size_t s0 = 0; s0 < subs.size();) {
+      int ns = (int)std::min<size_t>(W, subs.size() - s0);
+    retry_smaller:
       PatchLocal P;
       P.n_sub = ns;
       struct Tup {
@@ -244,6 +245,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
         }
         std::vector<int> slot;
         assign_slots((int)blocks.size(), sets, slot);
+        std::vector<char> touched(blocks.size(), 0);
         for (int i = S.begin; i < S.end; i++) {
           const int e = order[i].second;
           const int *ec = ecoef + (size_t)e * 10;
@@ -259,8 +261,10 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
               const int a = 2 * I + (tt >> 1), b = 2 * J + (tt & 1), bit = t * 4 + tt;
               uint32_t u = 255;
               if (!(I == J && tt == 2)) {
-                u = (uint32_t)slot[(size_t)bidx[(size_t)(i - S.begin) * 60 + t * 4 + tt]];
+                const int bi = bidx[(size_t)(i - S.begin) * 60 + t * 4 + tt];
+                u = (uint32_t)slot[(size_t)bi];
                 if (ec[a] > ec[b]) pe.tr[bit >> 5] |= 1u << (bit & 31);
+                if (!touched[(size_t)bi]) touched[(size_t)bi] = 1, pe.first[bit >> 5] |= 1u << (bit & 31);
               }
               word |= u << (8 * tt);
             }
@@ -305,8 +309,17 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
       std::sort(P.ent.begin(), P.ent.end(), [](const EntL &a, const EntL &b) { return a.habs < b.habs; });
       std::sort(P.nodes.begin(), P.nodes.end());
       P.nodes.erase(std::unique(P.nodes.begin(), P.nodes.end()), P.nodes.end());
+      // the write-out lists must fit the kernel's scratch area (bound: every entry a first touch)
+      if (BlobLayout((int)P.ent.size(), (int)P.ent.size(), (int)P.ops.size()).total > blob_limit) {
+        if (ns > 1) {
+          ns--;
+          goto retry_smaller;
+        }
+        P.bad = true;
+      }
       any_bad = any_bad || P.bad;
       plist.push_back(std::move(P));
+      s0 += ns;
     }
   }
   if (any_bad)
@@ -455,7 +468,7 @@ int tlfea_debug_patch_plan_build(int n_elem, int n_coef, const int *ecoef, const
   TL_CHECK(ecoef && x && y && z && off && cols && plan_out, "null input");
   auto *p = new tlfea::PatchPlanHost();
   std::string err;
-  const int rc = tlfea::build_patch_plan(n_elem, n_coef, ecoef, x, y, z, off, cols, W, p, &err);
+  const int rc = tlfea::build_patch_plan(n_elem, n_coef, ecoef, x, y, z, off, cols, W, 1 << 20, p, &err);
   if (rc != TLFEA_OK) {
     delete p;
     return tlfea::fail(rc, "%s", err.c_str());

@@ -29,7 +29,8 @@ struct PElem {          // 128 bytes, one per element, in processing order
   uint32_t blk4[15];    // per 2x2 tile of shape-function pairs (ek_kernel.cuh order): accumulator block of
                         // (a1+ta, b1+tb) in byte ta*2+tb; 255 = the redundant lower block of a diagonal tile
   uint32_t tr[2];       // bit tile*4+ta*2+tb: node[a] > node[b], the block is added transposed
-  int pad1[3];
+  uint32_t first[2];    // same bit order: this element is the first of its sub-patch to touch the block (store, no add)
+  int pad1;
 };
 static_assert(sizeof(PElem) == 128, "PElem is fetched as eight 16-byte pieces");
 
@@ -86,8 +87,9 @@ struct PatchPlanHost {
 };
 
 // Pure host code (no CUDA call): ecoef [n_elem][10]; x, y, z reference coordinates per coefficient; off / cols the
-// coefficient-level CSR pattern (sorted columns).  Returns 0 or a negative tlfea_status with *err set.
+// coefficient-level CSR pattern (sorted columns); blob_limit = largest write-out blob (bytes) a patch may have.
+// Returns 0 or a negative tlfea_status with *err set.
 int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y, const double *z,
-                     const int *off, const int *cols, int W, PatchPlanHost *out, std::string *err);
+                     const int *off, const int *cols, int W, int blob_limit, PatchPlanHost *out, std::string *err);
 
 }  // namespace tlfea

@@ -33,6 +33,8 @@ namespace tlfea {
 
 struct PKArgs {
   const PatchDesc *desc;  // first patch of this launch
+  int n_patches;          // patches of this launch; CTA b takes b, b + gridDim.x, ...
+  int debug;              // tuning aid (TLFEA_PK_DEBUG): 1 no write-out, 2 no accumulation, 4 no block step, 8 no Gauss-point step
   const PElem *elems;
   const unsigned char *blob;
   const double *x, *y, *z;
@@ -47,6 +49,8 @@ struct PKArgs {
   double *H;
 };
 
+// Shared memory of a CTA: [accumulators x W][prefetch buffers x W][scratch x W].  The scratch areas (Gauss-point
+// results of the pair in flight) are contiguous over the warps: the write-out lists of the patch land there.
 template <bool DAMP, int MODEL>
 struct PKShape {
   static constexpr bool MR = (MODEL == TL_MODEL_MR);
@@ -63,19 +67,20 @@ struct PKShape {
   static constexpr int OFF_X = OFF_DJ + 2 * DJ_D;
   static constexpr int OFF_V = OFF_X + 2 * X_D;
   static constexpr int OFF_PE = OFF_V + (DAMP ? 2 * X_D : 0);
-  static constexpr int OFF_U = OFF_PE + 2 * PE_D;
+  static constexpr int PREF_D = OFF_PE + 2 * PE_D;  // prefetch doubles per warp (even)
+  static constexpr int OFF_U = 0;
   static constexpr int OFF_REC = OFF_U + (U_D + 1) / 2 * 2;
   static constexpr int OFF_FP = OFF_REC + (REC_D + 1) / 2 * 2;
-  static constexpr int STG_D = OFF_FP + (FP_D + 1) / 2 * 2;  // staging doubles per warp (even)
-  static constexpr size_t smem_bytes(int warps) { return (size_t)warps * (ACC_D + STG_D) * sizeof(double); }
-  static constexpr int stage_bytes(int warps) { return warps * STG_D * (int)sizeof(double); }
+  static constexpr int SCR_D = OFF_FP + (FP_D + 1) / 2 * 2;  // scratch doubles per warp (even)
+  static constexpr size_t smem_bytes(int warps) { return (size_t)warps * (ACC_D + PREF_D + SCR_D) * sizeof(double); }
+  static constexpr int scratch_bytes(int warps) { return warps * SCR_D * (int)sizeof(double); }
 };
 
 __device__ __forceinline__ void bulk_prefetch_l2(const void *gmem, unsigned bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;\n" ::"l"(gmem), "r"(bytes) : "memory");
 }
 
-constexpr int PK_NB = 10;  // later-touch positions a thread keeps in flight
+constexpr int PK_NB = 10;  // later-touch (entry, column) positions a thread keeps in flight
 
 template <int W, bool DAMP, bool TANGENT, int MODEL>
 __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) {
@@ -85,41 +90,39 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   extern __shared__ __align__(16) double pk_smem[];
   __shared__ uint64_t s_bar[W][2];
   __shared__ uint64_t s_bar_blob;
-  __shared__ PatchDesc s_desc;
+  __shared__ PatchDesc s_desc[2];  // this CTA's current and next patch
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *acc = pk_smem + (size_t)warp * Sh::ACC_D;
-  double *stage0 = pk_smem + (size_t)W * Sh::ACC_D;
-  double *wb = stage0 + (size_t)warp * Sh::STG_D;
-  double *s_u = wb + Sh::OFF_U, *s_rec = wb + Sh::OFF_REC, *s_fp = wb + Sh::OFF_FP;
+  double *wb = pk_smem + (size_t)W * Sh::ACC_D + (size_t)warp * Sh::PREF_D;  // prefetch buffers of this warp
+  double *scr0 = pk_smem + (size_t)W * (Sh::ACC_D + Sh::PREF_D);
+  double *ws = scr0 + (size_t)warp * Sh::SCR_D;
+  double *s_u = ws + Sh::OFF_U, *s_rec = ws + Sh::OFF_REC, *s_fp = ws + Sh::OFF_FP;
 
-  if (threadIdx.x < 16)
-    reinterpret_cast<int *>(&s_desc)[threadIdx.x] = reinterpret_cast<const int *>(p.desc + blockIdx.x)[threadIdx.x];
+  auto load_desc = [&](int pk, int slot) {  // threads 0..15
+    if (pk < p.n_patches)
+      reinterpret_cast<int *>(&s_desc[slot])[threadIdx.x] = reinterpret_cast<const int *>(p.desc + pk)[threadIdx.x];
+  };
+  if (threadIdx.x < 16) {
+    load_desc(blockIdx.x, 0);
+    load_desc(blockIdx.x + gridDim.x, 1);
+  }
   if (lane == 0) {
     mbar_init(&s_bar[warp][0], 1);
     mbar_init(&s_bar[warp][1], 1);
   }
   if (threadIdx.x == 0) mbar_init(&s_bar_blob, 1);
-  if (TANGENT)
-    for (int i = lane; i < Sh::ACC_D; i += 32) acc[i] = 0.0;
   __syncthreads();
   if (TANGENT && threadIdx.x == 0)  // the write-out lists are needed last: pull them into L2 now
-    bulk_prefetch_l2(p.blob + (size_t)s_desc.blob_off * 16,
-                     (unsigned)BlobLayout(s_desc.n_ent, s_desc.n_first, s_desc.n_merge).total);
+    bulk_prefetch_l2(p.blob + (size_t)s_desc[0].blob_off * 16,
+                     (unsigned)BlobLayout(s_desc[0].n_ent, s_desc[0].n_first, s_desc[0].n_merge).total);
 
-  const int k0 = s_desc.sub_ptr[warp], k1 = s_desc.sub_ptr[warp + 1];
-  const int n_it = (k1 - k0 + 1) >> 1;
-
-  // ---- prefetch helpers (per warp)
-  auto issue_pe = [&](int it, int buf) {
-    if (it >= n_it) return;
-    const int kk = k0 + 2 * it, ne = min(2, k1 - kk);
+  // ---- prefetch helpers (per warp): plan records / data of the element pair [kk, kk + ne)
+  auto issue_pe = [&](int kk, int ne, int buf) {
     double *dst = wb + Sh::OFF_PE + buf * Sh::PE_D;
     const char *src = reinterpret_cast<const char *>(p.elems + kk);
     if (lane < ne * 8) cp_async16(reinterpret_cast<char *>(dst) + lane * 16, src + lane * 16);
   };
-  auto issue_data = [&](int it, int buf) {
-    if (it >= n_it) return;
-    const int kk = k0 + 2 * it, ne = min(2, k1 - kk);
+  auto issue_data = [&](int ne, int buf) {
     const PElem *pe = reinterpret_cast<const PElem *>(wb + Sh::OFF_PE + buf * Sh::PE_D);
     double *dh = wb + Sh::OFF_H + buf * Sh::H_D;
     if (lane == 0) {
@@ -173,37 +176,90 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   }
   const int a1 = 2 * tI, b1 = 2 * tJ;
 
-  if (n_it > 0) {
-    issue_pe(0, 0);
-    cp_async_commit();
-    cp_async_wait_all();
-    __syncwarp();
-    issue_pe(1, 1);
-    issue_data(0, 0);
-    cp_async_commit();
-  }
+  // The warp's element pairs form ONE stream over all patches of this CTA: while pair j computes, the data of
+  // pair j+1 and the plan records of pair j+2 are in flight, across patch boundaries (the next patch's descriptor is
+  // already in shared memory).  gi counts the pairs: buffer gi & 1, mbarrier phase (gi >> 1) & 1.
+  int gi = 0;
+  int pe_kk0 = -1, pe_kk1 = -1;  // first plan record held (or in flight) in each record buffer
+  int dt_kk0 = -1, dt_kk1 = -1;  // ... whose data has been requested into each data buffer
+  auto pe_get = [&](int b) { return b ? pe_kk1 : pe_kk0; };
+  auto dt_get = [&](int b) { return b ? dt_kk1 : dt_kk0; };
+  auto pe_set = [&](int b, int v) { if (b) pe_kk1 = v; else pe_kk0 = v; };
+  auto dt_set = [&](int b, int v) { if (b) dt_kk1 = v; else dt_kk0 = v; };
+  int n_done = 0;           // patches this CTA has finished (blob barrier phase)
+  for (int pk = blockIdx.x; pk < p.n_patches; pk += gridDim.x, n_done++) {
+    const PatchDesc &dc = s_desc[n_done & 1], &dn = s_desc[(n_done + 1) & 1];
+    const bool has_next = pk + (int)gridDim.x < p.n_patches;
+    const int k0 = dc.sub_ptr[warp], k1 = dc.sub_ptr[warp + 1];
+    const int n_it = (k1 - k0 + 1) >> 1;
+    const int k0n = has_next ? dn.sub_ptr[warp] : 0, k1n = has_next ? dn.sub_ptr[warp + 1] : 0;
+    const int n_itn = (k1n - k0n + 1) >> 1;
+    // the j-th pair after pair `it` of this patch (possibly in the next patch); false = none known yet
+    auto nth = [&](int it, int j, int &kk, int &ne) {
+      if (it + j < n_it) {
+        kk = k0 + 2 * (it + j);
+        ne = min(2, k1 - kk);
+        return true;
+      }
+      const int jj = it + j - n_it;
+      if (jj < n_itn) {
+        kk = k0n + 2 * jj;
+        ne = min(2, k1n - kk);
+        return true;
+      }
+      return false;
+    };
 
-  for (int it = 0; it < n_it; it++) {
-    const int buf = it & 1;
-    cp_async_wait_all();
-    mbar_wait(&s_bar[warp][buf], (it >> 1) & 1);
-    __syncwarp();
+  for (int it = 0; it < n_it; it++, gi++) {
+    const int buf = gi & 1;
     const int kk = k0 + 2 * it, ne = min(2, k1 - kk);
+    if (dt_get(buf) != kk) {  // cold start: nothing was requested ahead for this pair
+      if (pe_get(buf) != kk) {
+        issue_pe(kk, ne, buf);
+        pe_set(buf, kk);
+      }
+      cp_async_commit();
+      cp_async_wait_all();
+      __syncwarp();
+      issue_data(ne, buf);
+      dt_set(buf, kk);
+      cp_async_commit();
+    }
+    cp_async_wait_all();
+    mbar_wait(&s_bar[warp][buf], (gi >> 1) & 1);
+    __syncwarp();
     // what this lane needs of the plan records, before the buffer is recycled
-    unsigned blkw = 0, trb = 0;
+    unsigned blkw = 0, trb = 0, fsb = 0;
     int eid[2];
     {
       const PElem *pe = reinterpret_cast<const PElem *>(wb + Sh::OFF_PE + buf * Sh::PE_D);
       const int el = min(el2, ne - 1);
       blkw = pe[el].blk4[tile];
       trb = (pe[el].tr[(tile * 4) >> 5] >> ((tile * 4) & 31)) & 15u;
+      fsb = (pe[el].first[(tile * 4) >> 5] >> ((tile * 4) & 31)) & 15u;
       eid[0] = pe[0].elem;
       eid[1] = pe[ne - 1].elem;
     }
     __syncwarp();
-    issue_data(it + 1, buf ^ 1);  // its plan records landed with the wait above
-    issue_pe(it + 2, buf);
-    cp_async_commit();
+    {
+      int kq, nq;
+      if (nth(it, 1, kq, nq)) {  // data of the next pair: its plan records landed with the wait above
+        if (pe_get(buf ^ 1) != kq) {  // (not requested ahead: the pair before was the cold start)
+          issue_pe(kq, nq, buf ^ 1);
+          pe_set(buf ^ 1, kq);
+          cp_async_commit();
+          cp_async_wait_all();
+          __syncwarp();
+        }
+        issue_data(nq, buf ^ 1);
+        dt_set(buf ^ 1, kq);
+      }
+      if (nth(it, 2, kq, nq)) {
+        issue_pe(kq, nq, buf);
+        pe_set(buf, kq);
+      }
+      cp_async_commit();
+    }
 
     const double *s_h = wb + Sh::OFF_H + buf * Sh::H_D;
     const double *s_dj = wb + Sh::OFF_DJ + buf * Sh::DJ_D;
@@ -315,33 +371,34 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       }
     }
     // ------------------------------------------------------------ Gauss-point step, SVK
-    if (!MR && lane < ne * 5) {
-      const int el = lane / 5, q = lane - el * 5;
-      const int rot = lane >> 3;
+    // lane = (element, point, row i): the three lanes of a point build the same F (broadcast loads), then each
+    // finishes row i of P dV, of the force partials P dV h_a and of u_a = F h_a; row 0 also leaves
+    // M_q = dV [ (h mu + eta) F F^T + h (lambda trE - mu) I ] and dV for the block step.
+    if (!MR && lane < ne * 15 && !(p.debug & 8)) {
+      const int idx = lane / 3, part = lane - 3 * idx;
+      const int el = idx / 5, q = idx - el * 5;
       const double *hq = s_h + el * 150 + q * 30;
       const double *xe = s_x + el * 30;
       double F[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
       double Fd[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
 #pragma unroll
       for (int aa = 0; aa < 10; aa++) {
-        int ar = aa + rot;
-        if (ar >= 10) ar -= 10;
-        const double xa[3] = {xe[ar * 3], xe[ar * 3 + 1], xe[ar * 3 + 2]};
-        const double ha[3] = {hq[ar], hq[10 + ar], hq[20 + ar]};
+        const double xa[3] = {xe[aa * 3], xe[aa * 3 + 1], xe[aa * 3 + 2]};
+        const double ha[3] = {hq[aa], hq[10 + aa], hq[20 + aa]};
 #pragma unroll
         for (int i = 0; i < 3; i++)
 #pragma unroll
           for (int j = 0; j < 3; j++) F[i][j] += xa[i] * ha[j];
         if (DAMP) {
           const double *ve = wb + Sh::OFF_V + buf * Sh::X_D + el * 30;
-          const double va[3] = {ve[ar * 3], ve[ar * 3 + 1], ve[ar * 3 + 2]};
+          const double va[3] = {ve[aa * 3], ve[aa * 3 + 1], ve[aa * 3 + 2]};
 #pragma unroll
           for (int i = 0; i < 3; i++)
 #pragma unroll
             for (int j = 0; j < 3; j++) Fd[i][j] += va[i] * ha[j];
         }
       }
-      const double dV = s_dj[lane] * p.qw.w[q];
+      const double dV = s_dj[idx] * p.qw.w[q];
       double FFT[3][3], trFtF = 0.0;
 #pragma unroll
       for (int i = 0; i < 3; i++)
@@ -352,15 +409,19 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
         }
       const double trE = 0.5 * (trFtF - 3.0);
       const double lf = p.lambda * (0.5 * trFtF - 1.5);
-      double P[3][3];
+      double Fi[3], FFTi[3], Pi[3];
 #pragma unroll
-      for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++) {
+        Fi[j] = part == 0 ? F[0][j] : (part == 1 ? F[1][j] : F[2][j]);
+        FFTi[j] = part == 0 ? FFT[0][j] : (part == 1 ? FFT[1][j] : FFT[2][j]);
+      }
 #pragma unroll
-        for (int j = 0; j < 3; j++) {
-          const double FFtF = FFT[i][0] * F[0][j] + FFT[i][1] * F[1][j] + FFT[i][2] * F[2][j];
-          P[i][j] = lf * F[i][j] + p.mu * (FFtF - F[i][j]);
-        }
+      for (int j = 0; j < 3; j++) {
+        const double FFtF = FFTi[0] * F[0][j] + FFTi[1] * F[1][j] + FFTi[2] * F[2][j];
+        Pi[j] = lf * Fi[j] + p.mu * (FFtF - Fi[j]);
+      }
       if (DAMP) {
+        // P_vis = F (2 eta Edot + lambda_d tr(Edot) I), Edot = sym(Fdot^T F)   FEAT10DataFunc.cuh:139-223
         double Ed[3][3];
 #pragma unroll
         for (int i = 0; i < 3; i++)
@@ -376,35 +437,25 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
           }
         const double trEd = Ed[0][0] + Ed[1][1] + Ed[2][2];
 #pragma unroll
-        for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) {
+          double sv = 0.0;
 #pragma unroll
-          for (int j = 0; j < 3; j++) {
-            double sv = 0.0;
-#pragma unroll
-            for (int k = 0; k < 3; k++)
-              sv += F[i][k] * (2.0 * p.eta * Ed[k][j] + ((k == j) ? p.lambda_d * trEd : 0.0));
-            P[i][j] += sv;
-          }
-      }
-#pragma unroll
-      for (int i = 0; i < 3; i++)
-#pragma unroll
-        for (int j = 0; j < 3; j++) P[i][j] *= dV;
-      double *fpq = s_fp + lane * EK_GQ;
-      double *uq = s_u + lane * EK_GQ;
-#pragma unroll
-      for (int aa = 0; aa < 10; aa++) {
-        int ar = aa + rot;
-        if (ar >= 10) ar -= 10;
-        const double ha[3] = {hq[ar], hq[10 + ar], hq[20 + ar]};
-#pragma unroll
-        for (int i = 0; i < 3; i++) {
-          fpq[ar * 3 + i] = P[i][0] * ha[0] + P[i][1] * ha[1] + P[i][2] * ha[2];
-          if (TANGENT) uq[i * 10 + ar] = F[i][0] * ha[0] + F[i][1] * ha[1] + F[i][2] * ha[2];
+          for (int k = 0; k < 3; k++) sv += Fi[k] * (2.0 * p.eta * Ed[k][j] + ((k == j) ? p.lambda_d * trEd : 0.0));
+          Pi[j] += sv;
         }
       }
-      if (TANGENT) {
-        double *r = s_rec + lane * EK_REC;
+#pragma unroll
+      for (int j = 0; j < 3; j++) Pi[j] *= dV;
+      double *fpq = s_fp + idx * EK_GQ;
+      double *uq = s_u + idx * EK_GQ;
+#pragma unroll
+      for (int aa = 0; aa < 10; aa++) {
+        const double ha[3] = {hq[aa], hq[10 + aa], hq[20 + aa]};
+        fpq[aa * 3 + part] = Pi[0] * ha[0] + Pi[1] * ha[1] + Pi[2] * ha[2];
+        if (TANGENT) uq[part * 10 + aa] = Fi[0] * ha[0] + Fi[1] * ha[1] + Fi[2] * ha[2];
+      }
+      if (TANGENT && part == 0) {
+        double *r = s_rec + idx * EK_REC;
         const double sI = p.c4 * dV * (p.lambda * trE - p.mu);
         const double cf = p.c3 * dV;
         r[0] = cf * FFT[0][0] + sI;
@@ -427,7 +478,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     }
 
     // ------------------------------------------------------------ block step
-    if (TANGENT) {
+    if (TANGENT && !(p.debug & 4)) {
       const int el = min(el2, ne - 1);  // odd tail: the second half shadows the first and never adds
       const bool on = lane_on && (el2 < ne);
       const double *he = s_h + el * 150;
@@ -528,14 +579,29 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       // the plan arranges (assign_slots, patch_plan.cu).
 #pragma unroll 1
       for (int e = 0; e < 2; e++) {
-        if (on && el2 == e) {
+        if (on && el2 == e && !(p.debug & 2)) {
+          // the blocks of one element are distinct: load two blocks' old values, then add and store (the compiler
+          // cannot know the four pointers differ and would serialise load -> store -> load otherwise)
 #pragma unroll
-          for (int t = 0; t < 4; t++) {
-            if (t == 2 && tI == tJ) continue;  // (a1+1, a1) = transpose of (a1, a1+1): the upper block carries it
-            double *d = acc + ((blkw >> (8 * t)) & 255u) * 9;
-            const bool tr = (trb >> t) & 1u;
+          for (int t0 = 0; t0 < 4; t0 += 2) {
+            double *d0 = acc + ((blkw >> (8 * t0)) & 255u) * 9;
+            double *d1 = acc + ((blkw >> (8 * (t0 + 1))) & 255u) * 9;
+            const bool tr0 = (trb >> t0) & 1u, tr1 = (trb >> (t0 + 1)) & 1u;
+            // t0 = 2: (a1+1, a1) is the transpose of (a1, a1+1) on diagonal tiles -- the upper block carries it
+            const bool skip0 = (t0 == 2) && (tI == tJ);
+            // the first element of the sub-patch to touch a block stores it (no zero-fill of the accumulator)
+            const bool f0 = (fsb >> t0) & 1u, f1 = (fsb >> (t0 + 1)) & 1u;
+            double o0[9], o1[9];
 #pragma unroll
-            for (int m = 0; m < 9; m++) d[m] += tr ? A[t][(m % 3) * 3 + m / 3] : A[t][m];
+            for (int m = 0; m < 9; m++) o0[m] = (skip0 || f0) ? 0.0 : d0[m];
+#pragma unroll
+            for (int m = 0; m < 9; m++) o1[m] = f1 ? 0.0 : d1[m];
+            if (!skip0) {
+#pragma unroll
+              for (int m = 0; m < 9; m++) d0[m] = o0[m] + (tr0 ? A[t0][(m % 3) * 3 + m / 3] : A[t0][m]);
+            }
+#pragma unroll
+            for (int m = 0; m < 9; m++) d1[m] = o1[m] + (tr1 ? A[t0 + 1][(m % 3) * 3 + m / 3] : A[t0 + 1][m]);
           }
         }
         __syncwarp();
@@ -543,19 +609,23 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     }
     __syncwarp();
   }
-  cp_async_wait_all();
-  if (!TANGENT) return;
+  if (!TANGENT) {  // force only: no shared output, just keep the descriptor ring turning
+    __syncthreads();
+    if (threadIdx.x < 16) load_desc(pk + 2 * gridDim.x, n_done & 1);
+    __syncthreads();
+    continue;
+  }
 
   // ------------------------------------------------------------ write-out
-  __syncthreads();  // every accumulator is final and the staging area is dead
-  const int n_ent = s_desc.n_ent, n_first = s_desc.n_first, n_merge = s_desc.n_merge;
+  __syncthreads();  // every accumulator is final and the scratch areas are dead (prefetches live elsewhere)
+  const int n_ent = dc.n_ent, n_first = dc.n_first, n_merge = dc.n_merge;
   const BlobLayout L(n_ent, n_first, n_merge);
-  unsigned char *sb = reinterpret_cast<unsigned char *>(stage0);
+  unsigned char *sb = reinterpret_cast<unsigned char *>(scr0);
   if (threadIdx.x == 0) {
     asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
-    bulk_load(sb, p.blob + (size_t)s_desc.blob_off * 16, (unsigned)L.total, &s_bar_blob);
+    bulk_load(sb, p.blob + (size_t)dc.blob_off * 16, (unsigned)L.total, &s_bar_blob);
   }
-  mbar_wait(&s_bar_blob, 0);
+  mbar_wait(&s_bar_blob, n_done & 1);
   const int *round_end = reinterpret_cast<const int *>(sb);
   const uint32_t *ops = reinterpret_cast<const uint32_t *>(sb + L.ops);
   const uint2 *ent = reinterpret_cast<const uint2 *>(sb + L.ent);
@@ -567,65 +637,104 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     int lo = 0;
     for (int r = 0; r < 7 && lo < n_merge; r++) {
       const int hi = round_end[r];
-      for (int t = threadIdx.x; t < (hi - lo) * 9; t += NT) {
-        const int q = t / 9, i = t - 9 * q;
-        const uint32_t op = ops[lo + q];
-        blk_addr(op & 0xffffu)[i] += blk_addr(op >> 16)[i];
+      const int nw = (hi - lo) * 9;
+      for (int t = threadIdx.x; t < nw; t += 2 * NT) {
+        const int t2 = t + NT;
+        const int q = t / 9, i = t - 9 * q, q2 = t2 / 9, i2 = t2 - 9 * q2;
+        const uint32_t op = ops[lo + q], op2 = ops[lo + min(q2, hi - lo - 1)];
+        double *da = blk_addr(op & 0xffffu) + i, *db = blk_addr(op2 & 0xffffu) + i2;
+        const double a0 = *da, a1 = blk_addr(op >> 16)[i];
+        const double b0 = *db, b1 = blk_addr(op2 >> 16)[i2];
+        *da = a0 + a1;
+        if (t2 < nw) *db = b0 + b1;
       }
       __syncthreads();
       lo = hi;
     }
   }
 
-  double *Hb = p.H + s_desc.hbase;
-  const int pos_first = 3 * n_first, pos_all = 3 * n_ent;
-  for (int base = pos_first; base < pos_all || base == pos_first; base += NT * PK_NB) {
-    // later touches: issue the loads of the old values ...
+  double *Hb = p.H + ((p.debug & 16) ? (int64_t)(blockIdx.x & 255) * 65536 : dc.hbase);
+  const unsigned hmask = (p.debug & 16) ? 0x3fffu : 0xffffffffu;  // tuning aid: all traffic into a small window
+  // Thread = (entry, column e) of a 3x3 block of H, three rows d per thread: consecutive lanes store consecutive
+  // doubles of a scalar CSR row (an entry-per-thread mapping was measured: 2.3x the store sectors, 10 % slower).
+  // Threads stride over the entries by NT/3, so e and the entry phase are fixed per thread.
+  constexpr int KS = NT / 3;
+  const int we = (int)threadIdx.x % 3, wk = (int)threadIdx.x / 3;
+  const bool w_on = (int)threadIdx.x < 3 * KS;
+  auto block_col = [&](unsigned src, double v[3]) {  // column we of the entry's block, rows 0..2
+    const bool tr = src & 0x800u;
+    const double *bsrc = blk_addr(src) + (tr ? 3 * we : we);
+    const int st = tr ? 1 : 3;
+    v[0] = bsrc[0];
+    v[1] = bsrc[st];
+    v[2] = bsrc[2 * st];
+  };
+  // later touches: issue the loads of the old values (PK_NB entries per thread in flight) ...
+  for (int base = n_first; (base < n_ent || base == n_first) && !(p.debug & 1); base += KS * PK_NB) {
     double o[PK_NB][3];
 #pragma unroll
     for (int b = 0; b < PK_NB; b++) {
-      const int pos = base + b * NT + (int)threadIdx.x;
-      if (pos < pos_all) {
-        const int k = pos / 3, e = pos - 3 * k;
+      const int k = base + b * KS + wk;
+      if (w_on && k < n_ent) {
         const uint2 en = ent[k];
-        const double *hp = Hb + en.x + e;
+        const double *hp = Hb + (en.x & hmask) + we;
         const unsigned rl = en.y & 0xffffu;
         o[b][0] = hp[0];
         o[b][1] = hp[rl];
         o[b][2] = hp[2 * rl];
       }
     }
-    // ... first touches run underneath (only once)
-    if (base == pos_first) {
-      for (int pos = threadIdx.x; pos < pos_first; pos += NT) {
-        const int k = pos / 3, e = pos - 3 * k;
-        const uint2 en = ent[k];
-        double *hp = Hb + en.x + e;
-        const unsigned rl = en.y & 0xffffu, src = en.y >> 16;
-        const double *bsrc = blk_addr(src) + ((src & 0x800u) ? 3 * e : e);
-        const int st = (src & 0x800u) ? 1 : 3;
-        const double m = massb[k] * p.inv_h;
-        hp[0] = (e == 0 ? m : 0.0) + bsrc[0];
-        hp[rl] = (e == 1 ? m : 0.0) + bsrc[st];
-        hp[2 * rl] = (e == 2 ? m : 0.0) + bsrc[2 * st];
+    // ... first touches run underneath (only once): H block = (M_ij / h) I + sum
+    if (base == n_first && w_on) {
+      constexpr int FU = 4;  // entries per thread per trip: their shared-memory loads overlap
+      for (int k0f = wk; k0f < n_first; k0f += FU * KS) {
+        double *hp[FU];
+        unsigned rl[FU];
+        double v[FU][3];
+#pragma unroll
+        for (int u = 0; u < FU; u++) {
+          const int k = min(k0f + u * KS, n_first - 1);
+          const uint2 en = ent[k];
+          hp[u] = Hb + (en.x & hmask) + we;
+          rl[u] = en.y & 0xffffu;
+          block_col(en.y >> 16, v[u]);
+          const double m = massb[k] * p.inv_h;
+          if (we == 0) v[u][0] += m;
+          if (we == 1) v[u][1] += m;
+          if (we == 2) v[u][2] += m;
+        }
+#pragma unroll
+        for (int u = 0; u < FU; u++) {
+          if (k0f + u * KS < n_first) {
+            hp[u][0] = v[u][0];
+            hp[u][rl[u]] = v[u][1];
+            hp[u][2 * rl[u]] = v[u][2];
+          }
+        }
       }
     }
 #pragma unroll
     for (int b = 0; b < PK_NB; b++) {
-      const int pos = base + b * NT + (int)threadIdx.x;
-      if (pos < pos_all) {
-        const int k = pos / 3, e = pos - 3 * k;
+      const int k = base + b * KS + wk;
+      if (w_on && k < n_ent) {
         const uint2 en = ent[k];
-        double *hp = Hb + en.x + e;
-        const unsigned rl = en.y & 0xffffu, src = en.y >> 16;
-        const double *bsrc = blk_addr(src) + ((src & 0x800u) ? 3 * e : e);
-        const int st = (src & 0x800u) ? 1 : 3;
-        hp[0] = o[b][0] + bsrc[0];
-        hp[rl] = o[b][1] + bsrc[st];
-        hp[2 * rl] = o[b][2] + bsrc[2 * st];
+        double *hp = Hb + (en.x & hmask) + we;
+        const unsigned rl = en.y & 0xffffu;
+        double v[3];
+        block_col(en.y >> 16, v);
+        hp[0] = o[b][0] + v[0];
+        hp[rl] = o[b][1] + v[1];
+        hp[2 * rl] = o[b][2] + v[2];
       }
     }
   }
+  __syncthreads();  // nobody reads the accumulators, the lists or the current descriptor any more
+  if (threadIdx.x < 16) load_desc(pk + 2 * gridDim.x, n_done & 1);
+  if (has_next && threadIdx.x == 32 % NT)
+    bulk_prefetch_l2(p.blob + (size_t)dn.blob_off * 16, (unsigned)BlobLayout(dn.n_ent, dn.n_first, dn.n_merge).total);
+  __syncthreads();
+  }  // patches
+  cp_async_wait_all();
 }
 
 // mass section of every patch blob: mass[k] = M(row, column) of first-touch entry k.  The pattern block of an entry
