@@ -173,7 +173,15 @@ def cpu_sample(n_cpu: int, reps: int):
     """The CPU restatement of the reference algorithm on an n_cpu^3-cell block of the same mesh
     family: force + H, all host threads.  Returns (GP/s, threads, description, seconds)."""
     from oracle import oracle as orc
-    from tlfea import meshgen
+    import importlib.util
+
+    # the mesh generator is numpy-only: load it by path so this arm never imports the product package (and with it
+    # libtlfea_b200.so)
+    spec = importlib.util.spec_from_file_location("_tlfea_meshgen", os.path.join(PKG, "tlfea", "meshgen.py"))
+    meshgen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(meshgen)
+    # torchrun exports OMP_NUM_THREADS=1: the CPU arm uses every host core at every N
+    orc.set_num_threads(os.cpu_count() or 1)
 
     X, E = meshgen.kuhn_block(n_cpu)
     x = meshgen.perturb(X, 0.05 / n_cpu, 1234)
@@ -314,12 +322,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import __graft_entry__ as g
-
-    g.build()
+    # only the oracle is built and loaded in this arm: no product code on the path
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
     n_cpu = args.cpu_n
     # one "step" = one pass over the bounded sample
-    from oracle import oracle as orc  # noqa: F401
 
     gps, threads, desc, dt = cpu_sample(n_cpu, max(args.steps, 1))
     line = {
@@ -327,6 +333,8 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"feat10_kuhn_block_n{args.n}_svk_force_tangent_H", "sample": desc,
+                   "sample_workload": f"feat10_kuhn_block_n{n_cpu}_svk_force_tangent_H (bounded sample of the same mesh "
+                                      "family: the full n=119 pass takes ~40 s per step on 16 cores)",
                    "note": "CPU restatement (oracle/tlfea_oracle.c, OpenMP) of the reference algorithm; the reference's "
                            "CUDA sources are unbuildable here (Eigen, cuDSS, Bazel)"},
         "cpu_baseline": {"value": gps, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
@@ -351,7 +359,7 @@ def main():
     ap.add_argument("--no-ancf", action="store_true", help="skip the ANCF3443 plate / ANCF3243 chain configurations")
     ap.add_argument("--plate", type=int, default=1000, help="ANCF3443 plate: elements per edge (1000 -> 1M elements)")
     ap.add_argument("--chain", type=int, default=1000000, help="ANCF3243 chain: elements")
-    ap.add_argument("--assembly", type=int, default=-1, help="0 generic row gather, 1 element kernel + row reduce (default)")
+    ap.add_argument("--assembly", type=int, default=-1, help="0 generic row gather, 1 element kernel + row reduce, 2 single-pass patches (default for FEAT10)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
@@ -459,27 +467,101 @@ def main():
         tf = C.c_double(0)
         tlfea.lib.tlfea_fp64_peak(local, C.byref(tf))
         fp64 = tf.value
-    # two-phase assembly: gp_ms is the element kernel (ek_kernel), row_ms the row-reduce kernel (rk_kernel);
-    # the dominant one carries the roofline line, measured against the ALGORITHMIC bytes of the whole assembly
-    dom_is_row = row_ms >= gp_ms
+    # Assembly kernels: mode 2 (default) = pk_kernel launches, one per colour (gp_ms) + the ordered force gather
+    # (row_ms); mode 1 = ek_kernel (gp_ms) + rk_kernel (row_ms).  The roofline line is for the dominant kernel,
+    # measured against the ALGORITHMIC bytes of the whole assembly; frac_step charges the whole step.
+    st_patch = None
+    try:
+        st_patch = s.PatchStats()
+    except Exception:
+        pass
+    single_pass = st_patch is not None and args.assembly in (-1, 2)
+    dom_is_row = (row_ms >= gp_ms) and not single_pass
     dom_ms = max(row_ms if dom_is_row else gp_ms, 1e-9)
     achieved = algo_b / (dom_ms * 1e-3) / 1e9
-    # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full on this workload (n = 119, one GPU):
-    # profiles/r1i_ncu_full_ek_rk_n119.txt.  Other sizes were not captured.
-    ncu_traffic = {("rk", 119): 91.930448e9 + 29.111833e9, ("ek", 119): 14.840199e9 + 75.169257e9}
-    traffic = ncu_traffic.get(("rk" if dom_is_row else "ek", args.n)) if world == 1 else None
-    roofline = {"bound": "hbm", "kernel": "rk_kernel<10,5,3>" if dom_is_row else "ek_kernel<2,8,0,1>", "achieved": achieved, "peak": hbm_peak,
-                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
-                "traffic_unit": "bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)",
+    kname = (f"pk_kernel<{st_patch['warps']},0,1,0> x {st_patch['colours']} colours" if single_pass
+             else ("rk_kernel<10,5,3>" if dom_is_row else "ek_kernel<2,8,0,1,0>"))
+    # dram__bytes_read.sum + dram__bytes_write.sum summed over the launches of one assemble, written by
+    # tools/ncu_traffic.py from an ncu capture of this workload (profiles/ncu_traffic.json, keyed by kernel and n)
+    traffic, traffic_src = None, None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        ent = tj.get(f"{'pk' if single_pass else ('rk' if dom_is_row else 'ek')}_n{args.n}_w{world}")
+        if ent:
+            traffic, traffic_src = float(ent["bytes"]), ent.get("capture")
+    except Exception:
+        pass
+    t_hbm_ms = algo_b / (hbm_peak * 1e9) * 1e3
+    roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": hbm_peak,
+                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic, "traffic_capture": traffic_src,
+                "traffic_unit": "bytes per assemble (ncu dram__bytes_read.sum + dram__bytes_write.sum over its launches)",
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                "algorithmic_bytes_per_launch": algo_b, "kernel_ms": dom_ms, "rk_kernel_ms": row_ms, "ek_kernel_ms": gp_ms,
+                "algorithmic_bytes_per_launch": algo_b, "kernel_ms": dom_ms,
+                "assembly_kernel_ms": gp_ms, "second_kernel_ms": row_ms,
+                "second_kernel": "force_gather_kernel" if single_pass else "rk_kernel",
                 "step_share": dom_ms / max(ms_step, 1e-9)}
+    if single_pass:
+        roofline["patch_plan"] = st_patch
     if fp64:
         fl = ALGO_FLOP_PER_GP * n_elem_l * 5
+        t_fp64_ms = fl / (fp64 * 1e12) * 1e3
         roofline["fp64"] = {"achieved_tflops": fl / ((row_ms + gp_ms) * 1e-3) / 1e12, "peak_tflops": fp64,
                             "frac": fl / ((row_ms + gp_ms) * 1e-3) / 1e12 / fp64,
-                            "peak_source": "tlfea_fp64_peak DFMA micro-benchmark, same run",
+                            "peak_source": "tlfea_fp64_peak DFMA micro-benchmark of this library, same run (MEASURED_PEAKS.json "
+                                           "has no FP64 entry)",
                             "algorithmic_flop_per_gp": ALGO_FLOP_PER_GP}
+        # whole step against the binding roofline: max(HBM time, FP64 time) / measured step time
+        roofline["frac_step"] = max(t_hbm_ms, t_fp64_ms) / max(ms_step, 1e-9)
+        roofline["frac_step_terms_ms"] = {"hbm": t_hbm_ms, "fp64": t_fp64_ms, "step": ms_step}
+    else:
+        roofline["frac_step"] = t_hbm_ms / max(ms_step, 1e-9)
+
+    # ---- parity record: three size-independent numbers of the assembled state, over owned DOFs, all-reduced.  They
+    # must agree between N = 1, 2, 4, 8 (same mesh, different partition) to 1e-12: the scaling record is not
+    # correctness-blind.  Reference: the N = 1 run of this session (scratch file) or profiles/parity_golden.json.
+    parity = None
+    try:
+        lo = pn3 if slab.has_left else 0
+        nnz_l = int(s.nnz())
+        Hv = torch.as_tensor(_DevArray(tlfea.lib.tlfea_newton_devptr_hessian_values(s._h), nnz_l), device=dev)
+        acc = torch.zeros(4, dtype=torch.float64, device=dev)
+        acc[0] = (f_int[lo:] * f_int[lo:]).sum()
+        for c0 in range(0, nnz_l, 1 << 28):
+            blk = Hv[c0:c0 + (1 << 28)]
+            acc[1] += blk.sum()
+            acc[2] += blk.abs().sum()
+        ones = torch.ones(3 * n_nodes_l, dtype=torch.float64, device=dev)
+        y = torch.empty_like(ones)
+        torch.cuda.synchronize()
+        s.SpMV(ones.data_ptr(), y.data_ptr())
+        d.Sync()
+        partition.halo_sum(y, slab, rank, world, halo, dist)
+        acc[3] = (y[lo:] * y[lo:]).sum()
+        if world > 1:
+            dist.all_reduce(acc)
+        v = acc.tolist()
+        parity = {"f_int_l2": v[0] ** 0.5, "H_sum": v[1], "H_abs_sum": v[2], "H_times_ones_l2": v[3] ** 0.5}
+        del ones, y, Hv
+        if rank == 0:
+            scratch = os.path.join(ROOT, f".bench_parity_n{args.n}.json")
+            ref, src = None, None
+            if world == 1:
+                json.dump(parity, open(scratch, "w"))
+            elif os.path.exists(scratch):
+                ref, src = json.load(open(scratch)), "N=1 run of this session"
+            if ref is None:
+                try:
+                    ref = json.load(open(os.path.join(ROOT, "profiles", "parity_golden.json"))).get(f"n{args.n}")
+                    src = "profiles/parity_golden.json (N=1, committed)" if ref else None
+                except Exception:
+                    ref = None
+            if ref:
+                rel = {k: abs(parity[k] - ref[k]) / max(abs(ref["H_abs_sum"] if k == "H_sum" else ref[k]), 1e-300)
+                       for k in parity}
+                parity.update(rel_diff_vs_ref=rel, ref_source=src, tolerance=1e-12,
+                              parity_ok=bool(max(rel.values()) < 1e-12))
+    except Exception as ex:  # the headline line must still be printed
+        parity = {"error": repr(ex)}
 
     # ---- e2e: host buffers in, host f_int + ||g|| out, through the reference-facing API
     e2e = None
@@ -659,7 +741,8 @@ def main():
                        "h": H_STEP, "partition": f"x-slabs x{world}, sub-assembled H, NCCL halo sum of f_int",
                        "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
                        "setup_s": t_setup},
-            "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all,
+            "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all, "parity": parity,
+            "parity_ok": (parity or {}).get("parity_ok"),
             "newton": newton, "variants": variants, "other_configs": other, "clocks": clocks, "wall_ms_per_step": red[1].item() / args.steps,
         }
         _emit(line)

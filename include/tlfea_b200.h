@@ -212,7 +212,8 @@ int tlfea_newton_spmv(tlfea_newton *s, const double *d_x, double *d_y);
 /* sum of the CUDA-event time (ms) of assemble calls since the last reset, and their count */
 int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset);
 /* Assembly kernel selection: 2 (default) = single-pass patch assembly for FEAT10 (csrc/pk_kernel.cuh: on-chip
- * accumulation per patch, in-place update of H colour by colour) and the two-phase path for the ANCF elements;
+ * accumulation per patch, in-place update of H colour by colour) for FEAT10 + SVK (+ Kelvin-Voigt), the two-phase
+ * path for FEAT10 + Mooney-Rivlin and the ANCF elements; 3 = the patch assembly for every FEAT10 material;
  * 1 = element kernel + row reduce for every element type (csrc/ek_kernel.cuh, csrc/ancf_ek.cuh); 0 = generic
  * warp-per-row gather.  All are deterministic (no atomics); results agree to rounding. */
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode);

@@ -30,6 +30,7 @@ def test_patch_assembly_vs_oracle(n, warps, model, damp):
     fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
     d, s = _make(X, E, model, damp, fixed)
     s.SetPatchWarps(warps)
+    s.SetAssembly(3)  # the patch kernel for Mooney-Rivlin too (mode 2 routes it to the two-phase path)
     d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
     s.SetVelocityGuess(v.reshape(-1))
     s.Assemble()
@@ -88,7 +89,7 @@ def test_feat10_assemble_force_vs_oracle():
     v = 0.1 * np.random.Generator(np.random.PCG64(3)).uniform(-1, 1, size=X.shape)
     o = orc.T10Oracle(E, X)
     for model, damp in (("svk", False), ("svk", True), ("mr", True)):
-        for mode in (2, 1):
+        for mode in (3, 1):
             d, s = _make(X, E, model, damp)
             s.SetAssembly(mode)
             d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])

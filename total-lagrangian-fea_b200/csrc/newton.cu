@@ -385,7 +385,13 @@ static EKCfg ek_cfg() {
 static bool ek_supported(const tlfea_newton *s) {
   return s->asm_mode >= 1;  // every element type, SVK and Mooney-Rivlin, with or without Kelvin-Voigt damping
 }
-static bool pk_selected(const tlfea_newton *s) { return s->asm_mode == 2 && s->e->type == TLFEA_TYPE_T10; }
+// mode 2: FEAT10 + SVK (with or without Kelvin-Voigt damping) takes the single-pass patch kernel; Mooney-Rivlin keeps
+// the two-phase path, which is faster for it (its 81-entry tangent tensor leaves room for one 4-warp CTA per SM only:
+// 93 ms against 64 ms per 10.1 M-tet assemble).  mode 3 forces the patch kernel for every FEAT10 material.
+static bool pk_selected(const tlfea_newton *s) {
+  if (s->e->type != TLFEA_TYPE_T10) return false;
+  return s->asm_mode == 3 || (s->asm_mode == 2 && s->e->model == TL_MODEL_SVK);
+}
 
 // single-pass patch assembly (pk_kernel.cuh) + the ordered nodal force gather
 static int assemble_pk(tlfea_newton *s, bool tangent, bool damp) {
@@ -1448,8 +1454,9 @@ int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset
   return TLFEA_OK;
 }
 int tlfea_newton_set_assembly(tlfea_newton *s, int mode) {
-  TL_CHECK(s && mode >= 0 && mode <= 2,
-           "mode must be 0 (generic row gather), 1 (element kernel + row reduce) or 2 (single-pass patches, FEAT10)");
+  TL_CHECK(s && mode >= 0 && mode <= 3,
+           "mode must be 0 (generic row gather), 1 (element kernel + row reduce), 2 (single-pass patches for FEAT10 + "
+           "SVK, two-phase otherwise) or 3 (single-pass patches for every FEAT10 material)");
   s->asm_mode = mode;
   return TLFEA_OK;
 }

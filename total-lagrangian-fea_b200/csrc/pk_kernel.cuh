@@ -675,13 +675,13 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
 #pragma unroll
     for (int b = 0; b < PK_NB; b++) {
       const int k = base + b * KS + wk;
-      if (w_on && k < n_ent) {
+      if (w_on && k < n_ent && !(p.debug & 32)) {
         const uint2 en = ent[k];
         const double *hp = Hb + (en.x & hmask) + we;
         const unsigned rl = en.y & 0xffffu;
-        o[b][0] = hp[0];
-        o[b][1] = hp[rl];
-        o[b][2] = hp[2 * rl];
+        o[b][0] = __ldcg(hp);
+        o[b][1] = __ldcg(hp + rl);
+        o[b][2] = __ldcg(hp + 2 * rl);
       }
     }
     // ... first touches run underneath (only once): H block = (M_ij / h) I + sum
@@ -705,10 +705,16 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
         }
 #pragma unroll
         for (int u = 0; u < FU; u++) {
-          if (k0f + u * KS < n_first) {
-            hp[u][0] = v[u][0];
-            hp[u][rl[u]] = v[u][1];
-            hp[u][2 * rl[u]] = v[u][2];
+          if (k0f + u * KS < n_first && !(p.debug & 64)) {
+            if (p.debug & 256) {
+              __stcg(hp[u], v[u][0]);
+              __stcg(hp[u] + rl[u], v[u][1]);
+              __stcg(hp[u] + 2 * rl[u], v[u][2]);
+            } else {
+              hp[u][0] = v[u][0];
+              hp[u][rl[u]] = v[u][1];
+              hp[u][2 * rl[u]] = v[u][2];
+            }
           }
         }
       }
@@ -716,7 +722,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
 #pragma unroll
     for (int b = 0; b < PK_NB; b++) {
       const int k = base + b * KS + wk;
-      if (w_on && k < n_ent) {
+      if (w_on && k < n_ent && !(p.debug & 32)) {
         const uint2 en = ent[k];
         double *hp = Hb + (en.x & hmask) + we;
         const unsigned rl = en.y & 0xffffu;
