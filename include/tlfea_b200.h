@@ -192,6 +192,10 @@ int tlfea_newton_solve_step(tlfea_newton *s);
 /* last step's statistics: Newton iterations, total PCG iterations, final ||g||, final ||c|| */
 int tlfea_newton_last_stats(tlfea_newton *s, int *newton_iters, int *pcg_iters, double *norm_g, double *norm_c);
 int tlfea_newton_set_pcg(tlfea_newton *s, int max_iters, double rel_tol);
+/* The reference's linear solve is exact (cuDSS Cholesky, SyncedNewton.cu:1103-1114); the PCG stand-in reports how far it
+ * got: ||r|| / ||r0|| of the last linear solve of the last step, and converged = 0 if any linear solve of that step
+ * stopped at max_iters above rel_tol (with rel_tol = 0 the count is fixed and converged stays 1). */
+int tlfea_newton_last_linear_solve(tlfea_newton *s, double *rel_residual, int *converged);
 
 int64_t tlfea_newton_nnz(const tlfea_newton *s);
 int tlfea_newton_n_dofs(const tlfea_newton *s);

@@ -130,3 +130,61 @@ def test_gradient_vs_oracle_fixed_nodes():
     g_ref = orc.grad_L(o.off, o.cols, o.mass(RHO), v, vp, f_ref, fext, H_STEP, JT, lam, con, rho_alm)
     assert rel_err(g, g_ref) < TOL
     assert abs(ng - np.linalg.norm(g_ref)) < 1e-12 * np.linalg.norm(g_ref)
+
+
+def test_owned_range_keeps_external_terms_on_one_rank():
+    """Distributed residual (tlfea/dist_newton.py): M and f_int are sub-assembled and summed over ranks, f_ext and the
+    constraint terms are not -- outside the owned DOF range a rank must leave them out of g and of H, or shared nodes
+    would count them twice after the halo sum.  Emulated on one GPU with a shrunken owned range."""
+    import tlfea
+    from tlfea import meshgen
+
+    X, E = meshgen.kuhn_block(3)
+    nn = X.shape[0]
+    x = meshgen.perturb(X, 0.01, 3)
+    fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
+    fext = np.arange(3 * nn, dtype=np.float64) + 1.0
+    d, s = _make(X, E, "svk", False, fixed, alm_rho=1e10)
+    d.SetExternalForce(fext)
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    s.Assemble()
+    s.Residual()
+    g_all, H_all = s.RetrieveGradient(), s.RetrieveHessianValues()
+    lo = 3 * (int(fixed.max()) // 2)  # cuts through the pinned face
+    tlfea._lib.check(tlfea.lib.tlfea_newton_set_owned_range(s._h, lo, 3 * nn))
+    s.Assemble()
+    s.Residual()
+    g_own, H_own = s.RetrieveGradient(), s.RetrieveHessianValues()
+    assert np.array_equal(g_own[lo:], g_all[lo:])
+    con = (x - X)[fixed].reshape(-1)
+    extra = np.zeros(3 * nn)
+    extra[(3 * fixed[:, None] + np.arange(3)).ravel()] = H_STEP * 1e10 * con
+    want = g_all[:lo] + fext[:lo] - extra[:lo]
+    assert np.abs(g_own[:lo] - want).max() < 1e-9 * np.abs(g_all).max()
+    # the penalty h^2 rho on the diagonal of pinned DOFs is present only where owned
+    dH = H_all - H_own
+    n_unowned = int(((3 * fixed[:, None] + np.arange(3)).ravel() < lo).sum())
+    assert (np.abs(dH) > 0.5 * H_STEP**2 * 1e10).sum() == n_unowned and n_unowned > 0
+
+
+def test_setup_rejects_repeated_ids():
+    """A collapsed element (repeated node id) or a pinned node listed twice would lose updates in the ordered,
+    atomic-free assembly: both are refused at set-up."""
+    import tlfea
+    from tlfea import meshgen
+
+    X, E = meshgen.kuhn_block(2)
+    Eb = E.copy()
+    Eb[3, 5] = Eb[3, 1]
+    d = tlfea.GPU_FEAT10_Data(Eb.shape[0], X.shape[0])
+    d.Initialize()
+    d.Setup(*tlfea.tet5pt_quadrature(), X[:, 0], X[:, 1], X[:, 2], Eb)
+    d.SetDensity(RHO)
+    d.SetSVK(E_MOD, NU)
+    d.CalcDnDuPre()
+    with pytest.raises(tlfea.TlfeaError):
+        d.CalcMassMatrix()
+    d2 = tlfea.GPU_FEAT10_Data(E.shape[0], X.shape[0])
+    d2.Initialize()
+    with pytest.raises(tlfea.TlfeaError):
+        d2.SetNodalFixed(np.array([1, 4, 1], dtype=np.int32))

@@ -112,6 +112,7 @@ struct tlfea_elem {
   cudaStream_t stream = nullptr;
   bool own_stream = true;
   bool is_setup = false, is_precomputed = false, is_pattern = false, is_mass = false;
+  int pattern_version = 0;            // bumped whenever the coefficient pattern is (re)built: bound solvers must re-analyse
   int mass_version = 0;               // bumped by CalcMassMatrix: cached copies of the mass values refresh
   int cons_version = 0;               // bumped by UpdateNodalFixed: solvers refresh their constraint slots
   bool pat_extra = false;             // the pattern also holds J^T J couplings of linear constraints
@@ -173,6 +174,7 @@ struct tlfea_newton {
   int n_constraints = 0;
   tlfea_newton_params prm{};
   bool analyzed = false, fixed_pattern = false;
+  int pattern_version_seen = -1;  // the element pattern the solver's H, slots and plans were built for
   int64_t nnz = 0;  // DOF-level nnz = 9 * pattern.nnz
   double *d_H = nullptr;
   double *d_gp = nullptr;  // per-Gauss-point records
@@ -186,6 +188,7 @@ struct tlfea_newton {
   double *d_xp = nullptr, *d_yp = nullptr, *d_zp = nullptr;
   // constraint term h^2 rho J^T J as a (slot, coefficient) list with unique slots
   int cons_version_seen = 0;
+  int64_t cons_own_lo = 0, cons_own_hi = -2;  // owned range the constraint slots were built for
   int64_t own_lo = 0, own_hi = -1;  // DOF range owned by this rank (dot products of the distributed solve)
   int64_t n_cons_slots = 0;
   int64_t *d_cons_slot = nullptr;
@@ -197,6 +200,8 @@ struct tlfea_newton {
   int pcg_max_iters = 200;
   double pcg_rel_tol = 1e-8;
   int last_newton = 0, last_pcg = 0;
+  double last_pcg_rel = 0;     // ||r|| / ||r0|| reached by the last linear solve
+  bool last_pcg_converged = true;  // false: the last linear solve stopped at max_iters above rel_tol
   double last_norm_g = 0, last_norm_c = 0;
   // pipelined host-buffer step (tlfea_newton_assemble_host_begin / _end): copy stream, row-reduce stream,
   // events 0..15 = coordinate chunk k is on the device, 16 = tail of the main stream, 17 = residual kernels queued,

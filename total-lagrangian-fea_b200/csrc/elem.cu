@@ -284,6 +284,7 @@ int ensure_pattern(tlfea_elem *h) {
   TL_TRY(dmalloc(&h->d_mass, (size_t)h->pat.nnz));
   TL_CUDA(cudaMemsetAsync(h->d_mass, 0, (size_t)h->pat.nnz * sizeof(double), h->stream));
   h->is_pattern = true;
+  h->pattern_version++;
   return TLFEA_OK;
 }
 
@@ -527,6 +528,11 @@ int tlfea_elem_set_nodal_fixed(tlfea_elem *h, const int *fixed, int n_fixed) {
   // ANCF pins all 4 coefficients of a node? No: the reference pins what the caller lists
   // (coefficient indices for ANCF, node indices for FEAT10) -- 3 constraints per entry.
   for (int i = 0; i < n_fixed; i++) TL_CHECK(fixed[i] >= 0 && fixed[i] < h->n_coef, "fixed index out of range");
+  {  // a repeated entry would map two constraint rows to the same H slots (the reference's atomicAdd adds both)
+    std::vector<int> srt(fixed, fixed + n_fixed);
+    std::sort(srt.begin(), srt.end());
+    TL_CHECK(std::adjacent_find(srt.begin(), srt.end()) == srt.end(), "SetNodalFixed: an index is listed twice");
+  }
   h->n_fixed = n_fixed;
   h->n_constraint = 3 * n_fixed;
   TL_TRY(dmalloc(&h->d_fixed, (size_t)n_fixed));

@@ -24,7 +24,7 @@ __global__ void k_grad_L(int n_coef, const int *__restrict__ off, const int *__r
                          const double *__restrict__ v_prev, const double *__restrict__ f_int,
                          const double *__restrict__ f_ext, double inv_h, double h, const int *jt_off,
                          const int *jt_cols, const double *jt_vals, const double *lam, const double *con, double rho,
-                         double *g) {
+                         int64_t own_lo, int64_t own_hi, double *g) {
   int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (tid >= (int64_t)n_coef * 3) return;
   const int ni = (int)(tid / 3), di = (int)(tid % 3);
@@ -54,8 +54,11 @@ __global__ void k_grad_L(int n_coef, const int *__restrict__ off, const int *__r
     res += mass[idx] * (v[tj] - v_prev[tj]) * inv_h;
   }
   res -= (-f_int[tid]);
-  res -= f_ext[tid];
-  if (jt_off) {
+  // distributed solve: M and f_int are sub-assembled (summed over ranks by the halo sum), f_ext and the constraint
+  // terms are NOT -- only the rank that owns the DOF adds them
+  const bool own = tid >= own_lo && tid < own_hi;
+  if (own) res -= f_ext[tid];
+  if (jt_off && own) {
     for (int idx = jt_off[tid]; idx < jt_off[tid + 1]; idx++) {
       const int c = jt_cols[idx];
       res += h * jt_vals[idx] * (lam[c] + rho * con[c]);
@@ -66,15 +69,18 @@ __global__ void k_grad_L(int n_coef, const int *__restrict__ off, const int *__r
 
 // fixed-node constraints: J^T has exactly one unit entry per constrained DOF
 __global__ void k_grad_L_fixed(int n_fixed, const int *__restrict__ fixed, const double *__restrict__ lam,
-                               const double *__restrict__ con, double h, double rho, double *g) {
+                               const double *__restrict__ con, double h, double rho, int64_t own_lo, int64_t own_hi,
+                               double *g) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= 3 * n_fixed) return;
   const int64_t dof = (int64_t)fixed[c / 3] * 3 + c % 3;
+  if (dof < own_lo || dof >= own_hi) return;  // the owner rank adds the term (see k_grad_L)
   g[dof] += h * 1.0 * (lam[c] + rho * con[c]);
 }
 
 __global__ void k_fixed_cons_slots(int n_fixed, const int *__restrict__ fixed, const int *__restrict__ off,
-                                   const int *__restrict__ cols, int64_t *slot, double *val) {
+                                   const int *__restrict__ cols, int64_t own_lo, int64_t own_hi, int64_t *slot,
+                                   double *val) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= 3 * n_fixed) return;
   const int n = fixed[c / 3], d = c % 3;
@@ -92,7 +98,8 @@ __global__ void k_fixed_cons_slots(int n_fixed, const int *__restrict__ fixed, c
       hi = mid - 1;
   }
   slot[c] = 9 * (int64_t)rs + (int64_t)d * 3 * deg + 3 * pos + d;
-  val[c] = 1.0;
+  const int64_t dof = 3 * (int64_t)n + d;
+  val[c] = (dof >= own_lo && dof < own_hi) ? 1.0 : 0.0;  // h^2 rho J^T J goes into the owner rank's sub-assembled H
 }
 
 // H += h^2 rho * (J^T J) on its precomputed unique slots   (SyncedNewton.cu:291-341)
@@ -196,12 +203,17 @@ __global__ void k_block_jacobi_setup(int n_coef, const int *__restrict__ off, co
     else
       hi = mid - 1;
   }
+  double m[9] = {1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0};
+  if (deg == 0) {  // an isolated coefficient has no diagonal block to read
+#pragma unroll
+    for (int q = 0; q < 9; q++) Dinv[(int64_t)q * n_coef + i] = m[q];
+    return;
+  }
   const double *h0 = H + 9 * (int64_t)rs + 3 * pos, *h1 = h0 + 3 * deg, *h2 = h1 + 3 * deg;
   const double a = h0[0], b = h0[1], c = h0[2], d = h1[0], e = h1[1], f = h1[2], g = h2[0], hh = h2[1], k = h2[2];
   const double A = e * k - f * hh, B = -(d * k - f * g), C = d * hh - e * g;
   const double det = a * A + b * B + c * C;
-  double m[9] = {1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0};
-  if (deg > 0 && fabs(det) >= 1e-300) {
+  if (fabs(det) >= 1e-300) {
     const double id = 1.0 / det;
     m[0] = A * id;
     m[1] = -(b * k - c * hh) * id;
@@ -482,7 +494,7 @@ struct EkPlan {
     rec = (int64_t)e->S * e->S * 9;  // doubles of one element's block records [a][b][9]
     if (tangent && !s->d_stage) TL_TRY(dmalloc(&s->d_stage, (size_t)e->n_elem * rec));
     if (tangent && !s->d_rowdesc) {
-      int chunk = ek_chunk_elems();
+      int chunk = ek_chunk_elems() & ~1;  // element pairs: an odd chunk would misalign the 16-byte bulk copies
       if (chunk <= 0 || chunk >= e->n_elem) chunk = e->n_elem;
       s->ek_chunk = chunk;
       int *d_order = nullptr;
@@ -632,6 +644,11 @@ static int assemble_ek(tlfea_newton *s, bool tangent, bool damp) {
   return TLFEA_OK;
 }
 
+static int64_t own_lo_of(const tlfea_newton *s) { return std::max<int64_t>(0, s->own_lo); }
+static int64_t own_hi_of(const tlfea_newton *s) {
+  const int64_t n = 3 * (int64_t)s->e->n_coef;
+  return (s->own_hi < 0) ? n : std::min<int64_t>(n, s->own_hi);
+}
 // slots of the h^2 rho J^T J diagonal entries of pinned nodes (J = selection rows)
 static int fixed_cons_slots(tlfea_newton *s) {
   tlfea_elem *e = s->e;
@@ -646,12 +663,15 @@ static int fixed_cons_slots(tlfea_newton *s) {
   TL_TRY(dmalloc(&s->d_cons_val, (size_t)std::max<int64_t>(s->n_cons_slots, 1)));
   if (e->n_fixed > 0)
     TL_LAUNCH(k_fixed_cons_slots, blocks_for(3 * e->n_fixed, 256), 256, 0, e->stream, e->n_fixed, e->d_fixed,
-              e->pat.d_off, e->pat.d_cols, s->d_cons_slot, s->d_cons_val);
+              e->pat.d_off, e->pat.d_cols, own_lo_of(s), own_hi_of(s), s->d_cons_slot, s->d_cons_val);
   s->cons_version_seen = e->cons_version;
+  s->cons_own_lo = own_lo_of(s), s->cons_own_hi = own_hi_of(s);
   return TLFEA_OK;
 }
 static int refresh_constraints(tlfea_newton *s) {  // the element's pinned set changed (UpdateNodalFixed)
-  if (!s->analyzed || s->n_constraints == 0 || s->cons_version_seen == s->e->cons_version) return TLFEA_OK;
+  if (!s->analyzed || s->n_constraints == 0) return TLFEA_OK;
+  if (s->cons_version_seen == s->e->cons_version && s->cons_own_lo == own_lo_of(s) && s->cons_own_hi == own_hi_of(s))
+    return TLFEA_OK;
   TL_CHECK(s->e->cons_mode == TL_CONS_FIXED_NODES, "constraint kind changed under a live solver");
   return fixed_cons_slots(s);
 }
@@ -666,6 +686,10 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
   }
   TL_CUDA(cudaSetDevice(e->device));
   TL_TRY(ensure_pattern(e));
+  if (tangent)
+    TL_CHECK(s->pattern_version_seen == e->pattern_version,
+             "the element's sparsity pattern was rebuilt after AnalyzeHessianSparsity (SetLinearConstraintsCSR on a "
+             "live solver): create a new solver");
   TL_TRY(refresh_constraints(s));
   const bool damp = (e->eta != 0.0 || e->lambda_d != 0.0);
   TL_CUDA(cudaEventRecord(s->ev[0], e->stream));
@@ -772,10 +796,11 @@ static int compute_residual(tlfea_newton *s) {
   const bool lin = (s->n_constraints > 0 && e->cons_mode == TL_CONS_LINEAR_CSR);
   TL_LAUNCH(k_grad_L, blocks_for((int64_t)e->n_coef * 3, 256), 256, 0, e->stream, e->n_coef, e->pat.d_off,
             e->pat.d_cols, e->d_mass, s->d_v, s->d_v_prev, e->d_f_int, e->d_f_ext, 1.0 / h, h,
-            lin ? e->d_jt_off : nullptr, e->d_jt_cols, e->d_jt_vals, s->d_lambda, e->d_constraint, s->prm.rho, s->d_g);
+            lin ? e->d_jt_off : nullptr, e->d_jt_cols, e->d_jt_vals, s->d_lambda, e->d_constraint, s->prm.rho,
+            own_lo_of(s), own_hi_of(s), s->d_g);
   if (s->n_constraints > 0 && e->cons_mode == TL_CONS_FIXED_NODES && e->n_fixed > 0) {
     TL_LAUNCH(k_grad_L_fixed, blocks_for(3 * e->n_fixed, 256), 256, 0, e->stream, e->n_fixed, e->d_fixed,
-              s->d_lambda, e->d_constraint, h, s->prm.rho, s->d_g);
+              s->d_lambda, e->d_constraint, h, s->prm.rho, own_lo_of(s), own_hi_of(s), s->d_g);
   }
   TL_CUDA(cudaGetLastError());
   return TLFEA_OK;
@@ -796,20 +821,30 @@ static int pcg_solve(tlfea_newton *s, int *iters_out) {
   double r0 = 0;
   TL_TRY(norm2(s, r, n, &r0));
   int it = 0;
+  double rn = r0;
+  bool hit = (r0 == 0.0);
   if (r0 > 0.0) {
     for (it = 1; it <= s->pcg_max_iters; it++) {
       TL_LAUNCH(k_spmv, sb, 256, 0, e->stream, e->n_coef, e->pat.d_off, e->pat.d_cols, s->d_H, p, Ap);
       TL_TRY(dot(s, p, Ap, s->d_scal + 1));
       TL_LAUNCH(k_pcg_update_xr, gb, 256, 0, e->stream, n, s->d_scal, p, Ap, x, r);
-      double rn = 0;
-      TL_TRY(norm2(s, r, n, &rn));
-      if (rn <= s->pcg_rel_tol * r0) break;
+      if (s->pcg_rel_tol > 0.0) {  // rel_tol = 0: a fixed iteration count, no host synchronisation inside the loop
+        TL_TRY(norm2(s, r, n, &rn));
+        if (rn <= s->pcg_rel_tol * r0) {
+          hit = true;
+          break;
+        }
+      }
       TL_LAUNCH(k_block_jacobi, nb, 256, 0, e->stream, e->n_coef, Dinv, r, z);
       TL_TRY(dot(s, r, z, s->d_scal + 2));
       TL_LAUNCH(k_pcg_update_p, gb, 256, 0, e->stream, n, s->d_scal, z, p);
       TL_LAUNCH(k_copy_scalar, 1, 1, 0, e->stream, s->d_scal + 0, s->d_scal + 2);
     }
+    if (s->pcg_rel_tol <= 0.0) TL_TRY(norm2(s, r, n, &rn));  // what the fixed count reached
   }
+  // the reference's cuDSS solve is exact; an iterative stand-in must say how far it got
+  s->last_pcg_rel = (r0 > 0.0) ? rn / r0 : 0.0;
+  if (s->pcg_rel_tol > 0.0 && !hit) s->last_pcg_converged = false;
   TL_CUDA(cudaGetLastError());
   *iters_out = std::min(it, s->pcg_max_iters);
   return TLFEA_OK;
@@ -898,6 +933,8 @@ static int assemble_host_begin(tlfea_newton *s, const double *hx, const double *
   TL_CHECK(s->prm.time_step > 0.0, "time_step must be positive (SetParameters)");
   TL_CUDA(cudaSetDevice(e->device));
   TL_TRY(ensure_pattern(e));
+  TL_CHECK(s->pattern_version_seen == e->pattern_version,
+           "the element's sparsity pattern was rebuilt after AnalyzeHessianSparsity: create a new solver");
   TL_TRY(refresh_constraints(s));
   const bool damp = (e->eta != 0.0 || e->lambda_d != 0.0);
   bool overlap = ek_supported(s) && !pk_selected(s);
@@ -1084,6 +1121,7 @@ int tlfea_newton_analyze_sparsity(tlfea_newton *s) {
   tlfea_elem *e = s->e;
   TL_CUDA(cudaSetDevice(e->device));
   TL_TRY(ensure_pattern(e));
+  s->pattern_version_seen = e->pattern_version;
   s->nnz = 9 * e->pat.nnz;
   TL_TRY(dmalloc(&s->d_H, (size_t)s->nnz));
   s->rec_doubles = 0;  // Gauss-point records (row-gather path only) are allocated on first use
@@ -1207,6 +1245,8 @@ int tlfea_newton_solve_step(tlfea_newton *s) {
   s->last_newton = 0;
   s->last_pcg = 0;
   s->last_norm_c = 0;
+  s->last_pcg_rel = 0;
+  s->last_pcg_converged = true;
   for (int outer = 0; outer < s->prm.max_outer; outer++) {
     double norm_g0 = -1.0;
     for (int it = 0; it < s->prm.max_inner; it++) {
@@ -1253,6 +1293,13 @@ int tlfea_newton_last_stats(tlfea_newton *s, int *newton_iters, int *pcg_iters, 
   if (pcg_iters) *pcg_iters = s->last_pcg;
   if (norm_g) *norm_g = s->last_norm_g;
   if (norm_c) *norm_c = s->last_norm_c;
+  return TLFEA_OK;
+}
+
+int tlfea_newton_last_linear_solve(tlfea_newton *s, double *rel_residual, int *converged) {
+  TL_CHECK(s, "null handle");
+  if (rel_residual) *rel_residual = s->last_pcg_rel;
+  if (converged) *converged = s->last_pcg_converged ? 1 : 0;
   return TLFEA_OK;
 }
 

@@ -84,6 +84,20 @@ __global__ void k_max_diff(const int *__restrict__ off, int n, int *out) {
   if ((threadIdx.x & 31) == 0) atomicMax(out, v);
 }
 
+// The ordered (atomic-free) assembly adds the S x S blocks of an element to S distinct slots per row: a collapsed
+// element that repeats a coefficient id would lose updates, so it is rejected at set-up.
+__global__ void k_check_distinct(const int *__restrict__ ecoef, int n_elem, int S, int n_coef, int *err) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elem) return;
+  const int *ec = ecoef + (int64_t)e * S;
+  bool bad = false;
+  for (int a = 0; a < S; a++) {
+    bad = bad || ec[a] < 0 || ec[a] >= n_coef;
+    for (int b = a + 1; b < S; b++) bad = bad || (ec[a] == ec[b]);
+  }
+  if (bad) atomicExch(err, 1);
+}
+
 static int sort_keys(unsigned long long *d_in, unsigned long long *d_out, int64_t n, int end_bit, cudaStream_t st) {
   size_t tmp_bytes = 0;
   TL_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, d_in, d_out, n, 0, end_bit, st));
@@ -105,6 +119,19 @@ int build_pattern(const int *d_ecoef, int n_elem, int S, int n_coef, cudaStream_
   p.n_visits = (int64_t)n_elem * S;
   int coef_bits = 1;
   while ((1LL << coef_bits) < n_coef) coef_bits++;
+  {
+    int *d_bad = nullptr, h_bad = 0;
+    TL_TRY(dmalloc(&d_bad, 1));
+    TL_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), st));
+    TL_LAUNCH(k_check_distinct, blocks_for(n_elem, 256), 256, 0, st, d_ecoef, n_elem, S, n_coef, d_bad);
+    TL_CUDA(cudaMemcpyAsync(&h_bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, st));
+    TL_CUDA(cudaStreamSynchronize(st));
+    cudaFree(d_bad);
+    if (h_bad)
+      return fail(TLFEA_ERR_INVALID,
+                  "an element repeats a coefficient id or has one out of range (the ordered assembly needs pairwise "
+                  "distinct ids per element)");
+  }
 
   // ---- adjacency: sorted unique (i,j)
   {

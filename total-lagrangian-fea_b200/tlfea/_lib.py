@@ -103,6 +103,7 @@ _SIGS = {
     "tlfea_newton_solve_step": (C.c_int, [c_vp]),
     "tlfea_newton_last_stats": (C.c_int, [c_vp, c_ip, c_ip, c_dp, c_dp]),
     "tlfea_newton_set_pcg": (C.c_int, [c_vp, C.c_int, C.c_double]),
+    "tlfea_newton_last_linear_solve": (C.c_int, [c_vp, c_dp, c_ip]),
     "tlfea_newton_nnz": (C.c_int64, [c_vp]),
     "tlfea_newton_n_dofs": (C.c_int, [c_vp]),
     "tlfea_newton_get_hessian_csr": (C.c_int, [c_vp, c_i64p, c_ip, c_dp]),

@@ -113,7 +113,10 @@ class SyncedNewtonSolver(SolverBase):
         a, b = C.c_int(0), C.c_int(0)
         g, c = C.c_double(0), C.c_double(0)
         check(lib.tlfea_newton_last_stats(self._h, C.byref(a), C.byref(b), C.byref(g), C.byref(c)))
-        return {"newton_iters": a.value, "pcg_iters": b.value, "norm_g": g.value, "norm_c": c.value}
+        rel, conv = C.c_double(0), C.c_int(1)
+        check(lib.tlfea_newton_last_linear_solve(self._h, C.byref(rel), C.byref(conv)))
+        return {"newton_iters": a.value, "pcg_iters": b.value, "norm_g": g.value, "norm_c": c.value,
+                "pcg_rel_residual": rel.value, "pcg_converged": bool(conv.value)}
 
     def nnz(self) -> int:
         return lib.tlfea_newton_nnz(self._h)
