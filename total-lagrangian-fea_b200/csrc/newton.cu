@@ -670,8 +670,9 @@ static int fixed_cons_slots(tlfea_newton *s) {
 }
 static int refresh_constraints(tlfea_newton *s) {  // the element's pinned set changed (UpdateNodalFixed)
   if (!s->analyzed || s->n_constraints == 0) return TLFEA_OK;
-  if (s->cons_version_seen == s->e->cons_version && s->cons_own_lo == own_lo_of(s) && s->cons_own_hi == own_hi_of(s))
-    return TLFEA_OK;
+  const bool own_same = s->e->cons_mode != TL_CONS_FIXED_NODES ||
+                        (s->cons_own_lo == own_lo_of(s) && s->cons_own_hi == own_hi_of(s));
+  if (s->cons_version_seen == s->e->cons_version && own_same) return TLFEA_OK;
   TL_CHECK(s->e->cons_mode == TL_CONS_FIXED_NODES, "constraint kind changed under a live solver");
   return fixed_cons_slots(s);
 }
