@@ -582,7 +582,9 @@ def main():
         def e2e_pipelined():
             # same inputs, same outputs, same work: tlfea_newton_assemble_host_begin / _end overlap the chunked H2D
             # with the element kernel and the D2H of f_int / ||g|| with the row reduce (include/tlfea_b200.h)
-            s.AssembleFromHostBegin(hx[0], hx[1], hx[2])
+            # one GPU: the result buffer is registered up front, finished id ranges of f_int travel back under the
+            # remaining kernels; N > 1: the halo sum touches f_int between begin and end, one copy at the end
+            s.AssembleFromHostBegin(hx[0], hx[1], hx[2], hf if world == 1 else None)
             halo_sum()
             return s.AssembleFromHostEnd(hf)
 
@@ -628,8 +630,9 @@ def main():
                "pipelined_ms_per_step": t_pipe * 1e3 if np.isfinite(t_pipe) else None,
                "pipelined_bit_identical": bool(ok.item()),
                "what": "host x,y,z (pinned) in; f_int[3 Nn] and ||g|| back on the host; H stays device-resident for the "
-                       "solver, as in the reference.  Pipelined: chunked H2D under the element kernel, D2H under the "
-                       "row reduce; plain: the reference's call sequence, serialised"}
+                       "solver, as in the reference.  Pipelined: x, y, z go up in coefficient-id ranges, the patch kernels "
+                       "of a range start when it has landed, finished ranges of f_int go back under the remaining "
+                       "kernels; plain: the reference's call sequence, serialised"}
 
     # ---- second half of the metric: Newton iterations / s, single GPU only.
     # One inner iteration = force + H assembly, residual + norm, block-Jacobi PCG with a FIXED 50 iterations

@@ -184,6 +184,11 @@ int tlfea_newton_assemble_force(tlfea_newton *s);
  *           returns when f_int, ||g|| AND H are complete. */
 int tlfea_newton_assemble_host_begin(tlfea_newton *s, const double *x, const double *y, const double *z, int n);
 int tlfea_newton_assemble_host_end(tlfea_newton *s, double *f_int, int n, double *norm_g);
+/* Optional: the host buffer (3*n_coef doubles, pinned for overlap) that the NEXT _host_begin/_host_end pair will return
+ * f_int in.  Known before _begin, the single-pass FEAT10 path copies each coefficient-id range back as soon as its last
+ * chunk of patches is done, under the remaining kernels; the caller must not touch f_int on the device between _begin
+ * and _end (a multi-GPU caller that halo-sums f_int in between passes NULL and gets one copy at _end).  NULL clears. */
+int tlfea_newton_set_host_result_buffer(tlfea_newton *s, double *f_int_host, int n);
 /* constraints_eval + compute_grad_l + ||g||  SyncedNewton.cu:1056-1064; writes ||g||_2 to *norm_g */
 int tlfea_newton_residual(tlfea_newton *s, double *norm_g);
 /* One implicit step: OneStepNewtonCuDSS (SyncedNewton.cu:909-1394) with the
@@ -272,10 +277,11 @@ int tlfea_fp64_peak(int device, double *tflops);
 
 /* Test hooks for the single-pass FEAT10 assembly plan (csrc/patch_plan.cuh; new design, no reference line):
  * the plan is pure host data, built without a GPU, so the CPU test-suite can replay the kernel's summation
- * order.  ecoef is [n_elem][10] row-major coefficient ids; off/cols the coefficient-level CSR pattern. */
+ * order.  ecoef is [n_elem][10] row-major coefficient ids; off/cols the coefficient-level CSR pattern; n_chunks the
+ * id-range chunks of the launch order (color_ptr then has n_chunks * colours + 1 entries). */
 int tlfea_debug_patch_plan_build(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y,
-                                 const double *z, const int *off, const int *cols, int W, void **plan_out);
-/* sizes[8] = patches, colours, elements, rows, blob bytes, largest patch blob, uncovered pattern blocks, sum of local blocks */
+                                 const double *z, const int *off, const int *cols, int W, int n_chunks, void **plan_out);
+/* sizes[8] = patches, launches (chunks * colours), elements, rows, blob bytes, largest patch blob, uncovered pattern blocks, sum of local blocks */
 int tlfea_debug_patch_plan_sizes(void *plan, int64_t *sizes);
 int tlfea_debug_patch_plan_copy(void *plan, int *color_ptr, void *desc, void *elems, int *row_node, int64_t *row_ptr,
                                 void *blob, int64_t *uncovered);

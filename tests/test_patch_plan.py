@@ -18,7 +18,7 @@ TILES = [(0, j) for j in range(5)] + [(1, j) for j in range(1, 5)] + [(2, j) for
 CAPU = 216
 
 
-def build_plan(E, X, off, cols, W):
+def build_plan(E, X, off, cols, W, n_chunks=1):
     from tlfea import _lib
 
     assert PELEM.itemsize == 128 and PENT.itemsize == 8 and PDESC.itemsize == 64
@@ -30,7 +30,7 @@ def build_plan(E, X, off, cols, W):
     ip = lambda a: a.ctypes.data_as(_lib.c_ip)  # noqa: E731
     dp = lambda a: a.ctypes.data_as(_lib.c_dp)  # noqa: E731
     _lib.check(_lib.lib.tlfea_debug_patch_plan_build(E.shape[0], X.shape[0], ip(E), dp(x), dp(y), dp(z), ip(off),
-                                                      ip(cols), W, C.byref(h)))
+                                                      ip(cols), W, n_chunks, C.byref(h)))
     sizes = np.zeros(8, dtype=np.int64)
     _lib.check(_lib.lib.tlfea_debug_patch_plan_sizes(h, sizes.ctypes.data_as(_lib.c_i64p)))
     npatch, ncol, nel, nrow, nblob, maxblob, nunc, suml = (int(v) for v in sizes)
@@ -169,6 +169,32 @@ def test_plan_replay_matches_oracle_kuhn(n, W):
         assert len(plan["color_ptr"]) - 1 == 8
         assert (plan["desc"]["n_sub"] == 8).all()
     assert bank_conflict_factor(plan) < 1.35  # random placement gives ~2.3
+
+
+def test_plan_chunked_launch_order():
+    """Host-buffer pipelining: launches ordered (id-range chunk, colour).  Replaying that order still reproduces the
+    oracle's H (the first-touch flags follow the launch order), a chunk only reads ids below the end of its range."""
+    from tlfea import meshgen
+    from oracle import oracle as orc
+
+    X, E = meshgen.kuhn_block(4)
+    x = meshgen.perturb(X, 0.01, 9)
+    o = orc.T10Oracle(E, X)
+    mat = orc.Material.svk(7e8, 0.33)
+    h, rho, K = 1e-3, 2700.0, 4
+    plan = build_plan(E, X, o.off, o.cols, 4, K)
+    check_plan_invariants(plan, E, 4)
+    cp, rn, rp = plan["color_ptr"], plan["row_node"], plan["row_ptr"]
+    C_ = (len(cp) - 1) // K
+    assert (len(cp) - 1) == K * C_ and C_ >= 8
+    nn = X.shape[0]
+    for c in range(K):
+        for p in range(cp[c * C_], cp[(c + 1) * C_]):
+            mx = rn[rp[p]:rp[p + 1]].max()
+            assert min(K - 1, mx * K // nn) == c
+    Ke = [h * orc.element_tangent(E[e], x, o.grad_N[e], o.detJ[e], o.qw, mat) for e in range(E.shape[0])]
+    H = replay(plan, Ke, mass_lookup(o.off, o.cols, o.mass(rho)), h, o.cols.shape[0])
+    assert rel_err(H, o.hessian(x, mat, h, rho)) < 1e-13
 
 
 def test_plan_unstructured_permuted():

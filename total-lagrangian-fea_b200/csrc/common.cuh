@@ -157,8 +157,15 @@ struct tlfea_newton;
 namespace tlfea {
 int build_row_order(const tlfea_elem *h, int **d_order);
 int build_completion_order(const tlfea_elem *h, int chunk, int **d_order, std::vector<int> *chunk_ptr);
+// callbacks of the chunked launch order (host-buffer step): before the first and after the last kernel of chunk c
+struct PatchHooks {
+  void *ctx;
+  int (*before_chunk)(void *ctx, int chunk);
+  int (*after_chunk)(void *ctx, int chunk);
+};
 int patch_prepare(tlfea_newton *s);
-int patch_assemble(tlfea_newton *s, bool tangent, bool damp);
+int patch_assemble(tlfea_newton *s, bool tangent, bool damp, const PatchHooks *hooks = nullptr);
+int patch_chunks(tlfea_newton *s, int *n_chunks, const int **range_ready);
 void patch_release(tlfea_newton *s);
 int patch_stats(tlfea_newton *s, int64_t *out);
 }
@@ -210,6 +217,11 @@ struct tlfea_newton {
   cudaEvent_t ev_pipe[19] = {};
   std::vector<int> pipe_need;  // last coordinate chunk the element chunk j reads
   bool pipe_open = false, pipe_overlapped = false;
+  // single-pass (patch) host-buffer step: per id range, the event after its force gather; the caller's result buffer
+  // (registered before begin) receives finished ranges while later chunks still compute
+  cudaEvent_t ev_g[16] = {};
+  double *h_f_out = nullptr;
+  bool pipe_pk = false, pipe_f_copied = false;
   // timing
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   double ms_total = 0;

@@ -925,6 +925,89 @@ static int pipe_prepare(tlfea_newton *s) {
   return TLFEA_OK;
 }
 
+// Host-buffer step of the single-pass patch assembly.  The launch order is chunked by coefficient-id range
+// (patch_plan.cu): chunk c starts as soon as the c-th part of x, y, z is on the device, and after the last chunk that
+// touches an id range its nodal forces are gathered and (if the caller registered its result buffer) copied back while
+// the remaining chunks compute.  Same kernels, same order as the plain sequence: bit-identical H, f_int, ||g||.
+struct PkPipe {
+  tlfea_newton *s;
+  int K;
+  const int *ready;
+};
+static void pk_range(const tlfea_elem *e, int K, int r, int *i0, int *i1) {
+  *i0 = (int)((int64_t)e->n_coef * r / K);
+  *i1 = (int)((int64_t)e->n_coef * (r + 1) / K);
+}
+static int pk_before_chunk(void *ctx, int c) {
+  PkPipe *pp = static_cast<PkPipe *>(ctx);
+  TL_CUDA(cudaStreamWaitEvent(pp->s->e->stream, pp->s->ev_pipe[c], 0));
+  return TLFEA_OK;
+}
+static int pk_gather_range(tlfea_newton *s, int K, int r) {
+  tlfea_elem *e = s->e;
+  int i0, i1;
+  pk_range(e, K, r, &i0, &i1);
+  if (i1 > i0) {
+    TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)(i1 - i0) * 3, 128), 128, 0, e->stream, i1 - i0,
+              e->pat.d_inc_ptr + i0, e->pat.d_inc_ea, e->d_fe, e->d_f_int + 3 * (int64_t)i0, 0);
+    if (s->h_f_out) {
+      TL_CUDA(cudaEventRecord(s->ev_g[r], e->stream));
+      TL_CUDA(cudaStreamWaitEvent(s->st_copy, s->ev_g[r], 0));
+      TL_CUDA(cudaMemcpyAsync(s->h_f_out + 3 * (int64_t)i0, e->d_f_int + 3 * (int64_t)i0,
+                              (size_t)(i1 - i0) * 3 * sizeof(double), cudaMemcpyDeviceToHost, s->st_copy));
+    }
+  }
+  return TLFEA_OK;
+}
+static int pk_after_chunk(void *ctx, int c) {
+  PkPipe *pp = static_cast<PkPipe *>(ctx);
+  for (int r = 0; r < pp->K; r++)
+    if (pp->ready[r] == c || (c == 0 && pp->ready[r] < 0)) TL_TRY(pk_gather_range(pp->s, pp->K, r));
+  return TLFEA_OK;
+}
+
+static int assemble_host_begin_pk(tlfea_newton *s, const double *hx, const double *hy, const double *hz, bool damp) {
+  tlfea_elem *e = s->e;
+  int K = 1;
+  const int *ready = nullptr;
+  TL_TRY(patch_chunks(s, &K, &ready));
+  if (!s->st_copy) TL_CUDA(cudaStreamCreateWithFlags(&s->st_copy, cudaStreamNonBlocking));
+  for (int k = 0; k < K; k++) {
+    if (!s->ev_pipe[k]) TL_CUDA(cudaEventCreateWithFlags(&s->ev_pipe[k], cudaEventDisableTiming));
+    if (!s->ev_g[k]) TL_CUDA(cudaEventCreateWithFlags(&s->ev_g[k], cudaEventDisableTiming));
+  }
+  for (int k : {PIPE_EV_TAIL, PIPE_EV_RES})
+    if (!s->ev_pipe[k]) TL_CUDA(cudaEventCreateWithFlags(&s->ev_pipe[k], cudaEventDisableTiming));
+  cudaStream_t m = e->stream, c = s->st_copy;
+  TL_CUDA(cudaEventRecord(s->ev_pipe[PIPE_EV_TAIL], m));  // the copies may not overtake queued readers of x, y, z
+  TL_CUDA(cudaStreamWaitEvent(c, s->ev_pipe[PIPE_EV_TAIL], 0));
+  for (int r = 0; r < K; r++) {
+    int i0, i1;
+    pk_range(e, K, r, &i0, &i1);
+    const size_t bytes = (size_t)(i1 - i0) * sizeof(double);
+    if (bytes) {
+      TL_CUDA(cudaMemcpyAsync(e->d_x + i0, hx + i0, bytes, cudaMemcpyHostToDevice, c));
+      TL_CUDA(cudaMemcpyAsync(e->d_y + i0, hy + i0, bytes, cudaMemcpyHostToDevice, c));
+      TL_CUDA(cudaMemcpyAsync(e->d_z + i0, hz + i0, bytes, cudaMemcpyHostToDevice, c));
+    }
+    TL_CUDA(cudaEventRecord(s->ev_pipe[r], c));
+  }
+  PkPipe ctx{s, K, ready};
+  PatchHooks hooks{&ctx, pk_before_chunk, pk_after_chunk};
+  TL_CUDA(cudaEventRecord(s->ev[0], m));
+  TL_TRY(patch_assemble(s, true, damp, &hooks));
+  if (s->n_cons_slots > 0)
+    TL_LAUNCH(k_add_constraint_term, blocks_for(s->n_cons_slots, 256), 256, 0, m, s->n_cons_slots, s->d_cons_slot,
+              s->d_cons_val, s->prm.time_step * s->prm.time_step * s->prm.rho, s->d_H);
+  TL_CUDA(cudaEventRecord(s->ev[1], m));
+  TL_CUDA(cudaGetLastError());
+  s->pipe_open = true;
+  s->pipe_overlapped = false;
+  s->pipe_pk = true;
+  s->pipe_f_copied = (s->h_f_out != nullptr);
+  return TLFEA_OK;
+}
+
 static int assemble_host_begin(tlfea_newton *s, const double *hx, const double *hy, const double *hz) {
   tlfea_elem *e = s->e;
   TL_CHECK(!s->pipe_open, "assemble_host_begin called twice without assemble_host_end");
@@ -938,7 +1021,9 @@ static int assemble_host_begin(tlfea_newton *s, const double *hx, const double *
            "the element's sparsity pattern was rebuilt after AnalyzeHessianSparsity: create a new solver");
   TL_TRY(refresh_constraints(s));
   const bool damp = (e->eta != 0.0 || e->lambda_d != 0.0);
-  bool overlap = ek_supported(s) && !pk_selected(s);
+  s->pipe_pk = false;
+  if (pk_selected(s)) return assemble_host_begin_pk(s, hx, hy, hz, damp);
+  bool overlap = ek_supported(s);
   EkPlan pl;
   if (overlap) {
     TL_TRY(pl.init(s, true, damp));
@@ -1013,8 +1098,12 @@ static int assemble_host_end(tlfea_newton *s, double *h_f_int, double *norm_g) {
   }
   // the copies back to the host run on the copy engines while the rows are reduced
   if (norm_g) TL_CUDA(cudaMemcpyAsync(s->h_scal, s->d_scal + 4, sizeof(double), cudaMemcpyDeviceToHost, m));
-  if (h_f_int) TL_CUDA(cudaMemcpyAsync(h_f_int, e->d_f_int, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, m));
+  const bool f_done = s->pipe_pk && s->pipe_f_copied && h_f_int == s->h_f_out;  // ranges went back as they finished
+  if (h_f_int && !f_done)
+    TL_CUDA(cudaMemcpyAsync(h_f_int, e->d_f_int, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, m));
   TL_CUDA(cudaStreamSynchronize(m));
+  if (s->pipe_pk && s->pipe_f_copied) TL_CUDA(cudaStreamSynchronize(s->st_copy));
+  s->pipe_pk = false;
   if (norm_g) *norm_g = std::sqrt(s->h_scal[0]);
   if (s->pipe_overlapped) {  // H is complete, and later main-stream work is ordered after it
     TL_CUDA(cudaEventSynchronize(s->ev_pipe[PIPE_EV_ROWS]));
@@ -1089,6 +1178,8 @@ int tlfea_newton_destroy(tlfea_newton *s) {
   if (s->st_copy) cudaStreamDestroy(s->st_copy);
   if (s->st_rows) cudaStreamDestroy(s->st_rows);
   for (auto &ev : s->ev_pipe)
+    if (ev) cudaEventDestroy(ev);
+  for (auto &ev : s->ev_g)
     if (ev) cudaEventDestroy(ev);
   dfree(s->d_scal);
   if (s->h_scal) cudaFreeHost(s->h_scal);
@@ -1206,6 +1297,14 @@ int tlfea_newton_assemble_host_begin(tlfea_newton *s, const double *x, const dou
   TL_CHECK(s && x && y && z, "null input");
   TL_CHECK(n == s->e->n_coef, "Position vector size mismatch.");
   return assemble_host_begin(s, x, y, z);
+}
+
+int tlfea_newton_set_host_result_buffer(tlfea_newton *s, double *f_int_host, int n) {
+  TL_CHECK(s, "null handle");
+  TL_CHECK(!f_int_host || n == 3 * s->e->n_coef, "size mismatch");
+  TL_CHECK(!s->pipe_open, "a host-buffer step is in flight");
+  s->h_f_out = f_int_host;
+  return TLFEA_OK;
 }
 
 int tlfea_newton_assemble_host_end(tlfea_newton *s, double *f_int, int n, double *norm_g) {

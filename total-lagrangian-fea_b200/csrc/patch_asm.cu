@@ -12,8 +12,8 @@ namespace tlfea {
 
 struct PatchPlanDev {
   int W = 0;
-  int n_patches = 0, n_colors = 0;
-  std::vector<int> color_ptr;
+  int n_patches = 0, n_colors = 0, n_chunks = 1;
+  std::vector<int> color_ptr, range_ready;
   PatchDesc *d_desc = nullptr;
   PElem *d_elems = nullptr;
   unsigned char *d_blob = nullptr;
@@ -53,6 +53,15 @@ static int blob_limit(int W, int model) {
   return std::min(PKShape<false, TL_MODEL_SVK>::scratch_bytes(W), PKShape<true, TL_MODEL_SVK>::scratch_bytes(W));
 }
 
+static int patch_chunk_count() {
+  static int k = [] {
+    const char *e = getenv("TLFEA_PK_CHUNKS");  // id-range chunks of the launch order (host-buffer pipelining)
+    const int v = e ? atoi(e) : 4;
+    return std::min(std::max(v, 1), 16);
+  }();
+  return k;
+}
+
 int patch_warps() {
   static int w = [] {
     const char *e = getenv("TLFEA_PK_W");  // warps (= sub-patches) per patch: 4 (two CTAs per SM) or 8
@@ -80,7 +89,7 @@ int patch_prepare(tlfea_newton *s) {
   PatchPlanHost hp;
   std::string err;
   const int rc = build_patch_plan(e->n_elem, e->n_coef, ecoef.data(), x.data(), y.data(), z.data(), off.data(),
-                                  cols.data(), W, blob_limit(W, e->model), &hp, &err);
+                                  cols.data(), W, blob_limit(W, e->model), patch_chunk_count(), &hp, &err);
   if (rc != TLFEA_OK) return fail(rc, "%s", err.c_str());
   auto *pp = new PatchPlanDev();
   s->patch = pp;
@@ -88,6 +97,8 @@ int patch_prepare(tlfea_newton *s) {
   pp->n_patches = hp.n_patches;
   pp->n_colors = hp.n_colors;
   pp->color_ptr = hp.color_ptr;
+  pp->n_chunks = hp.n_chunks;
+  pp->range_ready = hp.range_ready;
   pp->max_blob = hp.max_blob_bytes;
   pp->sum_local_blocks = hp.sum_local_blocks;
   pp->blob_bytes = (int64_t)hp.blob.size();
@@ -106,6 +117,18 @@ int patch_prepare(tlfea_newton *s) {
     TL_TRY(dmalloc(&pp->d_unc_row, row.size()));
     TL_CUDA(cudaMemcpy(pp->d_unc, hp.uncovered.data(), hp.uncovered.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
     TL_CUDA(cudaMemcpy(pp->d_unc_row, row.data(), row.size() * sizeof(int), cudaMemcpyHostToDevice));
+  }
+  return TLFEA_OK;
+}
+
+// the plan for the configuration that will run (patch width follows the material model)
+static int ensure_plan(tlfea_newton *s) {
+  TL_TRY(patch_prepare(s));
+  auto *pp = static_cast<PatchPlanDev *>(s->patch);
+  const int want_w = (s->e->model == TL_MODEL_MR) ? 4 : (s->pk_w ? s->pk_w : patch_warps());
+  if (want_w != pp->W) {  // the material model changed under a live plan
+    patch_release(s);
+    TL_TRY(patch_prepare(s));
   }
   return TLFEA_OK;
 }
@@ -141,16 +164,10 @@ static int launch_pk(tlfea_elem *e, const PatchPlanDev *pp, const PKArgs &a, int
 }
 
 // Element forces fe (always) and, with tangent, H = M/h + h K_t (+ C_visc) in place, colour by colour.
-int patch_assemble(tlfea_newton *s, bool tangent, bool damp) {
+int patch_assemble(tlfea_newton *s, bool tangent, bool damp, const PatchHooks *hooks) {
   tlfea_elem *e = s->e;
-  TL_TRY(patch_prepare(s));
+  TL_TRY(ensure_plan(s));
   auto *pp = static_cast<PatchPlanDev *>(s->patch);
-  const int want_w = (e->model == TL_MODEL_MR) ? 4 : (s->pk_w ? s->pk_w : patch_warps());
-  if (want_w != pp->W) {  // the material model changed under a live plan
-    patch_release(s);
-    TL_TRY(patch_prepare(s));
-    pp = static_cast<PatchPlanDev *>(s->patch);
-  }
   const double h = s->prm.time_step;
   if (tangent && pp->mass_version_seen != e->mass_version) {
     TL_LAUNCH(pk_fill_mass_kernel, pp->n_patches, 128, 0, e->stream, pp->n_patches, e->n_coef, pp->d_desc, pp->d_blob,
@@ -194,11 +211,24 @@ int patch_assemble(tlfea_newton *s, bool tangent, bool damp) {
   if (pp->n_unc > 0)
     TL_LAUNCH(pk_uncovered_kernel, blocks_for(pp->n_unc, 256), 256, 0, e->stream, pp->n_unc, pp->d_unc, e->pat.d_off,
               pp->d_unc_row, e->d_mass, 1.0 / h, s->d_H);
-  for (int c = 0; c < pp->n_colors; c++) {
-    const int p0 = pp->color_ptr[c], np = pp->color_ptr[c + 1] - p0;
-    TL_TRY((damp ? launch_pk<true, true>(e, pp, a, p0, np) : launch_pk<false, true>(e, pp, a, p0, np)));
+  for (int ch = 0; ch < pp->n_chunks; ch++) {
+    if (hooks && hooks->before_chunk) TL_TRY(hooks->before_chunk(hooks->ctx, ch));
+    for (int c = 0; c < pp->n_colors; c++) {
+      const int l = ch * pp->n_colors + c;
+      const int p0 = pp->color_ptr[l], np = pp->color_ptr[l + 1] - p0;
+      TL_TRY((damp ? launch_pk<true, true>(e, pp, a, p0, np) : launch_pk<false, true>(e, pp, a, p0, np)));
+    }
+    if (hooks && hooks->after_chunk) TL_TRY(hooks->after_chunk(hooks->ctx, ch));
   }
   TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
+
+int patch_chunks(tlfea_newton *s, int *n_chunks, const int **range_ready) {
+  TL_TRY(ensure_plan(s));
+  auto *pp = static_cast<PatchPlanDev *>(s->patch);
+  *n_chunks = pp->n_chunks;
+  *range_ready = pp->range_ready.data();
   return TLFEA_OK;
 }
 
@@ -211,6 +241,7 @@ int patch_stats(tlfea_newton *s, int64_t *out) {
   out[3] = pp->sum_local_blocks;
   out[4] = pp->blob_bytes;
   out[5] = pp->n_unc;
+  out[6] = pp->n_chunks;
   return TLFEA_OK;
 }
 

@@ -97,7 +97,8 @@ void assign_slots(int nb, const std::vector<std::vector<int>> &sets, std::vector
 }  // namespace
 
 int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y, const double *z,
-                     const int *off, const int *cols, int W, int blob_limit, PatchPlanHost *out, std::string *err) {
+                     const int *off, const int *cols, int W, int blob_limit, int n_chunks, PatchPlanHost *out,
+                     std::string *err) {
   auto failm = [&](int code, const char *m) {
     if (err) *err = m;
     return code;
@@ -358,23 +359,46 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   std::vector<int>().swap(npat);
   std::vector<int>().swap(nptr);
 
-  // ---- 5. launch order (colour, Morton), first-touch flags, concatenation
+  // ---- 5. launch order, first-touch flags, concatenation.
+  // Launch l = chunk * n_colors + colour.  Chunk c holds the patches whose LARGEST coefficient id falls into the c-th
+  // of n_chunks equal id ranges: its kernels read no coordinate beyond that range (a host-buffer step starts them as
+  // soon as that part of x, y, z has been uploaded), and once a chunk is done every coefficient whose patches all
+  // lie in chunks <= c is final (its force can travel back to the host while later chunks compute).
+  const int K = std::max(1, std::min(n_chunks, 16));
+  std::vector<int> chunk_of((size_t)np, 0), node_final((size_t)n_coef, -1);
+  for (int p = 0; p < np; p++) {
+    const int mxid = pl[p]->nodes.empty() ? 0 : pl[p]->nodes.back();
+    chunk_of[p] = (int)std::min<int64_t>(K - 1, (int64_t)mxid * K / std::max(n_coef, 1));
+  }
+  for (int p = 0; p < np; p++)
+    for (int nd : pl[p]->nodes) node_final[nd] = std::max(node_final[nd], chunk_of[p]);
   std::vector<int> perm((size_t)np);
   for (int p = 0; p < np; p++) perm[p] = p;
-  std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return pl[a]->color < pl[b]->color; });
+  std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) {
+    return chunk_of[a] != chunk_of[b] ? chunk_of[a] < chunk_of[b] : pl[a]->color < pl[b]->color;
+  });
   PatchPlanHost &R = *out;
   R = PatchPlanHost();
   R.W = W;
   R.n_patches = np;
   R.n_colors = n_colors;
-  R.color_ptr.assign((size_t)n_colors + 1, 0);
-  for (int p = 0; p < np; p++) R.color_ptr[(size_t)pl[p]->color + 1]++;
-  for (int c = 0; c < n_colors; c++) R.color_ptr[c + 1] += R.color_ptr[c];
+  R.n_chunks = K;
+  const int n_launch = K * n_colors;
+  R.color_ptr.assign((size_t)n_launch + 1, 0);
+  for (int p = 0; p < np; p++) R.color_ptr[(size_t)chunk_of[p] * n_colors + pl[p]->color + 1]++;
+  for (int c = 0; c < n_launch; c++) R.color_ptr[c + 1] += R.color_ptr[c];
+  R.range_ready.assign((size_t)K, -1);
+  for (int r = 0; r < K; r++) {
+    const int64_t i0 = (int64_t)n_coef * r / K, i1 = (int64_t)n_coef * (r + 1) / K;
+    int m = -1;
+    for (int64_t i = i0; i < i1; i++) m = std::max(m, node_final[(size_t)i]);
+    R.range_ready[r] = m;
+  }
 
   const int64_t nnz = off[n_coef];
   std::vector<uint8_t> covered((size_t)nnz, 0);
-  for (int c = 0; c < n_colors; c++) {
-    // patches of one colour share no coefficient, hence no pattern block: no two threads touch the same byte
+  for (int c = 0; c < n_launch; c++) {
+    // patches of one launch share no coefficient, hence no pattern block: no two threads touch the same byte
 #pragma omp parallel for schedule(dynamic, 64)
     for (int q = R.color_ptr[c]; q < R.color_ptr[c + 1]; q++) {
       PatchLocal &P = *pl[perm[q]];
@@ -464,11 +488,11 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
 extern "C" {
 
 int tlfea_debug_patch_plan_build(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y,
-                                 const double *z, const int *off, const int *cols, int W, void **plan_out) {
+                                 const double *z, const int *off, const int *cols, int W, int n_chunks, void **plan_out) {
   TL_CHECK(ecoef && x && y && z && off && cols && plan_out, "null input");
   auto *p = new tlfea::PatchPlanHost();
   std::string err;
-  const int rc = tlfea::build_patch_plan(n_elem, n_coef, ecoef, x, y, z, off, cols, W, 1 << 20, p, &err);
+  const int rc = tlfea::build_patch_plan(n_elem, n_coef, ecoef, x, y, z, off, cols, W, 1 << 20, n_chunks, p, &err);
   if (rc != TLFEA_OK) {
     delete p;
     return tlfea::fail(rc, "%s", err.c_str());
@@ -481,7 +505,7 @@ int tlfea_debug_patch_plan_sizes(void *plan, int64_t *sizes) {
   TL_CHECK(plan && sizes, "null input");
   auto *p = static_cast<tlfea::PatchPlanHost *>(plan);
   sizes[0] = p->n_patches;
-  sizes[1] = p->n_colors;
+  sizes[1] = (int64_t)p->color_ptr.size() - 1;  // launches = chunks * colours
   sizes[2] = (int64_t)p->elems.size();
   sizes[3] = (int64_t)p->row_node.size();
   sizes[4] = (int64_t)p->blob.size();

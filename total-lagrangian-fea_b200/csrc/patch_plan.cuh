@@ -74,8 +74,9 @@ struct BlobLayout {
 
 struct PatchPlanHost {
   int W = 0;
-  int n_patches = 0, n_colors = 0;
-  std::vector<int> color_ptr;  // launch c runs patches [color_ptr[c], color_ptr[c+1])
+  int n_patches = 0, n_colors = 0, n_chunks = 1;
+  std::vector<int> color_ptr;    // launch l = chunk * n_colors + colour runs patches [color_ptr[l], color_ptr[l+1])
+  std::vector<int> range_ready;  // [n_chunks] last chunk that touches a coefficient of the r-th id range (-1: none)
   std::vector<PatchDesc> desc;
   std::vector<PElem> elems;
   std::vector<unsigned char> blob;  // all patches, each 16-byte aligned
@@ -87,9 +88,11 @@ struct PatchPlanHost {
 };
 
 // Pure host code (no CUDA call): ecoef [n_elem][10]; x, y, z reference coordinates per coefficient; off / cols the
-// coefficient-level CSR pattern (sorted columns); blob_limit = largest write-out blob (bytes) a patch may have.
+// coefficient-level CSR pattern (sorted columns); n_chunks = id-range chunks of the launch order (1 = colours only);
+// blob_limit = largest write-out blob (bytes) a patch may have.
 // Returns 0 or a negative tlfea_status with *err set.
 int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y, const double *z,
-                     const int *off, const int *cols, int W, int blob_limit, PatchPlanHost *out, std::string *err);
+                     const int *off, const int *cols, int W, int blob_limit, int n_chunks, PatchPlanHost *out,
+                     std::string *err);
 
 }  // namespace tlfea

@@ -100,6 +100,7 @@ _SIGS = {
     "tlfea_newton_residual": (C.c_int, [c_vp, c_dp]),
     "tlfea_newton_assemble_host_begin": (C.c_int, [c_vp, c_dp, c_dp, c_dp, C.c_int]),
     "tlfea_newton_assemble_host_end": (C.c_int, [c_vp, c_dp, C.c_int, c_dp]),
+    "tlfea_newton_set_host_result_buffer": (C.c_int, [c_vp, c_dp, C.c_int]),
     "tlfea_newton_solve_step": (C.c_int, [c_vp]),
     "tlfea_newton_last_stats": (C.c_int, [c_vp, c_ip, c_ip, c_dp, c_dp]),
     "tlfea_newton_set_pcg": (C.c_int, [c_vp, C.c_int, C.c_double]),
@@ -128,7 +129,7 @@ _SIGS = {
     "tlfea_dist_pack": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
     "tlfea_dist_unpack": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
     "tlfea_fp64_peak": (C.c_int, [C.c_int, c_dp]),
-    "tlfea_debug_patch_plan_build": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_dp, c_ip, c_ip, C.c_int,
+    "tlfea_debug_patch_plan_build": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_dp, c_ip, c_ip, C.c_int, C.c_int,
                                                C.POINTER(c_vp)]),
     "tlfea_debug_patch_plan_sizes": (C.c_int, [c_vp, c_i64p]),
     "tlfea_debug_patch_plan_copy": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),

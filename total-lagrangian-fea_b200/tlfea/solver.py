@@ -78,11 +78,16 @@ class SyncedNewtonSolver(SolverBase):
     def AssembleForce(self):
         check(lib.tlfea_newton_assemble_force(self._h))
 
-    def AssembleFromHostBegin(self, x, y, z):
+    def AssembleFromHostBegin(self, x, y, z, out=None):
         """UpdatePositions(x, y, z) + Assemble with the H2D copies overlapped with the element kernel
         (tlfea_newton_assemble_host_begin).  Returns without waiting; x, y, z must stay alive (and unchanged)
-        until AssembleFromHostEnd returns -- pass pinned float64 arrays for a truly asynchronous copy."""
+        until AssembleFromHostEnd returns -- pass pinned float64 arrays for a truly asynchronous copy.
+        out: the (pinned, contiguous float64) array AssembleFromHostEnd will be given; known here, finished parts of
+        f_int travel back under the remaining kernels (single-pass FEAT10 path; nothing may touch f_int in between)."""
         n = self.data.n_coef
+        if out is not None and not (out.dtype == np.float64 and out.flags["C_CONTIGUOUS"] and out.shape == (3 * n,)):
+            out = None
+        check(lib.tlfea_newton_set_host_result_buffer(self._h, _d(out) if out is not None else None, 3 * n))
         self._pipe_in = tuple(np.ascontiguousarray(a, dtype=np.float64) for a in (x, y, z))
         check(lib.tlfea_newton_assemble_host_begin(self._h, *(_d(a) for a in self._pipe_in), n))
 
@@ -98,7 +103,7 @@ class SyncedNewtonSolver(SolverBase):
         return ng.value, out
 
     def AssembleFromHost(self, x, y, z, out=None):
-        self.AssembleFromHostBegin(x, y, z)
+        self.AssembleFromHostBegin(x, y, z, out)
         return self.AssembleFromHostEnd(out)
 
     def Residual(self) -> float:
