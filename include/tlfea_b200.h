@@ -229,6 +229,11 @@ int tlfea_newton_set_assembly(tlfea_newton *s, int mode);
 /* Warps (= sub-patches) per patch of the single-pass assembly: 4 (two CTAs per SM, default) or 8.  Takes effect
  * when the plan is (re)built, i.e. before the first assemble.  New design, no reference line. */
 int tlfea_newton_set_patch_warps(tlfea_newton *s, int warps);
+/* Affine-element compression of the single-pass FEAT10 assembly: straight-sided tets are integrated from
+ * J^-T | detJ (80 B per element, found at CalcDnDuPre) instead of the 150 stored gradients + 5 detJ (1 240 B); curved
+ * elements keep the stored gradients.  Results agree to rounding.  Off by default (it trades HBM bytes for issue slots
+ * and the kernel is issue-bound); TLFEA_PK_AFFINE=1 turns it on for solvers that never call this. */
+int tlfea_newton_set_affine_compression(tlfea_newton *s, int on);
 /* out[8] = patches, colours, warps per patch, sum over patches of their distinct node pairs, bytes of write-out
  * lists, pattern blocks no element touches, 0, 0 (valid after the first FEAT10 assemble in mode 2) */
 int tlfea_newton_patch_stats(tlfea_newton *s, int64_t *out);

@@ -188,3 +188,35 @@ def test_setup_rejects_repeated_ids():
     d2.Initialize()
     with pytest.raises(tlfea.TlfeaError):
         d2.SetNodalFixed(np.array([1, 4, 1], dtype=np.int32))
+
+
+@pytest.mark.parametrize("frac_curved", [1.0, 0.3])
+def test_curved_and_affine_elements_mixed(frac_curved):
+    """Affine-element compression: straight-sided tets are assembled from J^-T | detJ (80 B), curved ones
+    from the stored gradients (1 240 B).  Here the REFERENCE mid-edge nodes of some elements are moved off their edge
+    midpoints, so both kinds (and pairs mixing them) go through the patch kernel; all against the oracle."""
+    from oracle import oracle as orc
+    from tlfea import meshgen
+
+    X, E = meshgen.kuhn_block(4)
+    rng = np.random.Generator(np.random.PCG64(21))
+    Xc = X.copy()
+    mids = np.unique(E[:, 4:])
+    pick = mids[rng.uniform(size=mids.size) < frac_curved]
+    Xc[pick] += 0.01 * rng.uniform(-1, 1, size=(pick.size, 3))
+    x = Xc + 0.01 * rng.uniform(-1, 1, size=X.shape)
+    o = orc.T10Oracle(E, Xc)
+    mat = _mat(orc, "svk", False)
+    f_ref, _, _ = o.force(x, mat)
+    H_ref = o.hessian(x, mat, H_STEP, RHO)
+    d, s = _make(Xc, E)
+    assert rel_err(d.RetrieveDnDuPreToCPU().reshape(o.grad_N.shape), o.grad_N) < TOL
+    d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
+    Hs = []
+    for on in (True, False):
+        s.SetAffineCompression(on)
+        s.Assemble()
+        assert rel_err(d.RetrieveInternalForceToCPU(), f_ref) < TOL
+        Hs.append(s.RetrieveHessianValues())
+        assert rel_err(Hs[-1], H_ref) < TOL
+    assert not np.array_equal(Hs[0], Hs[1]) or frac_curved == 1.0  # the compressed path really ran

@@ -15,7 +15,7 @@ PDESC = np.dtype([("sub_ptr", "<i4", (9,)), ("n_sub", "<i4"), ("n_ent", "<i4"), 
                   ("blob_off", "<u4"), ("hbase", "<i8")])
 TILES = [(0, j) for j in range(5)] + [(1, j) for j in range(1, 5)] + [(2, j) for j in range(2, 5)] + \
         [(3, 3), (3, 4), (4, 4)]
-CAPU = 216
+CAPU = 210
 
 
 def build_plan(E, X, off, cols, W, n_chunks=1):

@@ -125,6 +125,13 @@ struct tlfea_elem {
   double *d_xr = nullptr, *d_yr = nullptr, *d_zr = nullptr;        // reference coefficients (x12_jac,..)
   double *d_gradN = nullptr;  // [n_elem][Q][3S]
   double *d_detJ = nullptr;   // [n_elem][Q]
+  // FEAT10 affine-element compression: straight-sided tets have a constant Jacobian, so the 150 reference
+  // gradients of an element are J^-T times 150 mesh-independent numbers.  d_aff[e] = J^-T (9, row-major) | detJ;
+  // d_aff_flag[e] = 1 where the element is affine (else the kernels read d_gradN / d_detJ as before)
+  double *d_aff = nullptr;
+  unsigned char *d_aff_flag = nullptr;
+  int aff_version = 0;        // bumped by CalcDnDuPre
+  double t10_dn[150];         // dN_a/dxi_k at the caller's quadrature points: [q][a][k]
   double *d_F = nullptr, *d_P = nullptr;  // [n_elem][Q][9], allocated on first CalcP
   double *d_f_int = nullptr, *d_f_ext = nullptr;
   double *d_fe = nullptr;     // [n_elem][S][3] element force staging
@@ -178,6 +185,7 @@ struct tlfea_newton {
   int asm_mode = 2;
   void *patch = nullptr;  // PatchPlanDev (patch_asm.cu)
   int pk_w = 0;           // warps per patch (0 = TLFEA_PK_W or 4)
+  int pk_affine = -1;     // affine-element compression: -1 = TLFEA_PK_AFFINE (default off), 0 off, 1 on
   int n_constraints = 0;
   tlfea_newton_params prm{};
   bool analyzed = false, fixed_pattern = false;

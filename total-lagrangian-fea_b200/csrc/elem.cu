@@ -133,6 +133,61 @@ __global__ void t10_precompute_kernel(int n_elem, const int *__restrict__ ecoef,
   }
 }
 
+// Affine detection + compressed record: J at the 5 points; if it does not vary (1e-12 of its largest
+// entry) the element is straight-sided and gradN[q][j][a] = sum_k Ginv[j][k] dN_a/dxi_k(q) with Ginv = J^-T.
+__global__ void t10_affine_kernel(int n_elem, const int *__restrict__ ecoef, const double *__restrict__ x,
+                                  const double *__restrict__ y, const double *__restrict__ z, T10Quad qd, double *aff,
+                                  unsigned char *flag) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_elem) return;
+  double X[10][3];
+#pragma unroll
+  for (int a = 0; a < 10; a++) {
+    const int c = ecoef[(int64_t)e * 10 + a];
+    X[a][0] = x[c], X[a][1] = y[c], X[a][2] = z[c];
+  }
+  double J0[3][3], dmax = 0.0, jmax = 0.0;
+  for (int q = 0; q < 5; q++) {
+    double dN[10][3], J[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+    t10_dN(qd.x[q], qd.y[q], qd.z[q], dN);
+#pragma unroll
+    for (int a = 0; a < 10; a++)
+#pragma unroll
+      for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) J[i][j] += X[a][i] * dN[a][j];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+      for (int j = 0; j < 3; j++) {
+        if (q == 0) J0[i][j] = J[i][j], jmax = fmax(jmax, fabs(J[i][j]));
+        dmax = fmax(dmax, fabs(J[i][j] - J0[i][j]));
+      }
+  }
+  const double det = J0[0][0] * (J0[1][1] * J0[2][2] - J0[1][2] * J0[2][1]) -
+                     J0[0][1] * (J0[1][0] * J0[2][2] - J0[1][2] * J0[2][0]) +
+                     J0[0][2] * (J0[1][0] * J0[2][1] - J0[1][1] * J0[2][0]);
+  double JT[3][3];
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) JT[i][j] = J0[j][i];
+  double *o = aff + (int64_t)e * 10;
+  bool ok = (dmax <= 1e-12 * jmax) && jmax > 0.0;
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const double ek[3] = {k == 0 ? 1.0 : 0.0, k == 1 ? 1.0 : 0.0, k == 2 ? 1.0 : 0.0};
+    double hcol[3];
+    solve3_pp(JT, ek, hcol);  // column k of J^-T (zero if a pivot vanishes: then the general path keeps the element)
+    ok = ok && (hcol[0] != 0.0 || hcol[1] != 0.0 || hcol[2] != 0.0);
+    o[0 * 3 + k] = hcol[0];
+    o[1 * 3 + k] = hcol[1];
+    o[2 * 3 + k] = hcol[2];
+  }
+  o[9] = det;
+  flag[e] = ok ? 1 : 0;
+}
+
 // element mass matrix rho * sum_q N_a N_b detJ w  (mass_matrix_qp_kernel, FEAT10Data.cu:206-278)
 __global__ void t10_elem_mass_kernel(int n_elem, const double *__restrict__ detJ, T10Quad qd, double rho,
                                      double *Me) {
@@ -367,6 +422,8 @@ int tlfea_elem_destroy(tlfea_elem *h) {
   dfree(h->d_yr);
   dfree(h->d_zr);
   dfree(h->d_gradN);
+  dfree(h->d_aff);
+  dfree(h->d_aff_flag);
   dfree(h->d_detJ);
   dfree(h->d_F);
   dfree(h->d_P);
@@ -650,6 +707,22 @@ int tlfea_elem_precompute(tlfea_elem *h) {
     // reference gradients are taken at the CURRENT coordinates, as dn_du_pre_kernel reads x12
     TL_LAUNCH(t10_precompute_kernel, blocks_for((int64_t)h->n_elem * 5, 128), 128, 0, h->stream, h->n_elem,
               h->d_ecoef, h->d_x, h->d_y, h->d_z, qd, h->d_gradN, h->d_detJ);
+    if (!h->d_aff) TL_TRY(dmalloc(&h->d_aff, (size_t)h->n_elem * 10));
+    if (!h->d_aff_flag) TL_TRY(dmalloc(&h->d_aff_flag, (size_t)h->n_elem));
+    TL_LAUNCH(t10_affine_kernel, blocks_for(h->n_elem, 128), 128, 0, h->stream, h->n_elem, h->d_ecoef, h->d_x, h->d_y,
+              h->d_z, qd, h->d_aff, h->d_aff_flag);
+    for (int q = 0; q < 5; q++) {  // the mesh-independent table dN_a/dxi_k at the caller's points (host copy)
+      const double xi = qd.x[q], eta = qd.y[q], zeta = qd.z[q];
+      const double L[4] = {1.0 - xi - eta - zeta, xi, eta, zeta};
+      const double dL[4][3] = {{-1.0, -1.0, -1.0}, {1.0, 0.0, 0.0}, {0.0, 1.0, 0.0}, {0.0, 0.0, 1.0}};
+      const int ed[6][2] = {{0, 1}, {1, 2}, {0, 2}, {0, 3}, {1, 3}, {2, 3}};
+      for (int a = 0; a < 4; a++)
+        for (int k = 0; k < 3; k++) h->t10_dn[(q * 10 + a) * 3 + k] = (4.0 * L[a] - 1.0) * dL[a][k];
+      for (int m = 0; m < 6; m++)
+        for (int k = 0; k < 3; k++)
+          h->t10_dn[(q * 10 + 4 + m) * 3 + k] = 4.0 * (L[ed[m][0]] * dL[ed[m][1]][k] + L[ed[m][1]] * dL[ed[m][0]][k]);
+    }
+    h->aff_version++;
     TL_CUDA(cudaGetLastError());
   } else {
     TL_TRY(ancf_precompute(h));

@@ -1613,6 +1613,11 @@ int tlfea_newton_set_patch_warps(tlfea_newton *s, int warps) {
   s->pk_w = warps;
   return TLFEA_OK;
 }
+int tlfea_newton_set_affine_compression(tlfea_newton *s, int on) {
+  TL_CHECK(s, "null handle");
+  s->pk_affine = on ? 1 : 0;
+  return TLFEA_OK;
+}
 int tlfea_newton_patch_stats(tlfea_newton *s, int64_t *out) {
   TL_CHECK(s && out, "null input");
   for (int i = 0; i < 8; i++) out[i] = 0;

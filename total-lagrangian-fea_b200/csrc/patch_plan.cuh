@@ -18,7 +18,7 @@
 
 namespace tlfea {
 
-constexpr int PK_CAPU = 216;    // 3x3 blocks per warp accumulator (a Kuhn cell of 6 tets needs 210)
+constexpr int PK_CAPU = 210;    // 3x3 blocks per warp accumulator (a Kuhn cell of 6 tets needs exactly 210)
 constexpr int PK_MAXW = 8;      // sub-patches (= warps) per patch
 constexpr int PK_MAX_ROWLEN = 65535;
 

@@ -40,6 +40,8 @@ struct PKArgs {
   const double *x, *y, *z;
   const double *v;  // interleaved velocity (Kelvin-Voigt) or nullptr
   const double *gradN, *detJ;
+  const double *aff;  // [n_elem][10] J^-T | detJ of affine elements (plan record bit 0 of pad0), or nullptr
+  double dn[150];     // dN_a/dxi_k at the quadrature points, [q][a][k]: gradN of an affine element = J^-T dn
   QuadW qw;
   double lambda, mu, eta, lambda_d;
   double c1, c2, c3, c4;  // c1 = h lambda + lambda_d, c2 = c3 = h mu + eta, c4 = h
@@ -91,6 +93,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   __shared__ uint64_t s_bar[W][2];
   __shared__ uint64_t s_bar_blob;
   __shared__ PatchDesc s_desc[2];  // this CTA's current and next patch
+  __shared__ double s_dn[150];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *acc = pk_smem + (size_t)warp * Sh::ACC_D;
   double *wb = pk_smem + (size_t)W * Sh::ACC_D + (size_t)warp * Sh::PREF_D;  // prefetch buffers of this warp
@@ -111,6 +114,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     mbar_init(&s_bar[warp][1], 1);
   }
   if (threadIdx.x == 0) mbar_init(&s_bar_blob, 1);
+  for (int i = threadIdx.x; i < 150; i += NT) s_dn[i] = p.dn[i];
   __syncthreads();
   if (TANGENT && threadIdx.x == 0)  // the write-out lists are needed last: pull them into L2 now
     bulk_prefetch_l2(p.blob + (size_t)s_desc[0].blob_off * 16,
@@ -125,21 +129,27 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   auto issue_data = [&](int ne, int buf) {
     const PElem *pe = reinterpret_cast<const PElem *>(wb + Sh::OFF_PE + buf * Sh::PE_D);
     double *dh = wb + Sh::OFF_H + buf * Sh::H_D;
+    // affine elements (plan record flag): 80 bytes of J^-T | detJ instead of 1200 bytes of gradients + 40 of detJ
+    const bool af0 = p.aff && (pe[0].pad0 & 1), af1 = p.aff && ne > 1 && (pe[1].pad0 & 1);
     if (lane == 0) {
       const unsigned b = (unsigned)__cvta_generic_to_shared(&s_bar[warp][buf]);
+      const unsigned n_bulk = (af0 ? 0u : 1u) + ((ne > 1 && !af1) ? 1u : 0u);
       asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // the buffer was last read by ordinary loads
-      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(b), "r"(ne * 1200u) : "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(b), "r"(n_bulk * 1200u) : "memory");
       for (int el = 0; el < ne; el++) {
+        if (el == 0 ? af0 : af1) continue;
         const unsigned s = (unsigned)__cvta_generic_to_shared(dh + el * 150);
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(s),
                      "l"(p.gradN + (int64_t)pe[el].elem * 150), "r"(1200u), "r"(b)
                      : "memory");
       }
     }
-    double *dj = wb + Sh::OFF_DJ + buf * Sh::DJ_D;
     if (lane < ne * 5) {
       const int el = lane / 5, q = lane - 5 * el;
-      cp_async8(dj + lane, p.detJ + (int64_t)pe[el].elem * 5 + q);
+      if (el == 0 ? af0 : af1)
+        cp_async16(dh + el * 150 + 2 * q, p.aff + (int64_t)pe[el].elem * 10 + 2 * q);
+      else
+        cp_async8(wb + Sh::OFF_DJ + buf * Sh::DJ_D + lane, p.detJ + (int64_t)pe[el].elem * 5 + q);
     }
     double *dx = wb + Sh::OFF_X + buf * Sh::X_D;
     if (lane < ne * 10) {
@@ -230,7 +240,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     __syncwarp();
     // what this lane needs of the plan records, before the buffer is recycled
     unsigned blkw = 0, trb = 0, fsb = 0;
-    int eid[2];
+    int eid[2], affb = 0;
     {
       const PElem *pe = reinterpret_cast<const PElem *>(wb + Sh::OFF_PE + buf * Sh::PE_D);
       const int el = min(el2, ne - 1);
@@ -239,6 +249,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       fsb = (pe[el].first[(tile * 4) >> 5] >> ((tile * 4) & 31)) & 15u;
       eid[0] = pe[0].elem;
       eid[1] = pe[ne - 1].elem;
+      affb = p.aff ? ((pe[0].pad0 & 1) | ((ne > 1 && (pe[1].pad0 & 1)) ? 2 : 0)) : 0;
     }
     __syncwarp();
     {
@@ -264,6 +275,30 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     const double *s_h = wb + Sh::OFF_H + buf * Sh::H_D;
     const double *s_dj = wb + Sh::OFF_DJ + buf * Sh::DJ_D;
     const double *s_x = wb + Sh::OFF_X + buf * Sh::X_D;
+
+    // affine elements: expand gradN[q][j][a] = sum_k Ginv[j][k] dN_a/dxi_k(q) and detJ[q] = detJ in place
+    if (affb) {
+#pragma unroll 1
+      for (int el = 0; el < ne; el++) {
+        if (!((affb >> el) & 1)) continue;
+        double *hh = wb + Sh::OFF_H + buf * Sh::H_D + el * 150;
+        double G[9];
+#pragma unroll
+        for (int i = 0; i < 9; i++) G[i] = hh[i];
+        const double dj0 = hh[9];
+        __syncwarp();
+        for (int idx = lane; idx < 150; idx += 32) {
+          const int q = idx / 30, r = idx - 30 * q, j = r / 10, a = r - 10 * j;
+          const double *dn = s_dn + (q * 10 + a) * 3;
+          const double g0 = j == 0 ? G[0] : (j == 1 ? G[3] : G[6]);
+          const double g1 = j == 0 ? G[1] : (j == 1 ? G[4] : G[7]);
+          const double g2 = j == 0 ? G[2] : (j == 1 ? G[5] : G[8]);
+          hh[idx] = g0 * dn[0] + g1 * dn[1] + g2 * dn[2];
+        }
+        if (lane < 5) (wb + Sh::OFF_DJ + buf * Sh::DJ_D)[el * 5 + lane] = dj0;
+      }
+      __syncwarp();
+    }
 
     // ------------------------------------------------------------ Gauss-point step, Mooney-Rivlin
     // (ek_kernel.cuh: lane = (element, point, row i); T[i][J][k][L] = h dV dP_iJ/dF_kL + Kelvin-Voigt block)
@@ -766,6 +801,12 @@ __global__ void pk_fill_mass_kernel(int n_patches, int n_coef, const PatchDesc *
     const int slot = (int)((habs - 9 * (int64_t)off[lo]) / 3);
     massb[k] = mass[off[lo] + slot];
   }
+}
+
+// plan record flag: bit 0 of pad0 = the element is affine (elem.cu: t10_affine_kernel)
+__global__ void pk_set_affine_kernel(int64_t n, PElem *elems, const unsigned char *__restrict__ flag) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) elems[i].pad0 = flag[elems[i].elem] ? 1 : 0;
 }
 
 // pattern blocks no element touches (constraint couplings, unused coefficients): H block = (M_ij / h) I

@@ -177,6 +177,9 @@ class SyncedNewtonSolver(SolverBase):
     def SetPatchWarps(self, warps: int):
         check(lib.tlfea_newton_set_patch_warps(self._h, int(warps)))
 
+    def SetAffineCompression(self, on: bool):
+        check(lib.tlfea_newton_set_affine_compression(self._h, int(bool(on))))
+
     def PatchStats(self):
         import numpy as np
 
