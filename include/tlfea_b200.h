@@ -142,6 +142,11 @@ int tlfea_elem_get_detJ(tlfea_elem *h, double *out, int64_t n);                 
 int tlfea_elem_get_mass_csr(tlfea_elem *h, int *offsets, int *columns, double *values);  /* n_coef+1, nnz, nnz */
 int tlfea_elem_get_constraint(tlfea_elem *h, double *out, int n);
 int tlfea_elem_get_connectivity(tlfea_elem *h, int *out, int64_t n);
+/* RetrieveConstraintJacobianToCPU (ElementBase.h:21-49) in CSR form, rows = constraints, columns = DOFs: selection rows
+ * for SetNodalFixed (FEAT10Data.cu:501-536), the caller's matrix for SetLinearConstraintsCSR.  offsets holds
+ * n_constraint + 1 ints; columns / values tlfea_elem_constraint_jacobian_nnz entries. */
+int64_t tlfea_elem_constraint_jacobian_nnz(tlfea_elem *h);
+int tlfea_elem_get_constraint_jacobian_csr(tlfea_elem *h, int *offsets, int *columns, double *values);
 
 /* GetX12DevicePtr.. / GetExternalForceDevicePtr  FEAT10Data.cuh:648-670 */
 const double *tlfea_elem_devptr_x(tlfea_elem *h);
@@ -149,6 +154,16 @@ const double *tlfea_elem_devptr_y(tlfea_elem *h);
 const double *tlfea_elem_devptr_z(tlfea_elem *h);
 double *tlfea_elem_devptr_f_ext(tlfea_elem *h);
 double *tlfea_elem_devptr_f_int(tlfea_elem *h);
+
+/* Contact coupling adapter (the collision system itself stays the reference's: it only produces f_ext).
+ * tlfea_elem_pack_nodes_xyz fills the caller's CollisionSystemInput::d_nodes_xyz = [x(0..n-1), y(0..n-1), z(0..n-1)]
+ * (lib_src/collision/CollisionSystemBase.h:17-29) from the current positions, device to device, replacing the three
+ * cudaMemcpy of lib_bin/collision_system/test_item_drop.cc:566-575.  tlfea_elem_set_external_force_device writes
+ * f_ext = base + alpha * contact on the device (d_contact may be NULL), replacing the gravity copy + cublasDaxpy of
+ * test_item_drop.cc:589-598.  Both run on the handle's stream. */
+int tlfea_elem_pack_nodes_xyz(tlfea_elem *h, double *d_nodes_xyz, int n_nodes);
+int tlfea_elem_set_external_force_device(tlfea_elem *h, const double *d_base, const double *d_contact, double alpha,
+                                         int n);
 
 /* ------------------------------------------------------------------ solver */
 

@@ -180,3 +180,45 @@ def test_bunny_newton_step_vs_cpu_restatement(model):
     assert scale > 0 and st["newton_iters"] == n_newton, (st, n_newton)
     assert st["norm_c"] < outer_tol
     assert np.abs(pos_gpu - pos).max() < 1e-8 * scale + 1e-14, (np.abs(pos_gpu - pos).max(), scale)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("model", ["svk", "mr"])
+def test_cpp_bunny_driver_matches_the_python_mirror(tmp_path, model):
+    """examples/bunny_newton.cc -- the call sequence of lib_bin/mesh_deform/test_feat10_bunny_newton.cc written against
+    the reference's class and method names with Eigen-style containers (include/tlfea_shim.hpp templates) -- compiled
+    with g++, run on the GPU: positions after two steps equal the Python mirror's bit for bit (same library, same
+    calls), the VTK file has the reference's layout (FEAT10Data.cu:841-877)."""
+    import shutil
+    import subprocess
+
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.join(root, "total-lagrangian-fea_b200", "lib")
+    exe, vtk = tmp_path / "bunny", tmp_path / "bunny.vtk"
+    subprocess.check_call([gxx, "-std=c++17", "-O1", "-I", os.path.join(root, "include"), "-I",
+                           os.path.join(root, "examples"), os.path.join(root, "examples", "bunny_newton.cc"), "-o",
+                           str(exe), "-L", lib_dir, "-ltlfea_b200", "-Wl,-rpath," + lib_dir,
+                           "-Wl,--unresolved-symbols=ignore-in-shared-libs"])
+    out = subprocess.check_output([str(exe), NODE, ELE, model, "2", str(vtk)],
+                                  env=dict(os.environ, LD_LIBRARY_PATH=lib_dir), text=True)
+    pos_cpp = np.array([[float(t) for t in ln.split()[2:5]] for ln in out.splitlines() if ln.startswith("pos ")])
+    head = [ln for ln in out.splitlines() if ln.startswith("elements")][0].split()
+    assert int(head[1]) == 1066 and int(head[3]) == 2095
+    assert "connectivity round trip ok" in out
+    X, E, fixed, f_ext = _load()
+    assert f"J {3 * len(fixed)} x {3 * X.shape[0]}" in out
+    d, s = _make(model, X, E, fixed, f_ext)
+    d.CalcP()
+    d.CalcInternalForce()
+    s.SetPCG(50000, 1e-13)
+    for _ in range(2):
+        s.Solve()
+    gx, gy, gz = d.RetrievePositionToCPU()
+    assert pos_cpp.shape == (X.shape[0], 3)
+    assert np.array_equal(pos_cpp, np.stack([gx, gy, gz], axis=1))
+    lines = vtk.read_text().splitlines()
+    assert lines[3] == "DATASET UNSTRUCTURED_GRID" and lines[4] == f"POINTS {X.shape[0]} float"
+    assert f"CELLS {E.shape[0]} {E.shape[0] * 11}" in lines and lines[-1] == "24"

@@ -89,3 +89,9 @@ def test_cpp_shim_compiles_and_links_against_the_abi(tmp_path):
     subprocess.check_call([gxx, "-std=c++17", "-I", os.path.join(root, "include"), os.path.join(root, "examples", "beam_sag.cc"),
                            "-o", str(ex), "-L", lib_dir, "-ltlfea_b200", "-Wl,-rpath," + lib_dir,
                            "-Wl,--unresolved-symbols=ignore-in-shared-libs"])
+    # the bunny driver (Eigen-style containers through the shim's templates, examples/mini_matrix.hpp) builds too
+    bn = tmp_path / "bunny"
+    subprocess.check_call([gxx, "-std=c++17", "-Wall", "-Werror", "-I", os.path.join(root, "include"),
+                           "-I", os.path.join(root, "examples"), os.path.join(root, "examples", "bunny_newton.cc"),
+                           "-o", str(bn), "-L", lib_dir, "-ltlfea_b200", "-Wl,-rpath," + lib_dir,
+                           "-Wl,--unresolved-symbols=ignore-in-shared-libs"])

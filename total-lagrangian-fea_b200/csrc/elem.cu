@@ -345,6 +345,13 @@ int ensure_pattern(tlfea_elem *h) {
 
 }  // namespace tlfea
 
+// f_ext = base + alpha * contact   (test_item_drop.cc:589-598: gravity copied in, contact forces added by cublasDaxpy)
+__global__ void k_fext_sum(int n, const double *__restrict__ base, const double *__restrict__ contact, double alpha,
+                           double *f_ext) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) f_ext[i] = contact ? base[i] + alpha * contact[i] : base[i];
+}
+
 using namespace tlfea;
 
 extern "C" {
@@ -915,6 +922,33 @@ int tlfea_elem_get_constraint(tlfea_elem *h, double *out, int n) {
   if (n == 0) return TLFEA_OK;
   return d2h(h, out, h->d_constraint, (size_t)n * sizeof(double));
 }
+// Constraint Jacobian J (rows = constraints, columns = DOFs) in CSR: unit selection rows for pinned nodes
+// (FEAT10Data.cu:501-536), the caller's matrix for linear constraints (ANCF3243Data.cuh:810-940).
+int64_t tlfea_elem_constraint_jacobian_nnz(tlfea_elem *h) {
+  if (!h) return -1;
+  if (h->cons_mode == TL_CONS_FIXED_NODES) return 3 * (int64_t)h->n_fixed;
+  if (h->cons_mode == TL_CONS_LINEAR_CSR) return h->j_nnz;
+  return 0;
+}
+int tlfea_elem_get_constraint_jacobian_csr(tlfea_elem *h, int *offsets, int *columns, double *values) {
+  TL_CHECK(h && offsets && columns && values, "null input");
+  TL_CHECK(h->cons_mode != TL_CONS_NONE, "no constraints are set up");
+  TL_CUDA(cudaSetDevice(h->device));
+  if (h->cons_mode == TL_CONS_FIXED_NODES) {
+    std::vector<int> fx((size_t)h->n_fixed);
+    if (h->n_fixed > 0) TL_TRY(d2h(h, fx.data(), h->d_fixed, fx.size() * sizeof(int)));
+    for (int c = 0; c < 3 * h->n_fixed; c++) {
+      offsets[c] = c;
+      columns[c] = 3 * fx[(size_t)c / 3] + c % 3;
+      values[c] = 1.0;
+    }
+    offsets[3 * h->n_fixed] = 3 * h->n_fixed;
+    return TLFEA_OK;
+  }
+  TL_TRY(d2h(h, offsets, h->d_j_off, ((size_t)h->n_constraint + 1) * sizeof(int)));
+  TL_TRY(d2h(h, columns, h->d_j_cols, (size_t)h->j_nnz * sizeof(int)));
+  return d2h(h, values, h->d_j_vals, (size_t)h->j_nnz * sizeof(double));
+}
 int tlfea_elem_get_connectivity(tlfea_elem *h, int *out, int64_t n) {
   TL_CHECK(h && out && n == (int64_t)h->n_elem * h->nodes_per_elem, "size mismatch");
   return d2h(h, out, h->d_conn, (size_t)n * sizeof(int));
@@ -924,6 +958,29 @@ const double *tlfea_elem_devptr_x(tlfea_elem *h) { return h ? h->d_x : nullptr; 
 const double *tlfea_elem_devptr_y(tlfea_elem *h) { return h ? h->d_y : nullptr; }
 const double *tlfea_elem_devptr_z(tlfea_elem *h) { return h ? h->d_z : nullptr; }
 double *tlfea_elem_devptr_f_ext(tlfea_elem *h) { return h ? h->d_f_ext : nullptr; }
+
+// ---- contact coupling (CollisionSystemInput, lib_src/collision/CollisionSystemBase.h:17-29; the hand-off of
+// lib_bin/collision_system/test_item_drop.cc:560-602), all on the handle's stream, no host copy
+int tlfea_elem_pack_nodes_xyz(tlfea_elem *h, double *d_nodes_xyz, int n_nodes) {
+  TL_CHECK(h && d_nodes_xyz, "null input");
+  TL_CHECK(n_nodes == h->n_coef, "n_nodes must equal the element's coefficient count");
+  TL_CUDA(cudaSetDevice(h->device));
+  const size_t b = (size_t)n_nodes * sizeof(double);
+  TL_CUDA(cudaMemcpyAsync(d_nodes_xyz, h->d_x, b, cudaMemcpyDeviceToDevice, h->stream));
+  TL_CUDA(cudaMemcpyAsync(d_nodes_xyz + n_nodes, h->d_y, b, cudaMemcpyDeviceToDevice, h->stream));
+  TL_CUDA(cudaMemcpyAsync(d_nodes_xyz + 2 * (size_t)n_nodes, h->d_z, b, cudaMemcpyDeviceToDevice, h->stream));
+  return TLFEA_OK;
+}
+
+int tlfea_elem_set_external_force_device(tlfea_elem *h, const double *d_base, const double *d_contact, double alpha,
+                                         int n) {
+  TL_CHECK(h && d_base, "null input");
+  TL_CHECK(n == 3 * h->n_coef, "External force vector size mismatch.");
+  TL_CUDA(cudaSetDevice(h->device));
+  TL_LAUNCH(k_fext_sum, blocks_for(n, 256), 256, 0, h->stream, n, d_base, d_contact, alpha, h->d_f_ext);
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
 double *tlfea_elem_devptr_f_int(tlfea_elem *h) { return h ? h->d_f_int : nullptr; }
 
 }  // extern "C"

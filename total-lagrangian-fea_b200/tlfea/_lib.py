@@ -84,11 +84,15 @@ _SIGS = {
     "tlfea_elem_get_mass_csr": (C.c_int, [c_vp, c_ip, c_ip, c_dp]),
     "tlfea_elem_get_constraint": (C.c_int, [c_vp, c_dp, C.c_int]),
     "tlfea_elem_get_connectivity": (C.c_int, [c_vp, c_ip, C.c_int64]),
+    "tlfea_elem_constraint_jacobian_nnz": (C.c_int64, [c_vp]),
+    "tlfea_elem_get_constraint_jacobian_csr": (C.c_int, [c_vp, c_ip, c_ip, c_dp]),
     "tlfea_elem_devptr_x": (c_vp, [c_vp]),
     "tlfea_elem_devptr_y": (c_vp, [c_vp]),
     "tlfea_elem_devptr_z": (c_vp, [c_vp]),
     "tlfea_elem_devptr_f_ext": (c_vp, [c_vp]),
     "tlfea_elem_devptr_f_int": (c_vp, [c_vp]),
+    "tlfea_elem_pack_nodes_xyz": (C.c_int, [c_vp, c_vp, C.c_int]),
+    "tlfea_elem_set_external_force_device": (C.c_int, [c_vp, c_vp, c_vp, C.c_double, C.c_int]),
     "tlfea_newton_create": (C.c_int, [c_vp, C.c_int, C.POINTER(c_vp)]),
     "tlfea_newton_destroy": (C.c_int, [c_vp]),
     "tlfea_newton_set_params": (C.c_int, [c_vp, C.POINTER(NewtonParams)]),

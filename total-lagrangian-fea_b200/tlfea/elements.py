@@ -199,6 +199,16 @@ class ElementBase:
     def GetExternalForceDevicePtr(self):
         return lib.tlfea_elem_devptr_f_ext(self._h)
 
+    def PackNodesXYZ(self, d_nodes_xyz: int):
+        """CollisionSystemInput::d_nodes_xyz = [x | y | z] from the current positions (device pointer, 3 n doubles)."""
+        check(lib.tlfea_elem_pack_nodes_xyz(self._h, C.c_void_p(int(d_nodes_xyz)), self.n_coef))
+
+    def SetExternalForceDevice(self, d_base: int, d_contact: int = 0, alpha: float = 1.0):
+        """f_ext = base + alpha * contact on the device (gravity + contact forces, test_item_drop.cc:589-598)."""
+        check(lib.tlfea_elem_set_external_force_device(self._h, C.c_void_p(int(d_base)),
+                                                       C.c_void_p(int(d_contact)) if d_contact else None, float(alpha),
+                                                       3 * self.n_coef))
+
     def GetX12DevicePtr(self):
         return lib.tlfea_elem_devptr_x(self._h)
 
