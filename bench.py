@@ -402,9 +402,13 @@ def main():
     pn3 = 3 * slab.plane_nodes
     halo = torch.zeros(max(world - 1, 1) * pn3, dtype=torch.float64, device=dev)
 
+    # multi-GPU data plane inside the library: NCCL send/recv with the two slab neighbours on the element's stream
+    lib_halo = partition.LibHalo(s, slab, rank, world, dist, torch, dev) if world > 1 else None
+
     def halo_sum():
-        """interface-plane f_int summed over the two ranks that share each plane (tlfea/partition.py)"""
-        partition.halo_sum(f_int, slab, rank, world, halo, dist)
+        """interface-plane f_int summed over the two ranks that share each plane (csrc/dist.cu)"""
+        if lib_halo is not None:
+            lib_halo.halo_sum(f_int.data_ptr(), 3)
 
     def step():
         s.Assemble()
@@ -535,7 +539,8 @@ def main():
         torch.cuda.synchronize()
         s.SpMV(ones.data_ptr(), y.data_ptr())
         d.Sync()
-        partition.halo_sum(y, slab, rank, world, halo, dist)
+        if lib_halo is not None:
+            lib_halo.halo_sum(y.data_ptr(), 3)
         acc[3] = (y[lo:] * y[lo:]).sum()
         if world > 1:
             dist.all_reduce(acc)
@@ -661,7 +666,7 @@ def main():
         # of g, diag(H) and every SpMV result + all-reduced dot products over NCCL, fixed 50 PCG iterations
         from tlfea.dist_newton import DistNewton
 
-        dn = DistNewton(d, s, slab, rank, world, dist, torch, dev)
+        dn = DistNewton(d, s, slab, rank, world, dist, torch, dev, halo=lib_halo)
         for timed in (False, True):
             d.UpdatePositions(x[:, 0], x[:, 1], x[:, 2])
             s.Setup()
@@ -741,7 +746,9 @@ def main():
             "data": "synthetic",
             "config": {"workload": f"feat10_kuhn_block_n{args.n}_svk_force_tangent_H", "n_elem": n_elem_g,
                        "gauss_points": gp_total, "nnz_H_sum_over_ranks": nnz_g, "material": "SVK E=7e8 nu=0.33",
-                       "h": H_STEP, "partition": f"x-slabs x{world}, sub-assembled H, NCCL halo sum of f_int",
+                       "h": H_STEP, "partition": f"x-slabs x{world}, sub-assembled H, halo sum of f_int by NCCL send/recv with "
+                                                 "the slab neighbours inside the library (csrc/dist.cu)",
+                       "halo_bytes_sent_per_rank": (lib_halo.bytes_per_halo if lib_halo else 0),
                        "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
                        "setup_s": t_setup},
             "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all, "parity": parity,
@@ -751,6 +758,8 @@ def main():
         _emit(line)
     if world > 1:
         dist.barrier()
+        if lib_halo is not None:
+            lib_halo.finalize()
         dist.destroy_process_group()
 
 

@@ -258,12 +258,27 @@ int tlfea_newton_set_profile(tlfea_newton *s, int on);
 int tlfea_newton_kernel_ms(tlfea_newton *s, double *gp_ms, double *row_ms, double *other_ms);
 
 /* --------------------------------------------------------------- multi-GPU */
-/* Element-partitioned assembly (new design; the reference is single-GPU).
- * `interface_dofs` lists this rank's local DOF ids shared with other ranks in
- * the global canonical order; tlfea_dist_pack/unpack move them through a
- * contiguous buffer that the host side reduces with NCCL (torch.distributed).*/
-int tlfea_dist_pack(tlfea_newton *s, const double *d_vec, const int *d_idx, int n, double *d_buf);
-int tlfea_dist_unpack(tlfea_newton *s, double *d_vec, const int *d_idx, int n, const double *d_buf);
+/* Element-partitioned assembly and Newton iteration (new design; the reference is single-GPU).  One rank
+ * per GPU, each with its own element / solver handles over its part of the mesh; every rank assembles its own
+ * elements (sub-assembled H, no matrix exchange).  The DATA PLANE is in the library, over NCCL loaded at run time
+ * (libnccl.so.2; inside a torch process the copy torch uses), so a C++ host needs nothing but these calls:
+ *   tlfea_dist_unique_id   rank 0 creates the 128-byte ncclUniqueId; the host hands it to every rank (file, MPI, torch)
+ *   tlfea_dist_init        ncclCommInitRank on the solver's device (collective over the ranks)
+ *   tlfea_dist_set_halo    the coefficient-id ranges [coef_lo, coef_hi) this rank shares with each neighbour rank (the
+ *                          partitioner numbers interface planes contiguously); each shared coefficient has exactly
+ *                          two holders
+ *   tlfea_dist_halo_sum    d_vec (width doubles per coefficient: 3 = nodal vector, 9 = diagonal blocks) gets, on the
+ *                          shared ranges, the sum over both holders: pairwise ncclSend / ncclRecv in one group call on
+ *                          the handle's stream, added in neighbour order (bitwise the same on both sides)
+ *   tlfea_dist_allreduce_sum   n device-resident doubles (||g||^2, r.z, p.Ap), in place
+ * All asynchronous on the handle's stream. */
+int tlfea_dist_unique_id(void *out128);
+int tlfea_dist_init(tlfea_newton *s, const void *id128, int rank, int world);
+int tlfea_dist_set_halo(tlfea_newton *s, int n_nbr, const int *nbr_rank, const int64_t *coef_lo, const int64_t *coef_hi);
+int tlfea_dist_halo_sum(tlfea_newton *s, double *d_vec, int width);
+int tlfea_dist_allreduce_sum(tlfea_newton *s, double *d_buf, int n);
+int64_t tlfea_dist_halo_bytes(tlfea_newton *s); /* bytes this rank sends per halo sum of a nodal vector */
+int tlfea_dist_finalize(tlfea_newton *s);
 
 /* Distributed Newton/Krylov building blocks (north_star: "distributed Newton/Krylov residual norms use allreduce").
  * Every rank owns a sub-assembled H; between these calls the host side halo-sums interface entries of the vector

@@ -26,9 +26,16 @@ def _build(slab, device, torch):
     d.Setup(*tlfea.tet5pt_quadrature(), slab.X[:, 0], slab.X[:, 1], slab.X[:, 2], slab.E)
     d.SetDensity(RHO)
     d.SetSVK(E_MOD, NU)
-    fixed = np.nonzero(slab.node_gid < slab.plane_nodes)[0].astype(np.int32)  # global face x = 0
+    # pinned: the global face x = 0 AND a strip of every interface plane (gid-based, so both holders pin the same
+    # nodes); loaded: every node, by global id -- f_ext and the constraint terms of shared nodes may count once only
+    gid = slab.node_gid
+    plane = gid // slab.plane_nodes
+    fixed = np.nonzero((plane == 0) | ((plane % 4 == 0) & (gid % slab.plane_nodes < 9)))[0].astype(np.int32)
     if len(fixed):
         d.SetNodalFixed(fixed)
+    fext = np.zeros(3 * gid.shape[0])
+    fext[2::3] = -50.0 * (1.0 + (gid % 7))
+    d.SetExternalForce(fext)
     d.CalcDnDuPre()
     d.CalcMassMatrix()
     s = tlfea.SyncedNewtonSolver(d, 3 * len(fixed))
@@ -59,7 +66,8 @@ def _worker(rank, world, port, out_dir):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     slab = partition.kuhn_slab(N_CELLS, rank, world)
     d, s, _ = _build(slab, rank, torch)
-    dn = DistNewton(d, s, slab, rank, world, dist, torch, dev)
+    halo = partition.LibHalo(s, slab, rank, world, dist, torch, dev)  # the library's NCCL data plane
+    dn = DistNewton(d, s, slab, rank, world, dist, torch, dev, halo=halo)
     dn.begin_step()
     norms = []
     for _ in range(NEWTON_ITERS):
@@ -71,6 +79,7 @@ def _worker(rank, world, port, out_dir):
     np.savez(os.path.join(out_dir, f"rank{rank}.npz"), pos=np.stack([gx, gy, gz], axis=1), gid=slab.node_gid,
              norms=np.array(norms))
     dist.barrier()
+    halo.finalize()
     dist.destroy_process_group()
 
 

@@ -174,6 +174,7 @@ int patch_prepare(tlfea_newton *s);
 int patch_assemble(tlfea_newton *s, bool tangent, bool damp, const PatchHooks *hooks = nullptr);
 int patch_chunks(tlfea_newton *s, int *n_chunks, const int **range_ready);
 void patch_release(tlfea_newton *s);
+void dist_release(tlfea_newton *s);
 int patch_stats(tlfea_newton *s, int64_t *out);
 }
 
@@ -184,6 +185,7 @@ struct tlfea_newton {
   // (pk_kernel.cuh; the ANCF elements use the two-phase path)
   int asm_mode = 2;
   void *patch = nullptr;  // PatchPlanDev (patch_asm.cu)
+  void *dist = nullptr;   // DistCtx (dist.cu): NCCL communicator + halo neighbours of a partitioned mesh
   int pk_w = 0;           // warps per patch (0 = TLFEA_PK_W or 4)
   int pk_affine = -1;     // affine-element compression: -1 = TLFEA_PK_AFFINE (default off), 0 off, 1 on
   int n_constraints = 0;
@@ -231,7 +233,13 @@ struct tlfea_newton {
   double *h_f_out = nullptr;
   bool pipe_pk = false, pipe_f_copied = false;
   // timing
-  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  // A ring of event sets (start, end, two phase marks): tlfea_newton_assemble records and returns; elapsed times are
+  // read when the ring is full or when a timing getter is called -- no host synchronisation per assemble
+  static constexpr int EV_RING = 16;
+  cudaEvent_t ev_ring[EV_RING][4] = {};
+  cudaEvent_t *ev = ev_ring[0];
+  int ev_pending = 0;
+  bool ev_tangent[EV_RING] = {};
   double ms_total = 0;
   int calls = 0;
   bool profile = false;

@@ -764,21 +764,37 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
   return TLFEA_OK;
 }
 
-static int collect_timing(tlfea_newton *s, bool tangent) {
-  TL_CUDA(cudaEventSynchronize(s->ev[1]));
-  float ms = 0;
-  TL_CUDA(cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]));
-  s->ms_total += ms;
-  s->calls++;
-  if (s->profile && tangent) {
-    float a = 0, b = 0, c = 0;
-    cudaEventElapsedTime(&a, s->ev[0], s->ev[2]);
-    cudaEventElapsedTime(&b, s->ev[2], s->ev[3]);
-    cudaEventElapsedTime(&c, s->ev[3], s->ev[1]);
-    s->k_ms[0] += a;
-    s->k_ms[1] += b;
-    s->k_ms[2] += c;
+// reads the elapsed times of every pending event set (one host wait, on the newest set)
+static int drain_timing(tlfea_newton *s) {
+  if (s->ev_pending == 0) return TLFEA_OK;
+  TL_CUDA(cudaEventSynchronize(s->ev_ring[s->ev_pending - 1][1]));
+  for (int k = 0; k < s->ev_pending; k++) {
+    cudaEvent_t *ev = s->ev_ring[k];
+    float ms = 0;
+    TL_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[1]));
+    s->ms_total += ms;
+    s->calls++;
+    if (s->profile && s->ev_tangent[k]) {
+      float a = 0, b = 0, c = 0;
+      cudaEventElapsedTime(&a, ev[0], ev[2]);
+      cudaEventElapsedTime(&b, ev[2], ev[3]);
+      cudaEventElapsedTime(&c, ev[3], ev[1]);
+      s->k_ms[0] += a;
+      s->k_ms[1] += b;
+      s->k_ms[2] += c;
+    }
   }
+  s->ev_pending = 0;
+  s->ev = s->ev_ring[0];
+  return TLFEA_OK;
+}
+
+// the assemble just queued used the current event set: keep it pending, move on to the next set
+static int collect_timing(tlfea_newton *s, bool tangent) {
+  s->ev_tangent[s->ev_pending] = tangent;
+  s->ev_pending++;
+  if (s->ev_pending == tlfea_newton::EV_RING) return drain_timing(s);
+  s->ev = s->ev_ring[s->ev_pending];
   return TLFEA_OK;
 }
 
@@ -1139,7 +1155,8 @@ int tlfea_newton_create(tlfea_elem *e, int n_constraints, tlfea_newton **out) {
   TL_TRY(dmalloc(&s->d_zp, (size_t)e->n_coef));
   TL_TRY(dmalloc(&s->d_scal, 8 + DOT_BLOCKS));
   TL_CUDA(cudaMallocHost((void **)&s->h_scal, 8 * sizeof(double)));
-  for (auto &ev : s->ev) TL_CUDA(cudaEventCreate(&ev));
+  for (auto &set : s->ev_ring)
+    for (auto &ev : set) TL_CUDA(cudaEventCreate(&ev));
   TL_CUDA(cudaMemsetAsync(s->d_v, 0, nd * sizeof(double), e->stream));
   TL_CUDA(cudaMemsetAsync(s->d_v_prev, 0, nd * sizeof(double), e->stream));
   TL_CUDA(cudaMemsetAsync(s->d_lambda, 0, std::max(n_constraints, 1) * sizeof(double), e->stream));
@@ -1157,6 +1174,7 @@ int tlfea_newton_destroy(tlfea_newton *s) {
   else
     cudaDeviceSynchronize();  // the element handle went first: its stream is gone
   patch_release(s);
+  dist_release(s);
   dfree(s->d_H);
   dfree(s->d_gp);
   dfree(s->d_stage);
@@ -1183,8 +1201,9 @@ int tlfea_newton_destroy(tlfea_newton *s) {
     if (ev) cudaEventDestroy(ev);
   dfree(s->d_scal);
   if (s->h_scal) cudaFreeHost(s->h_scal);
-  for (auto &ev : s->ev)
-    if (ev) cudaEventDestroy(ev);
+  for (auto &set : s->ev_ring)
+    for (auto &ev : set)
+      if (ev) cudaEventDestroy(ev);
   delete s;
   return TLFEA_OK;
 }
@@ -1591,6 +1610,7 @@ double *tlfea_newton_devptr_krylov(tlfea_newton *s, int which) {
 
 int tlfea_newton_timing(tlfea_newton *s, double *ms_total, int *calls, int reset) {
   TL_CHECK(s, "null handle");
+  TL_TRY(drain_timing(s));
   if (ms_total) *ms_total = s->ms_total;
   if (calls) *calls = s->calls;
   if (reset) {
@@ -1625,40 +1645,16 @@ int tlfea_newton_patch_stats(tlfea_newton *s, int64_t *out) {
 }
 int tlfea_newton_set_profile(tlfea_newton *s, int on) {
   TL_CHECK(s, "null handle");
+  TL_TRY(drain_timing(s));
   s->profile = on != 0;
   return TLFEA_OK;
 }
 int tlfea_newton_kernel_ms(tlfea_newton *s, double *gp_ms, double *row_ms, double *other_ms) {
   TL_CHECK(s, "null handle");
+  TL_TRY(drain_timing(s));
   if (gp_ms) *gp_ms = s->k_ms[0];
   if (row_ms) *row_ms = s->k_ms[1];
   if (other_ms) *other_ms = s->k_ms[2];
-  return TLFEA_OK;
-}
-
-// ---------------------------------------------------------------------------
-__global__ void k_pack(int n, const double *__restrict__ vec, const int *__restrict__ idx, double *buf) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) buf[i] = vec[idx[i]];
-}
-__global__ void k_unpack(int n, double *vec, const int *__restrict__ idx, const double *__restrict__ buf) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) vec[idx[i]] = buf[i];
-}
-int tlfea_dist_pack(tlfea_newton *s, const double *d_vec, const int *d_idx, int n, double *d_buf) {
-  TL_CHECK(s && d_vec && d_idx && d_buf && n >= 0, "bad input");
-  if (n == 0) return TLFEA_OK;
-  TL_CUDA(cudaSetDevice(s->e->device));
-  TL_LAUNCH(k_pack, blocks_for(n, 256), 256, 0, s->e->stream, n, d_vec, d_idx, d_buf);
-  TL_CUDA(cudaGetLastError());
-  return TLFEA_OK;
-}
-int tlfea_dist_unpack(tlfea_newton *s, double *d_vec, const int *d_idx, int n, const double *d_buf) {
-  TL_CHECK(s && d_vec && d_idx && d_buf && n >= 0, "bad input");
-  if (n == 0) return TLFEA_OK;
-  TL_CUDA(cudaSetDevice(s->e->device));
-  TL_LAUNCH(k_unpack, blocks_for(n, 256), 256, 0, s->e->stream, n, d_vec, d_idx, d_buf);
-  TL_CUDA(cudaGetLastError());
   return TLFEA_OK;
 }
 

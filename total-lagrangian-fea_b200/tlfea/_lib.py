@@ -131,8 +131,13 @@ _SIGS = {
     "tlfea_newton_patch_stats": (C.c_int, [c_vp, c_i64p]),
     "tlfea_newton_set_profile": (C.c_int, [c_vp, C.c_int]),
     "tlfea_newton_kernel_ms": (C.c_int, [c_vp, c_dp, c_dp, c_dp]),
-    "tlfea_dist_pack": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
-    "tlfea_dist_unpack": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
+    "tlfea_dist_unique_id": (C.c_int, [c_vp]),
+    "tlfea_dist_init": (C.c_int, [c_vp, c_vp, C.c_int, C.c_int]),
+    "tlfea_dist_set_halo": (C.c_int, [c_vp, C.c_int, c_ip, c_i64p, c_i64p]),
+    "tlfea_dist_halo_sum": (C.c_int, [c_vp, c_vp, C.c_int]),
+    "tlfea_dist_allreduce_sum": (C.c_int, [c_vp, c_vp, C.c_int]),
+    "tlfea_dist_halo_bytes": (C.c_int64, [c_vp]),
+    "tlfea_dist_finalize": (C.c_int, [c_vp]),
     "tlfea_fp64_peak": (C.c_int, [C.c_int, c_dp]),
     "tlfea_debug_patch_plan_build": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_dp, c_ip, c_ip, C.c_int, C.c_int,
                                                C.POINTER(c_vp)]),

@@ -24,8 +24,11 @@ class _Dev:
 class DistNewton:
     """d: GPU_FEAT10_Data of the rank's slab, s: its SyncedNewtonSolver (analysed), dist: torch.distributed or None."""
 
-    def __init__(self, d, s, slab: Slab, rank: int, world: int, dist, torch, device):
+    def __init__(self, d, s, slab: Slab, rank: int, world: int, dist, torch, device, halo=None):
+        """halo: a partition.LibHalo -- the data plane then runs inside the library (NCCL send/recv with the neighbours,
+        all-reduce of the device scalars); None keeps the torch.distributed all-reduce of the compact interface vector."""
         self.d, self.s, self.slab, self.rank, self.world, self.dist, self.torch = d, s, slab, rank, world, dist, torch
+        self.lib_halo = halo
         self.h = s._h
         self.n = s.n_dofs
         check(lib.tlfea_newton_krylov_op(self.h, KOP["SAVE"]))  # also allocates the Krylov vectors
@@ -48,6 +51,10 @@ class DistNewton:
     def _halo(self, vec, width, buf):
         if self.world == 1:
             return
+        if self.lib_halo is not None:
+            self.lib_halo.halo_sum(vec.data_ptr(), width)
+            self.halo_bytes += self.lib_halo.bytes_per_halo * width // 3
+            return
         w = width * self.slab.plane_nodes
         r = self.rank
         buf.zero_()
@@ -65,7 +72,10 @@ class DistNewton:
     def _reduce_scalars(self, lo, hi):
         """sum the partial scalars scal[lo:hi] an op has just written (already-reduced entries must not be re-summed)"""
         if self.world > 1:
-            self.dist.all_reduce(self.scal[lo:hi])
+            if self.lib_halo is not None:
+                self.lib_halo.allreduce(self.scal[lo:hi].data_ptr(), hi - lo)
+            else:
+                self.dist.all_reduce(self.scal[lo:hi])
 
     def begin_step(self):
         self._op("SAVE")

@@ -116,3 +116,44 @@ def halo_sum(f_int, slab: Slab, rank: int, world: int, halo, dist):
         f_int[:pn3] = halo[(rank - 1) * pn3: rank * pn3]
     if slab.has_right:
         f_int[-pn3:] = halo[rank * pn3:(rank + 1) * pn3]
+
+
+class LibHalo:
+    """The library's own multi-GPU data plane (csrc/dist.cu: NCCL send/recv with the two x-neighbours, all-reduce of
+    device scalars).  torch.distributed is used ONCE, to hand rank 0's ncclUniqueId to the other ranks; a C++ host
+    would use a file or MPI for that."""
+
+    def __init__(self, solver, slab: Slab, rank: int, world: int, dist, torch, device):
+        import ctypes as C
+
+        from ._lib import check, lib
+
+        self.s, self.lib, self.check, self.C = solver, lib, check, C
+        ident = torch.zeros(128, dtype=torch.uint8, device=device)
+        if rank == 0:
+            raw = (C.c_ubyte * 128)()
+            check(lib.tlfea_dist_unique_id(C.cast(raw, C.c_void_p)))
+            ident.copy_(torch.tensor(list(raw), dtype=torch.uint8))
+        if world > 1:
+            dist.broadcast(ident, src=0)
+        raw = (C.c_ubyte * 128)(*ident.cpu().tolist())
+        check(lib.tlfea_dist_init(solver._h, C.cast(raw, C.c_void_p), rank, world))
+        nn, pn = slab.X.shape[0], slab.plane_nodes
+        nbr, lo, hi = [], [], []
+        if slab.has_left:
+            nbr.append(rank - 1), lo.append(0), hi.append(pn)
+        if slab.has_right:
+            nbr.append(rank + 1), lo.append(nn - pn), hi.append(nn)
+        self._arrs = ((C.c_int * max(len(nbr), 1))(*nbr), (C.c_int64 * max(len(nbr), 1))(*lo),
+                      (C.c_int64 * max(len(nbr), 1))(*hi))
+        check(lib.tlfea_dist_set_halo(solver._h, len(nbr), self._arrs[0], self._arrs[1], self._arrs[2]))
+        self.bytes_per_halo = int(lib.tlfea_dist_halo_bytes(solver._h))
+
+    def halo_sum(self, ptr: int, width: int = 3):
+        self.check(self.lib.tlfea_dist_halo_sum(self.s._h, self.C.c_void_p(int(ptr)), width))
+
+    def allreduce(self, ptr: int, n: int):
+        self.check(self.lib.tlfea_dist_allreduce_sum(self.s._h, self.C.c_void_p(int(ptr)), n))
+
+    def finalize(self):
+        self.check(self.lib.tlfea_dist_finalize(self.s._h))
