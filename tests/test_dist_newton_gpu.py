@@ -30,7 +30,7 @@ def _build(slab, device, torch):
     # nodes); loaded: every node, by global id -- f_ext and the constraint terms of shared nodes may count once only
     gid = slab.node_gid
     plane = gid // slab.plane_nodes
-    fixed = np.nonzero((plane == 0) | ((plane % 4 == 0) & (gid % slab.plane_nodes < 9)))[0].astype(np.int32)
+    fixed = np.nonzero((plane == 0) | ((plane == N_CELLS) & (gid % slab.plane_nodes < 9)))[0].astype(np.int32)
     if len(fixed):
         d.SetNodalFixed(fixed)
     fext = np.zeros(3 * gid.shape[0])
