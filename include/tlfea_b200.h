@@ -307,6 +307,19 @@ int tlfea_newton_set_owned_range(tlfea_newton *s, int64_t dof_lo, int64_t dof_hi
 int tlfea_newton_krylov_op(tlfea_newton *s, int op);
 double *tlfea_newton_devptr_krylov(tlfea_newton *s, int which);
 
+/* Allocation-free deterministic dot product: *d_out = sum_i d_a[i] * d_b[i] (d_a == d_b gives ||a||^2), all pointers
+ * DEVICE pointers on the current device, asynchronous on `stream` (a cudaStream_t, NULL = default stream).
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  It runs the same two
+ * kernels with the same fixed 592 x 256 grid and reduction tree as the handle-based path (tlfea_newton_residual's
+ * ||g||), so the results agree bitwise; the 592 partial sums live in a static __device__ array (4 736 B, held by every
+ * GPU that loads the library until exit) instead of a cudaMalloc'ed buffer.  The call makes no cudaMalloc / cudaFree
+ * and needs no handle.  Limits: n <= TLFEA_NOALLOC_DOT_MAX_N, otherwise TLFEA_ERR_INVALID with a message.  All calls on
+ * one device share the array: calls that overlap on the GPU (different streams, no ordering) RACE -- serialise them.
+ * Every call overwrites all partials, so nothing carries over from the previous call. */
+#define TLFEA_NOALLOC_DOT_MAX_N (((int64_t)1) << 32) /* 4 294 967 296 doubles = 32 GiB per vector */
+int tlfea_dot_noalloc(const double *d_a, const double *d_b, int64_t n, double *d_out, void *stream);
+
 /* FP64 FMA peak micro-benchmark (roofline denominator for the tangent kernel): TFLOP/s */
 int tlfea_fp64_peak(int device, double *tflops);
 

@@ -1699,3 +1699,40 @@ int tlfea_fp64_peak(int device, double *tflops) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of the deterministic dot product (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops).  Same two
+// kernels, same fixed grid and tree as dot()/norm2() above, so the result is bitwise the one tlfea_newton_residual
+// forms -- only the partial sums live in a file-scope device array instead of the handle's cudaMalloc'ed d_scal.
+// Every GPU that loads the library holds the array until exit.  All calls on a device share it: calls that overlap on
+// the GPU (different streams) race.  k_dot_partial overwrites every one of the DOT_BLOCKS partials on each call, so
+// nothing has to be cleared between calls.
+namespace tlfea {
+constexpr int64_t NOALLOC_DOT_MAX_N = TLFEA_NOALLOC_DOT_MAX_N;
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static __device__ __align__(256) double g_noalloc_partial[DOT_BLOCKS];  // 592 doubles = 4 736 B per GPU
+// device address of g_noalloc_partial per device (the host-side name is NOT a device address)
+static std::atomic<double *> g_noalloc_ptr[NOALLOC_MAX_DEVICES];
+}  // namespace tlfea
+
+extern "C" int tlfea_dot_noalloc(const double *d_a, const double *d_b, int64_t n, double *d_out, void *stream) {
+  TL_CHECK(d_a && d_b && d_out, "tlfea_dot_noalloc: null device pointer");
+  TL_CHECK(n >= 0, "tlfea_dot_noalloc: negative length");
+  TL_CHECK(n <= NOALLOC_DOT_MAX_N, "tlfea_dot_noalloc: n = %lld exceeds TLFEA_NOALLOC_DOT_MAX_N = %lld", (long long)n,
+           (long long)NOALLOC_DOT_MAX_N);
+  int dev = -1;
+  TL_CUDA(cudaGetDevice(&dev));
+  TL_CHECK(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "tlfea_dot_noalloc: device ordinal %d out of range", dev);
+  double *partial = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+  if (!partial) {  // once per device, with that device current
+    TL_CUDA(cudaGetSymbolAddress((void **)&partial, g_noalloc_partial));
+    TL_CHECK(partial != nullptr, "tlfea_dot_noalloc: cudaGetSymbolAddress gave a null address");
+    g_noalloc_ptr[dev].store(partial, std::memory_order_release);
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  TL_LAUNCH(k_dot_partial, DOT_BLOCKS, 256, 0, st, n, d_a, d_b, partial);
+  TL_LAUNCH(k_dot_final, 1, 1024, 0, st, DOT_BLOCKS, partial, d_out);
+  TL_CUDA(cudaGetLastError());
+  return TLFEA_OK;
+}
