@@ -21,6 +21,9 @@ def reg_of(f, l):
 hdr = cur = curfile = None
 reg = collections.defaultdict(collections.Counter)
 ins = collections.Counter()
+wav = collections.Counter()
+wid = collections.Counter()
+gsec = collections.Counter()
 for r in rows:
     if not r:
         continue
@@ -39,14 +42,17 @@ for r in rows:
                     reg[cur][h] += float(r[i] or 0)
                 except ValueError:
                     pass
-        try:
-            ins[cur] += float(r[hdr.index('Instructions Executed')] or 0)
-        except ValueError:
-            pass
+        for name, ctr in (('Instructions Executed', ins), ('L1 Wavefronts Shared', wav), ('L1 Wavefronts Shared Ideal', wid),
+                          ('L2 Theoretical Sectors Global', gsec)):
+            try:
+                ctr[cur] += float(r[hdr.index(name)] or 0)
+            except ValueError:
+                pass
 tot = sum(sum(c.values()) for c in reg.values())
 ti = sum(ins.values())
-print(f"samples {tot:.0f} warp instructions {ti:.0f}")
+tw = sum(wav.values())
+print(f"samples {tot:.0f} warp instructions {ti:.0f} shared wavefronts {tw:.0f} (ideal {sum(wid.values()):.0f}) global sectors {sum(gsec.values()):.0f}")
 for k, c in sorted(reg.items(), key=lambda kv: -sum(kv[1].values())):
     s = sum(c.values())
     top = ', '.join(f"{h[6:]} {100*v/s:.0f}%" for h, v in c.most_common(4))
-    print(f"{k:20s} samples {100*s/tot:5.1f}%  instr {100*ins[k]/ti:5.1f}% | {top}")
+    print(f"{k:20s} samples {100*s/tot:5.1f}%  instr {100*ins[k]/ti:5.1f}%  smem wavefronts {100*wav[k]/max(tw,1):5.1f}% (x{wav[k]/max(wid[k],1):.2f} of ideal)  gsectors {gsec[k]:.3g} | {top}")
