@@ -51,6 +51,12 @@ struct PKArgs {
   double *H;
 };
 
+// Gauss-point results of the SVK path: row stride of the per-(element, point) force-partial and u rows, both laid out
+// [a][i].  The Gauss-point step stores from lane = (element, point, row i): address = idx * 35 + 3 a + i, i.e. bank
+// 3 idx + i + const -- the 16 lanes of a half warp hit 16 different banks (the stride 33 of ek_kernel.cuh is for its
+// 10-lane step and gave a 9-way conflict here).
+constexpr int PK_GQ = 35;
+
 // Shared memory of a CTA: [accumulators x W][prefetch buffers x W][scratch x W].  The scratch areas (Gauss-point
 // results of the pair in flight) are contiguous over the warps: the write-out lists of the patch land there.
 template <bool DAMP, int MODEL>
@@ -61,9 +67,9 @@ struct PKShape {
   static constexpr int DJ_D = 10;
   static constexpr int X_D = 60;
   static constexpr int PE_D = 32;   // two plan records
-  static constexpr int U_D = MR ? 2 * 5 * EK_TS : 2 * 5 * EK_GQ;
+  static constexpr int U_D = MR ? 2 * 5 * EK_TS : 2 * 5 * PK_GQ;
   static constexpr int REC_D = MR ? 0 : 2 * 5 * EK_REC;
-  static constexpr int FP_D = MR ? 2 * 5 * EK_GQM : 2 * 5 * EK_GQ;
+  static constexpr int FP_D = MR ? 2 * 5 * EK_GQM : 2 * 5 * PK_GQ;
   static constexpr int OFF_H = 0;
   static constexpr int OFF_DJ = OFF_H + 2 * H_D;
   static constexpr int OFF_X = OFF_DJ + 2 * DJ_D;
@@ -78,11 +84,15 @@ struct PKShape {
   static constexpr int scratch_bytes(int warps) { return warps * SCR_D * (int)sizeof(double); }
 };
 
+// H[addr] += v performed by the L2 (no return value, nothing to wait for)
+__device__ __forceinline__ void red_add_f64(double *addr, double v) {
+  asm volatile("red.global.add.f64 [%0], %1;\n" ::"l"(addr), "d"(v) : "memory");
+}
+
 __device__ __forceinline__ void bulk_prefetch_l2(const void *gmem, unsigned bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;\n" ::"l"(gmem), "r"(bytes) : "memory");
 }
 
-constexpr int PK_NB = 10;  // later-touch (entry, column) positions a thread keeps in flight
 
 template <int W, bool DAMP, bool TANGENT, int MODEL>
 __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) {
@@ -481,13 +491,13 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       }
 #pragma unroll
       for (int j = 0; j < 3; j++) Pi[j] *= dV;
-      double *fpq = s_fp + idx * EK_GQ;
-      double *uq = s_u + idx * EK_GQ;
+      double *fpq = s_fp + idx * PK_GQ;
+      double *uq = s_u + idx * PK_GQ;
 #pragma unroll
       for (int aa = 0; aa < 10; aa++) {
         const double ha[3] = {hq[aa], hq[10 + aa], hq[20 + aa]};
         fpq[aa * 3 + part] = Pi[0] * ha[0] + Pi[1] * ha[1] + Pi[2] * ha[2];
-        if (TANGENT) uq[part * 10 + aa] = Fi[0] * ha[0] + Fi[1] * ha[1] + Fi[2] * ha[2];
+        if (TANGENT) uq[aa * 3 + part] = Fi[0] * ha[0] + Fi[1] * ha[1] + Fi[2] * ha[2];
       }
       if (TANGENT && part == 0) {
         double *r = s_rec + idx * EK_REC;
@@ -506,7 +516,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     // element forces: sum of the 5 point partials in fixed order, one coalesced 240-byte row per element
     for (int el = 0; el < ne; el++) {
       if (lane < 30) {
-        constexpr int FS = MR ? EK_GQM : EK_GQ;
+        constexpr int FS = MR ? EK_GQM : PK_GQ;
         const double *fq = s_fp + el * 5 * FS + lane;
         p.fe[(int64_t)eid[el] * 30 + lane] = (((fq[0] + fq[FS]) + fq[2 * FS]) + fq[3 * FS]) + fq[4 * FS];
       }
@@ -517,7 +527,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       const int el = min(el2, ne - 1);  // odd tail: the second half shadows the first and never adds
       const bool on = lane_on && (el2 < ne);
       const double *he = s_h + el * 150;
-      const double *ue = s_u + el * 5 * EK_GQ;
+      const double *ue = s_u + el * 5 * PK_GQ;
       const double *re = s_rec + el * 5 * EK_REC;
       double A[4][9], Gs[4][6];
 #pragma unroll
@@ -559,7 +569,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       }
 #pragma unroll
       for (int q = 0; q < (MR ? 0 : 5); q++) {
-        const double *hq = he + q * 30, *uq = ue + q * EK_GQ, *rq = re + q * EK_REC;
+        const double *hq = he + q * 30, *uq = ue + q * PK_GQ, *rq = re + q * EK_REC;
         const double dV = rq[6];
         double ha[2][3], hb[2][3], ua[2][3], ub[2][3], M[6];
 #pragma unroll
@@ -568,10 +578,10 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
           ha[1][j] = hq[j * 10 + a1 + 1];
           hb[0][j] = hq[j * 10 + b1];
           hb[1][j] = hq[j * 10 + b1 + 1];
-          ua[0][j] = uq[j * 10 + a1] * dV;
-          ua[1][j] = uq[j * 10 + a1 + 1] * dV;
-          ub[0][j] = uq[j * 10 + b1];
-          ub[1][j] = uq[j * 10 + b1 + 1];
+          ua[0][j] = uq[a1 * 3 + j] * dV;
+          ua[1][j] = uq[a1 * 3 + 3 + j] * dV;
+          ub[0][j] = uq[b1 * 3 + j];
+          ub[1][j] = uq[b1 * 3 + 3 + j];
         }
 #pragma unroll
         for (int i = 0; i < 6; i++) M[i] = rq[i];
@@ -688,84 +698,70 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     }
   }
 
-  double *Hb = p.H + ((p.debug & 16) ? (int64_t)(blockIdx.x & 255) * 65536 : dc.hbase);
-  const unsigned hmask = (p.debug & 16) ? 0x3fffu : 0xffffffffu;  // tuning aid: all traffic into a small window
+  double *Hb = p.H + dc.hbase;
   // Thread = (entry, column e) of a 3x3 block of H, three rows d per thread: consecutive lanes store consecutive
   // doubles of a scalar CSR row (an entry-per-thread mapping was measured: 2.3x the store sectors, 10 % slower).
   // Threads stride over the entries by NT/3, so e and the entry phase are fixed per thread.
   constexpr int KS = NT / 3;
   const int we = (int)threadIdx.x % 3, wk = (int)threadIdx.x / 3;
-  const bool w_on = (int)threadIdx.x < 3 * KS;
-  auto block_col = [&](unsigned src, double v[3]) {  // column we of the entry's block, rows 0..2
-    const bool tr = src & 0x800u;
-    const double *bsrc = blk_addr(src) + (tr ? 3 * we : we);
-    const int st = tr ? 1 : 3;
-    v[0] = bsrc[0];
-    v[1] = bsrc[st];
-    v[2] = bsrc[2 * st];
-  };
-  // later touches: issue the loads of the old values (PK_NB entries per thread in flight) ...
-  for (int base = n_first; (base < n_ent || base == n_first) && !(p.debug & 1); base += KS * PK_NB) {
-    double o[PK_NB][3];
+  if ((int)threadIdx.x < 3 * KS && !(p.debug & 1)) {
+    auto block_col = [&](unsigned src, double v[3]) {  // column we of the entry's block, rows 0..2
+      const bool tr = src & 0x800u;
+      const double *bsrc = blk_addr(src) + (tr ? 3 * we : we);
+      const int st = tr ? 1 : 3;
+      v[0] = bsrc[0];
+      v[1] = bsrc[st];
+      v[2] = bsrc[2 * st];
+    };
+    constexpr int FU = 4;  // entries per thread per trip: their shared-memory loads overlap
+    // first touches of an H block in the colour sequence: H block = (M_ij / h) I + sum, plain stores
+    for (int k0f = wk; k0f < n_first; k0f += FU * KS) {
+      double *hp[FU];
+      unsigned rl[FU];
+      double v[FU][3];
 #pragma unroll
-    for (int b = 0; b < PK_NB; b++) {
-      const int k = base + b * KS + wk;
-      if (w_on && k < n_ent && !(p.debug & 32)) {
+      for (int u = 0; u < FU; u++) {
+        const int k = min(k0f + u * KS, n_first - 1);
         const uint2 en = ent[k];
-        const double *hp = Hb + (en.x & hmask) + we;
-        const unsigned rl = en.y & 0xffffu;
-        o[b][0] = __ldcg(hp);
-        o[b][1] = __ldcg(hp + rl);
-        o[b][2] = __ldcg(hp + 2 * rl);
+        hp[u] = Hb + en.x + we;
+        rl[u] = en.y & 0xffffu;
+        block_col(en.y >> 16, v[u]);
+        const double m = massb[k] * p.inv_h;
+        if (we == 0) v[u][0] += m;
+        if (we == 1) v[u][1] += m;
+        if (we == 2) v[u][2] += m;
       }
-    }
-    // ... first touches run underneath (only once): H block = (M_ij / h) I + sum
-    if (base == n_first && w_on) {
-      constexpr int FU = 4;  // entries per thread per trip: their shared-memory loads overlap
-      for (int k0f = wk; k0f < n_first; k0f += FU * KS) {
-        double *hp[FU];
-        unsigned rl[FU];
-        double v[FU][3];
 #pragma unroll
-        for (int u = 0; u < FU; u++) {
-          const int k = min(k0f + u * KS, n_first - 1);
-          const uint2 en = ent[k];
-          hp[u] = Hb + (en.x & hmask) + we;
-          rl[u] = en.y & 0xffffu;
-          block_col(en.y >> 16, v[u]);
-          const double m = massb[k] * p.inv_h;
-          if (we == 0) v[u][0] += m;
-          if (we == 1) v[u][1] += m;
-          if (we == 2) v[u][2] += m;
-        }
-#pragma unroll
-        for (int u = 0; u < FU; u++) {
-          if (k0f + u * KS < n_first && !(p.debug & 64)) {
-            if (p.debug & 256) {
-              __stcg(hp[u], v[u][0]);
-              __stcg(hp[u] + rl[u], v[u][1]);
-              __stcg(hp[u] + 2 * rl[u], v[u][2]);
-            } else {
-              hp[u][0] = v[u][0];
-              hp[u][rl[u]] = v[u][1];
-              hp[u][2 * rl[u]] = v[u][2];
-            }
-          }
+      for (int u = 0; u < FU; u++) {
+        if (k0f + u * KS < n_first) {
+          hp[u][0] = v[u][0];
+          hp[u][rl[u]] = v[u][1];
+          hp[u][2 * rl[u]] = v[u][2];
         }
       }
     }
+    // later touches: H += sum.  One reduction per address per launch (patches of a launch share no coefficient) and
+    // launches are stream-ordered, so the order of the additions per H entry is the colour order: fixed, and the
+    // same IEEE additions a load-add-store would do -- but performed by the L2, with no load to wait for.
+    for (int k0 = n_first + wk; k0 < n_ent; k0 += FU * KS) {
+      double *hp[FU];
+      unsigned rl[FU];
+      double v[FU][3];
 #pragma unroll
-    for (int b = 0; b < PK_NB; b++) {
-      const int k = base + b * KS + wk;
-      if (w_on && k < n_ent && !(p.debug & 32)) {
+      for (int u = 0; u < FU; u++) {
+        const int k = min(k0 + u * KS, n_ent - 1);
         const uint2 en = ent[k];
-        double *hp = Hb + (en.x & hmask) + we;
-        const unsigned rl = en.y & 0xffffu;
-        double v[3];
-        block_col(en.y >> 16, v);
-        hp[0] = o[b][0] + v[0];
-        hp[rl] = o[b][1] + v[1];
-        hp[2 * rl] = o[b][2] + v[2];
+        hp[u] = Hb + en.x + we;
+        rl[u] = en.y & 0xffffu;
+        block_col(en.y >> 16, v[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < FU; u++) {
+        if (k0 + u * KS < n_ent) {
+          red_add_f64(hp[u], v[u][0]);
+          red_add_f64(hp[u] + rl[u], v[u][1]);
+          red_add_f64(hp[u] + 2 * rl[u], v[u][2]);
+        }
       }
     }
   }
