@@ -11,7 +11,9 @@ from conftest import rel_err
 PELEM = np.dtype([("elem", "<i4"), ("pad0", "<i4"), ("node", "<i4", (10,)), ("blk4", "<u4", (15,)),
                   ("tr", "<u4", (2,)), ("first", "<u4", (2,)), ("pad1", "<i4")])
 PENT = np.dtype([("hoff", "<u4"), ("rowlen", "<u2"), ("src", "<u2")])
-PDESC = np.dtype([("sub_ptr", "<i4", (9,)), ("n_sub", "<i4"), ("n_ent", "<i4"), ("n_first", "<i4"), ("n_merge", "<i4"),
+PENTF = np.dtype([("hoff", "<u4"), ("rowlen", "<u2"), ("src", "<u2"), ("mass", "<f8")])
+HDR_INTS, NSEG = 36, 9  # csrc/patch_plan.cuh: PK_HDR_INTS, PK_NSEG
+PDESC = np.dtype([("sub_ptr", "<i4", (9,)), ("n_sub", "<i4"), ("blob_bytes", "<i4"), ("n_first", "<i4"), ("n_merge", "<i4"),
                   ("blob_off", "<u4"), ("hbase", "<i8")])
 TILES = [(0, j) for j in range(5)] + [(1, j) for j in range(1, 5)] + [(2, j) for j in range(2, 5)] + \
         [(3, 3), (3, 4), (4, 4)]
@@ -21,7 +23,7 @@ CAPU = 210
 def build_plan(E, X, off, cols, W, n_chunks=1):
     from tlfea import _lib
 
-    assert PELEM.itemsize == 128 and PENT.itemsize == 8 and PDESC.itemsize == 64
+    assert PELEM.itemsize == 128 and PENT.itemsize == 8 and PENTF.itemsize == 16 and PDESC.itemsize == 64
     E = np.ascontiguousarray(E, dtype=np.int32)
     x, y, z = (np.ascontiguousarray(X[:, k], dtype=np.float64) for k in range(3))
     off = np.ascontiguousarray(off, dtype=np.int32)
@@ -51,12 +53,22 @@ def al16(b):
 
 
 def patch_sections(plan, d):
-    """(round_end, ops, entries) views of one patch's blob (csrc/patch_plan.cuh: BlobLayout)."""
+    """(round_end, ops, segments) of one patch's blob (csrc/patch_plan.cuh): segments = [(first16, later8)] * NSEG;
+    segment w < 8 = blocks warp w holds alone, segment 8 = merged blocks."""
     b0 = int(d["blob_off"]) * 16
-    o_ent = 32 + al16(d["n_merge"] * 4)
-    o_mass = o_ent + al16(d["n_ent"] * 8)
-    bl = plan["blob"][b0:b0 + o_mass + al16(d["n_first"] * 8)]
-    return bl[:32].view(np.int32), bl[32:32 + 4 * d["n_merge"]].view(np.uint32), bl[o_ent:o_ent + 8 * d["n_ent"]].view(PENT)
+    bl = plan["blob"][b0:b0 + int(d["blob_bytes"])]
+    hdr = bl[:4 * HDR_INTS].view(np.int32)
+    ops = bl[4 * HDR_INTS:4 * HDR_INTS + 4 * d["n_merge"]].view(np.uint32)
+    segs = []
+    end = 4 * HDR_INTS + al16(4 * int(d["n_merge"]))
+    for sg in range(NSEG):
+        o, nf, nl = (int(v) for v in hdr[8 + 3 * sg:11 + 3 * sg])
+        assert 16 * o == end  # segments are contiguous
+        segs.append((bl[16 * o:16 * o + 16 * nf].view(PENTF), bl[16 * o + 16 * nf:16 * o + 16 * nf + 8 * nl].view(PENT)))
+        end = 16 * o + 16 * nf + al16(8 * nl)
+    assert end == int(d["blob_bytes"])
+    assert sum(len(f) for f, _ in segs) == int(d["n_first"])
+    return hdr[:8], ops, segs
 
 
 def replay(plan, Ke, mass_of_hpos, h, nnz):
@@ -87,30 +99,47 @@ def replay(plan, Ke, mass_of_hpos, h, nnz):
                                 fs = (int(pe["first"][bit >> 5]) >> (bit & 31)) & 1
                                 assert fs == int(np.isnan(acc[w, u]).all())
                                 acc[w, u] = (0.0 if fs else acc[w, u]) + (blk.T if tr else blk)
-            round_end, ops, ent = patch_sections(plan, d)
+            round_end, ops, segs = patch_sections(plan, d)
+            acc = acc.reshape(-1)  # block addresses are offsets in doubles: warp * 9 CAPU + 9 slot
+            ablk = lambda a: acc[a:a + 9].reshape(3, 3)  # noqa: E731
+
+            def write_segment(seg):
+                for first, ents in ((True, seg[0]), (False, seg[1])):
+                    for en in ents:
+                        s_ = int(en["src"])
+                        b = ablk(s_ & 0x3fff)
+                        assert not np.isnan(b).any()
+                        val = b.T if s_ >> 15 else b
+                        pos = int(d["hbase"]) + int(en["hoff"])
+                        for dd in range(3):
+                            base = pos + dd * int(en["rowlen"])
+                            old = np.where(np.arange(3) == dd, mass_of_hpos(pos) / h, 0.0) if first else H[base:base + 3]
+                            assert first or not np.isnan(old).any()
+                            assert not first or np.isnan(H[base:base + 3]).all()
+                            H[base:base + 3] = old + val[dd]
+
+            merged = set(int(op) & 0xffff for op in ops)
+            for w in range(8):  # (a) every warp writes the blocks it holds alone, before any merge
+                for part in segs[w]:
+                    for en in part:
+                        a = int(en["src"]) & 0x3fff
+                        assert a // (9 * CAPU) == w and a not in merged
+                        assert not any((int(op) >> 16) == a for op in ops)
+                write_segment(segs[w])
             lo = 0
-            for r in range(7):
+            for r in range(7):  # (b) merge rounds
                 dsts = set()
                 for op in ops[lo:round_end[r]]:
                     dst, src = int(op) & 0xffff, int(op) >> 16
                     assert dst not in dsts  # within a round every destination is distinct
                     dsts.add(dst)
-                    acc[dst >> 8, dst & 255] += acc[src >> 8, src & 255]
+                    ablk(dst)[:] += ablk(src)
                 lo = round_end[r]
             assert lo == d["n_merge"]
-            for k in range(d["n_ent"]):
-                en = ent[k]
-                s = int(en["src"])
-                b = acc[(s >> 8) & 7, s & 255]
-                val = b.T if (s >> 11) & 1 else b
-                first = k < d["n_first"]
-                pos = int(d["hbase"]) + int(en["hoff"])
-                for dd in range(3):
-                    base = pos + dd * int(en["rowlen"])
-                    old = np.where(np.arange(3) == dd, mass_of_hpos(pos) / h, 0.0) if first else H[base:base + 3]
-                    assert first or not np.isnan(old).any()
-                    assert not first or np.isnan(H[base:base + 3]).all()
-                    H[base:base + 3] = old + val[dd]
+            for part in segs[8]:  # (c) entries of merged blocks
+                for en in part:
+                    assert (int(en["src"]) & 0x3fff) in merged
+            write_segment(segs[8])
     return H
 
 

@@ -7,7 +7,9 @@ rows = list(csv.reader(open(sys.argv[1])))
 src = open(os.path.join(ROOT, "total-lagrangian-fea_b200/csrc/pk_kernel.cuh")).read().split('\n')
 MARKS = [('Gauss-point step, Mooney', 'gp_mr'), ('Gauss-point step, SVK', 'gp_svk'), ('element forces: sum', 'force'),
          ('--- block step', 'block'), ('finished in place', 'finish'), ('ordered accumulation into', 'rmw'),
-         ('--- write-out', 'wo_blob'), ('pairs held by several warps', 'merge'), ('double *Hb = p.H', 'writeout'),
+         ('--- write-out', 'wo_own(a)'), ('the lists for after the barrier', 'wo_stage'), ('pairs held by several warps', 'merge(b)'),
+         ('entries of the merged blocks, all threads', 'wo_dep(c)'), ('Write-out of one entry segment', 'wo_segment_fn'),
+         ('template <int W, bool DAMP, bool TANGENT, int MODEL>', 'kernel_head'),
          ('nobody reads the accumulators', 'tail(zero,desc)'), ("The warp's element pairs form ONE stream", 'stream')]
 marks = [(i, n) for i, t in enumerate(src, 1) for k, n in MARKS if k in t]
 def reg_of(f, l):

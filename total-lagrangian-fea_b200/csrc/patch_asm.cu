@@ -49,12 +49,6 @@ static int sm_count(int device) {
   return n;
 }
 
-// bytes of write-out lists a patch may have: the scratch area of the kernel configuration that will run it
-static int blob_limit(int W, int model) {
-  if (model == TL_MODEL_MR) return std::min(PKShape<false, TL_MODEL_MR>::scratch_bytes(W), PKShape<true, TL_MODEL_MR>::scratch_bytes(W));
-  return std::min(PKShape<false, TL_MODEL_SVK>::scratch_bytes(W), PKShape<true, TL_MODEL_SVK>::scratch_bytes(W));
-}
-
 static int patch_chunk_count() {
   static int k = [] {
     const char *e = getenv("TLFEA_PK_CHUNKS");  // id-range chunks of the launch order (host-buffer pipelining)
@@ -91,7 +85,7 @@ int patch_prepare(tlfea_newton *s) {
   PatchPlanHost hp;
   std::string err;
   const int rc = build_patch_plan(e->n_elem, e->n_coef, ecoef.data(), x.data(), y.data(), z.data(), off.data(),
-                                  cols.data(), W, blob_limit(W, e->model), patch_chunk_count(), &hp, &err);
+                                  cols.data(), W, patch_chunk_count(), &hp, &err);
   if (rc != TLFEA_OK) return fail(rc, "%s", err.c_str());
   auto *pp = new PatchPlanDev();
   s->patch = pp;
@@ -141,8 +135,6 @@ static int launch_pk_t(tlfea_elem *e, const PatchPlanDev *pp, PKArgs a, int p0, 
   using Sh = PKShape<DAMP, MODEL>;
   constexpr size_t smem = Sh::smem_bytes(W);
   static_assert(smem <= 227 * 1024, "patch kernel configuration exceeds the shared memory of one SM");
-  TL_CHECK(pp->max_blob <= Sh::scratch_bytes(W), "patch write-out lists (%d bytes) exceed the scratch area (%d bytes)",
-           pp->max_blob, Sh::scratch_bytes(W));
   static thread_local int attr_dev = -1;
   if (attr_dev != e->device) {
     TL_CUDA(cudaFuncSetAttribute(pk_kernel<W, DAMP, TANGENT, MODEL>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -46,8 +46,9 @@ struct EntL {
   int64_t habs;   // 9*off[i] + 3*slot
   int64_t g;      // global pattern block
   int rowlen;
-  uint16_t src;
+  uint16_t src;   // accumulator offset in doubles | transposed << 15
   bool first;
+  int seg;        // warp that owns the source block alone, or PK_MAXW: the block is the destination of merge ops
 };
 struct PatchLocal {
   std::vector<PElem> elems;
@@ -97,7 +98,7 @@ void assign_slots(int nb, const std::vector<std::vector<int>> &sets, std::vector
 }  // namespace
 
 int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y, const double *z,
-                     const int *off, const int *cols, int W, int blob_limit, int n_chunks, PatchPlanHost *out,
+                     const int *off, const int *cols, int W, int n_chunks, PatchPlanHost *out,
                      std::string *err) {
   auto failm = [&](int code, const char *m) {
     if (err) *err = m;
@@ -205,12 +206,11 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
     auto &plist = per_oct[o];
     for (size_t s0 = 0; s0 < subs.size();) {
       int ns = (int)std::min<size_t>(W, subs.size() - s0);
-    retry_smaller:
       PatchLocal P;
       P.n_sub = ns;
       struct Tup {
         uint64_t key;
-        uint16_t s;  // accumulator block address: warp << 8 | slot
+        uint16_t s;  // accumulator block address in doubles: warp * 9 PK_CAPU + 9 slot
       };
       std::vector<Tup> tups;
       for (int w = 0; w < ns; w++) {
@@ -273,7 +273,8 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
           }
           P.elems.push_back(pe);
         }
-        for (size_t u = 0; u < blocks.size(); u++) tups.push_back({blocks[u], (uint16_t)(slot[u] | (w << 8))});
+        for (size_t u = 0; u < blocks.size(); u++)
+          tups.push_back({blocks[u], (uint16_t)(w * 9 * PK_CAPU + 9 * slot[u])});
       }
       P.sub_ptr[ns] = (int)P.elems.size();
       for (int w = ns; w < PK_MAXW; w++) P.sub_ptr[w + 1] = P.sub_ptr[ns];
@@ -297,7 +298,8 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
           const int slot = (int)(it - cb);
           if (it == ce || *it != c || 3 * deg > PK_MAX_ROWLEN) P.bad = true;
           P.ent.push_back({9 * (int64_t)off[r] + 3 * slot, (int64_t)off[r] + slot, 3 * deg,
-                           (uint16_t)(tups[k].s | (side ? 0x800u : 0u)), false});
+                           (uint16_t)(tups[k].s | (side ? 0x8000u : 0u)), false,
+                           (k2 - k > 1) ? PK_MAXW : (int)(tups[k].s / (9 * PK_CAPU))});
           P.nodes.push_back(r);
         }
         k = k2;
@@ -310,14 +312,6 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
       std::sort(P.ent.begin(), P.ent.end(), [](const EntL &a, const EntL &b) { return a.habs < b.habs; });
       std::sort(P.nodes.begin(), P.nodes.end());
       P.nodes.erase(std::unique(P.nodes.begin(), P.nodes.end()), P.nodes.end());
-      // the write-out lists must fit the kernel's scratch area (bound: every entry a first touch)
-      if (BlobLayout((int)P.ent.size(), (int)P.ent.size(), (int)P.ops.size()).total > blob_limit) {
-        if (ns > 1) {
-          ns--;
-          goto retry_smaller;
-        }
-        P.bad = true;
-      }
       any_bad = any_bad || P.bad;
       plist.push_back(std::move(P));
       s0 += ns;
@@ -409,8 +403,10 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
           en.first = true;
         }
       }
-      // first touches first, then (row, column): entry k < n_first starts from the mass term
-      std::stable_sort(P.ent.begin(), P.ent.end(), [](const EntL &a, const EntL &b) { return a.first > b.first; });
+      // by segment, first touches first, then (row, column)
+      std::stable_sort(P.ent.begin(), P.ent.end(), [](const EntL &a, const EntL &b) {
+        return a.seg != b.seg ? a.seg < b.seg : a.first > b.first;
+      });
     }
   }
   for (int64_t g = 0; g < nnz; g++)
@@ -421,16 +417,29 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   int64_t sum_local = 0;
   int max_blob = 0;
   bool span_bad = false;
+  // blob of a patch: header | ops | segments (patch_plan.cuh)
+  auto blob_layout = [](const PatchLocal &P, int *hdr) {  // returns the size; hdr (PK_HDR_INTS ints) may be null
+    int nf[PK_NSEG] = {0}, nl[PK_NSEG] = {0};
+    for (auto &en : P.ent) (en.first ? nf : nl)[en.seg]++;
+    int pos = PK_HDR_INTS * 4 + pk_al16((int)P.ops.size() * 4);
+    if (hdr) {
+      std::memset(hdr, 0, PK_HDR_INTS * sizeof(int));
+      for (int r = 0; r < 8; r++) hdr[r] = P.round_end[r];
+    }
+    for (int sg = 0; sg < PK_NSEG; sg++) {
+      if (hdr) hdr[8 + 3 * sg] = pos / 16, hdr[9 + 3 * sg] = nf[sg], hdr[10 + 3 * sg] = nl[sg];
+      pos += 16 * nf[sg] + pk_al16(8 * nl[sg]);
+    }
+    return pos;
+  };
   for (int q = 0; q < np; q++) {
     const PatchLocal &P = *pl[perm[q]];
-    int nf = 0;
-    for (auto &en : P.ent) nf += en.first;
-    const BlobLayout L((int)P.ent.size(), nf, (int)P.ops.size());
+    const int total = blob_layout(P, nullptr);
     e_off[q + 1] = e_off[q] + (int64_t)P.elems.size();
-    b_off[q + 1] = b_off[q] + L.total;
+    b_off[q + 1] = b_off[q] + total;
     r_off[q + 1] = r_off[q] + (int64_t)P.nodes.size();
     sum_local += (int64_t)P.ent.size();
-    max_blob = std::max(max_blob, L.total);
+    max_blob = std::max(max_blob, total);
   }
   if (b_off[np] / 16 > 4294967295LL) return failm(TLFEA_ERR_UNSUPPORTED, "patch plan: blob exceeds 64 GB");
   R.desc.resize((size_t)np);
@@ -448,12 +457,13 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
     for (auto &en : P.ent) nf += en.first, hmin = std::min(hmin, en.habs), hmax = std::max(hmax, en.habs);
     if (P.ent.empty()) hmin = 0;
     span_bad = span_bad || (hmax - hmin > 4294967295LL);
-    const BlobLayout L((int)P.ent.size(), nf, (int)P.ops.size());
+    int hdr[PK_HDR_INTS];
+    const int total = blob_layout(P, hdr);
     PatchDesc d;
     std::memset(&d, 0, sizeof(d));
     for (int w = 0; w <= PK_MAXW; w++) d.sub_ptr[w] = (int)e_off[q] + P.sub_ptr[w];
     d.n_sub = P.n_sub;
-    d.n_ent = (int)P.ent.size();
+    d.blob_bytes = total;
     d.n_first = nf;
     d.n_merge = (int)P.ops.size();
     d.blob_off = (uint32_t)(b_off[q] / 16);
@@ -462,16 +472,26 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
     std::copy(P.elems.begin(), P.elems.end(), R.elems.begin() + e_off[q]);
     std::copy(P.nodes.begin(), P.nodes.end(), R.row_node.begin() + r_off[q]);
     unsigned char *bl = R.blob.data() + b_off[q];
-    std::memcpy(bl, P.round_end, 32);
-    if (!P.ops.empty()) std::memcpy(bl + L.ops, P.ops.data(), P.ops.size() * sizeof(uint32_t));
-    PEnt *ent = reinterpret_cast<PEnt *>(bl + L.ent);
-    for (size_t k = 0; k < P.ent.size(); k++) {
-      const EntL &en = P.ent[k];
-      ent[k].hoff = (uint32_t)(en.habs - hmin);
-      ent[k].rowlen = (uint16_t)en.rowlen;
-      ent[k].src = en.src;
+    std::memcpy(bl, hdr, sizeof(hdr));
+    if (!P.ops.empty()) std::memcpy(bl + PK_HDR_INTS * 4, P.ops.data(), P.ops.size() * sizeof(uint32_t));
+    size_t k = 0;  // entries are sorted by (segment, first touch before later touch, H position)
+    for (int sg = 0; sg < PK_NSEG; sg++) {
+      PEntF *ef = reinterpret_cast<PEntF *>(bl + (size_t)hdr[8 + 3 * sg] * 16);
+      PEnt *el = reinterpret_cast<PEnt *>(ef + hdr[9 + 3 * sg]);
+      for (int i = 0; i < hdr[9 + 3 * sg]; i++, k++) {
+        const EntL &en = P.ent[k];
+        ef[i].hoff = (uint32_t)(en.habs - hmin);
+        ef[i].rowlen = (uint16_t)en.rowlen;
+        ef[i].src = en.src;
+        ef[i].mass = 0.0;  // filled on the device from the assembled mass values (pk_fill_mass_kernel)
+      }
+      for (int i = 0; i < hdr[10 + 3 * sg]; i++, k++) {
+        const EntL &en = P.ent[k];
+        el[i].hoff = (uint32_t)(en.habs - hmin);
+        el[i].rowlen = (uint16_t)en.rowlen;
+        el[i].src = en.src;
+      }
     }
-    // the mass section is filled on the device from the assembled mass values
   }
   if (span_bad) return failm(TLFEA_ERR_UNSUPPORTED, "patch plan: a patch spans more than 2^32 entries of H");
   return TLFEA_OK;
@@ -492,7 +512,7 @@ int tlfea_debug_patch_plan_build(int n_elem, int n_coef, const int *ecoef, const
   TL_CHECK(ecoef && x && y && z && off && cols && plan_out, "null input");
   auto *p = new tlfea::PatchPlanHost();
   std::string err;
-  const int rc = tlfea::build_patch_plan(n_elem, n_coef, ecoef, x, y, z, off, cols, W, 1 << 20, n_chunks, p, &err);
+  const int rc = tlfea::build_patch_plan(n_elem, n_coef, ecoef, x, y, z, off, cols, W, n_chunks, p, &err);
   if (rc != TLFEA_OK) {
     delete p;
     return tlfea::fail(rc, "%s", err.c_str());

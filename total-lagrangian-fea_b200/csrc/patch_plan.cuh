@@ -34,43 +34,51 @@ struct PElem {          // 128 bytes, one per element, in processing order
 };
 static_assert(sizeof(PElem) == 128, "PElem is fetched as eight 16-byte pieces");
 
-// Everything the write-out of a patch reads sits in one contiguous, 16-byte aligned BLOB so that it arrives by a
-// single TMA bulk copy into scratch shared memory:
-//   round_end int[8] | merge ops uint32[n_merge] | entries PEnt[n_ent] | mass double[n_first]
-// (sections padded to 16 bytes).
-//   * merge op (dst | src << 16): accumulator block src is added to accumulator block dst.  A node pair that
-//     several warps of the patch hold is first reduced into the block of the lowest warp, one extra warp per
-//     ROUND (ops of round r: [round_end[r-1], round_end[r]); within a round every dst is distinct).
-//   * entry: one 3x3 block of H (both orientations of a pair are separate entries), ordered (first touch before
-//     later touch, then row, then column).  Entry k < n_first starts from M_ij/h (mass[k], refreshed on the
-//     device when the mass changes), the others from the value already in H.
-//   accumulator block address (16 bits): bits 0-7 block, 8-10 warp; entry src adds bit 11 = read transposed.
-struct PEnt {            // 8 bytes
+// Everything the write-out of a patch reads sits in one contiguous, 16-byte aligned BLOB in global memory (pulled
+// into L2 by a bulk prefetch when the patch starts, read with pipelined loads at write-out):
+//   header int[PK_HDR_INTS] | merge ops uint32[n_merge] | segment 0 | ... | segment PK_MAXW
+//   header: round_end[8], then per segment s {offset from the blob start in 16-byte units, n_first, n_later}
+//   segment: PEntF[n_first] (16 bytes each) then PEnt[n_later] (8 bytes each), padded to 16 bytes
+//   * merge op (dst | src << 16): accumulator block src is added to accumulator block dst (addresses in doubles from
+//     the start of the accumulators).  A node pair that several warps of the patch hold is first reduced into the
+//     block of the lowest warp, one extra warp per ROUND (ops of round r: [round_end[r-1], round_end[r]); within a
+//     round every dst is distinct).
+//   * entry: one 3x3 block of H (both orientations of a pair are separate entries).  Segment w < PK_MAXW holds the
+//     entries whose source block belongs to warp w alone: warp w writes them out as soon as its own elements are
+//     done, without waiting for the other warps.  Segment PK_MAXW holds the entries of merged blocks (after the CTA
+//     barrier and the merge rounds).  Within a segment: first touches (of the H block in the launch sequence; they
+//     start from M_ij/h, carried in the entry and refreshed on the device when the mass changes) before later
+//     touches (added to the value already in H), then (row, column).
+//   entry src (16 bits): bits 0-13 offset of the accumulator block in doubles (warp * 9 PK_CAPU + 9 slot), bit 15 =
+//   read transposed.
+struct PEnt {            // 8 bytes: later touch
   uint32_t hoff;         // offset (doubles) of H(3i, 3j) from the patch's hbase: 9*off[i] + 3*slot - hbase
   uint16_t rowlen;       // 3*deg(i): distance between the three scalar rows of the block row
   uint16_t src;
 };
 static_assert(sizeof(PEnt) == 8, "PEnt layout");
+struct PEntF {           // 16 bytes: first touch
+  uint32_t hoff;
+  uint16_t rowlen;
+  uint16_t src;
+  double mass;           // M_ij (scalar per node pair); the H block starts from (M_ij / h) I
+};
+static_assert(sizeof(PEntF) == 16, "PEntF layout");
+constexpr int PK_NSEG = PK_MAXW + 1;
+constexpr int PK_HDR_INTS = 36;  // 8 + 3 * PK_NSEG = 35, padded to 16 bytes
+static_assert(9 * PK_CAPU * PK_MAXW < (1 << 14), "entry src: 14 bits of accumulator offset");
 
 struct PatchDesc {       // 64 bytes
   int sub_ptr[PK_MAXW + 1];  // PElem range of sub-patch w: [sub_ptr[w], sub_ptr[w+1])
   int n_sub;
-  int n_ent, n_first, n_merge;
+  int blob_bytes;            // whole blob of the patch (L2 prefetch)
+  int n_first, n_merge;      // first-touch entries over all segments (statistics); merge ops
   uint32_t blob_off;         // in 16-byte units
   int64_t hbase;
 };
 static_assert(sizeof(PatchDesc) == 64, "PatchDesc layout");
 
 __host__ __device__ inline int pk_al16(int b) { return (b + 15) & ~15; }
-struct BlobLayout {
-  int ops, ent, mass, total;  // byte offsets; round_end sits at 0
-  __host__ __device__ BlobLayout(int n_ent, int n_first, int n_merge) {
-    ops = 32;
-    ent = ops + pk_al16(n_merge * 4);
-    mass = ent + pk_al16(n_ent * 8);
-    total = mass + pk_al16(n_first * 8);
-  }
-};
 
 struct PatchPlanHost {
   int W = 0;
@@ -89,10 +97,9 @@ struct PatchPlanHost {
 
 // Pure host code (no CUDA call): ecoef [n_elem][10]; x, y, z reference coordinates per coefficient; off / cols the
 // coefficient-level CSR pattern (sorted columns); n_chunks = id-range chunks of the launch order (1 = colours only);
-// blob_limit = largest write-out blob (bytes) a patch may have.
 // Returns 0 or a negative tlfea_status with *err set.
 int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y, const double *z,
-                     const int *off, const int *cols, int W, int blob_limit, int n_chunks, PatchPlanHost *out,
+                     const int *off, const int *cols, int W, int n_chunks, PatchPlanHost *out,
                      std::string *err);
 
 }  // namespace tlfea

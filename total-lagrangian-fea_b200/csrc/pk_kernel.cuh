@@ -19,12 +19,16 @@
 //   * instead of writing 100 block records, each lane adds its blocks (upper triangle by global id; transposed
 //     where the local order is reversed) into the warp's PRIVATE accumulator in shared memory: first the first
 //     element of the pair, then the second -- program order is the summation order.
-// After a CTA barrier the patch's write-out lists arrive by one TMA bulk copy into the dead staging area and
-// every thread walks (entry, column) positions: sum the entry's sources in warp order, start from M_ij/h (first
-// touch of the H block in the colour sequence) or from the value in H (later touch), store to the three scalar
-// CSR rows.  Loads of old values are issued before the first-touch entries are processed, so their latency
-// hides under that work.  Patches of one launch share no coefficient (graph colouring): plain loads and
-// stores, order per H entry = (colour, warp, element).
+// Write-out, in place into the CSR values of H (lists: patch_plan.cuh; they are read straight from global memory,
+// pulled into L2 by a bulk prefetch one patch ahead):
+//   (a) as soon as a warp has finished its own elements it writes the H entries of the blocks it holds alone (83 %
+//       of the entries on a Kuhn block) -- no CTA barrier, the other warps keep computing;
+//   (b) after a CTA barrier the node pairs held by several warps are reduced in fixed warp order (merge rounds);
+//   (c) all threads write the entries of the merged blocks.
+// An entry either starts from M_ij/h (first touch of the H block in the colour sequence: plain stores) or is added to
+// the value already in H (later touch: red.global.add.f64, performed by the L2 -- one reduction per address per
+// launch, launches are stream-ordered, so the order per H entry is the colour order).  Patches of one launch share
+// no coefficient (graph colouring): no two CTAs touch the same address, order per H entry = (colour, warp, element).
 #pragma once
 #include "ek_kernel.cuh"
 #include "patch_plan.cuh"
@@ -56,6 +60,12 @@ struct PKArgs {
 // 3 idx + i + const -- the 16 lanes of a half warp hit 16 different banks (the stride 33 of ek_kernel.cuh is for its
 // 10-lane step and gave a 9-way conflict here).
 constexpr int PK_GQ = 35;
+#ifndef PK_FU_OWN
+#define PK_FU_OWN 4  // entries per thread per trip of the write-out: a warp's own segment / the merged blocks
+#endif
+#ifndef PK_FU_DEP
+#define PK_FU_DEP 2
+#endif
 
 // Shared memory of a CTA: [accumulators x W][prefetch buffers x W][scratch x W].  The scratch areas (Gauss-point
 // results of the pair in flight) are contiguous over the warps: the write-out lists of the patch land there.
@@ -94,6 +104,90 @@ __device__ __forceinline__ void bulk_prefetch_l2(const void *gmem, unsigned byte
 }
 
 
+// Write-out of one entry segment (patch_plan.cuh): thread = (entry slot, column e) of a 3x3 block of H, three rows d
+// per thread: consecutive lanes store consecutive doubles of a scalar CSR row (an entry-per-thread mapping was
+// measured: 2.3x the store sectors, 10 % slower).  The entries are read from shared memory (SMEM: the segment was
+// staged by a TMA bulk copy) or straight from global memory (lists that do not fit the staging area; the blob was
+// pulled into L2 when the patch started), FU per thread per trip with the next trip's loads in flight.
+//   first touches of an H block in the colour sequence: H block = (M_ij / h) I + sum, plain stores;
+//   later touches: H += sum as L2 reductions.  One reduction per address per launch (patches of a launch share no
+//   coefficient) and launches are stream-ordered, so the additions per H entry happen in colour order: the same
+//   IEEE additions a load-add-store would do, but with no load to wait for.
+template <int FU, bool SMEM>
+__device__ __forceinline__ void pk_write_segment(const unsigned char *seg, int nf, int nl, int slot, int nslots, int we,
+                                                 const double *acc0, double *Hb, double inv_h,
+                                                 unsigned hmask = 0xffffffffu) {
+  // everything that depends on the column e is per-thread constant and branch-free (lanes of a warp differ in e)
+  const unsigned acc_s = (unsigned)__cvta_generic_to_shared(acc0) + 8u * we;  // not transposed: + e, row stride 3
+  const unsigned we16 = 16u * we;                                              // transposed: + 3 e, row stride 1
+  const double m0 = (we == 0) ? inv_h : 0.0, m1 = (we == 1) ? inv_h : 0.0, m2 = (we == 2) ? inv_h : 0.0;
+  double *Hw = Hb + we;
+  auto block_col = [&](unsigned meta, double v[3]) {  // column e of the entry's block, rows 0..2
+    const unsigned tr = meta >> 31;
+    const unsigned a = acc_s + ((meta >> 13) & 0x1fff8u) + tr * we16, st = 24u - 16u * tr;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v[0]) : "r"(a));
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v[1]) : "r"(a + st));
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v[2]) : "r"(a + 2u * st));
+  };
+  auto ld4 = [](const uint4 *q) { return SMEM ? *q : __ldg(q); };
+  auto ld2 = [](const uint2 *q) { return SMEM ? *q : __ldg(q); };
+  auto put_first = [&](const uint4 e, const double v[3]) {  // H block = (M_ij / h) I + sum
+    const double m = __hiloint2double((int)e.w, (int)e.z);
+    double *hp = Hw + (e.x & hmask);
+    const unsigned rl = e.y & 0xffffu;
+    hp[0] = fma(m, m0, v[0]);
+    hp[rl] = fma(m, m1, v[1]);
+    hp[2 * rl] = fma(m, m2, v[2]);
+  };
+  auto put_later = [&](const uint2 e, const double v[3]) {  // H block += sum
+    double *hp = Hw + (e.x & hmask);
+    const unsigned rl = e.y & 0xffffu;
+    red_add_f64(hp, v[0]);
+    red_add_f64(hp + rl, v[1]);
+    red_add_f64(hp + 2 * rl, v[2]);
+  };
+  {
+    const uint4 *ef = reinterpret_cast<const uint4 *>(seg);
+    int k = slot;
+    for (; k + (FU - 1) * nslots < nf; k += FU * nslots) {  // full trips: FU independent entries, no guards
+      uint4 e[FU];
+      double v[FU][3];
+#pragma unroll
+      for (int u = 0; u < FU; u++) e[u] = ld4(ef + k + u * nslots);
+#pragma unroll
+      for (int u = 0; u < FU; u++) block_col(e[u].y, v[u]);
+#pragma unroll
+      for (int u = 0; u < FU; u++) put_first(e[u], v[u]);
+    }
+    for (; k < nf; k += nslots) {
+      const uint4 e = ld4(ef + k);
+      double v[3];
+      block_col(e.y, v);
+      put_first(e, v);
+    }
+  }
+  {
+    const uint2 *el = reinterpret_cast<const uint2 *>(seg + (size_t)nf * 16);
+    int k = slot;
+    for (; k + (FU - 1) * nslots < nl; k += FU * nslots) {
+      uint2 e[FU];
+      double v[FU][3];
+#pragma unroll
+      for (int u = 0; u < FU; u++) e[u] = ld2(el + k + u * nslots);
+#pragma unroll
+      for (int u = 0; u < FU; u++) block_col(e[u].y, v[u]);
+#pragma unroll
+      for (int u = 0; u < FU; u++) put_later(e[u], v[u]);
+    }
+    for (; k < nl; k += nslots) {
+      const uint2 e = ld2(el + k);
+      double v[3];
+      block_col(e.y, v);
+      put_later(e, v);
+    }
+  }
+}
+
 template <int W, bool DAMP, bool TANGENT, int MODEL>
 __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) {
   using Sh = PKShape<DAMP, MODEL>;
@@ -101,7 +195,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   constexpr int NT = W * 32;
   extern __shared__ __align__(16) double pk_smem[];
   __shared__ uint64_t s_bar[W][2];
-  __shared__ uint64_t s_bar_blob;
+  __shared__ uint64_t s_bar_wo[W + 2];  // write-out lists: [w] warp w's own segment, [W] merged-block entries, [W+1] merge ops
   __shared__ PatchDesc s_desc[2];  // this CTA's current and next patch
   __shared__ double s_dn[150];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -122,13 +216,14 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   if (lane == 0) {
     mbar_init(&s_bar[warp][0], 1);
     mbar_init(&s_bar[warp][1], 1);
+    mbar_init(&s_bar_wo[warp], 1);
   }
-  if (threadIdx.x == 0) mbar_init(&s_bar_blob, 1);
+  if (threadIdx.x < 2) mbar_init(&s_bar_wo[W + threadIdx.x], 1);
   for (int i = threadIdx.x; i < 150; i += NT) s_dn[i] = p.dn[i];
   __syncthreads();
   if (TANGENT && threadIdx.x == 0)  // the write-out lists are needed last: pull them into L2 now
     bulk_prefetch_l2(p.blob + (size_t)s_desc[0].blob_off * 16,
-                     (unsigned)BlobLayout(s_desc[0].n_ent, s_desc[0].n_first, s_desc[0].n_merge).total);
+                     (unsigned)s_desc[0].blob_bytes);
 
   // ---- prefetch helpers (per warp): plan records / data of the element pair [kk, kk + ne)
   auto issue_pe = [&](int kk, int ne, int buf) {
@@ -214,6 +309,40 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     const int n_it = (k1 - k0 + 1) >> 1;
     const int k0n = has_next ? dn.sub_ptr[warp] : 0, k1n = has_next ? dn.sub_ptr[warp + 1] : 0;
     const int n_itn = (k1n - k0n + 1) >> 1;
+    // write-out header of this patch (round ends, entry segments): lane l holds ints l and 32 + l; needed only after
+    // the warp's last element, so the loads cost nothing here
+    const unsigned char *blobp = p.blob + (size_t)dc.blob_off * 16;
+    int hv0 = 0, hv1 = 0;
+    if (TANGENT) {
+      hv0 = __ldg(reinterpret_cast<const int *>(blobp) + lane);
+      if (lane < PK_HDR_INTS - 32) hv1 = __ldg(reinterpret_cast<const int *>(blobp) + 32 + lane);
+    }
+    // The write-out lists are staged in the scratch areas by TMA bulk copies: the warp's own segment into its own
+    // scratch as soon as the Gauss-point results of its last pair have been consumed (the copy flies under the
+    // accumulation), the lists for after the CTA barrier into the scratch of warps 0 and 1 once those are done with
+    // theirs.  A list that does not fit is read from global memory instead (bar still completes its phase).
+    constexpr int SCR_BYTES = Sh::SCR_D * (int)sizeof(double);
+    auto stage = [&](double *dst, const unsigned char *src, int bytes, uint64_t *bar) {  // one lane
+      asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // dst was last accessed by ordinary loads / stores
+      if (bytes > 0) {
+        bulk_load(dst, src, (unsigned)bytes, bar);
+      } else {
+        const unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(b) : "memory");
+      }
+    };
+    int seg_so = 0, seg_nf = 0, seg_nl = 0;
+    bool seg_issued = false, seg_smem = false;
+    auto stage_own_segment = [&]() {  // whole warp
+      seg_so = __shfl_sync(0xffffffffu, hv0, 8 + 3 * warp);
+      seg_nf = __shfl_sync(0xffffffffu, hv0, 9 + 3 * warp);
+      seg_nl = __shfl_sync(0xffffffffu, hv0, 10 + 3 * warp);
+      const int bytes = 16 * seg_nf + pk_al16(8 * seg_nl);
+      seg_smem = bytes <= SCR_BYTES;
+      seg_issued = true;
+      __syncwarp();
+      if (lane == 0) stage(ws, blobp + (size_t)seg_so * 16, seg_smem ? bytes : 0, &s_bar_wo[warp]);
+    };
     // the j-th pair after pair `it` of this patch (possibly in the next patch); false = none known yet
     auto nth = [&](int it, int j, int &kk, int &ne) {
       if (it + j < n_it) {
@@ -604,20 +733,25 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
 #pragma unroll
         for (int t = 0; t < 4; t++) {
           const double dg = p.c4 * p.mu * (A[t][0] + A[t][4] + A[t][8]);
+          // a block that the accumulator holds transposed (global ids in the other order) is finished transposed:
+          // (c1 A + c2 A^T + sym)^T = c2 A + c1 A^T + sym -- two selects here instead of nine in the accumulation
+          const bool trt = (trb >> t) & 1u;
+          const double ca = trt ? p.c2 : p.c1, cb = trt ? p.c1 : p.c2;
           double k[9];
-          k[0] = p.c1 * A[t][0] + p.c2 * A[t][0] + Gs[t][0] + dg;
-          k[1] = p.c1 * A[t][1] + p.c2 * A[t][3] + Gs[t][1];
-          k[2] = p.c1 * A[t][2] + p.c2 * A[t][6] + Gs[t][2];
-          k[3] = p.c1 * A[t][3] + p.c2 * A[t][1] + Gs[t][1];
-          k[4] = p.c1 * A[t][4] + p.c2 * A[t][4] + Gs[t][3] + dg;
-          k[5] = p.c1 * A[t][5] + p.c2 * A[t][7] + Gs[t][4];
-          k[6] = p.c1 * A[t][6] + p.c2 * A[t][2] + Gs[t][2];
-          k[7] = p.c1 * A[t][7] + p.c2 * A[t][5] + Gs[t][4];
-          k[8] = p.c1 * A[t][8] + p.c2 * A[t][8] + Gs[t][5] + dg;
+          k[0] = ca * A[t][0] + cb * A[t][0] + Gs[t][0] + dg;
+          k[1] = ca * A[t][1] + cb * A[t][3] + Gs[t][1];
+          k[2] = ca * A[t][2] + cb * A[t][6] + Gs[t][2];
+          k[3] = ca * A[t][3] + cb * A[t][1] + Gs[t][1];
+          k[4] = ca * A[t][4] + cb * A[t][4] + Gs[t][3] + dg;
+          k[5] = ca * A[t][5] + cb * A[t][7] + Gs[t][4];
+          k[6] = ca * A[t][6] + cb * A[t][2] + Gs[t][2];
+          k[7] = ca * A[t][7] + cb * A[t][5] + Gs[t][4];
+          k[8] = ca * A[t][8] + cb * A[t][8] + Gs[t][5] + dg;
 #pragma unroll
           for (int i = 0; i < 9; i++) A[t][i] = k[i];
         }
       }
+      if (it == n_it - 1) stage_own_segment();  // u, M_q, the force partials of this pair are dead: K sits in registers
       // ordered accumulation into the warp's private accumulator: first element of the pair, then the second.
       // Every lane walks the 9 MEMORY positions of its block in the same order (a transposed block picks the other
       // register), so the 15 lanes of a half warp hit 15 different banks when their slots differ modulo 16 -- which
@@ -631,7 +765,8 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
           for (int t0 = 0; t0 < 4; t0 += 2) {
             double *d0 = acc + ((blkw >> (8 * t0)) & 255u) * 9;
             double *d1 = acc + ((blkw >> (8 * (t0 + 1))) & 255u) * 9;
-            const bool tr0 = (trb >> t0) & 1u, tr1 = (trb >> (t0 + 1)) & 1u;
+            // Mooney-Rivlin blocks are transposed here; SVK blocks were finished in the stored orientation
+            const bool tr0 = MR && ((trb >> t0) & 1u), tr1 = MR && ((trb >> (t0 + 1)) & 1u);
             // t0 = 2: (a1+1, a1) is the transpose of (a1, a1+1) on diagonal tiles -- the upper block carries it
             const bool skip0 = (t0 == 2) && (tI == tJ);
             // the first element of the sub-patch to touch a block stores it (no zero-fill of the accumulator)
@@ -662,140 +797,101 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   }
 
   // ------------------------------------------------------------ write-out
-  __syncthreads();  // every accumulator is final and the scratch areas are dead (prefetches live elsewhere)
-  const int n_ent = dc.n_ent, n_first = dc.n_first, n_merge = dc.n_merge;
-  const BlobLayout L(n_ent, n_first, n_merge);
-  unsigned char *sb = reinterpret_cast<unsigned char *>(scr0);
-  if (threadIdx.x == 0) {
-    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
-    bulk_load(sb, p.blob + (size_t)dc.blob_off * 16, (unsigned)L.total, &s_bar_blob);
+  // tuning aid (TLFEA_PK_DEBUG & 16): all H traffic of a CTA into a 128 KB window -- the assembly without its DRAM traffic
+  double *Hb = p.H + ((p.debug & 16) ? (int64_t)(blockIdx.x & 255) * 65536 : dc.hbase);
+  const unsigned hmask = (p.debug & 16) ? 0x3fffu : 0xffffffffu;
+  const bool wo_on = !(p.debug & 1);
+  // (a) the blocks this warp holds alone are final: their entries leave now, while the other warps still compute
+  const unsigned wo_par = n_done & 1;
+  if (!seg_issued) stage_own_segment();  // a warp without elements in this patch, or the block step switched off
+  mbar_wait(&s_bar_wo[warp], wo_par);
+  if (wo_on && lane < 30) {
+    if (seg_smem)
+      pk_write_segment<PK_FU_OWN, true>(reinterpret_cast<const unsigned char *>(ws), seg_nf, seg_nl, lane / 3, 10, lane % 3,
+                                pk_smem, Hb, p.inv_h, hmask);
+    else
+      pk_write_segment<PK_FU_OWN, false>(blobp + (size_t)seg_so * 16, seg_nf, seg_nl, lane / 3, 10, lane % 3, pk_smem, Hb,
+                                 p.inv_h, hmask);
   }
-  mbar_wait(&s_bar_blob, n_done & 1);
-  const int *round_end = reinterpret_cast<const int *>(sb);
-  const uint32_t *ops = reinterpret_cast<const uint32_t *>(sb + L.ops);
-  const uint2 *ent = reinterpret_cast<const uint2 *>(sb + L.ent);
-  const double *massb = reinterpret_cast<const double *>(sb + L.mass);
-  auto blk_addr = [&](unsigned a) { return pk_smem + (size_t)((a >> 8) & 7u) * Sh::ACC_D + (a & 255u) * 9; };
-
-  // pairs held by several warps: reduce into the lowest warp's block, one extra warp per round (fixed order)
-  if (n_merge > 0) {
+  // the lists for after the barrier: merged-block entries -> scratch of warp 0, merge ops -> scratch of warp 1 % W
+  const int n_merge = dc.n_merge;
+  const int dep_so = __shfl_sync(0xffffffffu, hv1, 0), dep_nf = __shfl_sync(0xffffffffu, hv1, 1),
+            dep_nl = __shfl_sync(0xffffffffu, hv1, 2);
+  const int dep_bytes = 16 * dep_nf + pk_al16(8 * dep_nl), ops_bytes = pk_al16(4 * n_merge);
+  const bool dep_smem = dep_bytes <= SCR_BYTES, ops_smem = ops_bytes <= SCR_BYTES;
+  __syncwarp();
+  if (warp == 0 && lane == 0) stage(ws, blobp + (size_t)dep_so * 16, dep_smem ? dep_bytes : 0, &s_bar_wo[W]);
+  if (warp == 1 % W && lane == 0) stage(ws, blobp + PK_HDR_INTS * 4, ops_smem ? ops_bytes : 0, &s_bar_wo[W + 1]);
+  // (b) pairs held by several warps: reduce into the lowest warp's block, one extra warp per round (fixed order);
+  // thread = merge op
+  __syncthreads();  // every accumulator is final
+  if (n_merge > 0 && wo_on) {
+    mbar_wait(&s_bar_wo[W + 1], wo_par);
+    const uint32_t *ops_g = reinterpret_cast<const uint32_t *>(blobp + PK_HDR_INTS * 4);
+    const uint32_t *ops_s = reinterpret_cast<const uint32_t *>(scr0 + (size_t)(1 % W) * Sh::SCR_D);
     int lo = 0;
     for (int r = 0; r < 7 && lo < n_merge; r++) {
-      const int hi = round_end[r];
-      const int nw = (hi - lo) * 9;
-      for (int t = threadIdx.x; t < nw; t += 2 * NT) {
-        const int t2 = t + NT;
-        const int q = t / 9, i = t - 9 * q, q2 = t2 / 9, i2 = t2 - 9 * q2;
-        const uint32_t op = ops[lo + q], op2 = ops[lo + min(q2, hi - lo - 1)];
-        double *da = blk_addr(op & 0xffffu) + i, *db = blk_addr(op2 & 0xffffu) + i2;
-        const double a0 = *da, a1 = blk_addr(op >> 16)[i];
-        const double b0 = *db, b1 = blk_addr(op2 >> 16)[i2];
-        *da = a0 + a1;
-        if (t2 < nw) *db = b0 + b1;
+      const int hi = __shfl_sync(0xffffffffu, hv0, r);
+      for (int q = lo + (int)threadIdx.x; q < hi; q += NT) {
+        const uint32_t op = ops_smem ? ops_s[q] : __ldg(ops_g + q);
+        double *da = pk_smem + (op & 0xffffu);
+        const double *sa = pk_smem + (op >> 16);
+        double a[9], b[9];
+#pragma unroll
+        for (int i = 0; i < 9; i++) a[i] = da[i], b[i] = sa[i];
+#pragma unroll
+        for (int i = 0; i < 9; i++) da[i] = a[i] + b[i];
       }
       __syncthreads();
       lo = hi;
     }
   }
-
-  double *Hb = p.H + dc.hbase;
-  // Thread = (entry, column e) of a 3x3 block of H, three rows d per thread: consecutive lanes store consecutive
-  // doubles of a scalar CSR row (an entry-per-thread mapping was measured: 2.3x the store sectors, 10 % slower).
-  // Threads stride over the entries by NT/3, so e and the entry phase are fixed per thread.
-  constexpr int KS = NT / 3;
-  const int we = (int)threadIdx.x % 3, wk = (int)threadIdx.x / 3;
-  if ((int)threadIdx.x < 3 * KS && !(p.debug & 1)) {
-    auto block_col = [&](unsigned src, double v[3]) {  // column we of the entry's block, rows 0..2
-      const bool tr = src & 0x800u;
-      const double *bsrc = blk_addr(src) + (tr ? 3 * we : we);
-      const int st = tr ? 1 : 3;
-      v[0] = bsrc[0];
-      v[1] = bsrc[st];
-      v[2] = bsrc[2 * st];
-    };
-    constexpr int FU = 4;  // entries per thread per trip: their shared-memory loads overlap
-    // first touches of an H block in the colour sequence: H block = (M_ij / h) I + sum, plain stores
-    for (int k0f = wk; k0f < n_first; k0f += FU * KS) {
-      double *hp[FU];
-      unsigned rl[FU];
-      double v[FU][3];
-#pragma unroll
-      for (int u = 0; u < FU; u++) {
-        const int k = min(k0f + u * KS, n_first - 1);
-        const uint2 en = ent[k];
-        hp[u] = Hb + en.x + we;
-        rl[u] = en.y & 0xffffu;
-        block_col(en.y >> 16, v[u]);
-        const double m = massb[k] * p.inv_h;
-        if (we == 0) v[u][0] += m;
-        if (we == 1) v[u][1] += m;
-        if (we == 2) v[u][2] += m;
-      }
-#pragma unroll
-      for (int u = 0; u < FU; u++) {
-        if (k0f + u * KS < n_first) {
-          hp[u][0] = v[u][0];
-          hp[u][rl[u]] = v[u][1];
-          hp[u][2 * rl[u]] = v[u][2];
-        }
-      }
-    }
-    // later touches: H += sum.  One reduction per address per launch (patches of a launch share no coefficient) and
-    // launches are stream-ordered, so the order of the additions per H entry is the colour order: fixed, and the
-    // same IEEE additions a load-add-store would do -- but performed by the L2, with no load to wait for.
-    for (int k0 = n_first + wk; k0 < n_ent; k0 += FU * KS) {
-      double *hp[FU];
-      unsigned rl[FU];
-      double v[FU][3];
-#pragma unroll
-      for (int u = 0; u < FU; u++) {
-        const int k = min(k0 + u * KS, n_ent - 1);
-        const uint2 en = ent[k];
-        hp[u] = Hb + en.x + we;
-        rl[u] = en.y & 0xffffu;
-        block_col(en.y >> 16, v[u]);
-      }
-#pragma unroll
-      for (int u = 0; u < FU; u++) {
-        if (k0 + u * KS < n_ent) {
-          red_add_f64(hp[u], v[u][0]);
-          red_add_f64(hp[u] + rl[u], v[u][1]);
-          red_add_f64(hp[u] + 2 * rl[u], v[u][2]);
-        }
-      }
+  // (c) entries of the merged blocks, all threads
+  {
+    constexpr int KS = NT / 3;
+    mbar_wait(&s_bar_wo[W], wo_par);
+    if (wo_on && (int)threadIdx.x < 3 * KS) {
+      if (dep_smem)
+        pk_write_segment<PK_FU_DEP, true>(reinterpret_cast<const unsigned char *>(scr0), dep_nf, dep_nl, (int)threadIdx.x / 3, KS,
+                                  (int)threadIdx.x % 3, pk_smem, Hb, p.inv_h, hmask);
+      else
+        pk_write_segment<PK_FU_DEP, false>(blobp + (size_t)dep_so * 16, dep_nf, dep_nl, (int)threadIdx.x / 3, KS,
+                                   (int)threadIdx.x % 3, pk_smem, Hb, p.inv_h, hmask);
     }
   }
   __syncthreads();  // nobody reads the accumulators, the lists or the current descriptor any more
   if (threadIdx.x < 16) load_desc(pk + 2 * gridDim.x, n_done & 1);
   if (has_next && threadIdx.x == 32 % NT)
-    bulk_prefetch_l2(p.blob + (size_t)dn.blob_off * 16, (unsigned)BlobLayout(dn.n_ent, dn.n_first, dn.n_merge).total);
+    bulk_prefetch_l2(p.blob + (size_t)dn.blob_off * 16, (unsigned)dn.blob_bytes);
   __syncthreads();
   }  // patches
   cp_async_wait_all();
 }
 
-// mass section of every patch blob: mass[k] = M(row, column) of first-touch entry k.  The pattern block of an entry
-// follows from its H position: 9*off[i] <= hbase + hoff < 9*off[i+1].
+// mass field of every first-touch entry: M(row, column) of the pattern block the entry writes.  The block follows from
+// the entry's H position: 9*off[i] <= hbase + hoff < 9*off[i+1].
 __global__ void pk_fill_mass_kernel(int n_patches, int n_coef, const PatchDesc *__restrict__ desc, unsigned char *blob,
                                     const int *__restrict__ off, const double *__restrict__ mass) {
   const int pch = blockIdx.x;
   if (pch >= n_patches) return;
   const PatchDesc d = desc[pch];
-  const BlobLayout L(d.n_ent, d.n_first, d.n_merge);
   unsigned char *sb = blob + (size_t)d.blob_off * 16;
-  const PEnt *ent = reinterpret_cast<const PEnt *>(sb + L.ent);
-  double *massb = reinterpret_cast<double *>(sb + L.mass);
-  for (int k = threadIdx.x; k < d.n_first; k += blockDim.x) {
-    const int64_t habs = d.hbase + ent[k].hoff;
-    const int64_t blk9 = habs / 9;
-    int lo = 0, hi = n_coef;  // largest i with off[i] <= blk9
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (off[mid] <= blk9) lo = mid;
-      else hi = mid;
+  const int *hdr = reinterpret_cast<const int *>(sb);
+  for (int sg = 0; sg < PK_NSEG; sg++) {
+    PEntF *ent = reinterpret_cast<PEntF *>(sb + (size_t)hdr[8 + 3 * sg] * 16);
+    const int nf = hdr[9 + 3 * sg];
+    for (int k = threadIdx.x; k < nf; k += blockDim.x) {
+      const int64_t habs = d.hbase + ent[k].hoff;
+      const int64_t blk9 = habs / 9;
+      int lo = 0, hi = n_coef;  // largest i with off[i] <= blk9
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (off[mid] <= blk9) lo = mid;
+        else hi = mid;
+      }
+      const int slot = (int)((habs - 9 * (int64_t)off[lo]) / 3);
+      ent[k].mass = mass[off[lo] + slot];
     }
-    const int slot = (int)((habs - 9 * (int64_t)off[lo]) / 3);
-    massb[k] = mass[off[lo] + slot];
   }
 }
 
