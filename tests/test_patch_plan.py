@@ -12,7 +12,7 @@ PELEM = np.dtype([("elem", "<i4"), ("pad0", "<i4"), ("node", "<i4", (10,)), ("bl
                   ("tr", "<u4", (2,)), ("first", "<u4", (2,)), ("pad1", "<i4")])
 PENT = np.dtype([("hoff", "<u4"), ("rowlen", "<u2"), ("src", "<u2")])
 PENTF = np.dtype([("hoff", "<u4"), ("rowlen", "<u2"), ("src", "<u2"), ("mass", "<f8")])
-HDR_INTS, NSEG = 36, 9  # csrc/patch_plan.cuh: PK_HDR_INTS, PK_NSEG
+HDR_INTS, MAXW = 64, 8  # csrc/patch_plan.cuh: PK_HDR_INTS, PK_MAXW
 PDESC = np.dtype([("sub_ptr", "<i4", (9,)), ("n_sub", "<i4"), ("blob_bytes", "<i4"), ("n_first", "<i4"), ("n_merge", "<i4"),
                   ("blob_off", "<u4"), ("hbase", "<i8")])
 TILES = [(0, j) for j in range(5)] + [(1, j) for j in range(1, 5)] + [(2, j) for j in range(2, 5)] + \
@@ -53,22 +53,28 @@ def al16(b):
 
 
 def patch_sections(plan, d):
-    """(round_end, ops, segments) of one patch's blob (csrc/patch_plan.cuh): segments = [(first16, later8)] * NSEG;
-    segment w < 8 = blocks warp w holds alone, segment 8 = merged blocks."""
+    """Chunks of one patch's blob (csrc/patch_plan.cuh): per warp w ((own first16, own later8), (merged first16,
+    merged later8), ops)."""
     b0 = int(d["blob_off"]) * 16
     bl = plan["blob"][b0:b0 + int(d["blob_bytes"])]
     hdr = bl[:4 * HDR_INTS].view(np.int32)
-    ops = bl[4 * HDR_INTS:4 * HDR_INTS + 4 * d["n_merge"]].view(np.uint32)
-    segs = []
-    end = 4 * HDR_INTS + al16(4 * int(d["n_merge"]))
-    for sg in range(NSEG):
-        o, nf, nl = (int(v) for v in hdr[8 + 3 * sg:11 + 3 * sg])
-        assert 16 * o == end  # segments are contiguous
-        segs.append((bl[16 * o:16 * o + 16 * nf].view(PENTF), bl[16 * o + 16 * nf:16 * o + 16 * nf + 8 * nl].view(PENT)))
-        end = 16 * o + 16 * nf + al16(8 * nl)
+    chunks = []
+    end = 4 * HDR_INTS
+    for w in range(MAXW):
+        o, nf, nl, df, dl, nops = (int(v) for v in hdr[8 * w:8 * w + 6])
+        assert 16 * o == end and (hdr[8 * w + 6:8 * w + 8] == 0).all()  # chunks are contiguous
+        at = 16 * o
+        own = (bl[at:at + 16 * nf].view(PENTF), bl[at + 16 * nf:at + 16 * nf + 8 * nl].view(PENT))
+        at += 16 * nf + al16(8 * nl)
+        dep = (bl[at:at + 16 * df].view(PENTF), bl[at + 16 * df:at + 16 * df + 8 * dl].view(PENT))
+        at += 16 * df + al16(8 * dl)
+        ops = bl[at:at + 4 * nops].view(np.uint32)
+        end = at + al16(4 * nops)
+        chunks.append((own, dep, ops))
     assert end == int(d["blob_bytes"])
-    assert sum(len(f) for f, _ in segs) == int(d["n_first"])
-    return hdr[:8], ops, segs
+    assert sum(len(c[0][0]) + len(c[1][0]) for c in chunks) == int(d["n_first"])
+    assert sum(len(c[2]) for c in chunks) == int(d["n_merge"])
+    return chunks
 
 
 def replay(plan, Ke, mass_of_hpos, h, nnz):
@@ -99,7 +105,7 @@ def replay(plan, Ke, mass_of_hpos, h, nnz):
                                 fs = (int(pe["first"][bit >> 5]) >> (bit & 31)) & 1
                                 assert fs == int(np.isnan(acc[w, u]).all())
                                 acc[w, u] = (0.0 if fs else acc[w, u]) + (blk.T if tr else blk)
-            round_end, ops, segs = patch_sections(plan, d)
+            chunks = patch_sections(plan, d)
             acc = acc.reshape(-1)  # block addresses are offsets in doubles: warp * 9 CAPU + 9 slot
             ablk = lambda a: acc[a:a + 9].reshape(3, 3)  # noqa: E731
 
@@ -118,28 +124,30 @@ def replay(plan, Ke, mass_of_hpos, h, nnz):
                             assert not first or np.isnan(H[base:base + 3]).all()
                             H[base:base + 3] = old + val[dd]
 
-            merged = set(int(op) & 0xffff for op in ops)
-            for w in range(8):  # (a) every warp writes the blocks it holds alone, before any merge
-                for part in segs[w]:
+            all_ops = [int(op) for c in chunks for op in c[2]]
+            merged = set(op & 0x3fff for op in all_ops)
+            sources = set(op >> 16 for op in all_ops)
+            for w, (own, dep, ops) in enumerate(chunks):  # (a) every warp writes the blocks it holds alone, before any merge
+                for part in own:
                     for en in part:
                         a = int(en["src"]) & 0x3fff
-                        assert a // (9 * CAPU) == w and a not in merged
-                        assert not any((int(op) >> 16) == a for op in ops)
-                write_segment(segs[w])
-            lo = 0
-            for r in range(7):  # (b) merge rounds
-                dsts = set()
-                for op in ops[lo:round_end[r]]:
-                    dst, src = int(op) & 0xffff, int(op) >> 16
-                    assert dst not in dsts  # within a round every destination is distinct
-                    dsts.add(dst)
+                        assert a // (9 * CAPU) == w and a not in merged and a not in sources
+                write_segment(own)
+            seen_dst = set()
+            for own, dep, ops in chunks:  # (b) warp w: dst += src in list order, one dst after the other ...
+                mine, prev = set(), None
+                for op in ops:
+                    dst, cont, src = int(op) & 0x3fff, (int(op) >> 15) & 1, int(op) >> 16
+                    assert cont == int(dst == prev) and (cont or dst not in seen_dst)  # the ops of a dst are consecutive
+                    assert src // (9 * CAPU) > dst // (9 * CAPU)  # into the lowest warp, ascending warp order
                     ablk(dst)[:] += ablk(src)
-                lo = round_end[r]
-            assert lo == d["n_merge"]
-            for part in segs[8]:  # (c) entries of merged blocks
-                for en in part:
-                    assert (int(en["src"]) & 0x3fff) in merged
-            write_segment(segs[8])
+                    seen_dst.add(dst)
+                    mine.add(dst)
+                    prev = dst
+                for part in dep:  # (c) ... then the entries of exactly those dsts
+                    for en in part:
+                        assert (int(en["src"]) & 0x3fff) in mine
+                write_segment(dep)
     return H
 
 

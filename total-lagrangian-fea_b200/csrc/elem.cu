@@ -663,6 +663,7 @@ int tlfea_elem_set_linear_constraints_csr(tlfea_elem *h, int n_c, const int *off
   TL_CUDA(cudaMemcpy(h->d_jt_off, t_off.data(), ((size_t)n_dof + 1) * sizeof(int), cudaMemcpyHostToDevice));
   TL_CUDA(cudaMemcpy(h->d_jt_cols, t_cols.data(), (size_t)nnz * sizeof(int), cudaMemcpyHostToDevice));
   TL_CUDA(cudaMemcpy(h->d_jt_vals, t_vals.data(), (size_t)nnz * sizeof(double), cudaMemcpyHostToDevice));
+  TL_CUDA(cudaDeviceSynchronize());  // pageable copies may return before their DMA lands; the handle's stream is non-blocking
   TL_CUDA(cudaMemset(h->d_constraint, 0, (size_t)n_c * sizeof(double)));
   h->cons_mode = TL_CONS_LINEAR_CSR;
   h->h_j_off.assign(off, off + n_c + 1);

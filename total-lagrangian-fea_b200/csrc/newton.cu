@@ -1285,6 +1285,7 @@ int tlfea_newton_analyze_sparsity(tlfea_newton *s) {
       TL_TRY(dmalloc(&s->d_cons_val, us.size()));
       TL_CUDA(cudaMemcpy(s->d_cons_slot, us.data(), us.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
       TL_CUDA(cudaMemcpy(s->d_cons_val, uv.data(), us.size() * sizeof(double), cudaMemcpyHostToDevice));
+      TL_CUDA(cudaDeviceSynchronize());  // pageable copies may return before their DMA lands; the handle's stream is non-blocking
     }
   }
   TL_CUDA(cudaGetLastError());

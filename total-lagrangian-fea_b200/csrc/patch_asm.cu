@@ -102,9 +102,12 @@ int patch_prepare(tlfea_newton *s) {
   TL_TRY(dmalloc(&pp->d_desc, hp.desc.size()));
   TL_TRY(dmalloc(&pp->d_elems, hp.elems.size()));
   TL_TRY(dmalloc(&pp->d_blob, hp.blob.size()));
-  TL_CUDA(cudaMemcpy(pp->d_desc, hp.desc.data(), hp.desc.size() * sizeof(PatchDesc), cudaMemcpyHostToDevice));
-  TL_CUDA(cudaMemcpy(pp->d_elems, hp.elems.data(), hp.elems.size() * sizeof(PElem), cudaMemcpyHostToDevice));
-  TL_CUDA(cudaMemcpy(pp->d_blob, hp.blob.data(), hp.blob.size(), cudaMemcpyHostToDevice));
+  // The uploads go on the handle's stream: it is a non-blocking stream, so a plain cudaMemcpy (legacy stream, and
+  // from pageable memory it may return while the DMA is still in flight) is NOT ordered against the kernels that
+  // follow -- pk_fill_mass_kernel could write the mass fields first and the tail of the copy overwrite them.
+  TL_CUDA(cudaMemcpyAsync(pp->d_desc, hp.desc.data(), hp.desc.size() * sizeof(PatchDesc), cudaMemcpyHostToDevice, e->stream));
+  TL_CUDA(cudaMemcpyAsync(pp->d_elems, hp.elems.data(), hp.elems.size() * sizeof(PElem), cudaMemcpyHostToDevice, e->stream));
+  TL_CUDA(cudaMemcpyAsync(pp->d_blob, hp.blob.data(), hp.blob.size(), cudaMemcpyHostToDevice, e->stream));
   pp->n_unc = (int64_t)hp.uncovered.size();
   if (pp->n_unc > 0) {
     std::vector<int> row(hp.uncovered.size());
@@ -112,9 +115,11 @@ int patch_prepare(tlfea_newton *s) {
       row[k] = (int)(std::upper_bound(off.begin(), off.end(), (int)hp.uncovered[k]) - off.begin()) - 1;
     TL_TRY(dmalloc(&pp->d_unc, hp.uncovered.size()));
     TL_TRY(dmalloc(&pp->d_unc_row, row.size()));
-    TL_CUDA(cudaMemcpy(pp->d_unc, hp.uncovered.data(), hp.uncovered.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
-    TL_CUDA(cudaMemcpy(pp->d_unc_row, row.data(), row.size() * sizeof(int), cudaMemcpyHostToDevice));
+    TL_CUDA(cudaMemcpyAsync(pp->d_unc, hp.uncovered.data(), hp.uncovered.size() * sizeof(int64_t), cudaMemcpyHostToDevice, e->stream));
+    TL_CUDA(cudaMemcpyAsync(pp->d_unc_row, row.data(), row.size() * sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    TL_CUDA(cudaStreamSynchronize(e->stream));  // row is a local
   }
+  TL_CUDA(cudaStreamSynchronize(e->stream));  // the host plan goes out of scope
   return TLFEA_OK;
 }
 

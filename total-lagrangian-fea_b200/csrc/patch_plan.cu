@@ -48,7 +48,7 @@ struct EntL {
   int rowlen;
   uint16_t src;   // accumulator offset in doubles | transposed << 15
   bool first;
-  int seg;        // warp that owns the source block alone, or PK_MAXW: the block is the destination of merge ops
+  int seg;        // chunk: the warp that owns the source block alone, or PK_MAXW + g: merged block of chunk g
 };
 struct PatchLocal {
   std::vector<PElem> elems;
@@ -56,8 +56,8 @@ struct PatchLocal {
   int n_sub = 0;
   std::vector<int> nodes;  // distinct coefficient ids (ascending)
   std::vector<EntL> ent;
-  std::vector<uint32_t> ops;  // merge ops, round by round
-  int round_end[8] = {0};
+  std::vector<uint32_t> ops[PK_MAXW];  // merge ops of chunk g (patch_plan.cuh)
+  int n_ops = 0;
   int color = -1;
   bool bad = false;
 };
@@ -282,13 +282,18 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
       std::sort(tups.begin(), tups.end(), [](const Tup &a, const Tup &b) {
         return a.key != b.key ? a.key < b.key : a.s < b.s;
       });
-      std::vector<std::vector<uint32_t>> rounds(8);
+      int n_mergedst = 0;
       for (size_t k = 0; k < tups.size();) {
         size_t k2 = k;
         while (k2 < tups.size() && tups[k2].key == tups[k].key) k2++;
         if (k2 - k > 8) P.bad = true;
-        for (size_t q = k + 1; q < k2 && q - k <= 7; q++)
-          rounds[q - k - 1].push_back((uint32_t)tups[k].s | ((uint32_t)tups[q].s << 16));
+        int seg = (int)(tups[k].s / (9 * PK_CAPU));
+        if (k2 - k > 1) {  // merged pair: dealt round-robin to the chunks
+          const int g = n_mergedst++ % W;
+          for (size_t q = k + 1; q < k2 && q - k <= 7; q++)
+            P.ops[g].push_back((uint32_t)tups[k].s | (q > k + 1 ? 0x8000u : 0u) | ((uint32_t)tups[q].s << 16));
+          seg = PK_MAXW + g;
+        }
         const int i = (int)(tups[k].key >> 32), j = (int)(tups[k].key & 0xffffffffu);
         for (int side = 0; side < (i == j ? 1 : 2); side++) {
           const int r = side ? j : i, c = side ? i : j;
@@ -298,17 +303,12 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
           const int slot = (int)(it - cb);
           if (it == ce || *it != c || 3 * deg > PK_MAX_ROWLEN) P.bad = true;
           P.ent.push_back({9 * (int64_t)off[r] + 3 * slot, (int64_t)off[r] + slot, 3 * deg,
-                           (uint16_t)(tups[k].s | (side ? 0x8000u : 0u)), false,
-                           (k2 - k > 1) ? PK_MAXW : (int)(tups[k].s / (9 * PK_CAPU))});
+                           (uint16_t)(tups[k].s | (side ? 0x8000u : 0u)), false, seg});
           P.nodes.push_back(r);
         }
         k = k2;
       }
-      for (int r = 0; r < 7; r++) {
-        P.ops.insert(P.ops.end(), rounds[r].begin(), rounds[r].end());
-        P.round_end[r] = (int)P.ops.size();
-      }
-      P.round_end[7] = (int)P.ops.size();
+      for (int g = 0; g < PK_MAXW; g++) P.n_ops += (int)P.ops[g].size();
       std::sort(P.ent.begin(), P.ent.end(), [](const EntL &a, const EntL &b) { return a.habs < b.habs; });
       std::sort(P.nodes.begin(), P.nodes.end());
       P.nodes.erase(std::unique(P.nodes.begin(), P.nodes.end()), P.nodes.end());
@@ -417,18 +417,20 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   int64_t sum_local = 0;
   int max_blob = 0;
   bool span_bad = false;
-  // blob of a patch: header | ops | segments (patch_plan.cuh)
+  // blob of a patch: header | chunks (patch_plan.cuh)
   auto blob_layout = [](const PatchLocal &P, int *hdr) {  // returns the size; hdr (PK_HDR_INTS ints) may be null
-    int nf[PK_NSEG] = {0}, nl[PK_NSEG] = {0};
+    int nf[2 * PK_MAXW] = {0}, nl[2 * PK_MAXW] = {0};
     for (auto &en : P.ent) (en.first ? nf : nl)[en.seg]++;
-    int pos = PK_HDR_INTS * 4 + pk_al16((int)P.ops.size() * 4);
-    if (hdr) {
-      std::memset(hdr, 0, PK_HDR_INTS * sizeof(int));
-      for (int r = 0; r < 8; r++) hdr[r] = P.round_end[r];
-    }
-    for (int sg = 0; sg < PK_NSEG; sg++) {
-      if (hdr) hdr[8 + 3 * sg] = pos / 16, hdr[9 + 3 * sg] = nf[sg], hdr[10 + 3 * sg] = nl[sg];
-      pos += 16 * nf[sg] + pk_al16(8 * nl[sg]);
+    int pos = PK_HDR_INTS * 4;
+    if (hdr) std::memset(hdr, 0, PK_HDR_INTS * sizeof(int));
+    for (int w = 0; w < PK_MAXW; w++) {
+      if (hdr) {
+        int *hw = hdr + 8 * w;
+        hw[0] = pos / 16, hw[1] = nf[w], hw[2] = nl[w], hw[3] = nf[PK_MAXW + w], hw[4] = nl[PK_MAXW + w];
+        hw[5] = (int)P.ops[w].size();
+      }
+      pos += 16 * nf[w] + pk_al16(8 * nl[w]) + 16 * nf[PK_MAXW + w] + pk_al16(8 * nl[PK_MAXW + w]) +
+             pk_al16(4 * (int)P.ops[w].size());
     }
     return pos;
   };
@@ -465,7 +467,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
     d.n_sub = P.n_sub;
     d.blob_bytes = total;
     d.n_first = nf;
-    d.n_merge = (int)P.ops.size();
+    d.n_merge = P.n_ops;
     d.blob_off = (uint32_t)(b_off[q] / 16);
     d.hbase = hmin;
     R.desc[q] = d;
@@ -473,24 +475,37 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
     std::copy(P.nodes.begin(), P.nodes.end(), R.row_node.begin() + r_off[q]);
     unsigned char *bl = R.blob.data() + b_off[q];
     std::memcpy(bl, hdr, sizeof(hdr));
-    if (!P.ops.empty()) std::memcpy(bl + PK_HDR_INTS * 4, P.ops.data(), P.ops.size() * sizeof(uint32_t));
-    size_t k = 0;  // entries are sorted by (segment, first touch before later touch, H position)
-    for (int sg = 0; sg < PK_NSEG; sg++) {
-      PEntF *ef = reinterpret_cast<PEntF *>(bl + (size_t)hdr[8 + 3 * sg] * 16);
-      PEnt *el = reinterpret_cast<PEnt *>(ef + hdr[9 + 3 * sg]);
-      for (int i = 0; i < hdr[9 + 3 * sg]; i++, k++) {
+    // entries are sorted by (segment, first touch before later touch, H position); segment = w (own) or PK_MAXW + w
+    size_t own_at[PK_MAXW + 1], dep_at[PK_MAXW + 1];
+    {
+      size_t k = 0;
+      for (int w = 0; w < PK_MAXW; w++) own_at[w] = k, k += (size_t)(hdr[8 * w + 1] + hdr[8 * w + 2]);
+      for (int w = 0; w < PK_MAXW; w++) dep_at[w] = k, k += (size_t)(hdr[8 * w + 3] + hdr[8 * w + 4]);
+    }
+    auto emit = [&](unsigned char *at, size_t k, int nf_, int nl_) {
+      PEntF *ef = reinterpret_cast<PEntF *>(at);
+      PEnt *el = reinterpret_cast<PEnt *>(ef + nf_);
+      for (int i = 0; i < nf_; i++, k++) {
         const EntL &en = P.ent[k];
         ef[i].hoff = (uint32_t)(en.habs - hmin);
         ef[i].rowlen = (uint16_t)en.rowlen;
         ef[i].src = en.src;
         ef[i].mass = 0.0;  // filled on the device from the assembled mass values (pk_fill_mass_kernel)
       }
-      for (int i = 0; i < hdr[10 + 3 * sg]; i++, k++) {
+      for (int i = 0; i < nl_; i++, k++) {
         const EntL &en = P.ent[k];
         el[i].hoff = (uint32_t)(en.habs - hmin);
         el[i].rowlen = (uint16_t)en.rowlen;
         el[i].src = en.src;
       }
+      return at + 16 * nf_ + pk_al16(8 * nl_);
+    };
+    for (int w = 0; w < PK_MAXW; w++) {
+      const int *hw = hdr + 8 * w;
+      unsigned char *at = bl + (size_t)hw[0] * 16;
+      at = emit(at, own_at[w], hw[1], hw[2]);
+      at = emit(at, dep_at[w], hw[3], hw[4]);
+      if (hw[5]) std::memcpy(at, P.ops[w].data(), (size_t)hw[5] * sizeof(uint32_t));
     }
   }
   if (span_bad) return failm(TLFEA_ERR_UNSUPPORTED, "patch plan: a patch spans more than 2^32 entries of H");

@@ -35,20 +35,23 @@ struct PElem {          // 128 bytes, one per element, in processing order
 static_assert(sizeof(PElem) == 128, "PElem is fetched as eight 16-byte pieces");
 
 // Everything the write-out of a patch reads sits in one contiguous, 16-byte aligned BLOB in global memory (pulled
-// into L2 by a bulk prefetch when the patch starts, read with pipelined loads at write-out):
-//   header int[PK_HDR_INTS] | merge ops uint32[n_merge] | segment 0 | ... | segment PK_MAXW
-//   header: round_end[8], then per segment s {offset from the blob start in 16-byte units, n_first, n_later}
-//   segment: PEntF[n_first] (16 bytes each) then PEnt[n_later] (8 bytes each), padded to 16 bytes
-//   * merge op (dst | src << 16): accumulator block src is added to accumulator block dst (addresses in doubles from
-//     the start of the accumulators).  A node pair that several warps of the patch hold is first reduced into the
-//     block of the lowest warp, one extra warp per ROUND (ops of round r: [round_end[r-1], round_end[r]); within a
-//     round every dst is distinct).
-//   * entry: one 3x3 block of H (both orientations of a pair are separate entries).  Segment w < PK_MAXW holds the
-//     entries whose source block belongs to warp w alone: warp w writes them out as soon as its own elements are
-//     done, without waiting for the other warps.  Segment PK_MAXW holds the entries of merged blocks (after the CTA
-//     barrier and the merge rounds).  Within a segment: first touches (of the H block in the launch sequence; they
-//     start from M_ij/h, carried in the entry and refreshed on the device when the mass changes) before later
-//     touches (added to the value already in H), then (row, column).
+// into L2 by a bulk prefetch one patch ahead):
+//   header int[PK_HDR_INTS] | chunk 0 | ... | chunk PK_MAXW-1
+//   header: per chunk w the 8 ints {offset from the blob start in 16-byte units, n_first own, n_later own,
+//           n_first merged, n_later merged, n_ops, 0, 0}
+//   chunk w (what warp w needs, contiguous so that ONE TMA bulk copy stages it in the warp's scratch area):
+//           PEntF[n_first own] PEnt[n_later own] pad16 | PEntF[n_first merged] PEnt[n_later merged] pad16 |
+//           uint32 ops[n_ops] pad16
+//   * own entries: the H entries of the accumulator blocks warp w holds ALONE.  Warp w writes them as soon as its
+//     own elements are done, without waiting for the other warps.
+//   * merge ops (dst | cont << 15 | src << 16, addresses in doubles from the start of the accumulators): a node pair
+//     that several warps hold is reduced into the block of the lowest warp: dst += src, sources in ascending warp
+//     order; the ops of one dst are consecutive, all but the first carry the continuation bit, and one thread does
+//     them in sequence.  The merged pairs of a patch are dealt round-robin to the chunks; after the CTA barrier warp
+//     w does the ops of chunk w and then writes the merged entries of chunk w (the entries of exactly those dsts).
+//   * entry: one 3x3 block of H (both orientations of a pair are separate entries).  First touches (of the H block
+//     in the launch sequence; they start from M_ij/h, carried in the entry and refreshed on the device when the mass
+//     changes) before later touches (added to the value already in H), then (row, column).
 //   entry src (16 bits): bits 0-13 offset of the accumulator block in doubles (warp * 9 PK_CAPU + 9 slot), bit 15 =
 //   read transposed.
 struct PEnt {            // 8 bytes: later touch
@@ -64,8 +67,7 @@ struct PEntF {           // 16 bytes: first touch
   double mass;           // M_ij (scalar per node pair); the H block starts from (M_ij / h) I
 };
 static_assert(sizeof(PEntF) == 16, "PEntF layout");
-constexpr int PK_NSEG = PK_MAXW + 1;
-constexpr int PK_HDR_INTS = 36;  // 8 + 3 * PK_NSEG = 35, padded to 16 bytes
+constexpr int PK_HDR_INTS = 8 * PK_MAXW;  // 64 ints: lane l of a warp holds ints l and 32 + l
 static_assert(9 * PK_CAPU * PK_MAXW < (1 << 14), "entry src: 14 bits of accumulator offset");
 
 struct PatchDesc {       // 64 bytes

@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   constexpr int NT = W * 32;
   extern __shared__ __align__(16) double pk_smem[];
   __shared__ uint64_t s_bar[W][2];
-  __shared__ uint64_t s_bar_wo[W + 2];  // write-out lists: [w] warp w's own segment, [W] merged-block entries, [W+1] merge ops
+  __shared__ uint64_t s_bar_wo[W];  // arrival of warp w's write-out chunk in its scratch area
   __shared__ PatchDesc s_desc[2];  // this CTA's current and next patch
   __shared__ double s_dn[150];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -218,7 +218,6 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     mbar_init(&s_bar[warp][1], 1);
     mbar_init(&s_bar_wo[warp], 1);
   }
-  if (threadIdx.x < 2) mbar_init(&s_bar_wo[W + threadIdx.x], 1);
   for (int i = threadIdx.x; i < 150; i += NT) s_dn[i] = p.dn[i];
   __syncthreads();
   if (TANGENT && threadIdx.x == 0)  // the write-out lists are needed last: pull them into L2 now
@@ -315,34 +314,41 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
     int hv0 = 0, hv1 = 0;
     if (TANGENT) {
       hv0 = __ldg(reinterpret_cast<const int *>(blobp) + lane);
-      if (lane < PK_HDR_INTS - 32) hv1 = __ldg(reinterpret_cast<const int *>(blobp) + 32 + lane);
+      if (W > 4) hv1 = __ldg(reinterpret_cast<const int *>(blobp) + 32 + lane);
     }
-    // The write-out lists are staged in the scratch areas by TMA bulk copies: the warp's own segment into its own
-    // scratch as soon as the Gauss-point results of its last pair have been consumed (the copy flies under the
-    // accumulation), the lists for after the CTA barrier into the scratch of warps 0 and 1 once those are done with
-    // theirs.  A list that does not fit is read from global memory instead (bar still completes its phase).
+    // descriptor of the patch after the next one: requested now, stored when the current descriptor is dead
+    int desc_next = 0;
+    if (threadIdx.x < 16 && pk + 2 * (int)gridDim.x < p.n_patches)
+      desc_next = __ldg(reinterpret_cast<const int *>(p.desc + pk + 2 * gridDim.x) + threadIdx.x);
+    // The warp's write-out chunk (own entries | merged entries | merge ops, patch_plan.cuh) is staged in its scratch
+    // area by ONE TMA bulk copy as soon as the Gauss-point results of its last pair have been consumed: the copy
+    // flies under the accumulation.  A chunk that does not fit is read from global memory instead.
     constexpr int SCR_BYTES = Sh::SCR_D * (int)sizeof(double);
-    auto stage = [&](double *dst, const unsigned char *src, int bytes, uint64_t *bar) {  // one lane
-      asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // dst was last accessed by ordinary loads / stores
-      if (bytes > 0) {
-        bulk_load(dst, src, (unsigned)bytes, bar);
-      } else {
-        const unsigned b = (unsigned)__cvta_generic_to_shared(bar);
-        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(b) : "memory");
+    int ck_off = 0, ck_nf = 0, ck_nl = 0, ck_df = 0, ck_dl = 0, ck_ops = 0;
+    bool ck_issued = false, ck_smem = false;
+    auto stage_chunk = [&]() {  // whole warp
+      const int hv = (warp < 4) ? hv0 : hv1, l0 = 8 * (warp & 3);
+      ck_off = __shfl_sync(0xffffffffu, hv, l0);
+      ck_nf = __shfl_sync(0xffffffffu, hv, l0 + 1);
+      ck_nl = __shfl_sync(0xffffffffu, hv, l0 + 2);
+      ck_df = __shfl_sync(0xffffffffu, hv, l0 + 3);
+      ck_dl = __shfl_sync(0xffffffffu, hv, l0 + 4);
+      ck_ops = __shfl_sync(0xffffffffu, hv, l0 + 5);
+      const int bytes = 16 * (ck_nf + ck_df) + pk_al16(8 * ck_nl) + pk_al16(8 * ck_dl) + pk_al16(4 * ck_ops);
+      ck_smem = bytes <= SCR_BYTES;
+      ck_issued = true;
+      __syncwarp();
+      if (lane == 0) {
+        asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // the scratch was last accessed by ordinary loads / stores
+        if (ck_smem && bytes > 0) {
+          bulk_load(ws, blobp + (size_t)ck_off * 16, (unsigned)bytes, &s_bar_wo[warp]);
+        } else {
+          const unsigned b = (unsigned)__cvta_generic_to_shared(&s_bar_wo[warp]);
+          asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(b) : "memory");
+        }
       }
     };
-    int seg_so = 0, seg_nf = 0, seg_nl = 0;
-    bool seg_issued = false, seg_smem = false;
-    auto stage_own_segment = [&]() {  // whole warp
-      seg_so = __shfl_sync(0xffffffffu, hv0, 8 + 3 * warp);
-      seg_nf = __shfl_sync(0xffffffffu, hv0, 9 + 3 * warp);
-      seg_nl = __shfl_sync(0xffffffffu, hv0, 10 + 3 * warp);
-      const int bytes = 16 * seg_nf + pk_al16(8 * seg_nl);
-      seg_smem = bytes <= SCR_BYTES;
-      seg_issued = true;
-      __syncwarp();
-      if (lane == 0) stage(ws, blobp + (size_t)seg_so * 16, seg_smem ? bytes : 0, &s_bar_wo[warp]);
-    };
+
     // the j-th pair after pair `it` of this patch (possibly in the next patch); false = none known yet
     auto nth = [&](int it, int j, int &kk, int &ne) {
       if (it + j < n_it) {
@@ -751,7 +757,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
           for (int i = 0; i < 9; i++) A[t][i] = k[i];
         }
       }
-      if (it == n_it - 1) stage_own_segment();  // u, M_q, the force partials of this pair are dead: K sits in registers
+      if (it == n_it - 1) stage_chunk();  // u, M_q, the force partials of this pair are dead: K sits in registers
       // ordered accumulation into the warp's private accumulator: first element of the pair, then the second.
       // Every lane walks the 9 MEMORY positions of its block in the same order (a transposed block picks the other
       // register), so the 15 lanes of a half warp hit 15 different banks when their slots differ modulo 16 -- which
@@ -791,7 +797,8 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   }
   if (!TANGENT) {  // force only: no shared output, just keep the descriptor ring turning
     __syncthreads();
-    if (threadIdx.x < 16) load_desc(pk + 2 * gridDim.x, n_done & 1);
+    if (threadIdx.x < 16 && pk + 2 * (int)gridDim.x < p.n_patches)
+      reinterpret_cast<int *>(&s_desc[n_done & 1])[threadIdx.x] = desc_next;
     __syncthreads();
     continue;
   }
@@ -802,65 +809,51 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   const unsigned hmask = (p.debug & 16) ? 0x3fffu : 0xffffffffu;
   const bool wo_on = !(p.debug & 1);
   // (a) the blocks this warp holds alone are final: their entries leave now, while the other warps still compute
-  const unsigned wo_par = n_done & 1;
-  if (!seg_issued) stage_own_segment();  // a warp without elements in this patch, or the block step switched off
-  mbar_wait(&s_bar_wo[warp], wo_par);
+  if (!ck_issued) stage_chunk();  // a warp without elements in this patch, or the block step switched off
+  mbar_wait(&s_bar_wo[warp], n_done & 1);
+  const unsigned char *ck = ck_smem ? reinterpret_cast<const unsigned char *>(ws) : blobp + (size_t)ck_off * 16;
+  const unsigned char *ck_dep = ck + 16 * ck_nf + pk_al16(8 * ck_nl);
+  const uint32_t *ops = reinterpret_cast<const uint32_t *>(ck_dep + 16 * ck_df + pk_al16(8 * ck_dl));
   if (wo_on && lane < 30) {
-    if (seg_smem)
-      pk_write_segment<PK_FU_OWN, true>(reinterpret_cast<const unsigned char *>(ws), seg_nf, seg_nl, lane / 3, 10, lane % 3,
-                                pk_smem, Hb, p.inv_h, hmask);
+    if (ck_smem)
+      pk_write_segment<PK_FU_OWN, true>(ck, ck_nf, ck_nl, lane / 3, 10, lane % 3, pk_smem, Hb, p.inv_h, hmask);
     else
-      pk_write_segment<PK_FU_OWN, false>(blobp + (size_t)seg_so * 16, seg_nf, seg_nl, lane / 3, 10, lane % 3, pk_smem, Hb,
-                                 p.inv_h, hmask);
+      pk_write_segment<PK_FU_OWN, false>(ck, ck_nf, ck_nl, lane / 3, 10, lane % 3, pk_smem, Hb, p.inv_h, hmask);
   }
-  // the lists for after the barrier: merged-block entries -> scratch of warp 0, merge ops -> scratch of warp 1 % W
-  const int n_merge = dc.n_merge;
-  const int dep_so = __shfl_sync(0xffffffffu, hv1, 0), dep_nf = __shfl_sync(0xffffffffu, hv1, 1),
-            dep_nl = __shfl_sync(0xffffffffu, hv1, 2);
-  const int dep_bytes = 16 * dep_nf + pk_al16(8 * dep_nl), ops_bytes = pk_al16(4 * n_merge);
-  const bool dep_smem = dep_bytes <= SCR_BYTES, ops_smem = ops_bytes <= SCR_BYTES;
-  __syncwarp();
-  if (warp == 0 && lane == 0) stage(ws, blobp + (size_t)dep_so * 16, dep_smem ? dep_bytes : 0, &s_bar_wo[W]);
-  if (warp == 1 % W && lane == 0) stage(ws, blobp + PK_HDR_INTS * 4, ops_smem ? ops_bytes : 0, &s_bar_wo[W + 1]);
-  // (b) pairs held by several warps: reduce into the lowest warp's block, one extra warp per round (fixed order);
-  // thread = merge op
   __syncthreads();  // every accumulator is final
-  if (n_merge > 0 && wo_on) {
-    mbar_wait(&s_bar_wo[W + 1], wo_par);
-    const uint32_t *ops_g = reinterpret_cast<const uint32_t *>(blobp + PK_HDR_INTS * 4);
-    const uint32_t *ops_s = reinterpret_cast<const uint32_t *>(scr0 + (size_t)(1 % W) * Sh::SCR_D);
-    int lo = 0;
-    for (int r = 0; r < 7 && lo < n_merge; r++) {
-      const int hi = __shfl_sync(0xffffffffu, hv0, r);
-      for (int q = lo + (int)threadIdx.x; q < hi; q += NT) {
-        const uint32_t op = ops_smem ? ops_s[q] : __ldg(ops_g + q);
-        double *da = pk_smem + (op & 0xffffu);
+  // (b) pairs held by several warps: dst += src in ascending warp order, one thread per dst (the ops of a dst are
+  // consecutive; all but the first carry the continuation bit).  Warp w does the ops of chunk w ...
+  if (wo_on) {
+    for (int q = lane; q < ck_ops; q += 32) {
+      uint32_t op = ck_smem ? ops[q] : __ldg(ops + q);
+      if (op & 0x8000u) continue;
+      double *da = pk_smem + (op & 0x3fffu);
+      double a[9];
+#pragma unroll
+      for (int i = 0; i < 9; i++) a[i] = da[i];
+      int j = q;
+      do {
         const double *sa = pk_smem + (op >> 16);
-        double a[9], b[9];
 #pragma unroll
-        for (int i = 0; i < 9; i++) a[i] = da[i], b[i] = sa[i];
+        for (int i = 0; i < 9; i++) a[i] += sa[i];
+        j++;
+        op = (j < ck_ops) ? (ck_smem ? ops[j] : __ldg(ops + j)) : 0u;
+      } while (op & 0x8000u);
 #pragma unroll
-        for (int i = 0; i < 9; i++) da[i] = a[i] + b[i];
-      }
-      __syncthreads();
-      lo = hi;
+      for (int i = 0; i < 9; i++) da[i] = a[i];
     }
-  }
-  // (c) entries of the merged blocks, all threads
-  {
-    constexpr int KS = NT / 3;
-    mbar_wait(&s_bar_wo[W], wo_par);
-    if (wo_on && (int)threadIdx.x < 3 * KS) {
-      if (dep_smem)
-        pk_write_segment<PK_FU_DEP, true>(reinterpret_cast<const unsigned char *>(scr0), dep_nf, dep_nl, (int)threadIdx.x / 3, KS,
-                                  (int)threadIdx.x % 3, pk_smem, Hb, p.inv_h, hmask);
+    __syncwarp();
+    // (c) ... and writes the H entries of exactly those dsts
+    if (lane < 30) {
+      if (ck_smem)
+        pk_write_segment<PK_FU_DEP, true>(ck_dep, ck_df, ck_dl, lane / 3, 10, lane % 3, pk_smem, Hb, p.inv_h, hmask);
       else
-        pk_write_segment<PK_FU_DEP, false>(blobp + (size_t)dep_so * 16, dep_nf, dep_nl, (int)threadIdx.x / 3, KS,
-                                   (int)threadIdx.x % 3, pk_smem, Hb, p.inv_h, hmask);
+        pk_write_segment<PK_FU_DEP, false>(ck_dep, ck_df, ck_dl, lane / 3, 10, lane % 3, pk_smem, Hb, p.inv_h, hmask);
     }
   }
   __syncthreads();  // nobody reads the accumulators, the lists or the current descriptor any more
-  if (threadIdx.x < 16) load_desc(pk + 2 * gridDim.x, n_done & 1);
+  if (threadIdx.x < 16 && pk + 2 * (int)gridDim.x < p.n_patches)
+    reinterpret_cast<int *>(&s_desc[n_done & 1])[threadIdx.x] = desc_next;
   if (has_next && threadIdx.x == 32 % NT)
     bulk_prefetch_l2(p.blob + (size_t)dn.blob_off * 16, (unsigned)dn.blob_bytes);
   __syncthreads();
@@ -877,9 +870,12 @@ __global__ void pk_fill_mass_kernel(int n_patches, int n_coef, const PatchDesc *
   const PatchDesc d = desc[pch];
   unsigned char *sb = blob + (size_t)d.blob_off * 16;
   const int *hdr = reinterpret_cast<const int *>(sb);
-  for (int sg = 0; sg < PK_NSEG; sg++) {
-    PEntF *ent = reinterpret_cast<PEntF *>(sb + (size_t)hdr[8 + 3 * sg] * 16);
-    const int nf = hdr[9 + 3 * sg];
+  for (int part = 0; part < 2 * PK_MAXW; part++) {  // own and merged first-touch entries of every chunk
+    const int *hw = hdr + 8 * (part >> 1);
+    unsigned char *at = sb + (size_t)hw[0] * 16;
+    if (part & 1) at += 16 * hw[1] + pk_al16(8 * hw[2]);
+    PEntF *ent = reinterpret_cast<PEntF *>(at);
+    const int nf = (part & 1) ? hw[3] : hw[1];
     for (int k = threadIdx.x; k < nf; k += blockDim.x) {
       const int64_t habs = d.hbase + ent[k].hoff;
       const int64_t blk9 = habs / 9;
