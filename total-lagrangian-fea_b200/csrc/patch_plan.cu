@@ -282,14 +282,20 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
       std::sort(tups.begin(), tups.end(), [](const Tup &a, const Tup &b) {
         return a.key != b.key ? a.key < b.key : a.s < b.s;
       });
-      int n_mergedst = 0;
+      int n_mergedst = 0, n_merged_total = 0;
+      for (size_t k = 0; k < tups.size();) {  // merged pairs of the patch (dealt to the chunks in contiguous runs)
+        size_t k2 = k;
+        while (k2 < tups.size() && tups[k2].key == tups[k].key) k2++;
+        n_merged_total += (k2 - k > 1);
+        k = k2;
+      }
       for (size_t k = 0; k < tups.size();) {
         size_t k2 = k;
         while (k2 < tups.size() && tups[k2].key == tups[k].key) k2++;
         if (k2 - k > 8) P.bad = true;
         int seg = (int)(tups[k].s / (9 * PK_CAPU));
         if (k2 - k > 1) {  // merged pair: dealt round-robin to the chunks
-          const int g = n_mergedst++ % W;
+          const int g = (int)((int64_t)(n_mergedst++) * W / n_merged_total);  // key order = row order: a chunk gets whole rows
           for (size_t q = k + 1; q < k2 && q - k <= 7; q++)
             P.ops[g].push_back((uint32_t)tups[k].s | (q > k + 1 ? 0x8000u : 0u) | ((uint32_t)tups[q].s << 16));
           seg = PK_MAXW + g;
