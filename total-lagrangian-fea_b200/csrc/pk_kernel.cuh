@@ -78,7 +78,7 @@ struct PKShape {
   static constexpr int X_D = 60;
   static constexpr int PE_D = 32;   // two plan records
   static constexpr int U_D = MR ? 2 * 5 * EK_TS : 2 * 5 * PK_GQ;
-  static constexpr int REC_D = MR ? 0 : 2 * 5 * EK_REC;
+  static constexpr int REC_D = 0;  // M_q | dV of the SVK path live in the spare doubles [30, 35) of the u and force-partial rows
   static constexpr int FP_D = MR ? 2 * 5 * EK_GQM : 2 * 5 * PK_GQ;
   static constexpr int OFF_H = 0;
   static constexpr int OFF_DJ = OFF_H + 2 * H_D;
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   double *wb = pk_smem + (size_t)W * Sh::ACC_D + (size_t)warp * Sh::PREF_D;  // prefetch buffers of this warp
   double *scr0 = pk_smem + (size_t)W * (Sh::ACC_D + Sh::PREF_D);
   double *ws = scr0 + (size_t)warp * Sh::SCR_D;
-  double *s_u = ws + Sh::OFF_U, *s_rec = ws + Sh::OFF_REC, *s_fp = ws + Sh::OFF_FP;
+  double *s_u = ws + Sh::OFF_U, *s_fp = ws + Sh::OFF_FP;
 
   auto load_desc = [&](int pk, int slot) {  // threads 0..15
     if (pk < p.n_patches)
@@ -635,16 +635,17 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
         if (TANGENT) uq[aa * 3 + part] = Fi[0] * ha[0] + Fi[1] * ha[1] + Fi[2] * ha[2];
       }
       if (TANGENT && part == 0) {
-        double *r = s_rec + idx * EK_REC;
+        // M_q (6) and dV go into the five spare doubles of the u row and the first two of the force-partial row
+        // (the force partials are summed before the block step, but nothing overwrites the row before the next pair)
         const double sI = p.c4 * dV * (p.lambda * trE - p.mu);
         const double cf = p.c3 * dV;
-        r[0] = cf * FFT[0][0] + sI;
-        r[1] = cf * FFT[0][1];
-        r[2] = cf * FFT[0][2];
-        r[3] = cf * FFT[1][1] + sI;
-        r[4] = cf * FFT[1][2];
-        r[5] = cf * FFT[2][2] + sI;
-        r[6] = dV;
+        uq[30] = cf * FFT[0][0] + sI;
+        uq[31] = cf * FFT[0][1];
+        uq[32] = cf * FFT[0][2];
+        uq[33] = cf * FFT[1][1] + sI;
+        uq[34] = cf * FFT[1][2];
+        fpq[30] = cf * FFT[2][2] + sI;
+        fpq[31] = dV;
       }
     }
     __syncwarp();
@@ -663,7 +664,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       const bool on = lane_on && (el2 < ne);
       const double *he = s_h + el * 150;
       const double *ue = s_u + el * 5 * PK_GQ;
-      const double *re = s_rec + el * 5 * EK_REC;
+      const double *fpe = s_fp + el * 5 * PK_GQ;
       double A[4][9], Gs[4][6];
 #pragma unroll
       for (int t = 0; t < 4; t++) {
@@ -704,8 +705,8 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       }
 #pragma unroll
       for (int q = 0; q < (MR ? 0 : 5); q++) {
-        const double *hq = he + q * 30, *uq = ue + q * PK_GQ, *rq = re + q * EK_REC;
-        const double dV = rq[6];
+        const double *hq = he + q * 30, *uq = ue + q * PK_GQ, *fq = fpe + q * PK_GQ;
+        const double dV = fq[31];
         double ha[2][3], hb[2][3], ua[2][3], ub[2][3], M[6];
 #pragma unroll
         for (int j = 0; j < 3; j++) {
@@ -719,7 +720,8 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
           ub[1][j] = uq[b1 * 3 + 3 + j];
         }
 #pragma unroll
-        for (int i = 0; i < 6; i++) M[i] = rq[i];
+        for (int i = 0; i < 5; i++) M[i] = uq[30 + i];
+        M[5] = fq[30];
 #pragma unroll
         for (int ta = 0; ta < 2; ta++)
 #pragma unroll
