@@ -136,7 +136,7 @@ static int ensure_plan(tlfea_newton *s) {
 }
 
 template <int W, bool DAMP, bool TANGENT, int MODEL>
-static int launch_pk_t(tlfea_elem *e, const PatchPlanDev *pp, PKArgs a, int p0, int np) {
+static int launch_pk_t(tlfea_elem *e, const PatchPlanDev *pp, PKArgs a, int p0, int np, bool pdl) {
   using Sh = PKShape<DAMP, MODEL>;
   constexpr size_t smem = Sh::smem_bytes(W);
   static_assert(smem <= 227 * 1024, "patch kernel configuration exceeds the shared memory of one SM");
@@ -152,15 +152,29 @@ static int launch_pk_t(tlfea_elem *e, const PatchPlanDev *pp, PKArgs a, int p0, 
   // persistent CTAs, as many as fit the SMs at once: each walks its patches with the prefetch stream running
   const int per_sm = std::max(1, std::min((int)((228 * 1024) / (smem + 1024)), 2048 / (W * 32)));
   const int grid = std::min(np, per_sm * sm_count(e->device));
-  TL_LAUNCH((pk_kernel<W, DAMP, TANGENT, MODEL>), grid, W * 32, smem, e->stream, a);
+  // Programmatic dependent launch: the CTAs of this launch take the SMs as those of the previous colour drain and
+  // compute their first patch (which reads nothing an earlier colour writes); they wait for the previous launch
+  // (griddepcontrol.wait in the kernel) only before their first access to H.  Hides the tail of every launch.
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(W * 32);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = e->stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  TL_CUDA(cudaLaunchKernelEx(&cfg, pk_kernel<W, DAMP, TANGENT, MODEL>, a));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
   return TLFEA_OK;
 }
 
 template <bool DAMP, bool TANGENT>
-static int launch_pk(tlfea_elem *e, const PatchPlanDev *pp, const PKArgs &a, int p0, int np) {
-  if (e->model == TL_MODEL_MR) return launch_pk_t<4, DAMP, TANGENT, TL_MODEL_MR>(e, pp, a, p0, np);
-  if (pp->W == 8) return launch_pk_t<8, DAMP, TANGENT, TL_MODEL_SVK>(e, pp, a, p0, np);
-  return launch_pk_t<4, DAMP, TANGENT, TL_MODEL_SVK>(e, pp, a, p0, np);
+static int launch_pk(tlfea_elem *e, const PatchPlanDev *pp, const PKArgs &a, int p0, int np, bool pdl) {
+  if (e->model == TL_MODEL_MR) return launch_pk_t<4, DAMP, TANGENT, TL_MODEL_MR>(e, pp, a, p0, np, pdl);
+  if (pp->W == 8) return launch_pk_t<8, DAMP, TANGENT, TL_MODEL_SVK>(e, pp, a, p0, np, pdl);
+  return launch_pk_t<4, DAMP, TANGENT, TL_MODEL_SVK>(e, pp, a, p0, np, pdl);
 }
 
 // Element forces fe (always) and, with tangent, H = M/h + h K_t (+ C_visc) in place, colour by colour.
@@ -219,10 +233,11 @@ int patch_assemble(tlfea_newton *s, bool tangent, bool damp, const PatchHooks *h
   a.fe = e->d_fe;
   a.H = s->d_H;
   if (!tangent) {  // no shared output: every patch in one launch
-    TL_TRY((damp ? launch_pk<true, false>(e, pp, a, 0, pp->n_patches) : launch_pk<false, false>(e, pp, a, 0, pp->n_patches)));
+    TL_TRY((damp ? launch_pk<true, false>(e, pp, a, 0, pp->n_patches, false) : launch_pk<false, false>(e, pp, a, 0, pp->n_patches, false)));
     TL_CUDA(cudaGetLastError());
     return TLFEA_OK;
   }
+  static const bool use_pdl = [] { const char *v = getenv("TLFEA_PK_PDL"); return !v || atoi(v) != 0; }();
   if (pp->n_unc > 0)
     TL_LAUNCH(pk_uncovered_kernel, blocks_for(pp->n_unc, 256), 256, 0, e->stream, pp->n_unc, pp->d_unc, e->pat.d_off,
               pp->d_unc_row, e->d_mass, 1.0 / h, s->d_H);
@@ -231,7 +246,9 @@ int patch_assemble(tlfea_newton *s, bool tangent, bool damp, const PatchHooks *h
     for (int c = 0; c < pp->n_colors; c++) {
       const int l = ch * pp->n_colors + c;
       const int p0 = pp->color_ptr[l], np = pp->color_ptr[l + 1] - p0;
-      TL_TRY((damp ? launch_pk<true, true>(e, pp, a, p0, np) : launch_pk<false, true>(e, pp, a, p0, np)));
+      // the first launch of a chunk follows other work in the stream (uploads, event waits): no early start for it
+      const bool pdl = use_pdl && (c > 0 || (ch > 0 && !hooks));
+      TL_TRY((damp ? launch_pk<true, true>(e, pp, a, p0, np, pdl) : launch_pk<false, true>(e, pp, a, p0, np, pdl)));
     }
     if (hooks && hooks->after_chunk) TL_TRY(hooks->after_chunk(hooks->ctx, ch));
   }

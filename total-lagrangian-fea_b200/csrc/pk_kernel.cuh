@@ -198,6 +198,9 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   __shared__ uint64_t s_bar_wo[W];  // arrival of warp w's write-out chunk in its scratch area
   __shared__ PatchDesc s_desc[2];  // this CTA's current and next patch
   __shared__ double s_dn[150];
+  // programmatic dependent launch (patch_asm.cu): let the next colour's CTAs be scheduled as ours exit
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+  bool dep_waited = false;  // this thread has waited for the previous launch (needed before its first access to H)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *acc = pk_smem + (size_t)warp * Sh::ACC_D;
   double *wb = pk_smem + (size_t)W * Sh::ACC_D + (size_t)warp * Sh::PREF_D;  // prefetch buffers of this warp
@@ -810,6 +813,10 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   double *Hb = p.H + ((p.debug & 16) ? (int64_t)(blockIdx.x & 255) * 65536 : dc.hbase);
   const unsigned hmask = (p.debug & 16) ? 0x3fffu : 0xffffffffu;
   const bool wo_on = !(p.debug & 1);
+  if (!dep_waited) {  // H belongs to the previous colour until its launch has completed
+    asm volatile("griddepcontrol.wait;\n" ::: "memory");
+    dep_waited = true;
+  }
   // (a) the blocks this warp holds alone are final: their entries leave now, while the other warps still compute
   if (!ck_issued) stage_chunk();  // a warp without elements in this patch, or the block step switched off
   mbar_wait(&s_bar_wo[warp], n_done & 1);
