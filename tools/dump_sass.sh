@@ -9,7 +9,7 @@ dump() {  # $1 = output name, $2 = grep pattern on the mangled function name
   local fn
   fn=$(cuobjdump -sass "$SO" | grep -o "Function : [^ ]*" | awk '{print $3}' | grep -E "$2" | head -1)
   [ -z "$fn" ] && { echo "no kernel matches $2"; return; }
-  cuobjdump -sass -fun "$fn" "$SO" > "profiles/${TAG}_sass_$1.txt"
+  cuobjdump -sass -fun "$fn" "$SO" 2>/dev/null > "profiles/${TAG}_sass_$1.txt"
   printf "%-28s %6d lines  UBLKCP %3d  LDGSTS %3d  DFMA %5d  LDS %4d  STS %4d  LDL %3d  STL %3d  (%s)\n" "$1" \
     "$(wc -l < profiles/${TAG}_sass_$1.txt)" "$(grep -c UBLKCP profiles/${TAG}_sass_$1.txt)" \
     "$(grep -c LDGSTS profiles/${TAG}_sass_$1.txt)" "$(grep -c DFMA profiles/${TAG}_sass_$1.txt)" \
