@@ -573,6 +573,10 @@ def main():
                 "step_share": dom_ms / max(ms_step, 1e-9)}
     if single_pass:
         roofline["patch_plan"] = st_patch
+    if world > 1:  # kernel time of every rank: the step waits for the slowest at the halo exchange
+        kall = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(kall, torch.tensor([row_ms + gp_ms], dtype=torch.float64, device=dev))
+        roofline["kernel_ms_per_rank"] = [float(k.item()) for k in kall]
     if fp64:
         fl = ALGO_FLOP_PER_GP * n_elem_l * 5
         t_fp64_ms = fl / (fp64 * 1e12) * 1e3

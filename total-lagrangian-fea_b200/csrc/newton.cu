@@ -399,7 +399,7 @@ static bool ek_supported(const tlfea_newton *s) {
 }
 // mode 2: FEAT10 + SVK (with or without Kelvin-Voigt damping) takes the single-pass patch kernel; Mooney-Rivlin keeps
 // the two-phase path, which is faster for it (its 81-entry tangent tensor leaves room for one 4-warp CTA per SM only:
-// 93 ms against 64 ms per 10.1 M-tet assemble).  mode 3 forces the patch kernel for every FEAT10 material.
+// 70.8 ms against 65.7 ms per 10.1 M-tet assemble).  mode 3 forces the patch kernel for every FEAT10 material.
 static bool pk_selected(const tlfea_newton *s) {
   if (s->e->type != TLFEA_TYPE_T10) return false;
   return s->asm_mode == 3 || (s->asm_mode == 2 && s->e->model == TL_MODEL_SVK);
