@@ -564,10 +564,14 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       const double *xe = s_x + el * 30;
       double F[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
       double Fd[3][3] = {{0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}, {0.0, 0.0, 0.0}};
+      double hr[10][3];  // the point's shape-function gradients stay in registers for the output loop below
 #pragma unroll
       for (int aa = 0; aa < 10; aa++) {
         const double xa[3] = {xe[aa * 3], xe[aa * 3 + 1], xe[aa * 3 + 2]};
-        const double ha[3] = {hq[aa], hq[10 + aa], hq[20 + aa]};
+        hr[aa][0] = hq[aa];
+        hr[aa][1] = hq[10 + aa];
+        hr[aa][2] = hq[20 + aa];
+        const double *ha = hr[aa];
 #pragma unroll
         for (int i = 0; i < 3; i++)
 #pragma unroll
@@ -633,7 +637,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
       double *uq = s_u + idx * PK_GQ;
 #pragma unroll
       for (int aa = 0; aa < 10; aa++) {
-        const double ha[3] = {hq[aa], hq[10 + aa], hq[20 + aa]};
+        const double *ha = hr[aa];
         fpq[aa * 3 + part] = Pi[0] * ha[0] + Pi[1] * ha[1] + Pi[2] * ha[2];
         if (TANGENT) uq[aa * 3 + part] = Fi[0] * ha[0] + Fi[1] * ha[1] + Fi[2] * ha[2];
       }
