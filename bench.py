@@ -101,6 +101,14 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def mark(self):
+        """Start of the timed region: drop what was sampled before (the sampler is started ahead of the warm-up so
+        that its start-up cost -- nvmlInit takes milliseconds -- is not inside anybody's timed region)."""
+        if getattr(self, "thread", None) is not None:
+            self.n_sm.clear()
+            self.n_pw.clear()
+            self.n_reasons.clear()
+
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if getattr(self, "thread", None) is not None:
@@ -487,14 +495,20 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    # Everything that costs host time on one rank only (the clock sampler's start-up on rank 0) happens BEFORE the
+    # warm-up: with a halo exchange in every step a rank that enters the timed loop late is waited for by its
+    # neighbours, and the maximum over ranks would include that wait (it did: 5 - 13 ms per run at N = 2).
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    s.SetProfile(True)
     for _ in range(args.warmup):
         step()
     sync_all()
     s.Timing(reset=True)
-    s.SetProfile(True)
-    sampler = ClockSampler(local)
     if rank == 0:
-        sampler.start()
+        sampler.mark()
+    sync_all()
     l0 = tlfea.lib.tlfea_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
@@ -577,6 +591,46 @@ def main():
         kall = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
         dist.all_gather(kall, torch.tensor([row_ms + gp_ms], dtype=torch.float64, device=dev))
         roofline["kernel_ms_per_rank"] = [float(k.item()) for k in kall]
+        # the same steps without the halo exchange, and the exchange alone: what the exchange costs
+        parts = []
+        for fn in (s.Assemble, halo_sum):
+            sync_all()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(args.steps):
+                fn()
+            e1.record()
+            sync_all()
+            t = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            parts.append(float(t.item()))
+        roofline["assemble_only_ms"], roofline["halo_only_ms"] = parts
+        step()  # the repeated exchanges summed the interface entries over and over: leave a clean state behind
+        sync_all()
+        if os.environ.get("TLFEA_BENCH_DEBUG"):  # host time of the two calls of a step: does the exchange block the host?
+            sync_all()
+            th = []
+            for _ in range(args.steps):
+                t0 = time.perf_counter()
+                s.Assemble()
+                t1 = time.perf_counter()
+                halo_sum()
+                t2 = time.perf_counter()
+                th.append((round((t1 - t0) * 1e3, 3), round((t2 - t1) * 1e3, 3)))
+            sync_all()
+            print(f"rank {rank} host ms per call (Assemble, halo_sum): {th}", file=sys.stderr, flush=True)
+            sync_all()
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 1)]
+            evs[0].record()
+            for i in range(args.steps):
+                s.Assemble()
+                evs[2 * i + 1].record()
+                halo_sum()
+                evs[2 * i + 2].record()
+            sync_all()
+            td = [(round(evs[2 * i].elapsed_time(evs[2 * i + 1]), 3), round(evs[2 * i + 1].elapsed_time(evs[2 * i + 2]), 3))
+                  for i in range(args.steps)]
+            print(f"rank {rank} device ms per step (Assemble, halo_sum): {td}", file=sys.stderr, flush=True)
     if fp64:
         fl = ALGO_FLOP_PER_GP * n_elem_l * 5
         t_fp64_ms = fl / (fp64 * 1e12) * 1e3
@@ -827,8 +881,10 @@ def main():
             "data": "synthetic",
             "config": {"workload": f"feat10_kuhn_block_n{args.n}_svk_force_tangent_H", "n_elem": n_elem_g,
                        "gauss_points": gp_total, "nnz_H_sum_over_ranks": nnz_g, "material": "SVK E=7e8 nu=0.33",
-                       "h": H_STEP, "partition": f"x-slabs x{world}, sub-assembled H, halo sum of f_int by NCCL send/recv with "
-                                                 "the slab neighbours inside the library (csrc/dist.cu)",
+                       "h": H_STEP, "partition": f"x-slabs x{world}, sub-assembled H, halo sum of f_int with the slab neighbours "
+                                                 "inside the library (csrc/dist.cu): "
+                                                 + ("peer-memory stores over NVLink + system-scope flags"
+                                                    if (lib_halo is not None and lib_halo.p2p) else "NCCL send/recv"),
                        "halo_bytes_sent_per_rank": (lib_halo.bytes_per_halo if lib_halo else 0),
                        "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
                        "setup_s": t_setup},

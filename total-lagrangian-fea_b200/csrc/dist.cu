@@ -73,9 +73,17 @@ struct DistCtx {
     int rank;
     int64_t c_lo, c_hi;  // shared coefficient ids [c_lo, c_hi)
     double *d_recv = nullptr;
+    // peer-memory path (tlfea_dist_p2p_*): the mailbox the neighbour writes into (ours, exported by IPC handle) and the
+    // neighbour's mailbox for messages from us (opened from its handle).  Layout: two 128-byte flag lines, then two
+    // slots of (c_hi - c_lo) * HALO_MAX_WIDTH doubles; message q uses slot q & 1 and sets that slot's flag to q.
+    unsigned char *d_mail = nullptr;   // local
+    unsigned char *d_peer = nullptr;   // in the neighbour's memory
+    unsigned int *d_done = nullptr;    // CTAs of the current put that have finished their part
   };
   std::vector<Nbr> nbr;
   int64_t halo_bytes = 0;  // bytes sent per halo sum of width 3 (reporting)
+  unsigned long long seq = 0;  // halo sums done over the peer-memory path
+  bool p2p = false;            // every neighbour connected
 };
 
 static constexpr int HALO_MAX_WIDTH = 9;
@@ -85,10 +93,57 @@ __global__ void k_halo_add(int64_t n, const double *__restrict__ buf, double *ve
   if (i < n) vec[i] += buf[i];
 }
 
+// ---- halo sum over peer memory (NVLink loads / stores between the GPUs of one node, no NCCL kernel in the step).
+// put: copy our shared range into the neighbour's mailbox slot; the last CTA to finish publishes the message number
+// in the slot's flag (system-scope release).  take: wait for the neighbour's message number in OUR mailbox, add the
+// slot to the vector.  A put never waits, so the exchange cannot deadlock; two slots suffice because the neighbour's
+// put q + 1, which our take q + 1 waits for, comes after its take q in its stream.
+constexpr int MAIL_FLAG_BYTES = 256;
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__global__ void __launch_bounds__(256) k_halo_put(int64_t n, const double *__restrict__ vec, unsigned char *peer_mail,
+                                                  int64_t slot_doubles, unsigned long long q, unsigned int *done) {
+  double *dst = reinterpret_cast<double *>(peer_mail + MAIL_FLAG_BYTES) + (q & 1ull) * slot_doubles;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = vec[i];
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(done, 1u);
+    if (prev == gridDim.x - 1) {
+      *done = 0;
+      __threadfence_system();
+      st_release_sys(reinterpret_cast<unsigned long long *>(peer_mail + 128 * (q & 1ull)), q);
+    }
+  }
+}
+__global__ void __launch_bounds__(256) k_halo_take(int64_t n, double *vec, const unsigned char *mail, int64_t slot_doubles,
+                                                   unsigned long long q) {
+  if (threadIdx.x == 0) {
+    const unsigned long long *flag = reinterpret_cast<const unsigned long long *>(mail + 128 * (q & 1ull));
+    while (ld_acquire_sys(flag) < q) __nanosleep(100);
+  }
+  __syncthreads();
+  const double *src = reinterpret_cast<const double *>(mail + MAIL_FLAG_BYTES) + (q & 1ull) * slot_doubles;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    vec[i] += __ldcg(src + i);
+}
+
 void dist_release(tlfea_newton *s) {
   auto *dc = static_cast<DistCtx *>(s->dist);
   if (!dc) return;
-  for (auto &nb : dc->nbr) dfree(nb.d_recv);
+  for (auto &nb : dc->nbr) {
+    dfree(nb.d_recv);
+    if (nb.d_peer) cudaIpcCloseMemHandle(nb.d_peer);
+    dfree(nb.d_mail);
+    dfree(nb.d_done);
+  }
   NcclApi *api = nccl_api();
   if (api && dc->comm) api->CommDestroy(dc->comm);
   delete dc;
@@ -137,13 +192,20 @@ int tlfea_dist_set_halo(tlfea_newton *s, int n_nbr, const int *nbr_rank, const i
   TL_CHECK(n_nbr >= 0 && (n_nbr == 0 || (nbr_rank && coef_lo && coef_hi)), "bad input");
   auto *dc = static_cast<DistCtx *>(s->dist);
   TL_CUDA(cudaSetDevice(s->e->device));
-  for (auto &nb : dc->nbr) dfree(nb.d_recv);
+  for (auto &nb : dc->nbr) {
+    dfree(nb.d_recv);
+    if (nb.d_peer) cudaIpcCloseMemHandle(nb.d_peer);
+    dfree(nb.d_mail);
+    dfree(nb.d_done);
+  }
   dc->nbr.clear();
   dc->halo_bytes = 0;
+  dc->p2p = false;
+  dc->seq = 0;
   for (int k = 0; k < n_nbr; k++) {
     TL_CHECK(nbr_rank[k] >= 0 && nbr_rank[k] < dc->world && nbr_rank[k] != dc->rank, "neighbour rank out of range");
     TL_CHECK(coef_lo[k] >= 0 && coef_lo[k] <= coef_hi[k] && coef_hi[k] <= s->e->n_coef, "shared range out of bounds");
-    DistCtx::Nbr nb{nbr_rank[k], coef_lo[k], coef_hi[k], nullptr};
+    DistCtx::Nbr nb{nbr_rank[k], coef_lo[k], coef_hi[k], nullptr, nullptr, nullptr, nullptr};
     TL_TRY(dmalloc(&nb.d_recv, (size_t)(nb.c_hi - nb.c_lo) * HALO_MAX_WIDTH));
     dc->halo_bytes += (nb.c_hi - nb.c_lo) * 3 * (int64_t)sizeof(double);
     dc->nbr.push_back(nb);
@@ -161,6 +223,21 @@ int tlfea_dist_halo_sum(tlfea_newton *s, double *d_vec, int width) {
   NcclApi *api = nccl_api();
   TL_CUDA(cudaSetDevice(s->e->device));
   cudaStream_t st = s->e->stream;
+  if (dc->p2p) {  // peer-memory path: puts first (they never wait), then the takes in neighbour order
+    const unsigned long long q = ++dc->seq;
+    for (auto &nb : dc->nbr) {
+      const int64_t n = (nb.c_hi - nb.c_lo) * width, slot = (nb.c_hi - nb.c_lo) * HALO_MAX_WIDTH;
+      const unsigned grid = (unsigned)std::min<int64_t>(std::max<int64_t>((n + 1023) / 1024, 1), 64);
+      TL_LAUNCH(k_halo_put, grid, 256, 0, st, n, d_vec + nb.c_lo * width, nb.d_peer, slot, q, nb.d_done);
+    }
+    for (auto &nb : dc->nbr) {
+      const int64_t n = (nb.c_hi - nb.c_lo) * width, slot = (nb.c_hi - nb.c_lo) * HALO_MAX_WIDTH;
+      const unsigned grid = (unsigned)std::min<int64_t>(std::max<int64_t>((n + 1023) / 1024, 1), 64);
+      TL_LAUNCH(k_halo_take, grid, 256, 0, st, n, d_vec + nb.c_lo * width, nb.d_mail, slot, q);
+    }
+    TL_CUDA(cudaGetLastError());
+    return TLFEA_OK;
+  }
   TL_NCCL(api, api->GroupStart());
   for (auto &nb : dc->nbr) {
     const size_t n = (size_t)(nb.c_hi - nb.c_lo) * width;
@@ -184,6 +261,49 @@ int tlfea_dist_allreduce_sum(tlfea_newton *s, double *d_buf, int n) {
   NcclApi *api = nccl_api();
   TL_CUDA(cudaSetDevice(s->e->device));
   TL_NCCL(api, api->AllReduce(d_buf, d_buf, (size_t)n, ncclDouble, ncclSum, dc->comm, s->e->stream));
+  return TLFEA_OK;
+}
+
+int tlfea_dist_p2p_export(tlfea_newton *s, int k, void *out64) {
+  TL_CHECK(s && s->dist && out64, "tlfea_dist_set_halo must run first");
+  auto *dc = static_cast<DistCtx *>(s->dist);
+  TL_CHECK(k >= 0 && k < (int)dc->nbr.size(), "neighbour index out of range");
+  TL_CUDA(cudaSetDevice(s->e->device));
+  auto &nb = dc->nbr[(size_t)k];
+  if (!nb.d_mail) {
+    const size_t bytes = MAIL_FLAG_BYTES + 2 * (size_t)(nb.c_hi - nb.c_lo) * HALO_MAX_WIDTH * sizeof(double);
+    TL_TRY(dmalloc(&nb.d_mail, bytes));
+    TL_TRY(dmalloc(&nb.d_done, 1));
+    TL_CUDA(cudaMemset(nb.d_mail, 0, bytes));
+    TL_CUDA(cudaMemset(nb.d_done, 0, sizeof(unsigned int)));
+    TL_CUDA(cudaDeviceSynchronize());
+  }
+  cudaIpcMemHandle_t h;
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  TL_CUDA(cudaIpcGetMemHandle(&h, nb.d_mail));
+  memcpy(out64, &h, sizeof(h));
+  return TLFEA_OK;
+}
+
+int tlfea_dist_p2p_connect(tlfea_newton *s, int k, const void *handle64) {
+  TL_CHECK(s && s->dist && handle64, "tlfea_dist_set_halo must run first");
+  auto *dc = static_cast<DistCtx *>(s->dist);
+  TL_CHECK(k >= 0 && k < (int)dc->nbr.size(), "neighbour index out of range");
+  TL_CUDA(cudaSetDevice(s->e->device));
+  auto &nb = dc->nbr[(size_t)k];
+  TL_CHECK(nb.d_mail, "tlfea_dist_p2p_export must run first for this neighbour");
+  if (nb.d_peer) {
+    cudaIpcCloseMemHandle(nb.d_peer);
+    nb.d_peer = nullptr;
+  }
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  void *ptr = nullptr;
+  TL_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  nb.d_peer = static_cast<unsigned char *>(ptr);
+  bool all = true;
+  for (auto &x : dc->nbr) all = all && x.d_peer && x.d_mail;
+  dc->p2p = all;
   return TLFEA_OK;
 }
 

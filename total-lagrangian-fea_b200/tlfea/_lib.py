@@ -138,6 +138,8 @@ _SIGS = {
     "tlfea_dist_allreduce_sum": (C.c_int, [c_vp, c_vp, C.c_int]),
     "tlfea_dist_halo_bytes": (C.c_int64, [c_vp]),
     "tlfea_dist_finalize": (C.c_int, [c_vp]),
+    "tlfea_dist_p2p_export": (C.c_int, [c_vp, C.c_int, c_vp]),
+    "tlfea_dist_p2p_connect": (C.c_int, [c_vp, C.c_int, c_vp]),
     "tlfea_dot_noalloc": (C.c_int, [c_vp, c_vp, C.c_int64, c_vp, c_vp]),
     "tlfea_fp64_peak": (C.c_int, [C.c_int, c_dp]),
     "tlfea_debug_patch_plan_build": (C.c_int, [C.c_int, C.c_int, c_ip, c_dp, c_dp, c_dp, c_ip, c_ip, C.c_int, C.c_int,

@@ -148,6 +148,36 @@ class LibHalo:
                       (C.c_int64 * max(len(nbr), 1))(*hi))
         check(lib.tlfea_dist_set_halo(solver._h, len(nbr), self._arrs[0], self._arrs[1], self._arrs[2]))
         self.bytes_per_halo = int(lib.tlfea_dist_halo_bytes(solver._h))
+        # peer-memory path of the halo sum (one node, NVLink): every rank exports the mailbox each neighbour writes
+        # into, the 64-byte IPC handles travel through torch.distributed once, every rank opens its neighbours'.
+        # Collective: either all ranks connect or all stay on the NCCL send/recv path.
+        import os
+
+        self.p2p = False
+        if world > 1 and os.environ.get("TLFEA_HALO_P2P", "1") != "0":
+            mine, ok = [], True
+            try:
+                for k, nb in enumerate(nbr):
+                    raw = (C.c_ubyte * 64)()
+                    check(lib.tlfea_dist_p2p_export(solver._h, k, C.cast(raw, C.c_void_p)))
+                    mine.append((rank, nb, bytes(raw)))
+            except Exception:
+                ok = False
+            gathered = [None] * world
+            dist.all_gather_object(gathered, (ok, mine))
+            if all(g[0] for g in gathered):
+                table = {(owner, frm): h for g in gathered for owner, frm, h in g[1]}
+                try:
+                    for k, nb in enumerate(nbr):
+                        raw = (C.c_ubyte * 64)(*table[(nb, rank)])
+                        check(lib.tlfea_dist_p2p_connect(solver._h, k, C.cast(raw, C.c_void_p)))
+                except Exception:
+                    ok = False
+            flags = [None] * world
+            dist.all_gather_object(flags, ok)
+            self.p2p = all(flags)
+            if not self.p2p:  # back to NCCL everywhere: re-declaring the halo drops the mailboxes
+                check(lib.tlfea_dist_set_halo(solver._h, len(nbr), self._arrs[0], self._arrs[1], self._arrs[2]))
 
     def halo_sum(self, ptr: int, width: int = 3):
         self.check(self.lib.tlfea_dist_halo_sum(self.s._h, self.C.c_void_p(int(ptr)), width))
