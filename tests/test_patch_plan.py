@@ -228,7 +228,9 @@ def test_plan_chunked_launch_order():
     for c in range(K):
         for p in range(cp[c * C_], cp[(c + 1) * C_]):
             mx = rn[rp[p]:rp[p + 1]].max()
-            assert min(K - 1, mx * K // nn) == c
+            tot = 4 * (K - 2) + 2  # csrc/patch_plan.cuh pk_chunk_bound: short first and last id range
+            bound = [nn * (0 if r == 0 else tot if r == K else 1 + 4 * (r - 1)) // tot for r in range(K + 1)]
+            assert bound[c] <= mx < bound[c + 1]
     Ke = [h * orc.element_tangent(E[e], x, o.grad_N[e], o.detJ[e], o.qw, mat) for e in range(E.shape[0])]
     H = replay(plan, Ke, mass_lookup(o.off, o.cols, o.mass(rho)), h, o.cols.shape[0])
     assert rel_err(H, o.hessian(x, mat, h, rho)) < 1e-13

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "patch_plan.cuh"
 #include "kernels.cuh"
 #include "ek_kernel.cuh"
 #include "ancf_ek.cuh"
@@ -951,34 +952,39 @@ struct PkPipe {
   const int *ready;
 };
 static void pk_range(const tlfea_elem *e, int K, int r, int *i0, int *i1) {
-  *i0 = (int)((int64_t)e->n_coef * r / K);
-  *i1 = (int)((int64_t)e->n_coef * (r + 1) / K);
+  *i0 = (int)pk_chunk_bound(e->n_coef, K, r);
+  *i1 = (int)pk_chunk_bound(e->n_coef, K, r + 1);
 }
 static int pk_before_chunk(void *ctx, int c) {
   PkPipe *pp = static_cast<PkPipe *>(ctx);
   TL_CUDA(cudaStreamWaitEvent(pp->s->e->stream, pp->s->ev_pipe[c], 0));
   return TLFEA_OK;
 }
-static int pk_gather_range(tlfea_newton *s, int K, int r) {
-  tlfea_elem *e = s->e;
-  int i0, i1;
-  pk_range(e, K, r, &i0, &i1);
-  if (i1 > i0) {
-    TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)(i1 - i0) * 3, 128), 128, 0, e->stream, i1 - i0,
-              e->pat.d_inc_ptr + i0, e->pat.d_inc_ea, e->d_fe, e->d_f_int + 3 * (int64_t)i0, 0);
-    if (s->h_f_out) {
-      TL_CUDA(cudaEventRecord(s->ev_g[r], e->stream));
-      TL_CUDA(cudaStreamWaitEvent(s->st_copy, s->ev_g[r], 0));
-      TL_CUDA(cudaMemcpyAsync(s->h_f_out + 3 * (int64_t)i0, e->d_f_int + 3 * (int64_t)i0,
-                              (size_t)(i1 - i0) * 3 * sizeof(double), cudaMemcpyDeviceToHost, s->st_copy));
-    }
-  }
-  return TLFEA_OK;
-}
+// nodal forces of the id sub-ranges that chunk c completes: ordered gather, then (if the caller registered its result
+// buffer) one event and the copies back, contiguous sub-ranges merged
 static int pk_after_chunk(void *ctx, int c) {
   PkPipe *pp = static_cast<PkPipe *>(ctx);
-  for (int r = 0; r < pp->K; r++)
-    if (pp->ready[r] == c || (c == 0 && pp->ready[r] < 0)) TL_TRY(pk_gather_range(pp->s, pp->K, r));
+  tlfea_newton *s = pp->s;
+  tlfea_elem *e = s->e;
+  const int NQ = pp->K * PK_GSUB;
+  std::vector<std::pair<int, int>> runs;  // [i0, i1) of coefficient ids
+  for (int q = 0; q < NQ; q++) {
+    if (!(pp->ready[q] == c || (c == 0 && pp->ready[q] < 0))) continue;
+    const int i0 = (int)pk_sub_bound(e->n_coef, pp->K, q), i1 = (int)pk_sub_bound(e->n_coef, pp->K, q + 1);
+    if (i1 <= i0) continue;
+    if (!runs.empty() && runs.back().second == i0) runs.back().second = i1;
+    else runs.push_back({i0, i1});
+  }
+  for (auto &r : runs)
+    TL_LAUNCH(force_gather_kernel, blocks_for((int64_t)(r.second - r.first) * 3, 128), 128, 0, e->stream,
+              r.second - r.first, e->pat.d_inc_ptr + r.first, e->pat.d_inc_ea, e->d_fe, e->d_f_int + 3 * (int64_t)r.first, 0);
+  if (s->h_f_out && !runs.empty()) {
+    TL_CUDA(cudaEventRecord(s->ev_g[c], e->stream));
+    TL_CUDA(cudaStreamWaitEvent(s->st_copy, s->ev_g[c], 0));
+    for (auto &r : runs)
+      TL_CUDA(cudaMemcpyAsync(s->h_f_out + 3 * (int64_t)r.first, e->d_f_int + 3 * (int64_t)r.first,
+                              (size_t)(r.second - r.first) * 3 * sizeof(double), cudaMemcpyDeviceToHost, s->st_copy));
+  }
   return TLFEA_OK;
 }
 

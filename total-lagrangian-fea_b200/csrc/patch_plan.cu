@@ -361,14 +361,16 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
 
   // ---- 5. launch order, first-touch flags, concatenation.
   // Launch l = chunk * n_colors + colour.  Chunk c holds the patches whose LARGEST coefficient id falls into the c-th
-  // of n_chunks equal id ranges: its kernels read no coordinate beyond that range (a host-buffer step starts them as
+  // of n_chunks id ranges (pk_chunk_bound: short first and last range): its kernels read no coordinate beyond that range (a host-buffer step starts them as
   // soon as that part of x, y, z has been uploaded), and once a chunk is done every coefficient whose patches all
   // lie in chunks <= c is final (its force can travel back to the host while later chunks compute).
   const int K = std::max(1, std::min(n_chunks, 16));
   std::vector<int> chunk_of((size_t)np, 0), node_final((size_t)n_coef, -1);
   for (int p = 0; p < np; p++) {
     const int mxid = pl[p]->nodes.empty() ? 0 : pl[p]->nodes.back();
-    chunk_of[p] = (int)std::min<int64_t>(K - 1, (int64_t)mxid * K / std::max(n_coef, 1));
+    int r = 0;
+    while (r + 1 < K && mxid >= pk_chunk_bound(n_coef, K, r + 1)) r++;
+    chunk_of[p] = r;
   }
   for (int p = 0; p < np; p++)
     for (int nd : pl[p]->nodes) node_final[nd] = std::max(node_final[nd], chunk_of[p]);
@@ -387,12 +389,12 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   R.color_ptr.assign((size_t)n_launch + 1, 0);
   for (int p = 0; p < np; p++) R.color_ptr[(size_t)chunk_of[p] * n_colors + pl[p]->color + 1]++;
   for (int c = 0; c < n_launch; c++) R.color_ptr[c + 1] += R.color_ptr[c];
-  R.range_ready.assign((size_t)K, -1);
-  for (int r = 0; r < K; r++) {
-    const int64_t i0 = (int64_t)n_coef * r / K, i1 = (int64_t)n_coef * (r + 1) / K;
+  R.range_ready.assign((size_t)K * PK_GSUB, -1);
+  for (int q = 0; q < K * PK_GSUB; q++) {
+    const int64_t i0 = pk_sub_bound(n_coef, K, q), i1 = pk_sub_bound(n_coef, K, q + 1);
     int m = -1;
     for (int64_t i = i0; i < i1; i++) m = std::max(m, node_final[(size_t)i]);
-    R.range_ready[r] = m;
+    R.range_ready[q] = m;
   }
 
   const int64_t nnz = off[n_coef];

@@ -82,11 +82,30 @@ static_assert(sizeof(PatchDesc) == 64, "PatchDesc layout");
 
 __host__ __device__ inline int pk_al16(int b) { return (b + 15) & ~15; }
 
+// Id-range chunks of the launch order (host-buffer pipelining): chunk r covers the coefficient ids
+// [pk_chunk_bound(r), pk_chunk_bound(r + 1)).  The first and the last range are a quarter of the others: the upload
+// of the first range and the download of the last one are the parts of a host-buffer step no kernel can hide.
+inline int64_t pk_chunk_bound(int64_t n_coef, int K, int r) {
+  if (K < 3) return n_coef * r / K;
+  const int64_t tot = 4 * (int64_t)(K - 2) + 2;
+  const int64_t w = (r <= 0) ? 0 : (r >= K ? tot : 1 + 4 * (int64_t)(r - 1));
+  return n_coef * w / tot;
+}
+// The nodal forces travel back in finer pieces: every chunk range is cut into PK_GSUB sub-ranges; sub-range q is final
+// after the last chunk that touches one of its ids (PatchPlanHost::range_ready[q]) -- only the sliver of a range next to
+// the following one has to wait for the following chunk.
+constexpr int PK_GSUB = 8;
+inline int64_t pk_sub_bound(int64_t n_coef, int K, int q) {
+  const int r = q / PK_GSUB, j = q - r * PK_GSUB;
+  const int64_t b0 = pk_chunk_bound(n_coef, K, r), b1 = pk_chunk_bound(n_coef, K, r + 1);
+  return b0 + (b1 - b0) * j / PK_GSUB;
+}
+
 struct PatchPlanHost {
   int W = 0;
   int n_patches = 0, n_colors = 0, n_chunks = 1;
   std::vector<int> color_ptr;    // launch l = chunk * n_colors + colour runs patches [color_ptr[l], color_ptr[l+1])
-  std::vector<int> range_ready;  // [n_chunks] last chunk that touches a coefficient of the r-th id range (-1: none)
+  std::vector<int> range_ready;  // [n_chunks * PK_GSUB] last chunk that touches a coefficient of the q-th id sub-range (-1: none)
   std::vector<PatchDesc> desc;
   std::vector<PElem> elems;
   std::vector<unsigned char> blob;  // all patches, each 16-byte aligned
