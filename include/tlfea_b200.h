@@ -244,6 +244,10 @@ int tlfea_newton_set_assembly(tlfea_newton *s, int mode);
 /* Warps (= sub-patches) per patch of the single-pass assembly: 4 (two CTAs per SM, default) or 8.  Takes effect
  * when the plan is (re)built, i.e. before the first assemble.  New design, no reference line. */
 int tlfea_newton_set_patch_warps(tlfea_newton *s, int warps);
+/* Id-range chunks of the patch launch order (the granularity at which a host-buffer step overlaps its copies with the
+ * kernels): 0 = automatic (at most 4, fewer for meshes too small to fill the launches), 1..16 = exactly that many.
+ * Takes effect when the plan is (re)built.  New design, no reference line. */
+int tlfea_newton_set_patch_chunks(tlfea_newton *s, int chunks);
 /* Affine-element compression of the single-pass FEAT10 assembly: straight-sided tets are integrated from
  * J^-T | detJ (80 B per element, found at CalcDnDuPre) instead of the 150 stored gradients + 5 detJ (1 240 B); curved
  * elements keep the stored gradients.  Results agree to rounding.  Off by default (it trades HBM bytes for issue slots

@@ -379,6 +379,7 @@ def test_host_pipelined_assemble_matches_the_plain_sequence(model, damp, permute
         X, E = X[perm], inv[E].astype(np.int32)
     fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
     d, s = _make(X, E, model, damp, fixed)
+    s.SetPatchChunks(4)  # the automatic choice gives a mesh this small one chunk: force the chunked pipeline
     if damp:
         s.SetVelocityGuess(0.1 * np.random.Generator(np.random.PCG64(1235)).uniform(-1, 1, size=3 * X.shape[0]))
     pinned = [torch.empty(X.shape[0], dtype=torch.float64).pin_memory().numpy() for _ in range(3)]

@@ -187,6 +187,7 @@ struct tlfea_newton {
   void *patch = nullptr;  // PatchPlanDev (patch_asm.cu)
   void *dist = nullptr;   // DistCtx (dist.cu): NCCL communicator + halo neighbours of a partitioned mesh
   int pk_w = 0;           // warps per patch (0 = TLFEA_PK_W or 4)
+  int pk_chunks = 0;      // id-range chunks of the launch order (0 = TLFEA_PK_CHUNKS or at most 4, by mesh size)
   int pk_affine = -1;     // affine-element compression: -1 = TLFEA_PK_AFFINE (default off), 0 off, 1 on
   int n_constraints = 0;
   tlfea_newton_params prm{};

@@ -1640,6 +1640,12 @@ int tlfea_newton_set_patch_warps(tlfea_newton *s, int warps) {
   s->pk_w = warps;
   return TLFEA_OK;
 }
+int tlfea_newton_set_patch_chunks(tlfea_newton *s, int chunks) {
+  TL_CHECK(s && chunks >= 0 && chunks <= 16, "id-range chunks must be 0 (automatic) or 1..16");
+  if (s->pk_chunks != chunks) patch_release(s);
+  s->pk_chunks = chunks;
+  return TLFEA_OK;
+}
 int tlfea_newton_set_affine_compression(tlfea_newton *s, int on) {
   TL_CHECK(s, "null handle");
   s->pk_affine = on ? 1 : 0;

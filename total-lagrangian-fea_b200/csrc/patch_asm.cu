@@ -52,8 +52,8 @@ static int sm_count(int device) {
 static int patch_chunk_count() {
   static int k = [] {
     const char *e = getenv("TLFEA_PK_CHUNKS");  // id-range chunks of the launch order (host-buffer pipelining)
-    const int v = e ? atoi(e) : 4;
-    return std::min(std::max(v, 1), 16);
+    if (e) return std::min(std::max(atoi(e), 1), 16);  // exact
+    return -4;                                         // at most 4, fewer for small meshes (patch_plan.cu)
   }();
   return k;
 }
@@ -85,7 +85,7 @@ int patch_prepare(tlfea_newton *s) {
   PatchPlanHost hp;
   std::string err;
   const int rc = build_patch_plan(e->n_elem, e->n_coef, ecoef.data(), x.data(), y.data(), z.data(), off.data(),
-                                  cols.data(), W, patch_chunk_count(), &hp, &err);
+                                  cols.data(), W, s->pk_chunks ? s->pk_chunks : patch_chunk_count(), &hp, &err);
   if (rc != TLFEA_OK) return fail(rc, "%s", err.c_str());
   auto *pp = new PatchPlanDev();
   s->patch = pp;

@@ -364,7 +364,9 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   // of n_chunks id ranges (pk_chunk_bound: short first and last range): its kernels read no coordinate beyond that range (a host-buffer step starts them as
   // soon as that part of x, y, z has been uploaded), and once a chunk is done every coefficient whose patches all
   // lie in chunks <= c is final (its force can travel back to the host while later chunks compute).
-  const int K = std::max(1, std::min(n_chunks, 16));
+  // n_chunks < 0: |n_chunks| is an upper bound -- every (chunk, colour) launch should give each of the ~300 resident CTAs a run of
+  // patches long enough to amortise its start (small meshes and the slabs of a many-GPU partition get fewer chunks)
+  const int K = (n_chunks < 0) ? std::max(1, std::min({-n_chunks, 16, np / 40000})) : std::max(1, std::min(n_chunks, 16));
   std::vector<int> chunk_of((size_t)np, 0), node_final((size_t)n_coef, -1);
   for (int p = 0; p < np; p++) {
     const int mxid = pl[p]->nodes.empty() ? 0 : pl[p]->nodes.back();

@@ -117,7 +117,8 @@ struct PatchPlanHost {
 };
 
 // Pure host code (no CUDA call): ecoef [n_elem][10]; x, y, z reference coordinates per coefficient; off / cols the
-// coefficient-level CSR pattern (sorted columns); n_chunks = id-range chunks of the launch order (1 = colours only);
+// coefficient-level CSR pattern (sorted columns); n_chunks = id-range chunks of the launch order (1 = colours only;
+// negative: at most |n_chunks|, fewer when the mesh has too few patches to fill the launches);
 // Returns 0 or a negative tlfea_status with *err set.
 int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, const double *y, const double *z,
                      const int *off, const int *cols, int W, int n_chunks, PatchPlanHost *out,

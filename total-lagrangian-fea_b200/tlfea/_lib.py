@@ -127,6 +127,7 @@ _SIGS = {
     "tlfea_newton_timing": (C.c_int, [c_vp, c_dp, c_ip, C.c_int]),
     "tlfea_newton_set_assembly": (C.c_int, [c_vp, C.c_int]),
     "tlfea_newton_set_patch_warps": (C.c_int, [c_vp, C.c_int]),
+    "tlfea_newton_set_patch_chunks": (C.c_int, [c_vp, C.c_int]),
     "tlfea_newton_set_affine_compression": (C.c_int, [c_vp, C.c_int]),
     "tlfea_newton_patch_stats": (C.c_int, [c_vp, c_i64p]),
     "tlfea_newton_set_profile": (C.c_int, [c_vp, C.c_int]),

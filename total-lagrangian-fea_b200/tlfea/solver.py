@@ -177,6 +177,10 @@ class SyncedNewtonSolver(SolverBase):
     def SetPatchWarps(self, warps: int):
         check(lib.tlfea_newton_set_patch_warps(self._h, int(warps)))
 
+    def SetPatchChunks(self, chunks: int):
+        """id-range chunks of the patch launch order: 0 = automatic, 1..16 = exactly that many"""
+        check(lib.tlfea_newton_set_patch_chunks(self._h, int(chunks)))
+
     def SetAffineCompression(self, on: bool):
         check(lib.tlfea_newton_set_affine_compression(self._h, int(bool(on))))
 
