@@ -71,6 +71,17 @@ inline void dfree(T *&p) {
 
 inline unsigned blocks_for(int64_t n, int threads) { return (unsigned)((n + threads - 1) / threads); }
 
+// SM count of a device (grids of the persistent kernels are sized in multiples of it), looked up once per thread
+inline int sm_count(int device) {
+  static thread_local int dev = -1, n = 148;
+  if (dev != device) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && v > 0) n = v;
+    dev = device;
+  }
+  return n;
+}
+
 constexpr int MAX_Q = 48;
 struct QuadW {
   double w[MAX_Q];  // combined quadrature weight per stiffness Gauss point

@@ -428,7 +428,7 @@ static int launch_ek_t(tlfea_elem *e, const EKArgs &a) {
     attr_dev = e->device;
   }
   const int n_groups = (a.n_elem + G - 1) / G;
-  const int grid = std::max(1, std::min(148, (n_groups + W - 1) / W));
+  const int grid = std::max(1, std::min(sm_count(e->device), (n_groups + W - 1) / W));
   TL_LAUNCH((ek_kernel<G, W, DAMP, TANGENT, MODEL>), grid, W * 32, smem, e->stream, a);
   TL_CUDA(cudaGetLastError());
   return TLFEA_OK;
@@ -452,7 +452,7 @@ static int launch_aek_t(tlfea_elem *e, const AEKArgs &a) {
                                  (int)Sh::SMEM));
   const int n_groups = (a.n_elem + EPB - 1) / EPB;
   const int per_sm = std::max(1, std::min((int)((227 * 1024) / (Sh::SMEM + 1024)), 2048 / Sh::THREADS));
-  const int grid = std::max(1, std::min(n_groups, 148 * per_sm));
+  const int grid = std::max(1, std::min(n_groups, sm_count(e->device) * per_sm));
   TL_LAUNCH((aek_kernel<S, Q, EPB, DAMP, TANGENT, MODEL>), grid, Sh::THREADS, Sh::SMEM, e->stream, a);
   TL_CUDA(cudaGetLastError());
   return TLFEA_OK;
@@ -603,7 +603,7 @@ struct EkPlan {
     r.desc = static_cast<const RowDesc *>(s->d_rowdesc) + r0;
     r.counter = s->d_tickets + k;
     const int blocks = (nr + RK_WARPS * RK_T - 1) / (RK_WARPS * RK_T);
-    const int grid = std::min(blocks, 148 * per_sm);
+    const int grid = std::min(blocks, sm_count(e->device) * per_sm);
     if (e->type == TLFEA_TYPE_3243)
       TL_LAUNCH((rk_kernel<8, 5, 3>), grid, RK_WARPS * 32, smem, st, r);
     else if (e->type == TLFEA_TYPE_3443)
@@ -744,7 +744,7 @@ static int do_assemble(tlfea_newton *s, bool tangent) {
     TL_CHECK(smem <= 200 * 1024, "coefficient row too long for the shared-memory row buffer (max_deg=%d)",
              e->pat.max_deg);
     const int rows_blocks = (e->n_coef + ROW_WARPS - 1) / ROW_WARPS;
-    const int grid = std::min(rows_blocks, 148 * 32);
+    const int grid = std::min(rows_blocks, sm_count(e->device) * 32);
     a.perm = nullptr;
     a.chunk = ROW_WARPS;
     {
@@ -1686,7 +1686,7 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double *out, int iters) {
 int tlfea_fp64_peak(int device, double *tflops) {
   TL_CHECK(tflops, "null out");
   TL_CUDA(cudaSetDevice(device));
-  const int blocks = 148 * 16, iters = 8192;
+  const int blocks = sm_count(device) * 16, iters = 8192;
   double *d = nullptr;
   TL_TRY(dmalloc(&d, (size_t)blocks * 256));
   cudaEvent_t a, b;

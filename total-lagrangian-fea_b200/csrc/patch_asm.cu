@@ -39,16 +39,6 @@ void patch_release(tlfea_newton *s) {
   s->patch = nullptr;
 }
 
-static int sm_count(int device) {
-  static thread_local int dev = -1, n = 148;
-  if (dev != device) {
-    cudaDeviceProp pr;
-    if (cudaGetDeviceProperties(&pr, device) == cudaSuccess) n = pr.multiProcessorCount;
-    dev = device;
-  }
-  return n;
-}
-
 static int patch_chunk_count() {
   static int k = [] {
     const char *e = getenv("TLFEA_PK_CHUNKS");  // id-range chunks of the launch order (host-buffer pipelining)
