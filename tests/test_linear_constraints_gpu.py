@@ -140,3 +140,83 @@ def test_welded_beams_step_holds_the_weld():
     assert st["norm_c"] < 1e-6
     assert gz[4 * 5] < 0.0  # the loaded tip of beam B moved down
     assert np.abs(pos[8] - ref[8]).max() > 1e-9  # beam A carries no load: it can only have moved through the weld
+
+
+def _plate_3443():
+    """two ANCF3443 elements side by side (6 nodes), node 0 clamped, the position coefficient of node 5 tied to node 4 by
+    rows with unequal weights (a general linear row, not a selection)."""
+    import tlfea
+    from test_ancf_gpu import plate
+
+    x, y, z, conn = plate(2, 1, L, 0.4)
+    nc = x.shape[0]
+    pos = np.stack([x, y, z], axis=1)
+    off, cols, vals, rhs = [0], [], [], []
+    for c in range(4):
+        for dd in range(3):
+            cols.append(3 * c + dd); vals.append(1.0); rhs.append(pos[c, dd]); off.append(len(cols))
+    ca, cb = 4 * 4, 4 * 5
+    for dd in range(3):
+        cols += [3 * ca + dd, 3 * cb + dd]; vals += [1.0, -0.5]; rhs.append(pos[ca, dd] - 0.5 * pos[cb, dd]); off.append(len(cols))
+    jc = (np.array(off, dtype=np.int32), np.array(cols, dtype=np.int32), np.array(vals), np.array(rhs))
+    d = tlfea.GPU_ANCF3443_Data(nc // 4, conn.shape[0])
+    d.Initialize()
+    d.Setup(L, 0.4, H, x, y, z, conn)
+    d.SetDensity(RHO)
+    d.SetSVK(E_MOD, NU)
+    f_ext = 30.0 * np.random.default_rng(3).uniform(-1, 1, 3 * nc)
+    d.SetExternalForce(f_ext)
+    d.SetLinearConstraintsCSR(*jc)
+    d.CalcDsDuPre()
+    d.CalcMassMatrix()
+    d.CalcConstraintData()
+    s = tlfea.SyncedNewtonSolver(d, jc[3].shape[0])
+    s.SetParameters(tlfea.SyncedNewtonParams(*PRM))
+    s.Setup()
+    s.AnalyzeHessianSparsity()
+    return d, s, (x, y, z, conn), jc, f_ext, (L, 0.4, H)
+
+
+@pytest.mark.parametrize("kind", [3243, 3443])
+def test_gradient_vs_oracle_linear_constraints(kind):
+    """g = M (v - v_prev)/h + f_int - f_ext + h J^T (lambda + rho c)  (solver_grad_L, SyncedNewton.cu:343-407) for the
+    ANCF elements under general linear CSR constraints, non-zero v, v_prev, f_ext and constraint violation, against
+    orc.grad_L with the oracle's own f_int and mass (lambda is zero after Setup, as in the reference)."""
+    import scipy.sparse as sp
+    from oracle import oracle as orc
+
+    if kind == 3243:
+        d, s, (x, y, z, conn), (j_off, j_cols, j_vals, rhs), f_ext = _build(False)
+        dims = (L, W, H)
+    else:
+        d, s, (x, y, z, conn), (j_off, j_cols, j_vals, rhs), f_ext, dims = _plate_3443()
+    nc, ne = x.shape[0], conn.shape[0]
+    rng = np.random.default_rng(21)
+    pos = np.stack([x, y, z], axis=1) + 2e-3 * rng.uniform(-1, 1, (nc, 3))
+    v, vp = 0.1 * rng.uniform(-1, 1, 3 * nc), 0.1 * rng.uniform(-1, 1, 3 * nc)
+    d.UpdatePositions(pos[:, 0].copy(), pos[:, 1].copy(), pos[:, 2].copy())
+    s.SetVelocityGuess(v)
+    s.SetVelocityPrev(vp)
+    s.Assemble()
+    ng = s.Residual()
+    g = s.RetrieveGradient()
+
+    ec = orc.ancf_ecoef(kind, conn)
+    b_off, b_cols = orc.coef_pattern(ec, nc)
+    w_off, w_cols = _widened_pattern(b_off, b_cols, j_off, j_cols, nc)
+    Binv = orc.ancf_binv(kind, [dims[0]] * ne, [dims[1]] * ne, [dims[2]] * ne)
+    LWH = np.tile(list(dims), (ne, 1))
+    gN, dJ = orc.ancf_precompute(kind, ec, x, y, z, LWH, Binv)
+    mat = orc.Material.svk(E_MOD, NU)
+    _, P = orc.compute_p(ec, pos, gN, mat)
+    f_int = orc.internal_force(ec, gN, dJ, orc.ancf_stiffness_weights(kind), P, nc)
+    mass_w = orc.ancf_mass(kind, ec, x, y, z, LWH, Binv, RHO, w_off, w_cols)
+    J = sp.csr_matrix((j_vals, j_cols, j_off), shape=(rhs.shape[0], 3 * nc))
+    con = J @ pos.reshape(-1) - rhs
+    assert np.abs(con).max() > 1e-4  # the constraints really are violated
+    JT = J.T.tocsr()
+    JT.sort_indices()
+    jt = (JT.indptr.astype(np.int32), JT.indices.astype(np.int32), JT.data)
+    g_ref = orc.grad_L(w_off, w_cols, mass_w, v, vp, f_int, f_ext, DT, jt, np.zeros_like(con), con, ALM)
+    assert np.abs(g - g_ref).max() <= 1e-12 * np.abs(g_ref).max()
+    assert abs(ng - np.linalg.norm(g_ref)) <= 1e-12 * np.linalg.norm(g_ref)
