@@ -3,9 +3,12 @@
 #include "patch_plan.cuh"
 
 #include <algorithm>
+#include <chrono>
 #include <climits>
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/tlfea_b200.h"
@@ -106,6 +109,14 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   };
   if (W < 1 || W > PK_MAXW) return failm(TLFEA_ERR_INVALID, "patch plan: W out of range");
   if (n_elem <= 0) return failm(TLFEA_ERR_INVALID, "patch plan: no elements");
+  const bool timing = getenv("TLFEA_PLAN_TIMING") != nullptr;
+  auto t_last = std::chrono::steady_clock::now();
+  auto lap = [&](const char *what) {
+    if (!timing) return;
+    const auto t = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "patch plan: %-28s %.3f s\n", what, std::chrono::duration<double>(t - t_last).count());
+    t_last = t;
+  };
   // ---- 1. spatial keys: Morton code of the cell that holds the centroid of the four vertices
   double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
   std::vector<double> cen((size_t)n_elem * 3);
@@ -166,6 +177,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   std::sort(order.begin(), order.end());
   std::vector<double>().swap(cen);
 
+  lap("1 keys + sort");
   // ---- 2. octants (2x2x2 cells): the unit a patch never leaves
   std::vector<int> oct_ptr;
   for (int i = 0; i < n_elem; i++)
@@ -173,6 +185,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   oct_ptr.push_back(n_elem);
   const int n_oct = (int)oct_ptr.size() - 1;
 
+  lap("2 octants");
   // ---- 3. sub-patches and patches per octant
   std::vector<std::vector<PatchLocal>> per_oct((size_t)n_oct);
   bool any_bad = false;
@@ -327,6 +340,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
     return failm(TLFEA_ERR_UNSUPPORTED, "patch plan: a node pair is missing from the pattern or a row is too long");
   std::vector<std::pair<uint64_t, int>>().swap(order);
 
+  lap("3 sub-patches, slots, entries");
   // ---- 4. colour the patch adjacency (patches sharing a coefficient), first fit in Morton order
   std::vector<PatchLocal *> pl;
   for (auto &v : per_oct)
@@ -359,6 +373,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   std::vector<int>().swap(npat);
   std::vector<int>().swap(nptr);
 
+  lap("4 colouring");
   // ---- 5. launch order, first-touch flags, concatenation.
   // Launch l = chunk * n_colors + colour.  Chunk c holds the patches whose LARGEST coefficient id falls into the c-th
   // of n_chunks id ranges (pk_chunk_bound: short first and last range): its kernels read no coordinate beyond that range (a host-buffer step starts them as
@@ -518,6 +533,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
       if (hw[5]) std::memcpy(at, P.ops[w].data(), (size_t)hw[5] * sizeof(uint32_t));
     }
   }
+  lap("5 order, flags, blobs");
   if (span_bad) return failm(TLFEA_ERR_UNSUPPORTED, "patch plan: a patch spans more than 2^32 entries of H");
   return TLFEA_OK;
 }
