@@ -69,14 +69,24 @@ struct PatchLocal {
 // the adds are bank-conflict free when those 15 slots differ modulo 16 (a block is 9 doubles = odd stride).
 // Greedy: blocks in order of first use take the residue class that collides least with the sets they belong to.
 void assign_slots(int nb, const std::vector<std::vector<int>> &sets, std::vector<int> &slot) {
-  std::vector<std::vector<int>> member((size_t)nb);
-  for (size_t q = 0; q < sets.size(); q++)
-    for (int b : sets[q]) member[(size_t)b].push_back((int)q);
-  std::vector<uint16_t> used(sets.size(), 0);  // residues taken per set
+  // block -> the sets it belongs to, as one flat CSR (no per-block allocation: this runs once per sub-patch)
+  const int ns = (int)sets.size();
+  std::vector<int> mptr((size_t)nb + 1, 0), mset;
+  for (auto &st : sets)
+    for (int b : st) mptr[(size_t)b + 1]++;
+  for (int b = 0; b < nb; b++) mptr[(size_t)b + 1] += mptr[(size_t)b];
+  mset.resize((size_t)mptr[(size_t)nb]);
+  {
+    std::vector<int> fillp(mptr.begin(), mptr.end() - 1);
+    for (int q = 0; q < ns; q++)
+      for (int b : sets[(size_t)q]) mset[(size_t)fillp[(size_t)b]++] = q;
+  }
+  std::vector<uint16_t> used((size_t)ns, 0);  // residues taken per set
   int cap[16], fill[16] = {0};
   for (int r = 0; r < 16; r++) cap[r] = (PK_CAPU - r + 15) / 16;
   slot.assign((size_t)nb, -1);
   std::vector<int> order;
+  order.reserve((size_t)nb);
   std::vector<char> seen((size_t)nb, 0);
   for (auto &st : sets)
     for (int b : st)
@@ -84,17 +94,25 @@ void assign_slots(int nb, const std::vector<std::vector<int>> &sets, std::vector
   for (int b = 0; b < nb; b++)
     if (!seen[(size_t)b]) order.push_back(b);
   for (int b : order) {
+    // residues already taken in any set of this block, counted per residue
+    int cnt[16] = {0};
+    for (int k = mptr[(size_t)b]; k < mptr[(size_t)b + 1]; k++) {
+      uint16_t u = used[(size_t)mset[(size_t)k]];
+      while (u) {
+        const int r = __builtin_ctz(u);
+        cnt[r]++;
+        u &= (uint16_t)(u - 1);
+      }
+    }
     int best = -1, best_cost = 1 << 30;
     for (int r = 0; r < 16; r++) {
       if (fill[r] >= cap[r]) continue;
-      int cost = 0;
-      for (int q : member[(size_t)b]) cost += (used[(size_t)q] >> r) & 1;
-      cost = cost * 64 + fill[r];  // ties: the emptiest class
+      const int cost = cnt[r] * 64 + fill[r];  // ties: the emptiest class
       if (cost < best_cost) best_cost = cost, best = r;
     }
     slot[(size_t)b] = best + 16 * fill[best];
     fill[best]++;
-    for (int q : member[(size_t)b]) used[(size_t)q] |= (uint16_t)(1u << best);
+    for (int k = mptr[(size_t)b]; k < mptr[(size_t)b + 1]; k++) used[(size_t)mset[(size_t)k]] |= (uint16_t)(1u << best);
   }
 }
 
