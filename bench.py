@@ -449,6 +449,23 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the tlfea hot path has no CPU fallback")
     torch.cuda.set_device(local)
+    numa_note = None
+    if world > 1 and os.environ.get("TLFEA_BENCH_AFFINITY", "1") != "0":
+        # one process per GPU, bound to the CPUs next to that GPU: the pinned host buffers of the host-buffer step are
+        # then allocated on the GPU's own socket (first touch) and the PCIe copies do not cross the socket link
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            hnd = nv.nvmlDeviceGetHandleByIndex(local)
+            words = nv.nvmlDeviceGetCpuAffinity(hnd, (os.cpu_count() + 63) // 64)
+            cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+            cpus &= os.sched_getaffinity(0)
+            if cpus:
+                os.sched_setaffinity(0, cpus)
+                numa_note = f"rank bound to the {len(cpus)} CPUs next to its GPU (nvmlDeviceGetCpuAffinity)"
+        except Exception as ex:  # no NVML / not permitted: run unbound
+            numa_note = f"unbound ({type(ex).__name__})"
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -891,7 +908,7 @@ def main():
                                                     if (lib_halo is not None and lib_halo.p2p) else "NCCL send/recv"),
                        "halo_bytes_sent_per_rank": (lib_halo.bytes_per_halo if lib_halo else 0),
                        "l2_policy": "inputs (gradN 1.2 KB/elem, H 2.8 KB/elem) are far larger than the 126 MB L2",
-                       "setup_s": t_setup, "first_assemble_s": t_first,
+                       "setup_s": t_setup, "first_assemble_s": t_first, "cpu_binding": numa_note,
                        "first_assemble_note": "one-time per sparsity pattern: host-side patch plan (Morton sort, sub-patches, "
                                               "colouring, write-out lists) + upload, inside the first warm-up step"},
             "roofline": roofline, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": launches_all, "parity": parity,
