@@ -129,8 +129,22 @@ __device__ __forceinline__ void pk_write_segment(const unsigned char *seg, int n
     asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v[1]) : "r"(a + st));
     asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v[2]) : "r"(a + 2u * st));
   };
-  auto ld4 = [](const uint4 *q) { return SMEM ? *q : __ldg(q); };
-  auto ld2 = [](const uint2 *q) { return SMEM ? *q : __ldg(q); };
+  // staged lists are read with explicit shared-memory loads: through the generic pointer they would be generic loads
+  // (longer latency, long scoreboard)
+  auto ld4 = [](const uint4 *q) {
+    if (!SMEM) return __ldg(q);
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "r"((unsigned)__cvta_generic_to_shared(q)));
+    return v;
+  };
+  auto ld2 = [](const uint2 *q) {
+    if (!SMEM) return __ldg(q);
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"((unsigned)__cvta_generic_to_shared(q)));
+    return v;
+  };
   auto put_first = [&](const uint4 e, const double v[3]) {  // H block = (M_ij / h) I + sum
     const double m = __hiloint2double((int)e.w, (int)e.z);
     double *hp = Hw + (e.x & hmask);
@@ -836,9 +850,15 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
   __syncthreads();  // every accumulator is final
   // (b) pairs held by several warps: dst += src in ascending warp order, one thread per dst (the ops of a dst are
   // consecutive; all but the first carry the continuation bit).  Warp w does the ops of chunk w ...
+  auto ld_op = [&](const uint32_t *q) {  // staged: an explicit shared-memory load, else read-only global
+    if (!ck_smem) return __ldg(q);
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(q)));
+    return v;
+  };
   if (wo_on) {
     for (int q = lane; q < ck_ops; q += 32) {
-      uint32_t op = ck_smem ? ops[q] : __ldg(ops + q);
+      uint32_t op = ld_op(ops + q);
       if (op & 0x8000u) continue;
       double *da = pk_smem + (op & 0x3fffu);
       double a[9];
@@ -850,7 +870,7 @@ __global__ void __launch_bounds__(W * 32, (W <= 4) ? 2 : 1) pk_kernel(PKArgs p) 
 #pragma unroll
         for (int i = 0; i < 9; i++) a[i] += sa[i];
         j++;
-        op = (j < ck_ops) ? (ck_smem ? ops[j] : __ldg(ops + j)) : 0u;
+        op = (j < ck_ops) ? ld_op(ops + j) : 0u;
       } while (op & 0x8000u);
 #pragma unroll
       for (int i = 0; i < 9; i++) da[i] = a[i];
