@@ -479,6 +479,9 @@ def main():
     import tlfea
     from tlfea import partition
 
+    # torchrun exports OMP_NUM_THREADS=1: give every rank its share of the host cores for the one-time plan build
+    if world > 1:
+        tlfea.lib.tlfea_set_host_threads(max(1, len(os.sched_getaffinity(0)) // world))
     launches0 = tlfea.lib.tlfea_launch_count()
     t_setup = time.perf_counter()
     slab, x, d, s = build_problem(args.n, rank, world, local)

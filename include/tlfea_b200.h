@@ -61,6 +61,10 @@ int tlfea_version(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 int64_t tlfea_launch_count(void);
 int tlfea_device_count(void);
+/* Host threads (OpenMP) of the one-time host-side analyses (the patch plan of the single-pass FEAT10 assembly):
+ * 0 = all processors.  Launchers that export OMP_NUM_THREADS=1 for every rank (torchrun) otherwise make every rank build
+ * its plan on one core.  New design, no reference line. */
+int tlfea_set_host_threads(int n);
 
 /* ---------------------------------------------------------------- elements */
 

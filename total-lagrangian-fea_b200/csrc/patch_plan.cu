@@ -563,6 +563,9 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
 // kernel's accumulation order in numpy (tests/test_patch_plan.py).
 // ---------------------------------------------------------------------------------------------
 #include "common.cuh"
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 extern "C" {
 
@@ -605,6 +608,14 @@ int tlfea_debug_patch_plan_copy(void *plan, int *color_ptr, void *desc, void *el
   if (row_ptr) std::memcpy(row_ptr, p->row_ptr.data(), p->row_ptr.size() * sizeof(int64_t));
   if (blob) std::memcpy(blob, p->blob.data(), p->blob.size());
   if (uncovered) std::memcpy(uncovered, p->uncovered.data(), p->uncovered.size() * sizeof(int64_t));
+  return TLFEA_OK;
+}
+
+int tlfea_set_host_threads(int n) {
+  TL_CHECK(n >= 0, "thread count must be >= 0 (0 = the OpenMP default)");
+#ifdef _OPENMP
+  omp_set_num_threads(n > 0 ? n : omp_get_num_procs());
+#endif
   return TLFEA_OK;
 }
 

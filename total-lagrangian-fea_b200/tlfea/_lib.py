@@ -45,6 +45,7 @@ _SIGS = {
     "tlfea_version": (C.c_int, []),
     "tlfea_launch_count": (C.c_int64, []),
     "tlfea_device_count": (C.c_int, []),
+    "tlfea_set_host_threads": (C.c_int, [C.c_int]),
     "tlfea_elem_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(c_vp)]),
     "tlfea_elem_destroy": (C.c_int, [c_vp]),
     "tlfea_elem_sync": (C.c_int, [c_vp]),
