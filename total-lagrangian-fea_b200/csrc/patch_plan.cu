@@ -207,8 +207,11 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
   // ---- 3. sub-patches and patches per octant
   std::vector<std::vector<PatchLocal>> per_oct((size_t)n_oct);
   bool any_bad = false;
-#pragma omp parallel for schedule(dynamic, 16) reduction(|| : any_bad)
+  double tacc[6] = {0, 0, 0, 0, 0, 0};
+#pragma omp parallel for schedule(dynamic, 16) reduction(|| : any_bad) reduction(+ : tacc[:6])
   for (int o = 0; o < n_oct; o++) {
+    auto t_prev = std::chrono::steady_clock::now();
+    auto TT = [&](int k) { auto t = std::chrono::steady_clock::now(); tacc[k] += std::chrono::duration<double>(t - t_prev).count(); t_prev = t; };
     // greedy sub-patches: add elements while the distinct upper pairs fit one accumulator
     std::vector<SubPatch> subs;
     std::vector<uint64_t> cur, add, merged;
@@ -234,6 +237,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
     sp.end = oct_ptr[o + 1];
     subs.push_back(sp);
 
+    TT(5);
     auto &plist = per_oct[o];
     for (size_t s0 = 0; s0 < subs.size();) {
       int ns = (int)std::min<size_t>(W, subs.size() - s0);
@@ -275,8 +279,10 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
             sets.push_back(std::move(st));
           }
         }
+        TT(0);
         std::vector<int> slot;
         assign_slots((int)blocks.size(), sets, slot);
+        TT(1);
         std::vector<char> touched(blocks.size(), 0);
         for (int i = S.begin; i < S.end; i++) {
           const int e = order[i].second;
@@ -307,6 +313,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
         for (size_t u = 0; u < blocks.size(); u++)
           tups.push_back({blocks[u], (uint16_t)(w * 9 * PK_CAPU + 9 * slot[u])});
       }
+      TT(2);
       P.sub_ptr[ns] = (int)P.elems.size();
       for (int w = ns; w < PK_MAXW; w++) P.sub_ptr[w + 1] = P.sub_ptr[ns];
       // pairs held by several warps: reduced into the lowest warp's block, one extra warp per round
@@ -345,11 +352,13 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
         }
         k = k2;
       }
+      TT(3);
       for (int g = 0; g < PK_MAXW; g++) P.n_ops += (int)P.ops[g].size();
       std::sort(P.ent.begin(), P.ent.end(), [](const EntL &a, const EntL &b) { return a.habs < b.habs; });
       std::sort(P.nodes.begin(), P.nodes.end());
       P.nodes.erase(std::unique(P.nodes.begin(), P.nodes.end()), P.nodes.end());
       any_bad = any_bad || P.bad;
+      TT(4);
       plist.push_back(std::move(P));
       s0 += ns;
     }
@@ -358,6 +367,7 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
     return failm(TLFEA_ERR_UNSUPPORTED, "patch plan: a node pair is missing from the pattern or a row is too long");
   std::vector<std::pair<uint64_t, int>>().swap(order);
 
+  if (timing) std::fprintf(stderr, "  phase 3 cpu-seconds: blocks+sets %.2f slots %.2f pelem %.2f tups+entries %.2f sort %.2f greedy %.2f\n", tacc[0], tacc[1], tacc[2], tacc[3], tacc[4], tacc[5]);
   lap("3 sub-patches, slots, entries");
   // ---- 4. colour the patch adjacency (patches sharing a coefficient), first fit in Morton order
   std::vector<PatchLocal *> pl;
