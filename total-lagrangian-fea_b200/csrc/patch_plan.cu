@@ -259,20 +259,44 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
         }
         std::sort(blocks.begin(), blocks.end());
         blocks.erase(std::unique(blocks.begin(), blocks.end()), blocks.end());
+        // key -> index in `blocks`: a small open-addressing table (the 360 look-ups per sub-patch were binary searches)
+        constexpr int HT = 1024;
+        static_assert(HT >= 4 * PK_CAPU, "hash table of the sub-patch blocks");
+        int ht_idx[HT];
+        uint64_t ht_key[HT];
+        for (int q = 0; q < HT; q++) ht_idx[q] = -1, ht_key[q] = 0;
+        auto ht_slot = [&](uint64_t key) {
+          uint64_t h = key * 0x9e3779b97f4a7c15ull;
+          int q = (int)(h >> 54);
+          while (ht_idx[q] >= 0 && ht_key[q] != key) q = (q + 1) & (HT - 1);
+          return q;
+        };
+        const bool use_ht = blocks.size() <= (size_t)HT / 2;
+        if (use_ht)
+          for (size_t u = 0; u < blocks.size(); u++) {
+            const int q = ht_slot(blocks[u]);
+            ht_key[q] = blocks[u];
+            ht_idx[q] = (int)u;
+          }
+        auto block_index = [&](uint64_t key) {
+          if (use_ht) return ht_idx[ht_slot(key)];
+          return (int)(std::lower_bound(blocks.begin(), blocks.end(), key) - blocks.begin());
+        };
         // the block sets that are added simultaneously: (element, t = ta*2+tb) over the 15 tiles
         std::vector<std::vector<int>> sets;
+        sets.reserve((size_t)(S.end - S.begin) * 4);
         std::vector<int> bidx((size_t)(S.end - S.begin) * 60, -1);
         for (int i = S.begin; i < S.end; i++) {
           const int *ec = ecoef + (size_t)order[i].second * 10;
           for (int tt = 0; tt < 4; tt++) {
             std::vector<int> st;
+            st.reserve(15);
             for (int t = 0; t < 15; t++) {
               int I, J;
               tile_ij(t, &I, &J);
               if (I == J && tt == 2) continue;
               const int a = 2 * I + (tt >> 1), b = 2 * J + (tt & 1);
-              const int bi = (int)(std::lower_bound(blocks.begin(), blocks.end(), upper_key(ec[a], ec[b])) -
-                                   blocks.begin());
+              const int bi = block_index(upper_key(ec[a], ec[b]));
               bidx[(size_t)(i - S.begin) * 60 + t * 4 + tt] = bi;
               st.push_back(bi);
             }
@@ -321,6 +345,8 @@ int build_patch_plan(int n_elem, int n_coef, const int *ecoef, const double *x, 
         return a.key != b.key ? a.key < b.key : a.s < b.s;
       });
       int n_mergedst = 0, n_merged_total = 0;
+      P.ent.reserve(2 * tups.size());
+      P.nodes.reserve(2 * tups.size());
       for (size_t k = 0; k < tups.size();) {  // merged pairs of the patch (dealt to the chunks in contiguous runs)
         size_t k2 = k;
         while (k2 < tups.size() && tups[k2].key == tups[k].key) k2++;
