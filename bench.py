@@ -738,9 +738,9 @@ def main():
         def e2e_pipelined():
             # same inputs, same outputs, same work: tlfea_newton_assemble_host_begin / _end overlap the chunked H2D
             # with the element kernel and the D2H of f_int / ||g|| with the row reduce (include/tlfea_b200.h)
-            # one GPU: the result buffer is registered up front, finished id ranges of f_int travel back under the
-            # remaining kernels; N > 1: the halo sum touches f_int between begin and end, one copy at the end
-            s.AssembleFromHostBegin(hx[0], hx[1], hx[2], hf if world == 1 else None)
+            # the result buffer is registered up front: finished id ranges of f_int travel back under the remaining
+            # kernels; N > 1: the halo sum completes the shared planes in between, End sends those ranges again
+            s.AssembleFromHostBegin(hx[0], hx[1], hx[2], hf)
             halo_sum()
             return s.AssembleFromHostEnd(hf)
 

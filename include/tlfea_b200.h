@@ -206,7 +206,7 @@ int tlfea_newton_assemble_host_end(tlfea_newton *s, double *f_int, int n, double
 /* Optional: the host buffer (3*n_coef doubles, pinned for overlap) that the NEXT _host_begin/_host_end pair will return
  * f_int in.  Known before _begin, the single-pass FEAT10 path copies each coefficient-id range back as soon as its last
  * chunk of patches is done, under the remaining kernels; the caller must not touch f_int on the device between _begin
- * and _end (a multi-GPU caller that halo-sums f_int in between passes NULL and gets one copy at _end).  NULL clears. */
+ * and _end, except through tlfea_dist_halo_sum: _end sends the id ranges shared with the neighbours again.  NULL clears. */
 int tlfea_newton_set_host_result_buffer(tlfea_newton *s, double *f_int_host, int n);
 /* constraints_eval + compute_grad_l + ||g||  SyncedNewton.cu:1056-1064; writes ||g||_2 to *norm_g */
 int tlfea_newton_residual(tlfea_newton *s, double *norm_g);

@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/tlfea_b200.h"
@@ -184,6 +185,8 @@ struct PatchHooks {
 int patch_prepare(tlfea_newton *s);
 int patch_assemble(tlfea_newton *s, bool tangent, bool damp, const PatchHooks *hooks = nullptr);
 int patch_chunks(tlfea_newton *s, int *n_chunks, const int **range_ready);
+// coefficient-id ranges [lo, hi) this rank shares with its neighbours (csrc/dist.cu); empty without a communicator
+void dist_halo_ranges(const tlfea_newton *s, std::vector<std::pair<int64_t, int64_t>> &out);
 void patch_release(tlfea_newton *s);
 void dist_release(tlfea_newton *s);
 int patch_stats(tlfea_newton *s, int64_t *out);

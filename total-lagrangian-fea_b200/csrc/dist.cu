@@ -135,6 +135,14 @@ __global__ void __launch_bounds__(256) k_halo_take(int64_t n, double *vec, const
     vec[i] += __ldcg(src + i);
 }
 
+void dist_halo_ranges(const tlfea_newton *s, std::vector<std::pair<int64_t, int64_t>> &out) {
+  out.clear();
+  const auto *dc = static_cast<const DistCtx *>(s->dist);
+  if (!dc) return;
+  for (auto &nb : dc->nbr)
+    if (nb.c_hi > nb.c_lo) out.push_back({nb.c_lo, nb.c_hi});
+}
+
 void dist_release(tlfea_newton *s) {
   auto *dc = static_cast<DistCtx *>(s->dist);
   if (!dc) return;

@@ -1123,6 +1123,18 @@ static int assemble_host_end(tlfea_newton *s, double *h_f_int, double *norm_g) {
   const bool f_done = s->pipe_pk && s->pipe_f_copied && h_f_int == s->h_f_out;  // ranges went back as they finished
   if (h_f_int && !f_done)
     TL_CUDA(cudaMemcpyAsync(h_f_int, e->d_f_int, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, m));
+  if (h_f_int && f_done) {
+    // partitioned mesh: the halo sum (tlfea_dist_halo_sum, queued on the main stream between begin and end) completed the
+    // entries of the shared id ranges after their first copy went out -- send those ranges again, behind the early copies
+    std::vector<std::pair<int64_t, int64_t>> shared;
+    dist_halo_ranges(s, shared);
+    if (!shared.empty()) {
+      TL_CUDA(cudaStreamSynchronize(s->st_copy));
+      for (auto &r : shared)
+        TL_CUDA(cudaMemcpyAsync(h_f_int + 3 * r.first, e->d_f_int + 3 * r.first,
+                                (size_t)(r.second - r.first) * 3 * sizeof(double), cudaMemcpyDeviceToHost, m));
+    }
+  }
   TL_CUDA(cudaStreamSynchronize(m));
   if (s->pipe_pk && s->pipe_f_copied) TL_CUDA(cudaStreamSynchronize(s->st_copy));
   s->pipe_pk = false;

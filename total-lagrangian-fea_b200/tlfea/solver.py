@@ -83,7 +83,8 @@ class SyncedNewtonSolver(SolverBase):
         (tlfea_newton_assemble_host_begin).  Returns without waiting; x, y, z must stay alive (and unchanged)
         until AssembleFromHostEnd returns -- pass pinned float64 arrays for a truly asynchronous copy.
         out: the (pinned, contiguous float64) array AssembleFromHostEnd will be given; known here, finished parts of
-        f_int travel back under the remaining kernels (single-pass FEAT10 path; nothing may touch f_int in between)."""
+        f_int travel back under the remaining kernels (single-pass FEAT10 path; nothing may touch f_int in between except the
+        library's own halo sum, whose shared ranges AssembleFromHostEnd sends again)."""
         n = self.data.n_coef
         if out is not None and not (out.dtype == np.float64 and out.flags["C_CONTIGUOUS"] and out.shape == (3 * n,)):
             out = None
