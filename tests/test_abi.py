@@ -95,3 +95,12 @@ def test_cpp_shim_compiles_and_links_against_the_abi(tmp_path):
                            "-I", os.path.join(root, "examples"), os.path.join(root, "examples", "bunny_newton.cc"),
                            "-o", str(bn), "-L", lib_dir, "-ltlfea_b200", "-Wl,-rpath," + lib_dir,
                            "-Wl,--unresolved-symbols=ignore-in-shared-libs"])
+
+
+def test_host_thread_setting_is_accepted_without_a_gpu():
+    """tlfea_set_host_threads only touches the OpenMP team of the host-side analyses: callable on the CPU box."""
+    from tlfea._lib import lib
+
+    assert lib.tlfea_set_host_threads(2) == 0
+    assert lib.tlfea_set_host_threads(0) == 0
+    assert lib.tlfea_set_host_threads(-1) != 0 and b"thread count" in lib.tlfea_last_error()
