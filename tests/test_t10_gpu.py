@@ -361,9 +361,10 @@ def test_diag_blocks_match_the_assembled_hessian(mesh):
     assert np.array_equal(D, ref)
 
 
-@pytest.mark.parametrize("model,damp,permute", [("svk", False, False), ("svk", True, False), ("mr", False, False),
-                                                ("svk", False, True)])
-def test_host_pipelined_assemble_matches_the_plain_sequence(model, damp, permute):
+@pytest.mark.parametrize("model,damp,permute,chunks", [("svk", False, False, 4), ("svk", True, False, 4),
+                                                       ("mr", False, False, 4), ("svk", False, True, 4),
+                                                       ("svk", False, False, 1), ("svk", False, True, 3)])
+def test_host_pipelined_assemble_matches_the_plain_sequence(model, damp, permute, chunks):
     """tlfea_newton_assemble_host_begin/_end (chunked H2D overlapped with the element kernel, H rows reduced on a
     second stream while f_int goes back to the host) against UpdatePositions + Assemble + Residual +
     RetrieveInternalForceToCPU: bit-identical H, f_int and ||g||, also when the node numbering is scrambled (every
@@ -379,7 +380,7 @@ def test_host_pipelined_assemble_matches_the_plain_sequence(model, damp, permute
         X, E = X[perm], inv[E].astype(np.int32)
     fixed = np.nonzero(X[:, 0] == 0.0)[0].astype(np.int32)
     d, s = _make(X, E, model, damp, fixed)
-    s.SetPatchChunks(4)  # the automatic choice gives a mesh this small one chunk: force the chunked pipeline
+    s.SetPatchChunks(chunks)  # the automatic choice gives a mesh this small one chunk: force the chunked pipeline
     if damp:
         s.SetVelocityGuess(0.1 * np.random.Generator(np.random.PCG64(1235)).uniform(-1, 1, size=3 * X.shape[0]))
     pinned = [torch.empty(X.shape[0], dtype=torch.float64).pin_memory().numpy() for _ in range(3)]
